@@ -1,0 +1,937 @@
+// kernels.cu — hand-written sm_100a kernels of the B200 state-vector device, behind the C ABI of
+// include/b200sv_kernels.h.  No C++ standard library, no reference headers: this translation unit
+// only knows amplitudes, bit positions and masks.
+//
+// Every kernel here is HBM-bound complex128 streaming work (<= 1 flop/byte), so the design rules
+// are: 128-bit (double2) coalesced accesses, >= 2 KiB contiguous rows per tile, as few HBM round
+// trips as possible (many gates per staged tile), deterministic warp-shuffle tree reductions.
+//
+// What the kernels replace in the reference stack (runtime/include/QuantumDevice.hpp):
+//   k_tile_program ........ NamedOperation :215 / MatrixOperation :250 (gate sweeps of lightning.qubit)
+//   k_bilinear_* .......... Expval :488, Var :503, Gradient :564 (inner products <phi|G|lambda>)
+//   k_probs_* ............. Probs :462, PartialProbs :472, first half of Measure :234
+//   k_collapse ............ second half of Measure :234
+//   k_sampler_* ........... Sample :384 / Counts :433 (alias sampler of SURVEY.md Appendix A.4)
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "b200sv_kernels.h"
+
+typedef double2 cplx;
+
+#define TT B200K_TILE_THREADS
+
+__device__ __forceinline__ cplx cmul(cplx a, cplx b)
+{
+    return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+__device__ __forceinline__ cplx cfma(cplx a, cplx b, cplx c)
+{ // a*b + c
+    return make_double2(fma(a.x, b.x, fma(-a.y, b.y, c.x)), fma(a.x, b.y, fma(a.y, b.x, c.y)));
+}
+__device__ __forceinline__ cplx cadd(cplx a, cplx b) { return make_double2(a.x + b.x, a.y + b.y); }
+// conj(a) * b
+__device__ __forceinline__ cplx cconjmul(cplx a, cplx b)
+{
+    return make_double2(a.x * b.x + a.y * b.y, a.x * b.y - a.y * b.x);
+}
+// multiply by i^k
+__device__ __forceinline__ cplx cmul_ipow(cplx a, int k)
+{
+    switch (k & 3) {
+    case 0: return a;
+    case 1: return make_double2(-a.y, a.x);
+    case 2: return make_double2(-a.x, -a.y);
+    default: return make_double2(a.y, -a.x);
+    }
+}
+
+// insert zero bits into g at every set position of mask (ascending)
+__device__ __forceinline__ uint32_t insert_zeros32(uint32_t g, uint32_t mask)
+{
+    while (mask) {
+        const int b = __ffs(mask) - 1;
+        g = ((g >> b) << (b + 1)) | (g & ((1u << b) - 1u));
+        mask &= mask - 1;
+    }
+    return g;
+}
+__device__ __forceinline__ uint64_t insert_zeros64(uint64_t g, uint64_t mask)
+{
+    while (mask) {
+        const int b = __ffsll((long long)mask) - 1;
+        g = ((g >> b) << (b + 1)) | (g & ((1ull << b) - 1ull));
+        mask &= mask - 1;
+    }
+    return g;
+}
+
+// =================================================================================================
+// Fused tile pass
+// =================================================================================================
+__global__ void __launch_bounds__(TT)
+k_tile_program(cplx *__restrict__ psi, const __grid_constant__ B200kTileProgram P)
+{
+    extern __shared__ cplx s[];
+    const int t = P.t, c = P.c, nhigh = P.nhigh;
+    const uint32_t nelem = 1u << t;
+    const uint32_t lowmask = (1u << c) - 1u;
+    const uint32_t tid = threadIdx.x;
+
+    // tile id -> base index: spread the tile id over the bits that are not tile bits
+    uint64_t base = (uint64_t)blockIdx.x << c;
+    for (int h = 0; h < nhigh; h++) {
+        const int p = P.high_pos[h];
+        base = ((base >> p) << (p + 1)) | (base & ((1ull << p) - 1ull));
+    }
+    const uint64_t obase = base | P.rank_base;
+
+    // ---- load: rows of 2^c contiguous amplitudes --------------------------------------------
+#pragma unroll 4
+    for (uint32_t e = tid; e < nelem; e += TT) {
+        uint64_t gi = base | (e & lowmask);
+        const uint32_t r = e >> c;
+        for (int h = 0; h < nhigh; h++) gi |= (uint64_t)((r >> h) & 1u) << P.high_pos[h];
+        s[e] = psi[gi];
+    }
+    __syncthreads();
+
+    // ---- op list ----------------------------------------------------------------------------
+    int o = 0;
+    while (o < P.n_ops) {
+        const uint32_t kind = P.ops[o].kind;
+        if (kind == B200K_OP_PHASE || kind == B200K_OP_PARITY) {
+            // run of diagonal ops: element-local, one pass over the tile for the whole run
+            int o1 = o + 1;
+            while (o1 < P.n_ops &&
+                   (P.ops[o1].kind == B200K_OP_PHASE || P.ops[o1].kind == B200K_OP_PARITY))
+                o1++;
+            for (uint32_t e = tid; e < nelem; e += TT) {
+                cplx v = s[e];
+                for (int q = o; q < o1; q++) {
+                    const B200kTileOp &op = P.ops[q];
+                    if ((obase & op.cmask_o) != op.cval_o) continue;
+                    if ((e & op.cmask) != op.cval) continue;
+                    if (op.kind == B200K_OP_PHASE) {
+                        v = cmul(v, make_double2(op.u.m[0], op.u.m[1]));
+                    }
+                    else {
+                        const int par = (__popc(e & op.a) + __popcll(obase & op.zmask_o)) & 1;
+                        v = cmul(v, par ? make_double2(op.u.m[2], op.u.m[3])
+                                        : make_double2(op.u.m[0], op.u.m[1]));
+                    }
+                }
+                s[e] = v;
+            }
+            __syncthreads();
+            o = o1;
+            continue;
+        }
+        const B200kTileOp &op = P.ops[o];
+        const bool active = (obase & op.cmask_o) == op.cval_o;
+        if (kind == B200K_OP_PAIR) {
+            if (active) {
+                const cplx m00 = make_double2(op.u.m[0], op.u.m[1]);
+                const cplx m01 = make_double2(op.u.m[2], op.u.m[3]);
+                const cplx m10 = make_double2(op.u.m[4], op.u.m[5]);
+                const cplx m11 = make_double2(op.u.m[6], op.u.m[7]);
+                const uint32_t ngroups = nelem >> __popc(op.tmask);
+                for (uint32_t g = tid; g < ngroups; g += TT) {
+                    const uint32_t i = insert_zeros32(g, op.tmask);
+                    if ((i & op.cmask) != op.cval) continue;
+                    const cplx va = s[i | op.a], vb = s[i | op.b];
+                    s[i | op.a] = cfma(m00, va, cmul(m01, vb));
+                    s[i | op.b] = cfma(m10, va, cmul(m11, vb));
+                }
+            }
+            __syncthreads();
+        }
+        else if (kind == B200K_OP_PAULIROT) {
+            if (active) {
+                const double cs = op.u.m[0], sn = op.u.m[1];
+                const uint32_t xm = op.tmask;
+                const uint32_t top = 1u << (31 - __clz(xm));
+                const int opar = __popcll(obase & op.zmask_o);
+                for (uint32_t g = tid; g < (nelem >> 1); g += TT) {
+                    const uint32_t i = insert_zeros32(g, top);
+                    if ((i & op.cmask) != op.cval) continue;
+                    const uint32_t j = i ^ xm;
+                    const cplx vi = s[i], vj = s[j];
+                    // (P v)_i = i^ny (-1)^par(j) v_j ;  new = cos * v - i sin * (P v)
+                    cplx pi = cmul_ipow(vj, (int)op.ny + 2 * ((__popc(j & op.a) + opar) & 1));
+                    cplx pj = cmul_ipow(vi, (int)op.ny + 2 * ((__popc(i & op.a) + opar) & 1));
+                    s[i] = make_double2(cs * vi.x + sn * pi.y, cs * vi.y - sn * pi.x);
+                    s[j] = make_double2(cs * vj.x + sn * pj.y, cs * vj.y - sn * pj.x);
+                }
+            }
+            __syncthreads();
+        }
+        else { // B200K_OP_DENSE
+            constexpr int MAXPER = (1 << B200K_MAX_TILE_BITS) / TT;
+            cplx outv[MAXPER];
+            if (active) {
+                const int k = (int)op.k;
+                const uint32_t dim = 1u << k;
+                const cplx *__restrict__ M = reinterpret_cast<const cplx *>(op.u.d.mat);
+#pragma unroll
+                for (int it = 0; it < MAXPER; it++) {
+                    const uint32_t e = tid + it * TT;
+                    if (e >= nelem) break;
+                    if ((e & op.cmask) != op.cval) {
+                        outv[it] = s[e];
+                        continue;
+                    }
+                    uint32_t row = 0;
+                    for (int j = 0; j < k; j++) row = (row << 1) | ((e >> op.u.d.tb[j]) & 1u);
+                    const uint32_t ebase = e & ~op.tmask;
+                    cplx acc = make_double2(0.0, 0.0);
+                    for (uint32_t col = 0; col < dim; col++) {
+                        uint32_t src = ebase;
+                        for (int j = 0; j < k; j++)
+                            src |= ((col >> (k - 1 - j)) & 1u) << op.u.d.tb[j];
+                        acc = cfma(__ldg(&M[row * dim + col]), s[src], acc);
+                    }
+                    outv[it] = acc;
+                }
+            }
+            __syncthreads();
+            if (active) {
+#pragma unroll
+                for (int it = 0; it < MAXPER; it++) {
+                    const uint32_t e = tid + it * TT;
+                    if (e >= nelem) break;
+                    s[e] = outv[it];
+                }
+            }
+            __syncthreads();
+        }
+        o++;
+    }
+
+    // ---- store --------------------------------------------------------------------------------
+#pragma unroll 4
+    for (uint32_t e = tid; e < nelem; e += TT) {
+        uint64_t gi = base | (e & lowmask);
+        const uint32_t r = e >> c;
+        for (int h = 0; h < nhigh; h++) gi |= (uint64_t)((r >> h) & 1u) << P.high_pos[h];
+        psi[gi] = s[e];
+    }
+}
+
+extern "C" int b200k_tile_program(double *psi, int n_local, const B200kTileProgram *prog,
+                                  void *stream)
+{
+    if (prog->t > B200K_MAX_TILE_BITS || prog->t > n_local || prog->n_ops > B200K_MAX_OPS ||
+        prog->nhigh > B200K_MAX_HIGH || prog->c + prog->nhigh != prog->t)
+        return (int)cudaErrorInvalidValue;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(k_tile_program,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)(sizeof(cplx) << B200K_MAX_TILE_BITS));
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    const uint64_t ntiles = 1ull << (n_local - prog->t);
+    if (ntiles > 0x7fffffffull) return (int)cudaErrorInvalidValue;
+    const size_t smem = sizeof(cplx) << prog->t;
+    k_tile_program<<<(unsigned)ntiles, TT, smem, (cudaStream_t)stream>>>(
+        reinterpret_cast<cplx *>(psi), *prog);
+    return (int)cudaGetLastError();
+}
+
+// =================================================================================================
+// Reductions: per-thread grid-stride accumulate -> warp shuffle tree -> per-block partials in
+// `scratch` -> single-block fixed-order final sum.  Deterministic run to run.
+// =================================================================================================
+#define RED_BLOCKS 1184 /* 148 SMs x 8 */
+#define RED_THREADS 256
+#define RED_MAXVALS 2
+
+extern "C" int64_t b200k_reduce_scratch_doubles(void) { return (int64_t)RED_BLOCKS * RED_MAXVALS; }
+
+template <int NV> __device__ __forceinline__ void block_reduce_store(double (&v)[NV], double *partial)
+{
+    __shared__ double sh[NV][RED_THREADS / 32];
+#pragma unroll
+    for (int q = 0; q < NV; q++) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) v[q] += __shfl_down_sync(0xffffffffu, v[q], off);
+    }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) {
+#pragma unroll
+        for (int q = 0; q < NV; q++) sh[q][w] = v[q];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int q = 0; q < NV; q++) {
+            double a = 0.0;
+            for (int i = 0; i < RED_THREADS / 32; i++) a += sh[q][i];
+            partial[(size_t)blockIdx.x * NV + q] = a;
+        }
+    }
+}
+
+template <int NV> __global__ void __launch_bounds__(RED_THREADS)
+k_reduce_final(const double *__restrict__ partial, int nblocks, double *__restrict__ out)
+{
+    double v[NV];
+#pragma unroll
+    for (int q = 0; q < NV; q++) v[q] = 0.0;
+    for (int i = threadIdx.x; i < nblocks; i += RED_THREADS) {
+#pragma unroll
+        for (int q = 0; q < NV; q++) v[q] += partial[(size_t)i * NV + q];
+    }
+    __shared__ double sh[NV][RED_THREADS / 32];
+#pragma unroll
+    for (int q = 0; q < NV; q++) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) v[q] += __shfl_down_sync(0xffffffffu, v[q], off);
+    }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) {
+#pragma unroll
+        for (int q = 0; q < NV; q++) sh[q][w] = v[q];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int q = 0; q < NV; q++) {
+            double a = 0.0;
+            for (int i = 0; i < RED_THREADS / 32; i++) a += sh[q][i];
+            out[q] = a;
+        }
+    }
+}
+
+static inline int red_blocks_for(uint64_t work)
+{
+    uint64_t b = (work + RED_THREADS - 1) / RED_THREADS;
+    if (b < 1) b = 1;
+    if (b > RED_BLOCKS) b = RED_BLOCKS;
+    return (int)b;
+}
+
+// ---- <phi| P |lam> for a Pauli word --------------------------------------------------------------
+__global__ void __launch_bounds__(RED_THREADS)
+k_bilinear_pauli(const cplx *__restrict__ phi, const cplx *__restrict__ lam, int n, uint64_t rank_base,
+                 uint64_t xm, uint64_t zm, int ny, uint64_t cmask, uint64_t cval,
+                 double *__restrict__ partial)
+{
+    double acc[2] = {0.0, 0.0};
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t start = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (xm == 0) {
+        const uint64_t N = 1ull << n;
+        for (uint64_t i = start; i < N; i += stride) {
+            const uint64_t gi = i | rank_base;
+            if ((gi & cmask) != cval) continue;
+            cplx tq = cconjmul(phi[i], lam[i]);
+            tq = cmul_ipow(tq, ny + 2 * (__popcll(gi & zm) & 1));
+            acc[0] += tq.x;
+            acc[1] += tq.y;
+        }
+    }
+    else {
+        const uint64_t top = 1ull << (63 - __clzll((long long)xm));
+        const uint64_t NP = 1ull << (n - 1);
+        const bool same = (phi == lam);
+        for (uint64_t g = start; g < NP; g += stride) {
+            const uint64_t i = insert_zeros64(g, top);
+            const uint64_t gi = i | rank_base;
+            if ((gi & cmask) != cval) continue;
+            const uint64_t j = i ^ xm, gj = gi ^ xm;
+            const cplx li = lam[i], lj = lam[j];
+            const cplx pi = same ? li : phi[i];
+            const cplx pj = same ? lj : phi[j];
+            // conj(phi_i) * ph(j) * lam_j + conj(phi_j) * ph(i) * lam_i
+            cplx t1 = cmul_ipow(cconjmul(pi, lj), ny + 2 * (__popcll(gj & zm) & 1));
+            cplx t2 = cmul_ipow(cconjmul(pj, li), ny + 2 * (__popcll(gi & zm) & 1));
+            acc[0] += t1.x + t2.x;
+            acc[1] += t1.y + t2.y;
+        }
+    }
+    block_reduce_store<2>(acc, partial);
+}
+
+extern "C" int b200k_bilinear_pauli(const double *phi, const double *lam, int n_local,
+                                    uint64_t rank_base, uint64_t xmask, uint64_t zmask, int ny,
+                                    uint64_t cmask, uint64_t cval, double *scratch, double *out,
+                                    void *stream)
+{
+    if (xmask >> n_local) return (int)cudaErrorInvalidValue;
+    const uint64_t work = xmask ? (1ull << (n_local - 1)) : (1ull << n_local);
+    const int nb = red_blocks_for(work);
+    k_bilinear_pauli<<<nb, RED_THREADS, 0, (cudaStream_t)stream>>>(
+        (const cplx *)phi, (const cplx *)lam, n_local, rank_base, xmask, zmask, ny, cmask, cval,
+        scratch);
+    k_reduce_final<2><<<1, RED_THREADS, 0, (cudaStream_t)stream>>>(scratch, nb, out);
+    return (int)cudaGetLastError();
+}
+
+// ---- <phi| (proj_ctrl (x) g on span{a,b}) |lam> ---------------------------------------------------
+struct G8 {
+    double v[8];
+};
+__global__ void __launch_bounds__(RED_THREADS)
+k_bilinear_pair(const cplx *__restrict__ phi, const cplx *__restrict__ lam, int n, uint64_t rank_base,
+                uint64_t tmask, uint64_t a, uint64_t b, G8 g, uint64_t cmask, uint64_t cval,
+                double *__restrict__ partial)
+{
+    double acc[2] = {0.0, 0.0};
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t NG = 1ull << (n - __popcll(tmask));
+    const cplx g00 = make_double2(g.v[0], g.v[1]), g01 = make_double2(g.v[2], g.v[3]);
+    const cplx g10 = make_double2(g.v[4], g.v[5]), g11 = make_double2(g.v[6], g.v[7]);
+    for (uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; q < NG; q += stride) {
+        const uint64_t i = insert_zeros64(q, tmask);
+        if (((i | rank_base) & cmask) != cval) continue;
+        const cplx la = lam[i | a], lb = lam[i | b];
+        const cplx pa = phi[i | a], pb = phi[i | b];
+        const cplx ga = cfma(g00, la, cmul(g01, lb));
+        const cplx gb = cfma(g10, la, cmul(g11, lb));
+        const cplx t1 = cconjmul(pa, ga), t2 = cconjmul(pb, gb);
+        acc[0] += t1.x + t2.x;
+        acc[1] += t1.y + t2.y;
+    }
+    block_reduce_store<2>(acc, partial);
+}
+
+extern "C" int b200k_bilinear_pair(const double *phi, const double *lam, int n_local,
+                                   uint64_t rank_base, uint64_t tmask, uint64_t a, uint64_t b,
+                                   const double *g8, uint64_t cmask, uint64_t cval, double *scratch,
+                                   double *out, void *stream)
+{
+    if (tmask == 0 || (tmask >> n_local)) return (int)cudaErrorInvalidValue;
+    G8 g;
+    for (int i = 0; i < 8; i++) g.v[i] = g8[i];
+    const uint64_t work = 1ull << (n_local - __builtin_popcountll(tmask));
+    const int nb = red_blocks_for(work);
+    k_bilinear_pair<<<nb, RED_THREADS, 0, (cudaStream_t)stream>>>(
+        (const cplx *)phi, (const cplx *)lam, n_local, rank_base, tmask, a, b, g, cmask, cval,
+        scratch);
+    k_reduce_final<2><<<1, RED_THREADS, 0, (cudaStream_t)stream>>>(scratch, nb, out);
+    return (int)cudaGetLastError();
+}
+
+// ---- sum_t coef_t <psi| Z-string_t |psi> in one read pass -----------------------------------------
+__global__ void __launch_bounds__(RED_THREADS)
+k_expval_diag_batch(const cplx *__restrict__ psi, int n, uint64_t rank_base,
+                    const uint64_t *__restrict__ zmasks, const double *__restrict__ coefs, int nterms,
+                    double *__restrict__ partial)
+{
+    extern __shared__ unsigned char smraw[];
+    uint64_t *sz = reinterpret_cast<uint64_t *>(smraw);
+    double *sc = reinterpret_cast<double *>(smraw + sizeof(uint64_t) * nterms);
+    for (int q = threadIdx.x; q < nterms; q += blockDim.x) {
+        sz[q] = zmasks[q];
+        sc[q] = coefs[q];
+    }
+    __syncthreads();
+    double acc[1] = {0.0};
+    const uint64_t N = 1ull << n;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += stride) {
+        const cplx v = psi[i];
+        const double p = v.x * v.x + v.y * v.y;
+        const uint64_t gi = i | rank_base;
+        double w = 0.0;
+        for (int q = 0; q < nterms; q++) w += (__popcll(gi & sz[q]) & 1) ? -sc[q] : sc[q];
+        acc[0] = fma(p, w, acc[0]);
+    }
+    block_reduce_store<1>(acc, partial);
+}
+
+extern "C" int b200k_expval_diag_batch(const double *psi, int n_local, uint64_t rank_base,
+                                       const uint64_t *zmasks, const double *coefs, int nterms,
+                                       double *scratch, double *out, void *stream)
+{
+    if (nterms < 1 || nterms > 2048) return (int)cudaErrorInvalidValue;
+    const int nb = red_blocks_for(1ull << n_local);
+    k_expval_diag_batch<<<nb, RED_THREADS, 16 * (size_t)nterms, (cudaStream_t)stream>>>(
+        (const cplx *)psi, n_local, rank_base, zmasks, coefs, nterms, scratch);
+    k_reduce_final<1><<<1, RED_THREADS, 0, (cudaStream_t)stream>>>(scratch, nb, out);
+    return (int)cudaGetLastError();
+}
+
+// =================================================================================================
+// Probabilities
+// =================================================================================================
+__global__ void __launch_bounds__(256)
+k_probs_all(const cplx *__restrict__ psi, double *__restrict__ out, uint64_t N)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x * 2;
+    for (uint64_t i = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 2; i < N; i += stride) {
+        const cplx a = psi[i], b = psi[i + 1];
+        *reinterpret_cast<double2 *>(out + i) =
+            make_double2(a.x * a.x + a.y * a.y, b.x * b.x + b.y * b.y);
+    }
+}
+__global__ void k_probs_all1(const cplx *psi, double *out)
+{
+    out[0] = psi[0].x * psi[0].x + psi[0].y * psi[0].y;
+}
+
+extern "C" int b200k_probs_all(const double *psi, double *out, int n_local, void *stream)
+{
+    const uint64_t N = 1ull << n_local;
+    if (N == 1) {
+        k_probs_all1<<<1, 1, 0, (cudaStream_t)stream>>>((const cplx *)psi, out);
+        return (int)cudaGetLastError();
+    }
+    uint64_t nb = (N / 2 + 255) / 256;
+    if (nb > 148 * 32) nb = 148 * 32;
+    k_probs_all<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>((const cplx *)psi, out, N);
+    return (int)cudaGetLastError();
+}
+
+// Marginal on k target bits.  A group of GS threads (1, 32 or 256) owns one (bin, split) work item
+// and sums |psi|^2 over its slice of the 2^(n-k) complementary indices.
+struct TB64 {
+    uint8_t tb[64];
+};
+static inline void probs_shape(int n, int k, int *gs, int *splits)
+{
+    const int rest = n - k; // log2 of elements per bin
+    int g = rest >= 8 ? 256 : (rest >= 5 ? 32 : 1);
+    // want ~2^18 threads in flight: bins * splits * gs >= 2^18 where possible
+    int s = 0; // log2 splits
+    while ((k + s) + (g == 256 ? 8 : g == 32 ? 5 : 0) < 18 && rest - s > (g == 256 ? 10 : g == 32 ? 7 : 2))
+        s++;
+    *gs = g;
+    *splits = 1 << s;
+}
+extern "C" int b200k_probs_splits(int n_local, int k)
+{
+    int gs, sp;
+    probs_shape(n_local, k, &gs, &sp);
+    return sp;
+}
+
+template <int GS> __global__ void __launch_bounds__(256)
+k_probs_partial(const cplx *__restrict__ psi, int n, int k, TB64 T, uint64_t tmask, int log_splits,
+                double *__restrict__ partial)
+{
+    const uint64_t nitems = 1ull << (k + log_splits);
+    const uint64_t gid = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / GS;
+    const int lane = threadIdx.x % GS;
+    if (gid >= nitems) return; // whole group exits together (GS divides blockDim)
+    const uint64_t bin = gid >> log_splits, split = gid & ((1ull << log_splits) - 1);
+    uint64_t binbits = 0;
+    for (int j = 0; j < k; j++) binbits |= ((bin >> (k - 1 - j)) & 1ull) << T.tb[j];
+    const uint64_t per = 1ull << (n - k - log_splits);
+    const uint64_t r0 = split * per;
+    double acc = 0.0;
+    for (uint64_t r = lane; r < per; r += GS) {
+        const uint64_t i = insert_zeros64(r0 + r, tmask) | binbits;
+        const cplx v = psi[i];
+        acc += v.x * v.x + v.y * v.y;
+    }
+    if (GS >= 32) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, off);
+    }
+    if (GS == 256) {
+        __shared__ double sh[8];
+        if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double a = 0.0;
+            for (int i = 0; i < 8; i++) a += sh[i];
+            partial[gid] = a;
+        }
+    }
+    else if (lane == 0) {
+        partial[gid] = acc;
+    }
+}
+__global__ void k_probs_finish(const double *__restrict__ partial, int log_splits, uint64_t nbins,
+                               double *__restrict__ out)
+{
+    const uint64_t o = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (o >= nbins) return;
+    double a = 0.0;
+    const uint64_t ns = 1ull << log_splits;
+    for (uint64_t q = 0; q < ns; q++) a += partial[(o << log_splits) + q];
+    out[o] = a;
+}
+
+extern "C" int b200k_probs_partial(const double *psi, int n_local, const uint8_t *tb, int k,
+                                   double *scratch, double *out, void *stream)
+{
+    if (k < 0 || k > n_local || k > 62) return (int)cudaErrorInvalidValue;
+    TB64 T;
+    uint64_t tmask = 0;
+    for (int j = 0; j < k; j++) {
+        T.tb[j] = tb[j];
+        tmask |= 1ull << tb[j];
+    }
+    int gs, sp;
+    probs_shape(n_local, k, &gs, &sp);
+    int ls = 0;
+    while ((1 << ls) < sp) ls++;
+    const uint64_t nitems = 1ull << (k + ls);
+    const uint64_t nthreads = nitems * (uint64_t)gs;
+    const uint64_t nb = (nthreads + 255) / 256;
+    if (nb > 0x7fffffffull) return (int)cudaErrorInvalidValue;
+    cudaStream_t st = (cudaStream_t)stream;
+    const cplx *p = (const cplx *)psi;
+    if (gs == 256) k_probs_partial<256><<<(unsigned)nb, 256, 0, st>>>(p, n_local, k, T, tmask, ls, scratch);
+    else if (gs == 32) k_probs_partial<32><<<(unsigned)nb, 256, 0, st>>>(p, n_local, k, T, tmask, ls, scratch);
+    else k_probs_partial<1><<<(unsigned)nb, 256, 0, st>>>(p, n_local, k, T, tmask, ls, scratch);
+    const uint64_t nbins = 1ull << k;
+    k_probs_finish<<<(unsigned)((nbins + 255) / 256), 256, 0, st>>>(scratch, ls, nbins, out);
+    return (int)cudaGetLastError();
+}
+
+// =================================================================================================
+// Element-wise passes
+// =================================================================================================
+__global__ void __launch_bounds__(256)
+k_collapse(cplx *__restrict__ psi, uint64_t N, uint64_t rank_base, uint64_t bit, int keep, double scale)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += stride) {
+        const bool b = ((i | rank_base) & bit) != 0;
+        if (b == (keep != 0)) {
+            cplx v = psi[i];
+            psi[i] = make_double2(v.x * scale, v.y * scale);
+        }
+        else {
+            psi[i] = make_double2(0.0, 0.0);
+        }
+    }
+}
+static inline unsigned ew_blocks(uint64_t N)
+{
+    uint64_t nb = (N + 255) / 256;
+    if (nb > 148 * 32) nb = 148 * 32;
+    return (unsigned)nb;
+}
+extern "C" int b200k_collapse(double *psi, int n_local, uint64_t rank_base, int pos, int keep,
+                              double scale, void *stream)
+{
+    const uint64_t N = 1ull << n_local;
+    k_collapse<<<ew_blocks(N), 256, 0, (cudaStream_t)stream>>>((cplx *)psi, N, rank_base, 1ull << pos,
+                                                              keep, scale);
+    return (int)cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256)
+k_pauli_apply(cplx *__restrict__ out, const cplx *__restrict__ in, uint64_t N, uint64_t rank_base,
+              uint64_t xm, uint64_t zm, int ny, cplx coef, int accumulate)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += stride) {
+        const uint64_t j = i ^ xm;
+        cplx v = cmul_ipow(in[j], ny + 2 * (__popcll((j | rank_base) & zm) & 1));
+        v = cmul(v, coef);
+        if (accumulate) v = cadd(v, out[i]);
+        out[i] = v;
+    }
+}
+extern "C" int b200k_pauli_apply(double *out, const double *in, int n_local, uint64_t rank_base,
+                                 uint64_t xmask, uint64_t zmask, int ny, double coef_re,
+                                 double coef_im, int accumulate, void *stream)
+{
+    if (xmask >> n_local) return (int)cudaErrorInvalidValue;
+    const uint64_t N = 1ull << n_local;
+    k_pauli_apply<<<ew_blocks(N), 256, 0, (cudaStream_t)stream>>>(
+        (cplx *)out, (const cplx *)in, N, rank_base, xmask, zmask, ny,
+        make_double2(coef_re, coef_im), accumulate);
+    return (int)cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256)
+k_axpy(cplx *__restrict__ acc, const cplx *__restrict__ x, double coef, uint64_t N)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += stride) {
+        const cplx a = acc[i], b = x[i];
+        acc[i] = make_double2(fma(coef, b.x, a.x), fma(coef, b.y, a.y));
+    }
+}
+extern "C" int b200k_axpy(double *acc, const double *x, double coef, int n_local, void *stream)
+{
+    const uint64_t N = 1ull << n_local;
+    k_axpy<<<ew_blocks(N), 256, 0, (cudaStream_t)stream>>>((cplx *)acc, (const cplx *)x, coef, N);
+    return (int)cudaGetLastError();
+}
+
+__global__ void k_set_one(cplx *psi, int64_t idx) { psi[idx] = make_double2(1.0, 0.0); }
+extern "C" int b200k_set_basis(double *psi, int n_local, int64_t local_index, void *stream)
+{
+    cudaError_t e = cudaMemsetAsync(psi, 0, sizeof(cplx) << n_local, (cudaStream_t)stream);
+    if (e != cudaSuccess) return (int)e;
+    if (local_index >= 0) k_set_one<<<1, 1, 0, (cudaStream_t)stream>>>((cplx *)psi, local_index);
+    return (int)cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256)
+k_scatter_state(cplx *__restrict__ psi, const cplx *__restrict__ vals, int k, TB64 T)
+{
+    const uint64_t K = 1ull << k;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; r < K; r += stride) {
+        uint64_t idx = 0;
+        for (int j = 0; j < k; j++) idx |= ((r >> (k - 1 - j)) & 1ull) << T.tb[j];
+        psi[idx] = vals[r];
+    }
+}
+extern "C" int b200k_scatter_state(double *psi, const double *vals, int n_local, const uint8_t *tb,
+                                   int k, void *stream)
+{
+    if (k < 0 || k > n_local || k > 62) return (int)cudaErrorInvalidValue;
+    cudaError_t e = cudaMemsetAsync(psi, 0, sizeof(cplx) << n_local, (cudaStream_t)stream);
+    if (e != cudaSuccess) return (int)e;
+    TB64 T;
+    for (int j = 0; j < k; j++) T.tb[j] = tb[j];
+    k_scatter_state<<<ew_blocks(1ull << k), 256, 0, (cudaStream_t)stream>>>((cplx *)psi,
+                                                                          (const cplx *)vals, k, T);
+    return (int)cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256)
+k_append_qubit(cplx *__restrict__ dst, const cplx *__restrict__ src, uint64_t Nold)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < Nold; i += stride) {
+        dst[2 * i] = src[i];
+        dst[2 * i + 1] = make_double2(0.0, 0.0);
+    }
+}
+extern "C" int b200k_append_qubit(double *dst, const double *src, int n_local_old, void *stream)
+{
+    const uint64_t N = 1ull << n_local_old;
+    k_append_qubit<<<ew_blocks(N), 256, 0, (cudaStream_t)stream>>>((cplx *)dst, (const cplx *)src, N);
+    return (int)cudaGetLastError();
+}
+
+// =================================================================================================
+// Alias sampler without the sequential table build.
+//
+// Reference algorithm (verified against doc/releases/changelog-0.9.0.md:
+// 299-315): first[i] = N p[i]; indices with first < 1 go on an `under` stack, the others on an
+// `over` stack (both filled in ascending order, so popped in DESCENDING index order); the top
+// `over` item donates to successive `under` items until it drops below 1, becomes the top `under`
+// item itself and is served first by the next donor.  A shot draws idx = floor(u1 N) and moves to
+// partner[idx] iff u2 >= first[idx].
+//
+// Restated with prefix sums in descending index order: D = inclusive prefix of deficits 1-first
+// over `under` items, E = inclusive prefix of excesses first-1 over `over` items.
+//   under item u : first unchanged; partner = first over item m with E_m >= D_u - deficit_u
+//   over item m  : let u* = first under item with D_u* > E_m.  None -> never drops below 1 ->
+//                  always accepted.  Else first = 1 - (D_u* - E_m), partner = next over item.
+// Only the buckets the shots actually hit are evaluated; chunk sums (descending chunks of CH
+// entries, summed sequentially in a fixed order) give each query an O(CH + log) walk.
+// =================================================================================================
+#define SAMP_CH 1024
+
+// scratch layout (doubles): [cumD: nch+1][cumE: nch+1]   (exclusive prefix over descending chunks)
+extern "C" int64_t b200k_sampler_scratch_doubles(int64_t nbins)
+{
+    const int64_t nch = (nbins + SAMP_CH - 1) / SAMP_CH;
+    return 4 * (nch + 1);
+}
+
+__global__ void k_samp_chunk_sums(const double *__restrict__ p, int64_t N, int64_t nch,
+                                  double *__restrict__ sumD, double *__restrict__ sumE)
+{
+    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nch) return;
+    // chunk q covers descending positions [q*CH, (q+1)*CH): indices N-1-q*CH downwards
+    const int64_t hi = N - 1 - q * SAMP_CH;
+    int64_t lo = hi - SAMP_CH + 1;
+    if (lo < 0) lo = 0;
+    const double dN = (double)N;
+    double d = 0.0, e = 0.0;
+    for (int64_t i = hi; i >= lo; i--) {
+        const double f = dN * p[i];
+        if (f < 1.0) d += 1.0 - f;
+        else e += f - 1.0;
+    }
+    sumD[q] = d;
+    sumE[q] = e;
+}
+
+// single block, 1024 threads: exclusive scan of the chunk sums in a fixed sequential order
+__global__ void __launch_bounds__(1024)
+k_samp_scan(const double *__restrict__ sumD, const double *__restrict__ sumE, int64_t nch,
+            double *__restrict__ cumD, double *__restrict__ cumE)
+{
+    __shared__ double segD[1024], segE[1024];
+    __shared__ double totD, totE;
+    const int tid = threadIdx.x;
+    const int64_t per = (nch + 1023) / 1024;
+    int64_t q0 = tid * per, q1 = q0 + per;
+    if (q0 > nch) q0 = nch;
+    if (q1 > nch) q1 = nch;
+    double d = 0.0, e = 0.0;
+    for (int64_t q = q0; q < q1; q++) {
+        d += sumD[q];
+        e += sumE[q];
+    }
+    segD[tid] = d;
+    segE[tid] = e;
+    __syncthreads();
+    if (tid == 0) {
+        double rd = 0.0, re = 0.0;
+        for (int i = 0; i < 1024; i++) {
+            const double td = segD[i], te = segE[i];
+            segD[i] = rd;
+            segE[i] = re;
+            rd += td;
+            re += te;
+        }
+        totD = rd;
+        totE = re;
+    }
+    __syncthreads();
+    const double bd = segD[tid], be = segE[tid];
+    d = 0.0;
+    e = 0.0;
+    for (int64_t q = q0; q < q1; q++) {
+        cumD[q] = bd + d;
+        cumE[q] = be + e;
+        d += sumD[q];
+        e += sumE[q];
+    }
+    if (tid == 0) {
+        cumD[nch] = totD;
+        cumE[nch] = totE;
+    }
+}
+
+extern "C" int b200k_sampler_prepare(const double *probs, int64_t nbins, double *scratch,
+                                     void *stream)
+{
+    const int64_t nch = (nbins + SAMP_CH - 1) / SAMP_CH;
+    double *cumD = scratch, *cumE = scratch + (nch + 1);
+    double *sumD = scratch + 2 * (nch + 1), *sumE = scratch + 3 * (nch + 1);
+    cudaStream_t st = (cudaStream_t)stream;
+    k_samp_chunk_sums<<<(unsigned)((nch + 127) / 128), 128, 0, st>>>(probs, nbins, nch, sumD, sumE);
+    k_samp_scan<<<1, 1024, 0, st>>>(sumD, sumE, nch, cumD, cumE);
+    return (int)cudaGetLastError();
+}
+
+// first chunk q in [0, nch) with cum[q+1] >= x (strict=false) or cum[q+1] > x (strict=true);
+// returns nch if none.
+__device__ __forceinline__ int64_t samp_find_chunk(const double *cum, int64_t nch, double x, bool strict)
+{
+    int64_t lo = 0, hi = nch; // answer in [lo, hi]
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        const double v = cum[mid + 1];
+        const bool ok = strict ? (v > x) : (v >= x);
+        if (ok) hi = mid;
+        else lo = mid + 1;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(128)
+k_samp_draw(const double *__restrict__ p, int64_t N, int64_t nch, const double *__restrict__ cumD,
+            const double *__restrict__ cumE, const double *__restrict__ u, int64_t nshots,
+            int64_t *__restrict__ out)
+{
+    const int64_t sidx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (sidx >= nshots) return;
+    const double dN = (double)N;
+    const double u1 = u[2 * sidx], u2 = u[2 * sidx + 1];
+    int64_t idx = (int64_t)(u1 * dN);
+    if (idx >= N) idx = N - 1;
+    const double f = dN * p[idx];
+    const int64_t q = (N - 1 - idx) / SAMP_CH;
+    const int64_t chunk_hi = N - 1 - q * SAMP_CH;
+    int64_t result = idx;
+    if (f < 1.0) {
+        // under item: accepted iff u2 < first = f
+        if (u2 >= f) {
+            // X = exclusive prefix of deficits before idx
+            double x = 0.0;
+            for (int64_t i = chunk_hi; i > idx; i--) {
+                const double fi = dN * p[i];
+                if (fi < 1.0) x += 1.0 - fi;
+            }
+            x = cumD[q] + x;
+            // partner = first over item m (descending) with E_m >= x
+            int64_t qq = samp_find_chunk(cumE, nch, x, false);
+            bool found = false;
+            while (qq < nch && !found) {
+                const int64_t hi = N - 1 - qq * SAMP_CH;
+                int64_t lo = hi - SAMP_CH + 1;
+                if (lo < 0) lo = 0;
+                double e = 0.0;
+                for (int64_t i = hi; i >= lo; i--) {
+                    const double fi = dN * p[i];
+                    if (fi >= 1.0) {
+                        e += fi - 1.0;
+                        if (cumE[qq] + e >= x) {
+                            result = i;
+                            found = true;
+                            break;
+                        }
+                    }
+                }
+                qq++;
+            }
+        }
+    }
+    else {
+        // over item: E_m inclusive
+        double e = 0.0;
+        for (int64_t i = chunk_hi; i >= idx; i--) {
+            const double fi = dN * p[i];
+            if (fi >= 1.0) e += fi - 1.0;
+        }
+        const double Em = cumE[q] + e;
+        // first under item with D > Em
+        int64_t qq = samp_find_chunk(cumD, nch, Em, true);
+        bool found = false;
+        double Dstar = 0.0;
+        while (qq < nch && !found) {
+            const int64_t hi = N - 1 - qq * SAMP_CH;
+            int64_t lo = hi - SAMP_CH + 1;
+            if (lo < 0) lo = 0;
+            double d = 0.0;
+            for (int64_t i = hi; i >= lo; i--) {
+                const double fi = dN * p[i];
+                if (fi < 1.0) {
+                    d += 1.0 - fi;
+                    if (cumD[qq] + d > Em) {
+                        Dstar = cumD[qq] + d;
+                        found = true;
+                        break;
+                    }
+                }
+            }
+            qq++;
+        }
+        if (found) {
+            const double first = 1.0 - (Dstar - Em);
+            if (u2 >= first) {
+                // partner = next over item below idx
+                for (int64_t i = idx - 1; i >= 0; i--) {
+                    if (dN * p[i] >= 1.0) {
+                        result = i;
+                        break;
+                    }
+                }
+            }
+        }
+    }
+    out[sidx] = result;
+}
+
+extern "C" int b200k_sampler_draw(const double *probs, int64_t nbins, const double *scratch,
+                                  const double *u, int64_t nshots, int64_t *out_idx, void *stream)
+{
+    if (nshots <= 0) return 0;
+    const int64_t nch = (nbins + SAMP_CH - 1) / SAMP_CH;
+    const double *cumD = scratch, *cumE = scratch + (nch + 1);
+    k_samp_draw<<<(unsigned)((nshots + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+        probs, nbins, nch, cumD, cumE, u, nshots, out_idx);
+    return (int)cudaGetLastError();
+}

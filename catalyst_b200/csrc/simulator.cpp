@@ -1,0 +1,1587 @@
+// simulator.cpp — host layer of the B200 state-vector device (see simulator.hpp).
+//
+// Gate and measurement semantics follow the reference's device contract
+// (runtime/include/QuantumDevice.hpp:215-567) as lightning.qubit implements it; conventions that
+// the reference pins in-tree are cited where they are used.  The arithmetic runs only on the GPU:
+// there is no CPU code path for any amplitude.
+#include "simulator.hpp"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <sstream>
+
+namespace b200 {
+
+#define B200_FAIL(msg) throw ::b200::Error(std::string(msg))
+#define B200_FAIL_IF(cond, msg)                                                                    \
+    do {                                                                                           \
+        if (cond) B200_FAIL(msg);                                                                  \
+    } while (0)
+#define CUDA_CHECK(expr)                                                                           \
+    do {                                                                                           \
+        cudaError_t _e = (cudaError_t)(expr);                                                      \
+        if (_e != cudaSuccess) {                                                                   \
+            std::ostringstream _s;                                                                 \
+            _s << "CUDA error " << (int)_e << " (" << cudaGetErrorString(_e) << ") at "           \
+               << __FILE__ << ":" << __LINE__ << " in " #expr;                                     \
+            cudaGetLastError();                                                                    \
+            throw ::b200::Error(_s.str());                                                         \
+        }                                                                                          \
+    } while (0)
+
+static const cplx I_(0.0, 1.0);
+
+class DeviceBuffer {
+  public:
+    explicit DeviceBuffer(size_t bytes) : bytes_(bytes)
+    {
+        CUDA_CHECK(cudaMalloc(&p_, bytes ? bytes : 16));
+    }
+    ~DeviceBuffer() { cudaFree(p_); }
+    DeviceBuffer(const DeviceBuffer &) = delete;
+    DeviceBuffer &operator=(const DeviceBuffer &) = delete;
+    double *d() const { return static_cast<double *>(p_); }
+    void *p() const { return p_; }
+    size_t bytes() const { return bytes_; }
+
+  private:
+    void *p_ = nullptr;
+    size_t bytes_;
+};
+
+// -------------------------------------------------------------------------------------------------
+Options parse_kwargs(const char *kwargs)
+{
+    // str(dict) as produced by the frontend, e.g. "{'shots': 0, 'mcmc': False}"
+    // (reference parser: runtime/lib/backend/common/Utils.hpp:107-156 — strip braces, quotes and
+    // spaces, split on ',' and ':').
+    Options o;
+    if (!kwargs) return o;
+    std::string s;
+    for (const char *p = kwargs; *p; p++)
+        if (*p != '{' && *p != '}' && *p != '\'' && *p != '"' && *p != ' ') s.push_back(*p);
+    std::stringstream ss(s);
+    std::string item;
+    while (std::getline(ss, item, ',')) {
+        const auto pos = item.find(':');
+        if (pos == std::string::npos) continue;
+        const std::string k = item.substr(0, pos), v = item.substr(pos + 1);
+        auto as_int = [&](int64_t dflt) -> int64_t {
+            if (v == "True" || v == "true") return 1;
+            if (v == "False" || v == "false") return 0;
+            if (v == "None" || v.empty()) return dflt;
+            try {
+                return std::stoll(v);
+            }
+            catch (...) {
+                throw Error("Invalid value for device kwarg '" + k + "': " + v);
+            }
+        };
+        if (k == "shots") o.shots = as_int(0);
+        else if (k == "tile_bits") o.tile_bits = (int)as_int(o.tile_bits);
+        else if (k == "min_row_bits") o.min_row_bits = (int)as_int(o.min_row_bits);
+        else if (k == "fuse") o.fuse = as_int(1) != 0;
+        else if (k == "device") o.device = (int)as_int(-1);
+    }
+    B200_FAIL_IF(o.tile_bits < 1 || o.tile_bits > B200K_MAX_TILE_BITS, "tile_bits out of range");
+    B200_FAIL_IF(o.min_row_bits < 0 || o.min_row_bits > o.tile_bits, "min_row_bits out of range");
+    return o;
+}
+
+// -------------------------------------------------------------------------------------------------
+Simulator::Simulator(const Options &opt) : opt_(opt)
+{
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        cudaGetLastError();
+        B200_FAIL("b200sv: no CUDA device available (this device has no CPU fallback): " +
+                  std::string(e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e)));
+    }
+    int dev = opt_.device;
+    if (dev < 0) {
+        const char *lr = std::getenv("LOCAL_RANK");
+        dev = lr ? std::atoi(lr) % count : 0;
+    }
+    B200_FAIL_IF(dev >= count, "b200sv: CUDA device ordinal out of range");
+    cuda_device_ = dev;
+    CUDA_CHECK(cudaSetDevice(dev));
+    cudaStream_t st;
+    CUDA_CHECK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    stream_ = st;
+    cudaEvent_t a, b;
+    CUDA_CHECK(cudaEventCreate(&a));
+    CUDA_CHECK(cudaEventCreate(&b));
+    ev0_ = a;
+    ev1_ = b;
+    pinned_doubles_ = 1 << 16;
+    CUDA_CHECK(cudaMallocHost((void **)&pinned_, pinned_doubles_ * sizeof(double)));
+    scratch_ = std::make_unique<DeviceBuffer>((size_t)b200k_reduce_scratch_doubles() * sizeof(double));
+    results_ = std::make_unique<DeviceBuffer>(4096 * sizeof(double));
+}
+
+Simulator::~Simulator()
+{
+    cudaSetDevice(cuda_device_);
+    if (stream_) cudaStreamSynchronize((cudaStream_t)stream_);
+    psi_.reset();
+    tmp_.reset();
+    acc_.reset();
+    scratch_.reset();
+    results_.reset();
+    probs_buf_.reset();
+    misc_.reset();
+    matrix_arena_.reset();
+    if (pinned_) cudaFreeHost(pinned_);
+    if (ev0_) cudaEventDestroy((cudaEvent_t)ev0_);
+    if (ev1_) cudaEventDestroy((cudaEvent_t)ev1_);
+    if (stream_) cudaStreamDestroy((cudaStream_t)stream_);
+}
+
+void Simulator::ensure_buffer(std::unique_ptr<DeviceBuffer> &buf, size_t bytes)
+{
+    if (buf && buf->bytes() >= bytes) return;
+    if (buf) CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    buf.reset();
+    buf = std::make_unique<DeviceBuffer>(bytes);
+}
+
+void Simulator::allocate(int64_t n)
+{
+    CUDA_CHECK(cudaSetDevice(cuda_device_));
+    B200_FAIL_IF(n < 0 || n > 40, "Invalid number of qubits");
+    if (n_ > 0 || psi_) release();
+    n_ = n;
+    const size_t bytes = sizeof(cplx) << n;
+    try {
+        psi_ = std::make_unique<DeviceBuffer>(bytes);
+    }
+    catch (const Error &e) {
+        n_ = 0;
+        throw Error(std::string("AllocateQubits: cannot allocate the state vector in HBM: ") +
+                    e.what());
+    }
+    CUDA_CHECK(b200k_set_basis(psi_->d(), (int)n_, 0, stream_));
+    note_launch();
+}
+
+void Simulator::allocate_one()
+{
+    if (!psi_) {
+        allocate(1);
+        return;
+    }
+    flush();
+    auto nb = std::make_unique<DeviceBuffer>(sizeof(cplx) << (n_ + 1));
+    CUDA_CHECK(b200k_append_qubit(nb->d(), psi_->d(), (int)n_, stream_));
+    note_launch();
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    psi_ = std::move(nb);
+    tmp_.reset();
+    acc_.reset();
+    n_ += 1;
+}
+
+void Simulator::release()
+{
+    if (stream_) cudaStreamSynchronize((cudaStream_t)stream_);
+    queue_.clear();
+    psi_.reset();
+    tmp_.reset();
+    acc_.reset();
+    probs_buf_.reset();
+    n_ = 0;
+    obs_.clear();
+    tape_.clear();
+    tape_obs_.clear();
+    recording_ = false;
+}
+
+void Simulator::reset_stats() { stats_ = b200sv_stats{}; }
+
+void *Simulator::device_pointer() { return psi_ ? psi_->p() : nullptr; }
+
+// ---- RNG ----------------------------------------------------------------------------------------
+void Simulator::set_prng(b200sv_rng_next_fn fn, void *ctx)
+{
+    rng_fn_ = fn;
+    rng_ctx_ = ctx;
+    own_seeded_ = false;
+}
+void Simulator::seed(uint32_t s)
+{
+    own_gen_ = std::mt19937(s);
+    own_seeded_ = true;
+    rng_fn_ = nullptr;
+}
+uint32_t Simulator::prng_peek()
+{
+    if (own_seeded_) {
+        std::mt19937 c = own_gen_;
+        return (uint32_t)c();
+    }
+    return 0;
+}
+uint32_t Simulator::rng_next()
+{
+    if (rng_fn_) return rng_fn_(rng_ctx_);
+    return (uint32_t)own_gen_();
+}
+namespace {
+struct BorrowedEngine { // same min/max as std::mt19937 => identical generate_canonical arithmetic
+    using result_type = uint32_t;
+    std::function<uint32_t()> next;
+    static constexpr result_type min() { return 0; }
+    static constexpr result_type max() { return 0xffffffffu; }
+    result_type operator()() { return next(); }
+};
+} // namespace
+
+// ---- wires ----------------------------------------------------------------------------------------
+int Simulator::lbit(int64_t wire) const
+{
+    B200_FAIL_IF(wire < 0 || wire >= n_, "Invalid wire index " + std::to_string(wire));
+    return (int)(n_ - 1 - wire); // wire 0 = most significant bit
+}
+uint64_t Simulator::bit_of(int64_t wire) const { return 1ull << lbit(wire); }
+
+void Simulator::check_wires(const std::vector<int64_t> &wires, const std::vector<int64_t> &cw) const
+{
+    uint64_t seen = 0;
+    for (auto w : wires) {
+        const uint64_t b = bit_of(w);
+        B200_FAIL_IF(seen & b, "Repeated wire in operation");
+        seen |= b;
+    }
+    for (auto w : cw) {
+        const uint64_t b = bit_of(w);
+        B200_FAIL_IF(seen & b, "Control wire overlaps another wire of the operation");
+        seen |= b;
+    }
+}
+
+// ---- gate canonicalisation ------------------------------------------------------------------------
+static void dagger2(cplx *m)
+{
+    const cplx t01 = m[1];
+    m[0] = std::conj(m[0]);
+    m[1] = std::conj(m[2]);
+    m[2] = std::conj(t01);
+    m[3] = std::conj(m[3]);
+}
+
+void Simulator::canonicalize(std::vector<GateOp> &out, const std::string &name,
+                             const std::vector<double> &p, const std::vector<int64_t> &wires,
+                             bool inverse, const std::vector<int64_t> &cw,
+                             const std::vector<bool> &cv, const std::string &pauli_word) const
+{
+    B200_FAIL_IF(cw.size() != cv.size(), "Control wires/values size mismatch");
+    check_wires(wires, cw);
+    uint64_t cmask = 0, cval = 0;
+    for (size_t i = 0; i < cw.size(); i++) {
+        cmask |= bit_of(cw[i]);
+        if (cv[i]) cval |= bit_of(cw[i]);
+    }
+    auto need = [&](size_t nw, size_t np) {
+        B200_FAIL_IF(wires.size() != nw, "Invalid number of wires for " + name);
+        B200_FAIL_IF(p.size() != np, "Invalid number of parameters for " + name);
+    };
+    const size_t first = out.size();
+    auto W = [&](size_t i) { return bit_of(wires[i]); };
+    auto pair = [&](uint64_t xm, uint64_t a, uint64_t b, cplx m00, cplx m01, cplx m10, cplx m11,
+                    uint64_t extra_c = 0) {
+        GateOp g;
+        g.kind = GateOp::PAIR;
+        g.xmask = xm;
+        g.a = a;
+        g.b = b;
+        g.m[0] = m00; g.m[1] = m01; g.m[2] = m10; g.m[3] = m11;
+        g.cmask = cmask | extra_c;
+        g.cval = cval | extra_c;
+        out.push_back(std::move(g));
+    };
+    auto one = [&](cplx m00, cplx m01, cplx m10, cplx m11, size_t wi = 0, uint64_t extra_c = 0) {
+        pair(W(wi), 0, W(wi), m00, m01, m10, m11, extra_c);
+    };
+    auto phase = [&](cplx e, uint64_t ones) { // e where all `ones` bits are 1 (and controls hold)
+        GateOp g;
+        g.kind = GateOp::PHASE;
+        g.m[0] = e;
+        g.cmask = cmask | ones;
+        g.cval = cval | ones;
+        out.push_back(std::move(g));
+    };
+    auto parity = [&](uint64_t zm, cplx e0, cplx e1, uint64_t extra_c = 0) {
+        GateOp g;
+        g.kind = GateOp::PARITY;
+        g.zmask = zm;
+        g.m[0] = e0;
+        g.m[1] = e1;
+        g.cmask = cmask | extra_c;
+        g.cval = cval | extra_c;
+        out.push_back(std::move(g));
+    };
+    const double th = p.empty() ? 0.0 : p[0];
+    const double c = std::cos(th / 2), s = std::sin(th / 2);
+    const double isq2 = 1.0 / std::sqrt(2.0);
+    const cplx em = std::exp(-I_ * (th / 2)), ep = std::exp(I_ * (th / 2));
+    auto rot = [&](double phi, double theta, double omega, cplx *m) {
+        const double cc = std::cos(theta / 2), ss = std::sin(theta / 2);
+        m[0] = std::exp(-I_ * ((phi + omega) / 2)) * cc;
+        m[1] = -std::exp(I_ * ((phi - omega) / 2)) * ss;
+        m[2] = std::exp(-I_ * ((phi - omega) / 2)) * ss;
+        m[3] = std::exp(I_ * ((phi + omega) / 2)) * cc;
+    };
+
+    if (name == "Identity") {
+        for (auto w : wires) (void)bit_of(w);
+        return;
+    }
+    else if (name == "PauliX") { need(1, 0); one(0, 1, 1, 0); }
+    else if (name == "PauliY") { need(1, 0); one(0, -I_, I_, 0); }
+    else if (name == "PauliZ") { need(1, 0); phase(-1.0, W(0)); }
+    else if (name == "Hadamard") { need(1, 0); one(isq2, isq2, isq2, -isq2); }
+    else if (name == "S") { need(1, 0); phase(I_, W(0)); }
+    else if (name == "T") { need(1, 0); phase(std::exp(I_ * (M_PI / 4)), W(0)); }
+    else if (name == "PhaseShift") { need(1, 1); phase(std::exp(I_ * th), W(0)); }
+    else if (name == "RX") { need(1, 1); one(c, -I_ * s, -I_ * s, c); }
+    else if (name == "RY") { need(1, 1); one(c, -s, s, c); }
+    else if (name == "RZ") { need(1, 1); parity(W(0), em, ep); }
+    else if (name == "Rot") {
+        need(1, 3);
+        cplx m[4];
+        rot(p[0], p[1], p[2], m);
+        one(m[0], m[1], m[2], m[3]);
+    }
+    else if (name == "CNOT") { need(2, 0); one(0, 1, 1, 0, 1, W(0)); }
+    else if (name == "CY") { need(2, 0); one(0, -I_, I_, 0, 1, W(0)); }
+    else if (name == "CZ") { need(2, 0); phase(-1.0, W(0) | W(1)); }
+    else if (name == "SWAP") { need(2, 0); pair(W(0) | W(1), W(1), W(0), 0, 1, 1, 0); }
+    else if (name == "ISWAP") { need(2, 0); pair(W(0) | W(1), W(1), W(0), 0, I_, I_, 0); }
+    else if (name == "PSWAP") {
+        need(2, 1);
+        const cplx e = std::exp(I_ * th);
+        pair(W(0) | W(1), W(1), W(0), 0, e, e, 0);
+    }
+    else if (name == "IsingXX") {
+        need(2, 1);
+        pair(W(0) | W(1), 0, W(0) | W(1), c, -I_ * s, -I_ * s, c);
+        pair(W(0) | W(1), W(1), W(0), c, -I_ * s, -I_ * s, c);
+    }
+    else if (name == "IsingYY") {
+        need(2, 1);
+        pair(W(0) | W(1), 0, W(0) | W(1), c, I_ * s, I_ * s, c);
+        pair(W(0) | W(1), W(1), W(0), c, -I_ * s, -I_ * s, c);
+    }
+    else if (name == "IsingXY") { need(2, 1); pair(W(0) | W(1), W(1), W(0), c, I_ * s, I_ * s, c); }
+    else if (name == "IsingZZ") { need(2, 1); parity(W(0) | W(1), em, ep); }
+    else if (name == "ControlledPhaseShift") { need(2, 1); phase(std::exp(I_ * th), W(0) | W(1)); }
+    else if (name == "CRX") { need(2, 1); one(c, -I_ * s, -I_ * s, c, 1, W(0)); }
+    else if (name == "CRY") { need(2, 1); one(c, -s, s, c, 1, W(0)); }
+    else if (name == "CRZ") { need(2, 1); parity(W(1), em, ep, W(0)); }
+    else if (name == "CRot") {
+        need(2, 3);
+        cplx m[4];
+        rot(p[0], p[1], p[2], m);
+        one(m[0], m[1], m[2], m[3], 1, W(0));
+    }
+    else if (name == "CSWAP") {
+        need(3, 0);
+        pair(W(1) | W(2), W(2), W(1), 0, 1, 1, 0, W(0));
+    }
+    else if (name == "Toffoli") { need(3, 0); one(0, 1, 1, 0, 2, W(0) | W(1)); }
+    else if (name == "SingleExcitation") {
+        need(2, 1);
+        pair(W(0) | W(1), W(1), W(0), c, -s, s, c);
+    }
+    else if (name == "DoubleExcitation") {
+        need(4, 1);
+        pair(W(0) | W(1) | W(2) | W(3), W(2) | W(3), W(0) | W(1), c, -s, s, c);
+    }
+    else if (name == "MultiRZ") {
+        B200_FAIL_IF(p.size() != 1, "Invalid number of parameters for MultiRZ");
+        B200_FAIL_IF(wires.empty(), "MultiRZ needs at least one wire");
+        uint64_t zm = 0;
+        for (size_t i = 0; i < wires.size(); i++) zm |= W(i);
+        parity(zm, em, ep);
+    }
+    else if (name == "GlobalPhase") {
+        B200_FAIL_IF(p.size() != 1, "Invalid number of parameters for GlobalPhase");
+        phase(std::exp(-I_ * th), 0);
+    }
+    else if (name == "PCPhase") {
+        // params = {theta, dim} (reference: runtime/lib/capi/RuntimeCAPI.cpp:470-485): the first
+        // `dim` basis states of the wires get e^{i theta}, the rest e^{-i theta}.  Written as a
+        // global phase e^{-i theta} times e^{2 i theta} on {val < dim}, the latter split into one
+        // bit-pattern predicate per set bit of dim.
+        B200_FAIL_IF(p.size() != 2, "Invalid number of parameters for PCPhase");
+        const size_t k = wires.size();
+        B200_FAIL_IF(k == 0 || k > 62, "Invalid number of wires for PCPhase");
+        B200_FAIL_IF(p[1] < 0, "Invalid dimension for PCPhase");
+        const uint64_t full = 1ull << k;
+        const uint64_t dim = p[1] >= (double)full ? full : (uint64_t)p[1];
+        phase(std::exp(-I_ * th), 0);
+        const cplx e2 = std::exp(I_ * (2 * th));
+        if (dim >= full) phase(e2, 0);
+        else
+            for (size_t j = 0; j < k; j++) { // j = position from the most significant wire
+                const int sh = (int)(k - 1 - j);
+                if (!((dim >> sh) & 1)) continue;
+                // values with the bits above j equal to dim's and bit j = 0
+                GateOp g;
+                g.kind = GateOp::PHASE;
+                g.m[0] = e2;
+                g.cmask = cmask;
+                g.cval = cval;
+                for (size_t q = 0; q <= j; q++) {
+                    g.cmask |= W(q);
+                    if (q < j && ((dim >> (k - 1 - q)) & 1)) g.cval |= W(q);
+                }
+                out.push_back(std::move(g));
+            }
+    }
+    else if (name == "PauliRot") {
+        B200_FAIL_IF(p.size() != 1, "Invalid number of parameters for PauliRot");
+        B200_FAIL_IF(pauli_word.size() != wires.size(), "Pauli word / wires length mismatch");
+        GateOp g;
+        g.kind = GateOp::PAULIROT;
+        for (size_t i = 0; i < wires.size(); i++) {
+            switch (pauli_word[i]) {
+            case 'I': break;
+            case 'X': g.xmask |= W(i); break;
+            case 'Y': g.xmask |= W(i); g.zmask |= W(i); g.ny++; break;
+            case 'Z': g.zmask |= W(i); break;
+            default: B200_FAIL("Invalid Pauli word");
+            }
+        }
+        if (g.xmask == 0) {
+            if (g.zmask == 0) phase(em, 0);
+            else parity(g.zmask, em, ep);
+        }
+        else {
+            g.m[0] = cplx(c, s);
+            g.cmask = cmask;
+            g.cval = cval;
+            out.push_back(std::move(g));
+        }
+    }
+    else {
+        B200_FAIL("Unsupported gate: " + name);
+    }
+    if (inverse) {
+        for (size_t i = first; i < out.size(); i++) {
+            GateOp &g = out[i];
+            switch (g.kind) {
+            case GateOp::PAIR: dagger2(g.m); break;
+            case GateOp::PHASE: g.m[0] = std::conj(g.m[0]); break;
+            case GateOp::PARITY: g.m[0] = std::conj(g.m[0]); g.m[1] = std::conj(g.m[1]); break;
+            case GateOp::PAULIROT: g.m[0] = cplx(g.m[0].real(), -g.m[0].imag()); break;
+            default: break;
+            }
+        }
+        std::reverse(out.begin() + first, out.end()); // all emitted pieces commute; keep it exact
+    }
+}
+
+void Simulator::canonicalize_matrix(std::vector<GateOp> &out, const CVec &matrix,
+                                    const std::vector<int64_t> &wires, bool inverse,
+                                    const std::vector<int64_t> &cw, const std::vector<bool> &cv) const
+{
+    B200_FAIL_IF(cw.size() != cv.size(), "Control wires/values size mismatch");
+    B200_FAIL_IF(wires.empty(), "Invalid number of wires for MatrixOperation");
+    check_wires(wires, cw);
+    const size_t k = wires.size();
+    B200_FAIL_IF(k > 10, "MatrixOperation on more than 10 wires is not supported by this device");
+    const size_t dim = size_t(1) << k;
+    B200_FAIL_IF(matrix.size() != dim * dim, "Invalid given matrix size");
+    uint64_t cmask = 0, cval = 0;
+    for (size_t i = 0; i < cw.size(); i++) {
+        cmask |= bit_of(cw[i]);
+        if (cv[i]) cval |= bit_of(cw[i]);
+    }
+    GateOp g;
+    g.cmask = cmask;
+    g.cval = cval;
+    if (k == 1) {
+        g.kind = GateOp::PAIR;
+        g.xmask = bit_of(wires[0]);
+        g.a = 0;
+        g.b = g.xmask;
+        for (int i = 0; i < 4; i++) g.m[i] = matrix[i];
+        if (inverse) dagger2(g.m);
+    }
+    else {
+        g.kind = GateOp::DENSE;
+        auto m = std::make_shared<CVec>(dim * dim);
+        for (size_t r = 0; r < dim; r++)
+            for (size_t cc = 0; cc < dim; cc++)
+                (*m)[r * dim + cc] = inverse ? std::conj(matrix[cc * dim + r]) : matrix[r * dim + cc];
+        g.matrix = std::move(m);
+        for (auto w : wires) {
+            g.targets.push_back(lbit(w));
+            g.xmask |= bit_of(w);
+        }
+    }
+    out.push_back(std::move(g));
+}
+
+// ---- queue ------------------------------------------------------------------------------------------
+static void matmul2(const cplx *a, const cplx *b, cplx *o)
+{ // o = a * b
+    const cplx r0 = a[0] * b[0] + a[1] * b[2], r1 = a[0] * b[1] + a[1] * b[3];
+    const cplx r2 = a[2] * b[0] + a[3] * b[2], r3 = a[2] * b[1] + a[3] * b[3];
+    o[0] = r0; o[1] = r1; o[2] = r2; o[3] = r3;
+}
+
+void Simulator::enqueue(std::vector<GateOp> &&ops)
+{
+    for (auto &g : ops) {
+        if (opt_.fuse && g.kind == GateOp::PAIR && g.cmask == 0 && g.a == 0 && g.b == g.xmask &&
+            !queue_.empty()) {
+            GateOp &l = queue_.back();
+            if (l.kind == GateOp::PAIR && l.cmask == 0 && l.xmask == g.xmask && l.a == 0 &&
+                l.b == l.xmask) {
+                matmul2(g.m, l.m, l.m); // new gate acts after the queued one
+                continue;
+            }
+        }
+        queue_.push_back(std::move(g));
+    }
+    if (queue_.size() >= 8192) flush();
+}
+
+void Simulator::named_op(const std::string &name, const std::vector<double> &params,
+                         const std::vector<int64_t> &wires, bool inverse,
+                         const std::vector<int64_t> &cw, const std::vector<bool> &cv,
+                         const std::string &pauli_word)
+{
+    B200_FAIL_IF(!psi_, "No qubits allocated");
+    std::vector<GateOp> ops;
+    canonicalize(ops, name, params, wires, inverse, cw, cv, pauli_word);
+    if (name != "Identity") {
+        stats_.gates_enqueued++;
+        if (name != "GlobalPhase" || !cw.empty())
+            stats_.algorithmic_bytes += 32.0 * std::ldexp(1.0, (int)(n_ - (int64_t)cw.size()));
+    }
+    enqueue(std::move(ops));
+    if (recording_) // reference tape model: runtime/lib/backend/common/CacheManager.hpp:89-103
+        tape_.push_back({name, params, wires, inverse, {}, cw, cv, pauli_word});
+}
+
+void Simulator::matrix_op(const CVec &matrix, const std::vector<int64_t> &wires, bool inverse,
+                          const std::vector<int64_t> &cw, const std::vector<bool> &cv)
+{
+    B200_FAIL_IF(!psi_, "No qubits allocated");
+    std::vector<GateOp> ops;
+    canonicalize_matrix(ops, matrix, wires, inverse, cw, cv);
+    stats_.gates_enqueued++;
+    stats_.algorithmic_bytes += 32.0 * std::ldexp(1.0, (int)(n_ - (int64_t)cw.size()));
+    enqueue(std::move(ops));
+    if (recording_) tape_.push_back({"QubitUnitary", {}, wires, inverse, matrix, cw, cv, ""});
+}
+
+void Simulator::flush()
+{
+    if (queue_.empty()) return;
+    CUDA_CHECK(cudaSetDevice(cuda_device_));
+    std::vector<GateOp> ops;
+    ops.swap(queue_);
+    if (timing_) CUDA_CHECK(cudaEventRecord((cudaEvent_t)ev0_, (cudaStream_t)stream_));
+    run_ops(psi_->d(), ops);
+    if (timing_) {
+        CUDA_CHECK(cudaEventRecord((cudaEvent_t)ev1_, (cudaStream_t)stream_));
+        CUDA_CHECK(cudaEventSynchronize((cudaEvent_t)ev1_));
+        float ms = 0;
+        CUDA_CHECK(cudaEventElapsedTime(&ms, (cudaEvent_t)ev0_, (cudaEvent_t)ev1_));
+        stats_.gate_device_ms += ms;
+    }
+}
+
+void Simulator::synchronize()
+{
+    flush();
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+}
+
+// ---- planner: queue -> fused tile passes --------------------------------------------------------------
+// A pass stages tiles made of the low `c` index bits plus the high bits its ops need as
+// non-diagonal targets.  Ops are taken greedily in program order; an op that does not fit is
+// deferred and blocks later ops that do not commute with it (two ops commute when, on every
+// shared bit, both act diagonally — controls count as diagonal).
+static int fit_rows(uint64_t req, int t)
+{
+    if (__builtin_popcountll(req) > t) return -1;
+    int c = t;
+    while (c > 0 && __builtin_popcountll(req >> c) > t - c) c--;
+    return c;
+}
+
+void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
+{
+    const int t = (int)std::min<int64_t>(opt_.tile_bits, n_);
+    const int cmin = std::min(opt_.min_row_bits, t);
+    const size_t LOOKAHEAD = 2048;
+    std::vector<char> done(ops.size(), 0);
+    size_t first = 0, remaining = ops.size();
+    std::vector<const GateOp *> pass;
+    while (remaining) {
+        uint64_t req = 0, blockedX = 0, blockedZ = 0;
+        int c_cur = t;
+        pass.clear();
+        for (size_t i = first; i < ops.size() && pass.size() < B200K_MAX_OPS && i - first < LOOKAHEAD;
+             i++) {
+            if (done[i]) continue;
+            const GateOp &op = ops[i];
+            const uint64_t xs = op.xmask, zs = op.zsupport();
+            const bool commutes = !(xs & (blockedX | blockedZ)) && !(zs & blockedX);
+            if (commutes) {
+                const uint64_t nreq = req | xs;
+                const int c = fit_rows(nreq, t);
+                B200_FAIL_IF(c < 0 && pass.empty(),
+                             "Operation acts non-diagonally on more qubits than one tile holds");
+                if (c >= 0 && (c >= cmin || pass.empty())) {
+                    req = nreq;
+                    c_cur = c;
+                    pass.push_back(&op);
+                    done[i] = 1;
+                    remaining--;
+                    if (!opt_.fuse) break;
+                    continue;
+                }
+            }
+            if (!opt_.fuse) break;
+            blockedX |= xs;
+            blockedZ |= zs;
+        }
+        while (first < ops.size() && done[first]) first++;
+        // high tile bits: required positions >= c, padded with the lowest free positions
+        std::vector<int> high;
+        for (int p = c_cur; p < 64; p++)
+            if ((req >> p) & 1) high.push_back(p);
+        for (int p = c_cur; (int)high.size() < t - c_cur; p++)
+            if (!((req >> p) & 1)) high.push_back(p);
+        std::sort(high.begin(), high.end());
+        launch_pass(vec, pass, high, c_cur);
+    }
+}
+
+const double *Simulator::upload_matrix(const CVec &m)
+{
+    const size_t bytes = m.size() * sizeof(cplx);
+    const size_t cap = size_t(64) << 20;
+    if (!matrix_arena_) matrix_arena_ = std::make_unique<DeviceBuffer>(cap);
+    const size_t aligned = (bytes + 255) & ~size_t(255);
+    B200_FAIL_IF(aligned > cap, "matrix too large for the device matrix arena");
+    if (arena_used_ + aligned > cap) {
+        CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+        arena_used_ = 0;
+    }
+    char *dst = static_cast<char *>(matrix_arena_->p()) + arena_used_;
+    CUDA_CHECK(cudaMemcpyAsync(dst, m.data(), bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+    arena_used_ += aligned;
+    return reinterpret_cast<const double *>(dst);
+}
+
+void Simulator::launch_pass(double *vec, const std::vector<const GateOp *> &ops,
+                            const std::vector<int> &high, int c)
+{
+    B200kTileProgram P;
+    std::memset(&P, 0, sizeof(P));
+    const int t = c + (int)high.size();
+    P.t = t;
+    P.c = c;
+    P.nhigh = (int)high.size();
+    B200_FAIL_IF(P.nhigh > B200K_MAX_HIGH, "too many scattered tile bits");
+    for (size_t h = 0; h < high.size(); h++) P.high_pos[h] = (uint8_t)high[h];
+    P.rank_base = 0;
+    int loc[64];
+    for (int p = 0; p < 64; p++) loc[p] = p < c ? p : -1;
+    for (size_t h = 0; h < high.size(); h++) loc[high[h]] = c + (int)h;
+    auto split = [&](uint64_t mask, uint32_t &inside, uint64_t &outside) {
+        inside = 0;
+        outside = 0;
+        while (mask) {
+            const int p = __builtin_ctzll(mask);
+            mask &= mask - 1;
+            if (loc[p] >= 0) inside |= 1u << loc[p];
+            else outside |= 1ull << p;
+        }
+    };
+    auto inside_only = [&](uint64_t mask) -> uint32_t {
+        uint32_t in;
+        uint64_t outm;
+        split(mask, in, outm);
+        B200_FAIL_IF(outm != 0, "internal: target bit outside the tile");
+        return in;
+    };
+    P.n_ops = (int)ops.size();
+    for (size_t i = 0; i < ops.size(); i++) {
+        const GateOp &g = *ops[i];
+        B200kTileOp &o = P.ops[i];
+        split(g.cmask, o.cmask, o.cmask_o);
+        split(g.cval, o.cval, o.cval_o);
+        switch (g.kind) {
+        case GateOp::PAIR:
+            o.kind = B200K_OP_PAIR;
+            o.tmask = inside_only(g.xmask);
+            o.a = inside_only(g.a);
+            o.b = inside_only(g.b);
+            for (int q = 0; q < 4; q++) {
+                o.u.m[2 * q] = g.m[q].real();
+                o.u.m[2 * q + 1] = g.m[q].imag();
+            }
+            break;
+        case GateOp::PHASE:
+            o.kind = B200K_OP_PHASE;
+            o.u.m[0] = g.m[0].real();
+            o.u.m[1] = g.m[0].imag();
+            break;
+        case GateOp::PARITY:
+            o.kind = B200K_OP_PARITY;
+            split(g.zmask, o.a, o.zmask_o);
+            o.u.m[0] = g.m[0].real();
+            o.u.m[1] = g.m[0].imag();
+            o.u.m[2] = g.m[1].real();
+            o.u.m[3] = g.m[1].imag();
+            break;
+        case GateOp::PAULIROT:
+            o.kind = B200K_OP_PAULIROT;
+            o.tmask = inside_only(g.xmask);
+            split(g.zmask, o.a, o.zmask_o);
+            o.ny = (uint32_t)(g.ny & 3);
+            o.u.m[0] = g.m[0].real();
+            o.u.m[1] = g.m[0].imag();
+            break;
+        case GateOp::DENSE:
+            o.kind = B200K_OP_DENSE;
+            o.k = (uint32_t)g.targets.size();
+            o.tmask = inside_only(g.xmask);
+            for (size_t j = 0; j < g.targets.size(); j++) o.u.d.tb[j] = (uint8_t)loc[g.targets[j]];
+            o.u.d.mat = upload_matrix(*g.matrix);
+            break;
+        }
+    }
+    CUDA_CHECK(b200k_tile_program(vec, (int)n_, &P, stream_));
+    stats_.tile_passes++;
+    stats_.kernel_ops += (int64_t)ops.size();
+}
+
+// ---- state preparation ----------------------------------------------------------------------------
+void Simulator::set_basis_state(const std::vector<int8_t> &bits, const std::vector<int64_t> &wires)
+{
+    B200_FAIL_IF(!psi_, "No qubits allocated");
+    B200_FAIL_IF(bits.size() != wires.size(),
+                 "BasisState parameter and wires must be of equal length.");
+    check_wires(wires, {});
+    queue_.clear(); // the whole register is overwritten
+    uint64_t idx = 0;
+    for (size_t j = 0; j < wires.size(); j++) {
+        B200_FAIL_IF(bits[j] != 0 && bits[j] != 1, "BasisState parameter must consist of 0 or 1 integers.");
+        if (bits[j]) idx |= bit_of(wires[j]);
+    }
+    CUDA_CHECK(b200k_set_basis(psi_->d(), (int)n_, (int64_t)idx, stream_));
+    note_launch();
+}
+
+void Simulator::set_state(const CVec &st, const std::vector<int64_t> &wires)
+{
+    B200_FAIL_IF(!psi_, "No qubits allocated");
+    check_wires(wires, {});
+    const size_t k = wires.size();
+    B200_FAIL_IF(st.size() != (size_t(1) << k), "Invalid state size: must be 2^len(wires)");
+    queue_.clear();
+    bool natural = (int64_t)k == n_;
+    for (size_t j = 0; j < k && natural; j++) natural = wires[j] == (int64_t)j;
+    if (natural) {
+        CUDA_CHECK(cudaMemcpyAsync(psi_->p(), st.data(), st.size() * sizeof(cplx),
+                                   cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+        CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+        return;
+    }
+    ensure_buffer(misc_, st.size() * sizeof(cplx));
+    CUDA_CHECK(cudaMemcpyAsync(misc_->p(), st.data(), st.size() * sizeof(cplx), cudaMemcpyHostToDevice,
+                               (cudaStream_t)stream_));
+    std::vector<uint8_t> tb(k);
+    for (size_t j = 0; j < k; j++) tb[j] = (uint8_t)lbit(wires[j]);
+    CUDA_CHECK(b200k_scatter_state(psi_->d(), misc_->d(), (int)n_, tb.data(), (int)k, stream_));
+    note_launch();
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+}
+
+// ---- observables --------------------------------------------------------------------------------------
+// Keys are indices into a per-activation table, monotonically increasing (pattern:
+// runtime/lib/backend/openqasm/OpenQasmObsManager.hpp:96-189).
+int64_t Simulator::obs_named(int id, const CVec &matrix, const std::vector<int64_t> &wires)
+{
+    B200_FAIL_IF(id < 0 || id > 5, "Invalid observable id");
+    for (auto w : wires) (void)bit_of(w);
+    ObsNode o;
+    if (id == 5) {
+        const size_t dim = size_t(1) << wires.size();
+        B200_FAIL_IF(wires.empty() || matrix.size() != dim * dim, "Invalid Hermitian matrix size");
+        check_wires(wires, {});
+        o.kind = ObsKind::Hermitian;
+        o.matrix = matrix;
+    }
+    else {
+        B200_FAIL_IF(wires.empty(), "Invalid number of wires for a named observable");
+        // the frontend may pass Identity on many wires (frontend/catalyst/jax_tracer.py:1002-1013)
+        B200_FAIL_IF(id != 0 && wires.size() != 1, "Named observables act on exactly one wire");
+        o.kind = ObsKind::Named;
+    }
+    o.named_id = id;
+    o.wires = wires;
+    obs_.push_back(std::move(o));
+    return (int64_t)obs_.size() - 1;
+}
+int64_t Simulator::obs_tensor(const std::vector<int64_t> &keys)
+{
+    for (auto k : keys) B200_FAIL_IF(k < 0 || (size_t)k >= obs_.size(), "Invalid observable key");
+    ObsNode o;
+    o.kind = ObsKind::Tensor;
+    o.children = keys;
+    obs_.push_back(std::move(o));
+    return (int64_t)obs_.size() - 1;
+}
+int64_t Simulator::obs_hamiltonian(const std::vector<double> &coeffs, const std::vector<int64_t> &keys)
+{
+    B200_FAIL_IF(coeffs.size() != keys.size(), "Invalid size for the list of coefficients and observables");
+    for (auto k : keys) B200_FAIL_IF(k < 0 || (size_t)k >= obs_.size(), "Invalid observable key");
+    ObsNode o;
+    o.kind = ObsKind::Hamiltonian;
+    o.coeffs = coeffs;
+    o.children = keys;
+    obs_.push_back(std::move(o));
+    return (int64_t)obs_.size() - 1;
+}
+
+void Simulator::flatten(int64_t key, std::vector<ObsTerm> &out) const
+{
+    B200_FAIL_IF(key < 0 || (size_t)key >= obs_.size(), "Invalid key for cached observables");
+    const ObsNode &o = obs_[key];
+    switch (o.kind) {
+    case ObsKind::Named:
+    case ObsKind::Hermitian: {
+        ObsTerm t;
+        t.factors.push_back({o.named_id, o.wires, o.kind == ObsKind::Hermitian ? &o.matrix : nullptr});
+        out.push_back(std::move(t));
+        return;
+    }
+    case ObsKind::Tensor: {
+        std::vector<ObsTerm> acc(1);
+        for (auto c : o.children) {
+            std::vector<ObsTerm> sub;
+            flatten(c, sub);
+            std::vector<ObsTerm> next;
+            next.reserve(acc.size() * sub.size());
+            for (auto &a : acc)
+                for (auto &s : sub) {
+                    ObsTerm t = a;
+                    t.coef *= s.coef;
+                    t.factors.insert(t.factors.end(), s.factors.begin(), s.factors.end());
+                    next.push_back(std::move(t));
+                }
+            acc.swap(next);
+            B200_FAIL_IF(acc.size() > (size_t(1) << 20), "Observable expands to too many terms");
+        }
+        for (auto &t : acc) out.push_back(std::move(t));
+        return;
+    }
+    case ObsKind::Hamiltonian:
+        for (size_t i = 0; i < o.children.size(); i++) {
+            std::vector<ObsTerm> sub;
+            flatten(o.children[i], sub);
+            for (auto &t : sub) {
+                t.coef *= o.coeffs[i];
+                out.push_back(std::move(t));
+            }
+        }
+        return;
+    }
+}
+
+bool Simulator::term_to_paulis(const ObsTerm &t, std::vector<PauliTerm> &out) const
+{
+    uint64_t used = 0;
+    int nh = 0;
+    for (auto &f : t.factors) {
+        if (f.named_id == 5) return false;
+        if (f.named_id == 0) continue;
+        const uint64_t b = bit_of(f.wires[0]);
+        if (used & b) return false; // repeated wire: take the generic (sequential) path
+        used |= b;
+        if (f.named_id == 4) nh++;
+    }
+    if (nh > 6) return false;
+    std::vector<PauliTerm> acc(1);
+    acc[0].coef = t.coef;
+    for (auto &f : t.factors) {
+        if (f.named_id == 0) continue;
+        const uint64_t b = bit_of(f.wires[0]);
+        if (f.named_id == 4) { // Hadamard = (X + Z) / sqrt(2)
+            std::vector<PauliTerm> next;
+            for (auto &a : acc) {
+                PauliTerm x = a, z = a;
+                x.coef *= 1.0 / std::sqrt(2.0);
+                z.coef *= 1.0 / std::sqrt(2.0);
+                x.xmask |= b;
+                z.zmask |= b;
+                next.push_back(x);
+                next.push_back(z);
+            }
+            acc.swap(next);
+            continue;
+        }
+        for (auto &a : acc) {
+            if (f.named_id == 1) a.xmask |= b;
+            else if (f.named_id == 2) { a.xmask |= b; a.zmask |= b; a.ny++; }
+            else a.zmask |= b;
+        }
+    }
+    for (auto &a : acc) out.push_back(a);
+    return true;
+}
+
+void Simulator::factor_ops(const ObsFactor &f, std::vector<GateOp> &ops) const
+{
+    static const char *nm[] = {"Identity", "PauliX", "PauliY", "PauliZ", "Hadamard"};
+    if (f.named_id == 5) canonicalize_matrix(ops, *f.matrix, f.wires, false, {}, {});
+    else if (f.named_id != 0) canonicalize(ops, nm[f.named_id], {}, f.wires, false, {}, {}, "");
+}
+
+double *Simulator::result_slot(int slot) { return results_->d() + 2 * (size_t)slot; }
+
+void Simulator::read_results(int nslots, std::vector<double> &host)
+{
+    host.resize(2 * (size_t)nslots);
+    if (nslots == 0) return;
+    CUDA_CHECK(cudaMemcpyAsync(host.data(), results_->p(), host.size() * sizeof(double),
+                               cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+}
+
+cplx Simulator::inner(const double *a, const double *b)
+{
+    CUDA_CHECK(b200k_bilinear_pauli(a, b, (int)n_, 0, 0, 0, 0, 0, 0, scratch_->d(), result_slot(0), stream_));
+    note_launch();
+    std::vector<double> h;
+    read_results(1, h);
+    return {h[0], h[1]};
+}
+
+void Simulator::apply_observable(int64_t key, const double *vin, double *vout)
+{
+    std::vector<ObsTerm> terms;
+    flatten(key, terms);
+    bool first = true;
+    const size_t bytes = sizeof(cplx) << n_;
+    for (auto &t : terms) {
+        std::vector<PauliTerm> pts;
+        if (term_to_paulis(t, pts)) {
+            for (auto &p : pts) {
+                CUDA_CHECK(b200k_pauli_apply(vout, vin, (int)n_, 0, p.xmask, p.zmask, p.ny,
+                                             p.coef.real(), p.coef.imag(), first ? 0 : 1, stream_));
+                note_launch();
+                first = false;
+            }
+            continue;
+        }
+        ensure_buffer(tmp_, bytes);
+        CUDA_CHECK(cudaMemcpyAsync(tmp_->p(), vin, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
+        std::vector<GateOp> ops;
+        for (auto &f : t.factors) factor_ops(f, ops);
+        if (!ops.empty()) run_ops(tmp_->d(), ops);
+        if (first) {
+            CUDA_CHECK(b200k_pauli_apply(vout, tmp_->d(), (int)n_, 0, 0, 0, 0, t.coef, 0.0, 0, stream_));
+        }
+        else {
+            CUDA_CHECK(b200k_axpy(vout, tmp_->d(), t.coef, (int)n_, stream_));
+        }
+        note_launch();
+        first = false;
+    }
+    if (first) CUDA_CHECK(cudaMemsetAsync(vout, 0, bytes, (cudaStream_t)stream_));
+}
+
+double Simulator::expval(int64_t key)
+{
+    B200_FAIL_IF(!psi_, "No qubits allocated");
+    B200_FAIL_IF(key < 0 || (size_t)key >= obs_.size(), "Invalid key for cached observables");
+    if (recording_) tape_obs_.push_back({key, 1}); // CacheManager.hpp:111-114
+    flush();
+    std::vector<ObsTerm> terms;
+    flatten(key, terms);
+    std::vector<PauliTerm> diag, offd;
+    std::vector<const ObsTerm *> generic;
+    for (auto &t : terms) {
+        std::vector<PauliTerm> pts;
+        if (term_to_paulis(t, pts)) {
+            for (auto &p : pts) (p.xmask ? offd : diag).push_back(p);
+        }
+        else generic.push_back(&t);
+    }
+    const int BATCH = 1024;
+    const int ndiag_slots = (int)((diag.size() + BATCH - 1) / BATCH);
+    const int nslots = ndiag_slots + (int)offd.size() + (int)generic.size();
+    ensure_buffer(results_, std::max<size_t>(4096, 2 * (size_t)nslots) * sizeof(double));
+    int slot = 0;
+    // all-diagonal words: one read pass per batch
+    if (!diag.empty()) {
+        const size_t nt = diag.size();
+        ensure_buffer(misc_, nt * 16);
+        std::vector<uint64_t> zm(nt);
+        std::vector<double> cf(nt);
+        for (size_t i = 0; i < nt; i++) {
+            zm[i] = diag[i].zmask;
+            cf[i] = diag[i].coef.real();
+        }
+        uint64_t *dz = static_cast<uint64_t *>(misc_->p());
+        double *dc = reinterpret_cast<double *>(dz + nt);
+        CUDA_CHECK(cudaMemcpyAsync(dz, zm.data(), nt * 8, cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+        CUDA_CHECK(cudaMemcpyAsync(dc, cf.data(), nt * 8, cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+        for (size_t o = 0; o < nt; o += BATCH) {
+            const int cnt = (int)std::min<size_t>(BATCH, nt - o);
+            CUDA_CHECK(b200k_expval_diag_batch(psi_->d(), (int)n_, 0, dz + o, dc + o, cnt, scratch_->d(),
+                                               result_slot(slot++), stream_));
+            note_launch();
+        }
+        CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_)); // zm/cf are stack-owned
+    }
+    for (auto &p : offd) {
+        CUDA_CHECK(b200k_bilinear_pauli(psi_->d(), psi_->d(), (int)n_, 0, p.xmask, p.zmask, p.ny, 0, 0,
+                                        scratch_->d(), result_slot(slot++), stream_));
+        note_launch();
+    }
+    const size_t bytes = sizeof(cplx) << n_;
+    for (auto *t : generic) {
+        ensure_buffer(tmp_, bytes);
+        CUDA_CHECK(cudaMemcpyAsync(tmp_->p(), psi_->p(), bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
+        std::vector<GateOp> ops;
+        for (auto &f : t->factors) factor_ops(f, ops);
+        if (!ops.empty()) run_ops(tmp_->d(), ops);
+        CUDA_CHECK(b200k_bilinear_pauli(psi_->d(), tmp_->d(), (int)n_, 0, 0, 0, 0, 0, 0, scratch_->d(),
+                                        result_slot(slot++), stream_));
+        note_launch();
+    }
+    std::vector<double> h;
+    read_results(nslots, h);
+    double e = 0.0;
+    slot = 0;
+    for (int i = 0; i < ndiag_slots; i++) e += h[2 * slot++];
+    for (auto &p : offd) e += p.coef.real() * h[2 * slot++];
+    for (auto *t : generic) e += t->coef * h[2 * slot++];
+    return e;
+}
+
+double Simulator::var(int64_t key)
+{
+    B200_FAIL_IF(!psi_, "No qubits allocated");
+    B200_FAIL_IF(key < 0 || (size_t)key >= obs_.size(), "Invalid key for cached observables");
+    if (recording_) tape_obs_.push_back({key, 2});
+    flush();
+    const size_t bytes = sizeof(cplx) << n_;
+    ensure_buffer(acc_, bytes);
+    apply_observable(key, psi_->d(), acc_->d());
+    CUDA_CHECK(b200k_bilinear_pauli(psi_->d(), acc_->d(), (int)n_, 0, 0, 0, 0, 0, 0, scratch_->d(),
+                                    result_slot(0), stream_));
+    CUDA_CHECK(b200k_bilinear_pauli(acc_->d(), acc_->d(), (int)n_, 0, 0, 0, 0, 0, 0, scratch_->d(),
+                                    result_slot(1), stream_));
+    note_launch();
+    note_launch();
+    std::vector<double> h;
+    read_results(2, h);
+    return h[2] - h[0] * h[0];
+}
+
+// ---- State / Probs ----------------------------------------------------------------------------------
+static void d2h_strided(void *stream, const void *dsrc, size_t elem_bytes, size_t count, void *hdst,
+                        int64_t stride)
+{
+    cudaStream_t st = (cudaStream_t)stream;
+    if (stride == 1) {
+        CUDA_CHECK(cudaMemcpyAsync(hdst, dsrc, elem_bytes * count, cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        return;
+    }
+    // honour DataView strides (reference: runtime/include/DataView.hpp:124-134)
+    const size_t chunk = size_t(1) << 20;
+    std::vector<char> stage(std::min(chunk, count) * elem_bytes);
+    for (size_t o = 0; o < count; o += chunk) {
+        const size_t cnt = std::min(chunk, count - o);
+        CUDA_CHECK(cudaMemcpyAsync(stage.data(), static_cast<const char *>(dsrc) + o * elem_bytes,
+                                   cnt * elem_bytes, cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        for (size_t i = 0; i < cnt; i++)
+            std::memcpy(static_cast<char *>(hdst) + (int64_t)(o + i) * stride * (int64_t)elem_bytes,
+                        stage.data() + i * elem_bytes, elem_bytes);
+    }
+}
+
+void Simulator::state(double *out_ri, int64_t stride)
+{
+    B200_FAIL_IF(!psi_, "No qubits allocated");
+    flush();
+    d2h_strided(stream_, psi_->p(), sizeof(cplx), size_t(1) << n_, out_ri, stride);
+}
+
+void Simulator::probs(const std::vector<int64_t> &wires_in, double *out, int64_t stride)
+{
+    B200_FAIL_IF(!psi_, "No qubits allocated");
+    flush();
+    check_wires(wires_in, {});
+    bool all = wires_in.empty();
+    if ((int64_t)wires_in.size() == n_) {
+        all = true;
+        for (size_t j = 0; j < wires_in.size(); j++) all = all && wires_in[j] == (int64_t)j;
+    }
+    const size_t k = wires_in.empty() ? (size_t)n_ : wires_in.size();
+    ensure_buffer(probs_buf_, sizeof(double) << k);
+    if (all) {
+        CUDA_CHECK(b200k_probs_all(psi_->d(), probs_buf_->d(), (int)n_, stream_));
+    }
+    else {
+        std::vector<uint8_t> tb(k);
+        for (size_t j = 0; j < k; j++) tb[j] = (uint8_t)lbit(wires_in[j]);
+        const size_t sp = (size_t)b200k_probs_splits((int)n_, (int)k);
+        ensure_buffer(misc_, (sizeof(double) << k) * sp);
+        CUDA_CHECK(b200k_probs_partial(psi_->d(), (int)n_, tb.data(), (int)k, misc_->d(),
+                                       probs_buf_->d(), stream_));
+    }
+    note_launch();
+    if (out) d2h_strided(stream_, probs_buf_->p(), sizeof(double), size_t(1) << k, out, stride);
+}
+
+// ---- Sample -------------------------------------------------------------------------------------------
+// Reference stream (verified against doc/releases/changelog-0.9.0.md:
+// 299-315): one 32-bit output of the runtime generator seeds a fresh mt19937 per call; each shot
+// takes two uniform_real_distribution<double> draws from it.
+std::vector<int64_t> Simulator::sample_indices(const std::vector<int64_t> &wires, int64_t shots)
+{
+    B200_FAIL_IF(shots < 0, "Invalid number of shots");
+    probs(wires, nullptr, 1); // leaves the distribution in probs_buf_ on the device
+    const size_t k = wires.empty() ? (size_t)n_ : wires.size();
+    const int64_t nbins = int64_t(1) << k;
+    std::mt19937 rng;
+    if (rng_fn_ || own_seeded_) rng = std::mt19937(rng_next());
+    else rng = std::mt19937(std::random_device{}());
+    std::vector<int64_t> idx((size_t)shots);
+    if (shots == 0) return idx;
+    std::vector<double> u(2 * (size_t)shots);
+    std::uniform_real_distribution<double> U(0.0, 1.0);
+    for (auto &x : u) x = U(rng);
+    const size_t scr = (size_t)b200k_sampler_scratch_doubles(nbins) * sizeof(double);
+    const size_t ubytes = u.size() * sizeof(double);
+    const size_t ibytes = idx.size() * sizeof(int64_t);
+    ensure_buffer(misc_, scr + ubytes + ibytes + 64);
+    char *base = static_cast<char *>(misc_->p());
+    double *dscr = reinterpret_cast<double *>(base);
+    double *du = reinterpret_cast<double *>(base + ((scr + 15) & ~size_t(15)));
+    int64_t *di = reinterpret_cast<int64_t *>(reinterpret_cast<char *>(du) + ubytes);
+    cudaStream_t st = (cudaStream_t)stream_;
+    CUDA_CHECK(cudaMemcpyAsync(du, u.data(), ubytes, cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(b200k_sampler_prepare(probs_buf_->d(), nbins, dscr, stream_));
+    CUDA_CHECK(b200k_sampler_draw(probs_buf_->d(), nbins, dscr, du, shots, di, stream_));
+    note_launch();
+    CUDA_CHECK(cudaMemcpyAsync(idx.data(), di, ibytes, cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    return idx;
+}
+
+// ---- Measure --------------------------------------------------------------------------------------------
+// Draw semantics: runtime/lib/backend/common/Utils.hpp:312-338 (float cast of the draw and one
+// extra discarded generator output are part of the stream; verified against
+// doc/releases/changelog-0.8.0.md:70-108).
+bool Simulator::measure(int64_t wire, int postselect)
+{
+    B200_FAIL_IF(!psi_, "No qubits allocated");
+    double p[2];
+    probs({wire}, p, 1);
+    bool res;
+    if (postselect != -1) {
+        B200_FAIL_IF(postselect < 0 || postselect > 1, "Invalid postselect value");
+        B200_FAIL_IF(p[postselect] == 0, "Probability of postselect value is 0");
+        res = postselect == 1;
+    }
+    else {
+        std::uniform_real_distribution<> dis(0., 1.);
+        float draw;
+        if (rng_fn_ || own_seeded_) {
+            BorrowedEngine eng{[this] { return rng_next(); }};
+            draw = (float)dis(eng);
+            (void)rng_next();
+        }
+        else {
+            std::random_device rd;
+            std::mt19937 g(rd());
+            draw = (float)dis(g);
+        }
+        res = draw > p[0];
+    }
+    const double scale = 1.0 / std::sqrt(p[res ? 1 : 0]);
+    CUDA_CHECK(b200k_collapse(psi_->d(), (int)n_, 0, lbit(wire), res ? 1 : 0, scale, stream_));
+    note_launch();
+    return res;
+}
+
+// ---- tape + adjoint Jacobian ------------------------------------------------------------------------
+void Simulator::start_tape()
+{
+    B200_FAIL_IF(recording_, "Cannot re-activate the cache manager");
+    recording_ = true;
+    tape_.clear();
+    tape_obs_.clear();
+}
+void Simulator::stop_tape()
+{
+    B200_FAIL_IF(!recording_, "Cannot stop an already stopped cache manager");
+    recording_ = false;
+}
+int64_t Simulator::tape_num_params() const
+{
+    size_t P = 0;
+    for (auto &op : tape_) P += op.params.size();
+    return (int64_t)P;
+}
+
+namespace {
+// U(theta) = exp(i * sigma * theta * G) with G = projector(controls) (x) generator.
+struct Generator {
+    double sigma = 0;
+    bool is_pair = false;
+    uint64_t xmask = 0, zmask = 0;
+    int ny = 0;               // Pauli form
+    uint64_t tmask = 0, a = 0, b = 0;
+    double g[8] = {0};        // pair form
+    uint64_t extra_cmask = 0; // projector bits that must be 1
+};
+} // namespace
+
+std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
+{
+    B200_FAIL_IF(!psi_, "No qubits allocated");
+    const size_t P = (size_t)tape_num_params();
+    std::vector<size_t> train;
+    if (train_in.empty())
+        for (size_t i = 0; i < P; i++) train.push_back(i);
+    else
+        for (auto t : train_in) {
+            B200_FAIL_IF(t < 0 || (size_t)t >= P, "Invalid trainable parameter index");
+            train.push_back((size_t)t);
+        }
+    const size_t T = train.size(), K = tape_obs_.size();
+    std::vector<double> jac(K * T, 0.0);
+    if (K * T == 0) return jac;
+    for (auto &o : tape_obs_)
+        B200_FAIL_IF(o.second != 1, "Unsupported measurements to compute gradient; Adjoint "
+                                    "differentiation method only supports expectation return type");
+    B200_FAIL_IF(!std::is_sorted(train.begin(), train.end()), "trainable parameters must be sorted");
+    flush();
+    const size_t bytes = sizeof(cplx) << n_;
+    cudaStream_t st = (cudaStream_t)stream_;
+    DeviceBuffer lambda(bytes);
+    std::vector<std::unique_ptr<DeviceBuffer>> phi;
+    CUDA_CHECK(cudaMemcpyAsync(lambda.p(), psi_->p(), bytes, cudaMemcpyDeviceToDevice, st));
+    for (size_t k = 0; k < K; k++) {
+        phi.push_back(std::make_unique<DeviceBuffer>(bytes));
+        apply_observable(tape_obs_[k].first, psi_->d(), phi[k]->d());
+    }
+    ensure_buffer(results_, std::max<size_t>(4096, 2 * K * T) * sizeof(double));
+
+    auto generator_of = [&](const TapeOp &op) -> Generator {
+        Generator g;
+        const std::string &nm = op.name;
+        auto W = [&](size_t i) { return bit_of(op.wires[i]); };
+        auto pauli1 = [&](char c, size_t wi) {
+            if (c == 'X') g.xmask |= W(wi);
+            else if (c == 'Y') { g.xmask |= W(wi); g.zmask |= W(wi); g.ny++; }
+            else if (c == 'Z') g.zmask |= W(wi);
+        };
+        auto pairg = [&](uint64_t tm, uint64_t a, uint64_t b, cplx g00, cplx g01, cplx g10, cplx g11) {
+            g.is_pair = true;
+            g.tmask = tm; g.a = a; g.b = b;
+            const cplx v[4] = {g00, g01, g10, g11};
+            for (int i = 0; i < 4; i++) { g.g[2 * i] = v[i].real(); g.g[2 * i + 1] = v[i].imag(); }
+        };
+        g.sigma = -0.5;
+        if (nm == "RX") pauli1('X', 0);
+        else if (nm == "RY") pauli1('Y', 0);
+        else if (nm == "RZ") pauli1('Z', 0);
+        else if (nm == "PhaseShift") { g.sigma = 1.0; g.extra_cmask = W(0); }
+        else if (nm == "IsingXX") { pauli1('X', 0); pauli1('X', 1); }
+        else if (nm == "IsingYY") { pauli1('Y', 0); pauli1('Y', 1); }
+        else if (nm == "IsingZZ") { pauli1('Z', 0); pauli1('Z', 1); }
+        else if (nm == "IsingXY") { g.sigma = 0.5; pairg(W(0) | W(1), W(1), W(0), 0, 1, 1, 0); }
+        else if (nm == "ControlledPhaseShift") { g.sigma = 1.0; g.extra_cmask = W(0) | W(1); }
+        else if (nm == "CRX") { pauli1('X', 1); g.extra_cmask = W(0); }
+        else if (nm == "CRY") { pauli1('Y', 1); g.extra_cmask = W(0); }
+        else if (nm == "CRZ") { pauli1('Z', 1); g.extra_cmask = W(0); }
+        else if (nm == "SingleExcitation") pairg(W(0) | W(1), W(1), W(0), 0, -I_, I_, 0);
+        else if (nm == "DoubleExcitation")
+            pairg(W(0) | W(1) | W(2) | W(3), W(2) | W(3), W(0) | W(1), 0, -I_, I_, 0);
+        else if (nm == "MultiRZ")
+            for (size_t i = 0; i < op.wires.size(); i++) pauli1('Z', i);
+        else if (nm == "PauliRot")
+            for (size_t i = 0; i < op.wires.size(); i++) pauli1(op.pauli_word[i], i);
+        else if (nm == "GlobalPhase") g.sigma = -1.0;
+        else if (nm == "PSWAP") { g.sigma = 1.0; pairg(W(0) | W(1), W(1), W(0), 1, 0, 0, 1); }
+        else
+            B200_FAIL("The operation is not supported using the adjoint differentiation method: " + nm);
+        if (op.inverse) g.sigma = -g.sigma;
+        return g;
+    };
+
+    std::vector<GateOp> pending; // adjoint ops not yet applied to lambda / phi
+    auto apply_pending = [&]() {
+        if (pending.empty()) return;
+        run_ops(lambda.d(), pending);
+        for (size_t k = 0; k < K; k++) run_ops(phi[k]->d(), pending);
+        pending.clear();
+    };
+
+    int64_t tp = (int64_t)T - 1;
+    int64_t cur = (int64_t)P - 1;
+    std::vector<double> sig(K * T, 0.0);
+    for (int64_t j = (int64_t)tape_.size() - 1; j >= 0 && tp >= 0; j--) {
+        const TapeOp &op = tape_[j];
+        B200_FAIL_IF(op.params.size() > 1,
+                     "The operation is not supported using the adjoint differentiation method: " + op.name);
+        if (!op.params.empty()) {
+            if ((size_t)cur == train[tp]) {
+                apply_pending();
+                const Generator g = generator_of(op);
+                uint64_t cmask = g.extra_cmask, cval = g.extra_cmask;
+                for (size_t i = 0; i < op.ctrl_wires.size(); i++) {
+                    cmask |= bit_of(op.ctrl_wires[i]);
+                    if (op.ctrl_values[i]) cval |= bit_of(op.ctrl_wires[i]);
+                }
+                for (size_t k = 0; k < K; k++) {
+                    double *slot = result_slot((int)(k * T + (size_t)tp));
+                    if (g.is_pair)
+                        CUDA_CHECK(b200k_bilinear_pair(phi[k]->d(), lambda.d(), (int)n_, 0, g.tmask, g.a,
+                                                       g.b, g.g, cmask, cval, scratch_->d(), slot, stream_));
+                    else
+                        CUDA_CHECK(b200k_bilinear_pauli(phi[k]->d(), lambda.d(), (int)n_, 0, g.xmask,
+                                                        g.zmask, g.ny, cmask, cval, scratch_->d(), slot,
+                                                        stream_));
+                    note_launch();
+                    sig[k * T + (size_t)tp] = g.sigma;
+                }
+                tp--;
+            }
+            cur--;
+        }
+        if (op.name == "QubitUnitary")
+            canonicalize_matrix(pending, op.matrix, op.wires, !op.inverse, op.ctrl_wires, op.ctrl_values);
+        else
+            canonicalize(pending, op.name, op.params, op.wires, !op.inverse, op.ctrl_wires,
+                         op.ctrl_values, op.pauli_word);
+    }
+    std::vector<double> h;
+    read_results((int)(K * T), h);
+    for (size_t i = 0; i < K * T; i++) jac[i] = -2.0 * sig[i] * h[2 * i + 1];
+    return jac;
+}
+
+} // namespace b200
+
+// =====================================================================================================
+// C ABI
+// =====================================================================================================
+using b200::Simulator;
+
+struct b200sv_device {
+    std::unique_ptr<Simulator> sim;
+};
+
+static thread_local std::string g_err;
+
+#define B200_TRY(...)                                                                              \
+    try {                                                                                          \
+        __VA_ARGS__;                                                                               \
+        return 0;                                                                                  \
+    }                                                                                              \
+    catch (const std::exception &e) {                                                              \
+        g_err = e.what();                                                                          \
+        return -1;                                                                                 \
+    }
+
+static std::vector<int64_t> wv(const int64_t *w, int64_t n) { return std::vector<int64_t>(w, w + (n > 0 ? n : 0)); }
+static std::vector<bool> bv(const uint8_t *v, int64_t n)
+{
+    std::vector<bool> r((size_t)(n > 0 ? n : 0));
+    for (int64_t i = 0; i < n; i++) r[(size_t)i] = v[i] != 0;
+    return r;
+}
+static b200::CVec cvv(const double *ri, size_t n)
+{
+    b200::CVec r(n);
+    for (size_t i = 0; i < n; i++) r[i] = b200::cplx(ri[2 * i], ri[2 * i + 1]);
+    return r;
+}
+
+extern "C" {
+
+const char *b200sv_last_error(void) { return g_err.c_str(); }
+const char *b200sv_version(void) { return "b200sv 0.1 (sm_100a)"; }
+
+b200sv_device *b200sv_create(const char *kwargs)
+{
+    try {
+        auto d = std::make_unique<b200sv_device>();
+        d->sim = std::make_unique<Simulator>(b200::parse_kwargs(kwargs));
+        return d.release();
+    }
+    catch (const std::exception &e) {
+        g_err = e.what();
+        return nullptr;
+    }
+}
+void b200sv_destroy(b200sv_device *d) { delete d; }
+
+int b200sv_allocate_qubits(b200sv_device *d, int64_t n) { B200_TRY(d->sim->allocate(n)) }
+int b200sv_allocate_qubit(b200sv_device *d) { B200_TRY(d->sim->allocate_one()) }
+int b200sv_release_qubits(b200sv_device *d) { B200_TRY(d->sim->release()) }
+int64_t b200sv_num_qubits(b200sv_device *d) { return d->sim->num_qubits(); }
+int b200sv_set_shots(b200sv_device *d, int64_t shots) { B200_TRY(d->sim->set_shots(shots)) }
+int64_t b200sv_get_shots(b200sv_device *d) { return d->sim->shots(); }
+int b200sv_set_prng(b200sv_device *d, b200sv_rng_next_fn next, void *ctx) { B200_TRY(d->sim->set_prng(next, ctx)) }
+int b200sv_seed(b200sv_device *d, uint32_t seed) { B200_TRY(d->sim->seed(seed)) }
+uint32_t b200sv_prng_peek(b200sv_device *d) { return d->sim->prng_peek(); }
+
+int b200sv_named_operation(b200sv_device *d, const char *name, const double *params, int64_t nparams,
+                           const int64_t *wires, int64_t nwires, int inverse,
+                           const int64_t *ctrl_wires, const uint8_t *ctrl_values, int64_t nctrl,
+                           const char *pauli_word)
+{
+    B200_TRY(d->sim->named_op(name, std::vector<double>(params, params + (nparams > 0 ? nparams : 0)),
+                              wv(wires, nwires), inverse != 0, wv(ctrl_wires, nctrl),
+                              bv(ctrl_values, nctrl), pauli_word ? pauli_word : ""))
+}
+int b200sv_matrix_operation(b200sv_device *d, const double *matrix_ri, const int64_t *wires,
+                            int64_t nwires, int inverse, const int64_t *ctrl_wires,
+                            const uint8_t *ctrl_values, int64_t nctrl)
+{
+    B200_TRY(if (nwires < 1 || nwires > 10) throw b200::Error("Invalid number of wires for MatrixOperation");
+             d->sim->matrix_op(cvv(matrix_ri, (size_t(1) << nwires) * (size_t(1) << nwires)),
+                               wv(wires, nwires), inverse != 0, wv(ctrl_wires, nctrl),
+                               bv(ctrl_values, nctrl)))
+}
+int b200sv_set_state(b200sv_device *d, const double *state_ri, int64_t stride, const int64_t *wires,
+                     int64_t nwires)
+{
+    B200_TRY(if (nwires < 0 || nwires > 40) throw b200::Error("Invalid number of wires");
+             b200::CVec st(size_t(1) << nwires);
+             for (size_t i = 0; i < st.size(); i++)
+                 st[i] = b200::cplx(state_ri[2 * (int64_t)i * stride], state_ri[2 * (int64_t)i * stride + 1]);
+             d->sim->set_state(st, wv(wires, nwires)))
+}
+int b200sv_set_basis_state(b200sv_device *d, const int8_t *bits, int64_t stride, const int64_t *wires,
+                           int64_t nwires)
+{
+    B200_TRY(std::vector<int8_t> b((size_t)(nwires > 0 ? nwires : 0));
+             for (int64_t i = 0; i < nwires; i++) b[(size_t)i] = bits[i * stride];
+             d->sim->set_basis_state(b, wv(wires, nwires)))
+}
+
+int64_t b200sv_observable(b200sv_device *d, int obs_id, const double *matrix_ri, int64_t nmatrix,
+                          const int64_t *wires, int64_t nwires)
+{
+    try {
+        return d->sim->obs_named(obs_id, cvv(matrix_ri, (size_t)(nmatrix > 0 ? nmatrix : 0)), wv(wires, nwires));
+    }
+    catch (const std::exception &e) {
+        g_err = e.what();
+        return -1;
+    }
+}
+int64_t b200sv_tensor_observable(b200sv_device *d, const int64_t *keys, int64_t nkeys)
+{
+    try {
+        return d->sim->obs_tensor(wv(keys, nkeys));
+    }
+    catch (const std::exception &e) {
+        g_err = e.what();
+        return -1;
+    }
+}
+int64_t b200sv_hamiltonian_observable(b200sv_device *d, const double *coeffs, const int64_t *keys,
+                                      int64_t nkeys)
+{
+    try {
+        return d->sim->obs_hamiltonian(std::vector<double>(coeffs, coeffs + (nkeys > 0 ? nkeys : 0)),
+                                       wv(keys, nkeys));
+    }
+    catch (const std::exception &e) {
+        g_err = e.what();
+        return -1;
+    }
+}
+
+int b200sv_expval(b200sv_device *d, int64_t key, double *out) { B200_TRY(*out = d->sim->expval(key)) }
+int b200sv_var(b200sv_device *d, int64_t key, double *out) { B200_TRY(*out = d->sim->var(key)) }
+int b200sv_state(b200sv_device *d, double *out_ri, int64_t stride) { B200_TRY(d->sim->state(out_ri, stride)) }
+int b200sv_probs(b200sv_device *d, const int64_t *wires, int64_t nwires, double *out, int64_t stride)
+{
+    B200_TRY(d->sim->probs(wv(wires, nwires), out, stride))
+}
+int b200sv_sample(b200sv_device *d, const int64_t *wires, int64_t nwires, int64_t shots, double *out,
+                  int64_t stride0, int64_t stride1)
+{
+    // layout: row-major (shot, wire) of 0.0/1.0, first listed wire first
+    // (reference: runtime/include/QuantumDevice.hpp:369-396)
+    B200_TRY(const auto idx = d->sim->sample_indices(wv(wires, nwires), shots);
+             const int64_t k = nwires > 0 ? nwires : d->sim->num_qubits();
+             for (int64_t s = 0; s < shots; s++)
+                 for (int64_t w = 0; w < k; w++)
+                     out[s * stride0 + w * stride1] = (double)((idx[(size_t)s] >> (k - 1 - w)) & 1))
+}
+int b200sv_counts(b200sv_device *d, const int64_t *wires, int64_t nwires, int64_t shots,
+                  double *eigvals, int64_t eig_stride, int64_t *counts, int64_t cnt_stride)
+{
+    // eigvals[i] = i, counts[i] = #shots whose bitstring (first wire = MSB) is i; every entry
+    // is written (reference: runtime/include/QuantumDevice.hpp:409-449)
+    B200_TRY(const auto idx = d->sim->sample_indices(wv(wires, nwires), shots);
+             const int64_t k = nwires > 0 ? nwires : d->sim->num_qubits();
+             const int64_t nb = int64_t(1) << k;
+             for (int64_t i = 0; i < nb; i++) {
+                 eigvals[i * eig_stride] = (double)i;
+                 counts[i * cnt_stride] = 0;
+             }
+             for (auto i : idx) counts[i * cnt_stride] += 1)
+}
+int b200sv_measure(b200sv_device *d, int64_t wire, int postselect, int *out)
+{
+    B200_TRY(*out = d->sim->measure(wire, postselect) ? 1 : 0)
+}
+
+int b200sv_start_tape_recording(b200sv_device *d) { B200_TRY(d->sim->start_tape()) }
+int b200sv_stop_tape_recording(b200sv_device *d) { B200_TRY(d->sim->stop_tape()) }
+int64_t b200sv_tape_num_params(b200sv_device *d) { return d->sim->tape_num_params(); }
+int64_t b200sv_tape_num_observables(b200sv_device *d) { return d->sim->tape_num_obs(); }
+int b200sv_gradient(b200sv_device *d, double *const *grad_rows, const int64_t *row_sizes,
+                    const int64_t *strides, int64_t nrows, const int64_t *train, int64_t ntrain)
+{
+    B200_TRY(const int64_t K = d->sim->tape_num_obs();
+             const int64_t P = d->sim->tape_num_params();
+             const int64_t T = ntrain > 0 ? ntrain : P;
+             if (K * T == 0) return 0;
+             if (nrows != K) throw b200::Error("Invalid number of pre-allocated gradients");
+             for (int64_t k = 0; k < K; k++)
+                 if (row_sizes[k] < T) throw b200::Error("Invalid size of pre-allocated gradients");
+             const auto jac = d->sim->gradient(wv(train, ntrain));
+             for (int64_t k = 0; k < K; k++)
+                 for (int64_t j = 0; j < T; j++) grad_rows[k][j * strides[k]] = jac[(size_t)(k * T + j)])
+}
+
+int b200sv_get_stats(b200sv_device *d, b200sv_stats *out) { B200_TRY(*out = d->sim->stats()) }
+int b200sv_reset_stats(b200sv_device *d) { B200_TRY(d->sim->reset_stats()) }
+int b200sv_set_timing(b200sv_device *d, int on) { B200_TRY(d->sim->set_timing(on != 0)) }
+int b200sv_flush(b200sv_device *d) { B200_TRY(d->sim->flush()) }
+int b200sv_synchronize(b200sv_device *d) { B200_TRY(d->sim->synchronize()) }
+void *b200sv_device_pointer(b200sv_device *d) { return d->sim->device_pointer(); }
+
+} // extern "C"

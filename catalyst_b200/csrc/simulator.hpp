@@ -1,0 +1,213 @@
+// simulator.hpp — C++ host layer of the B200 state-vector device.
+//
+// Owns the complex128 state vector in HBM, turns the eager one-gate-at-a-time calls of the
+// reference's device interface (runtime/include/QuantumDevice.hpp:215-567) into a lazy queue of
+// canonical ops, plans that queue into fused tile passes (one HBM round trip each) and launches the
+// sm_100a kernels through the thin C ABI of include/b200sv_kernels.h.  No reference headers and no
+// PyTorch here; the vtable adapter for Catalyst's runtime lives in plugin.cpp.
+#pragma once
+
+#include <complex>
+#include <cstdint>
+#include <functional>
+#include <map>
+#include <memory>
+#include <optional>
+#include <random>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "b200sv.h"
+#include "b200sv_kernels.h"
+
+namespace b200 {
+
+using cplx = std::complex<double>;
+using CVec = std::vector<cplx>;
+
+struct Error : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+// ---- canonical op: everything a gate can become, in LOGICAL bit space (bit n-1-w for wire w) ----
+struct GateOp {
+    enum Kind { PAIR, PHASE, PARITY, PAULIROT, DENSE } kind = PAIR;
+    uint64_t xmask = 0;          // non-diagonal target bits
+    uint64_t cmask = 0, cval = 0; // control predicate (also selects where a PHASE applies)
+    uint64_t a = 0, b = 0;       // PAIR: basis patterns (subsets of xmask)
+    uint64_t zmask = 0;          // PARITY / PAULIROT: z part
+    int ny = 0;                  // PAULIROT: number of Y factors
+    cplx m[4];                   // PAIR: 2x2; PHASE: m[0]; PARITY: m[0] even, m[1] odd;
+                                 // PAULIROT: m[0] = (cos, sin)
+    std::vector<int> targets;    // DENSE: logical bits, most significant first
+    std::shared_ptr<CVec> matrix; // DENSE
+    uint64_t zsupport() const { return cmask | (kind == PARITY || kind == PAULIROT ? zmask : 0); }
+};
+
+enum class ObsKind { Named, Hermitian, Tensor, Hamiltonian };
+struct ObsNode {
+    ObsKind kind;
+    int named_id = 0;
+    std::vector<int64_t> wires;
+    CVec matrix;
+    std::vector<double> coeffs;
+    std::vector<int64_t> children;
+};
+
+struct TapeOp {
+    std::string name;
+    std::vector<double> params;
+    std::vector<int64_t> wires;
+    bool inverse;
+    CVec matrix;
+    std::vector<int64_t> ctrl_wires;
+    std::vector<bool> ctrl_values;
+    std::string pauli_word;
+};
+
+// A flattened observable term: coef * product of factors
+struct ObsFactor {
+    int named_id;  // 0..4 named, 5 hermitian
+    std::vector<int64_t> wires;
+    const CVec *matrix = nullptr;
+};
+struct ObsTerm {
+    double coef = 1.0;
+    std::vector<ObsFactor> factors; // applied first-to-last
+};
+struct PauliTerm {
+    cplx coef;
+    uint64_t xmask = 0, zmask = 0;
+    int ny = 0;
+};
+
+struct Options {
+    int64_t shots = 0;
+    int tile_bits = 11;
+    int min_row_bits = 7;
+    bool fuse = true;
+    int device = -1; // -1: LOCAL_RANK or 0
+};
+
+class DeviceBuffer;
+
+class Simulator {
+  public:
+    explicit Simulator(const Options &opt);
+    ~Simulator();
+    Simulator(const Simulator &) = delete;
+    Simulator &operator=(const Simulator &) = delete;
+
+    // lifecycle
+    void allocate(int64_t n);
+    void allocate_one();
+    void release();
+    int64_t num_qubits() const { return n_; }
+    void set_shots(int64_t s) { opt_.shots = s; }
+    int64_t shots() const { return opt_.shots; }
+    void set_prng(b200sv_rng_next_fn fn, void *ctx);
+    void seed(uint32_t s);
+    uint32_t prng_peek();
+
+    // gates
+    void named_op(const std::string &name, const std::vector<double> &params,
+                  const std::vector<int64_t> &wires, bool inverse,
+                  const std::vector<int64_t> &cw, const std::vector<bool> &cv,
+                  const std::string &pauli_word);
+    void matrix_op(const CVec &matrix, const std::vector<int64_t> &wires, bool inverse,
+                   const std::vector<int64_t> &cw, const std::vector<bool> &cv);
+    void set_state(const CVec &st, const std::vector<int64_t> &wires);
+    void set_basis_state(const std::vector<int8_t> &bits, const std::vector<int64_t> &wires);
+
+    // observables
+    int64_t obs_named(int id, const CVec &matrix, const std::vector<int64_t> &wires);
+    int64_t obs_tensor(const std::vector<int64_t> &keys);
+    int64_t obs_hamiltonian(const std::vector<double> &coeffs, const std::vector<int64_t> &keys);
+
+    // measurements
+    double expval(int64_t key);
+    double var(int64_t key);
+    void state(double *out_ri, int64_t stride);
+    void probs(const std::vector<int64_t> &wires, double *out, int64_t stride);
+    std::vector<int64_t> sample_indices(const std::vector<int64_t> &wires, int64_t shots);
+    bool measure(int64_t wire, int postselect);
+
+    // tape / gradient
+    void start_tape();
+    void stop_tape();
+    int64_t tape_num_params() const;
+    int64_t tape_num_obs() const { return (int64_t)tape_obs_.size(); }
+    std::vector<double> gradient(const std::vector<int64_t> &train); // K x T row-major
+
+    // instrumentation
+    b200sv_stats stats() const { return stats_; }
+    void reset_stats();
+    void set_timing(bool on) { timing_ = on; }
+    void flush();
+    void synchronize();
+    void *device_pointer();
+
+  private:
+    // --- helpers -------------------------------------------------------------------------------
+    uint64_t bit_of(int64_t wire) const;
+    int lbit(int64_t wire) const;
+    void check_wires(const std::vector<int64_t> &wires, const std::vector<int64_t> &cw) const;
+    void canonicalize(std::vector<GateOp> &out, const std::string &name,
+                      const std::vector<double> &params, const std::vector<int64_t> &wires,
+                      bool inverse, const std::vector<int64_t> &cw, const std::vector<bool> &cv,
+                      const std::string &pauli_word) const;
+    void canonicalize_matrix(std::vector<GateOp> &out, const CVec &matrix,
+                             const std::vector<int64_t> &wires, bool inverse,
+                             const std::vector<int64_t> &cw, const std::vector<bool> &cv) const;
+    void enqueue(std::vector<GateOp> &&ops);
+    // plan + launch a list of canonical ops on an arbitrary device vector of 2^n amplitudes
+    void run_ops(double *vec, std::vector<GateOp> &ops);
+    void launch_pass(double *vec, const std::vector<const GateOp *> &ops,
+                     const std::vector<int> &req_high, int c);
+    const double *upload_matrix(const CVec &m);
+
+    void flatten(int64_t key, std::vector<ObsTerm> &out) const;
+    bool term_to_paulis(const ObsTerm &t, std::vector<PauliTerm> &out) const;
+    // vec_out = O vec_in  (vec_out != vec_in); uses tmp_ for non-Pauli terms
+    void apply_observable(int64_t key, const double *vec_in, double *vec_out);
+    void factor_ops(const ObsFactor &f, std::vector<GateOp> &ops) const;
+    cplx inner(const double *a, const double *b);
+    void read_results(int nslots, std::vector<double> &host);
+    double *result_slot(int slot);
+
+    double uniform01();
+    uint32_t rng_next();
+
+    void ensure_buffer(std::unique_ptr<DeviceBuffer> &buf, size_t bytes);
+    void note_launch() { stats_.other_launches++; }
+
+    Options opt_;
+    int64_t n_ = 0;
+    int cuda_device_ = 0;
+    void *stream_ = nullptr;
+    std::unique_ptr<DeviceBuffer> psi_, tmp_, acc_, scratch_, results_, probs_buf_, misc_;
+    std::unique_ptr<DeviceBuffer> matrix_arena_;
+    size_t arena_used_ = 0;
+    double *pinned_ = nullptr;
+    size_t pinned_doubles_ = 0;
+
+    std::vector<GateOp> queue_;
+    std::vector<ObsNode> obs_;
+    bool recording_ = false;
+    std::vector<TapeOp> tape_;
+    std::vector<std::pair<int64_t, int>> tape_obs_;
+
+    b200sv_rng_next_fn rng_fn_ = nullptr;
+    void *rng_ctx_ = nullptr;
+    std::mt19937 own_gen_;
+    bool own_seeded_ = false;
+
+    b200sv_stats stats_{};
+    bool timing_ = false;
+    void *ev0_ = nullptr, *ev1_ = nullptr;
+};
+
+Options parse_kwargs(const char *kwargs);
+
+} // namespace b200

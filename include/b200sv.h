@@ -1,0 +1,132 @@
+/* b200sv.h — C ABI of the B200 state-vector device (libb200sv.so).
+ *
+ * This is the boundary a binding of the reference's device interface attaches to.  Each entry point
+ * names the method of `Catalyst::Runtime::QuantumDevice` it implements (reference:
+ * runtime/include/QuantumDevice.hpp, cited per function) and keeps that method's argument meaning
+ * and error behaviour; the C++ vtable adapter that Catalyst's runtime dlopen()s
+ * (catalyst_b200/csrc/plugin.cpp -> librtd_b200sv.so, factory symbol `B200StateVectorFactory`,
+ * reference: QuantumDevice.hpp:30-33) is a thin shim over these calls.  INTEGRATION.md shows both
+ * bindings.
+ *
+ * Conventions
+ *   - `wires` are device wire indices 0..n-1; wire 0 is the most significant bit of every
+ *     index-like output (reference: QuantumDevice.hpp:409-412,
+ *     frontend/test/pytest/test_measurements_results.py:166-184).
+ *   - complex128 data crosses as interleaved (re, im) doubles; matrices are row-major with the
+ *     first listed wire as the most significant row/column bit (QuantumDevice.hpp:244).
+ *   - every int-returning function returns 0 on success, nonzero on error; the message is
+ *     retrievable with b200sv_last_error() (the adapter rethrows it as RuntimeException,
+ *     reference: runtime/include/Exception.hpp:26-86).
+ *   - gate calls only enqueue work; any call that returns data flushes and synchronises.
+ *   - there is NO CPU fallback: creating a device without a usable CUDA device fails.
+ */
+#ifndef B200SV_H
+#define B200SV_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200sv_device b200sv_device;
+
+const char *b200sv_last_error(void);
+const char *b200sv_version(void);
+
+/* <Name>Factory(kwargs) — QuantumDevice.hpp:30-33; kwargs is the Python str(dict) the frontend
+ * bakes into quantum.device (runtime/lib/backend/common/Utils.hpp:107-156).  Recognised keys:
+ * shots, tile_bits, min_row_bits, fuse (0/1), device (CUDA ordinal).  Unknown keys are ignored
+ * like lightning's mcmc/num_burnin/kernel_name. Returns NULL on error. */
+b200sv_device *b200sv_create(const char *kwargs);
+void b200sv_destroy(b200sv_device *d);
+
+/* AllocateQubits :88 / AllocateQubit :122 / ReleaseQubits :103 / GetNumQubits :110 */
+int b200sv_allocate_qubits(b200sv_device *d, int64_t n);
+int b200sv_allocate_qubit(b200sv_device *d); /* appends one wire in |0> */
+int b200sv_release_qubits(b200sv_device *d); /* frees the state; object stays reusable */
+int64_t b200sv_num_qubits(b200sv_device *d);
+/* SetDeviceShots :164 / GetDeviceShots :171 */
+int b200sv_set_shots(b200sv_device *d, int64_t shots);
+int64_t b200sv_get_shots(b200sv_device *d);
+/* SetDevicePRNG :192 — the runtime lends a std::mt19937*; across a C ABI that is a callback that
+ * returns the engine's next 32-bit output.  NULL => unseeded (fresh random_device seed per draw,
+ * as runtime/lib/backend/common/Utils.hpp:329-334). */
+typedef uint32_t (*b200sv_rng_next_fn)(void *ctx);
+int b200sv_set_prng(b200sv_device *d, b200sv_rng_next_fn next, void *ctx);
+/* convenience for hosts without a runtime generator: own std::mt19937(seed)
+ * (reference: runtime/lib/capi/ExecutionContext.hpp:309-321) */
+int b200sv_seed(b200sv_device *d, uint32_t seed);
+uint32_t b200sv_prng_peek(b200sv_device *d); /* next raw output without consuming (tests) */
+
+/* NamedOperation :215-219 (caller runtime/lib/capi/RuntimeCAPI.cpp:449-814).
+ * pauli_word is optional_params[0] of PauliRot (RuntimeCAPI.cpp:812-813), else NULL. */
+int b200sv_named_operation(b200sv_device *d, const char *name, const double *params, int64_t nparams,
+                           const int64_t *wires, int64_t nwires, int inverse,
+                           const int64_t *ctrl_wires, const uint8_t *ctrl_values, int64_t nctrl,
+                           const char *pauli_word);
+/* MatrixOperation :250-255 (caller RuntimeCAPI.cpp:816-859) */
+int b200sv_matrix_operation(b200sv_device *d, const double *matrix_ri, const int64_t *wires,
+                            int64_t nwires, int inverse, const int64_t *ctrl_wires,
+                            const uint8_t *ctrl_values, int64_t nctrl);
+/* SetState :284 / SetBasisState :270 */
+int b200sv_set_state(b200sv_device *d, const double *state_ri, int64_t stride, const int64_t *wires,
+                     int64_t nwires);
+int b200sv_set_basis_state(b200sv_device *d, const int8_t *bits, int64_t stride, const int64_t *wires,
+                           int64_t nwires);
+
+/* Observable :317 / TensorObservable :335 / HamiltonianObservable :353 — return key >= 0, -1 on error.
+ * obs_id follows enum ObsId of runtime/include/Types.h:36-43 (0 Identity .. 4 Hadamard, 5 Hermitian). */
+int64_t b200sv_observable(b200sv_device *d, int obs_id, const double *matrix_ri, int64_t nmatrix,
+                          const int64_t *wires, int64_t nwires);
+int64_t b200sv_tensor_observable(b200sv_device *d, const int64_t *keys, int64_t nkeys);
+int64_t b200sv_hamiltonian_observable(b200sv_device *d, const double *coeffs, const int64_t *keys,
+                                      int64_t nkeys);
+
+/* Expval :488 / Var :503 */
+int b200sv_expval(b200sv_device *d, int64_t key, double *out);
+int b200sv_var(b200sv_device *d, int64_t key, double *out);
+/* State :518 — out has 2^n complex entries spaced `stride` complex elements apart (DataView) */
+int b200sv_state(b200sv_device *d, double *out_ri, int64_t stride);
+/* Probs :462 (nwires == 0) / PartialProbs :472 — out has 2^k doubles spaced `stride` apart */
+int b200sv_probs(b200sv_device *d, const int64_t *wires, int64_t nwires, double *out, int64_t stride);
+/* Sample :384 / PartialSample :396 — out(shot, wire) = out[shot*stride0 + wire*stride1] in {0.0, 1.0} */
+int b200sv_sample(b200sv_device *d, const int64_t *wires, int64_t nwires, int64_t shots, double *out,
+                  int64_t stride0, int64_t stride1);
+/* Counts :433 / PartialCounts :446 — all 2^k entries of both outputs are written */
+int b200sv_counts(b200sv_device *d, const int64_t *wires, int64_t nwires, int64_t shots,
+                  double *eigvals, int64_t eig_stride, int64_t *counts, int64_t cnt_stride);
+/* Measure :234 — postselect -1 = none (RuntimeCAPI.cpp:950-960); *out = 0/1 */
+int b200sv_measure(b200sv_device *d, int64_t wire, int postselect, int *out);
+
+/* StartTapeRecording :574 / StopTapeRecording :581 / Gradient :564-567 (caller RuntimeCAPI.cpp:386-447).
+ * grad_rows[k] receives d<O_k>/d theta_j for the recorded expvals k, j over `train` (ntrain == 0 =>
+ * all recorded gate parameters in program order); element j of row k is grad_rows[k][j*strides[k]]. */
+int b200sv_start_tape_recording(b200sv_device *d);
+int b200sv_stop_tape_recording(b200sv_device *d);
+int64_t b200sv_tape_num_params(b200sv_device *d);
+int64_t b200sv_tape_num_observables(b200sv_device *d);
+int b200sv_gradient(b200sv_device *d, double *const *grad_rows, const int64_t *row_sizes,
+                    const int64_t *strides, int64_t nrows, const int64_t *train, int64_t ntrain);
+
+/* ---- instrumentation (counters behind the device, not in the reference) ---- */
+typedef struct b200sv_stats {
+    int64_t gates_enqueued;   /* logical gates received (Identity excluded) */
+    int64_t kernel_ops;       /* canonical ops executed inside tile passes */
+    int64_t tile_passes;      /* launches of the fused tile kernel = HBM round trips */
+    int64_t other_launches;   /* reductions, probs, collapse, sampler, copies */
+    double gate_device_ms;    /* CUDA-event time of the tile passes since the last reset */
+    double algorithmic_bytes; /* sum over gates of 2*16*2^(n-c) */
+} b200sv_stats;
+int b200sv_get_stats(b200sv_device *d, b200sv_stats *out);
+int b200sv_reset_stats(b200sv_device *d);
+int b200sv_set_timing(b200sv_device *d, int on); /* record CUDA events around each flush */
+int b200sv_flush(b200sv_device *d);              /* launch everything queued (no host sync) */
+int b200sv_synchronize(b200sv_device *d);        /* flush + wait */
+/* device pointer of the local shard (for benchmarks / zero-copy consumers) */
+void *b200sv_device_pointer(b200sv_device *d);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,131 @@
+/* b200sv_kernels.h — thin C ABI between the C++ host layer and the hand-written sm_100a kernels.
+ *
+ * Plain pointers and sizes only: no C++ types, no torch types.  Every entry point enqueues work on
+ * the given CUDA stream and returns a cudaError_t-compatible int (0 = success).  Device pointers
+ * are complex128 amplitudes stored as interleaved (re, im) doubles (16 bytes per amplitude).
+ *
+ * Index convention (reference: runtime/include/QuantumDevice.hpp:409-412 and
+ * frontend/test/pytest/test_measurements_results.py:166-184 — wire 0 is the most significant bit):
+ * this layer only sees *bit positions* of the amplitude index; the host maps wires to positions.
+ * On a sharded state the full index is (rank << n_local) | local_index; `rank_base` carries the
+ * rank bits so that control predicates and diagonal phases on global qubits need no data movement.
+ *
+ * What each kernel replaces in the reference stack: the per-gate / per-measurement sweeps that
+ * lightning.qubit performs behind QuantumDevice::NamedOperation / MatrixOperation / Expval / Var /
+ * Probs / Sample / Measure / Gradient (runtime/include/QuantumDevice.hpp:215-567).
+ */
+#ifndef B200SV_KERNELS_H
+#define B200SV_KERNELS_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- fused tile pass --------------------------------------------------------------------------
+ * One launch = one HBM round trip over the whole local shard.  Each CTA stages a tile of 2^t
+ * amplitudes in shared memory (the low `c` index bits — contiguous 16*2^c-byte rows — plus
+ * `nhigh` arbitrary higher bits), runs the whole op list on it, and writes it back. */
+enum {
+    B200K_OP_PAIR = 0,     /* 2x2 matrix between basis patterns a and b of the target bits      */
+    B200K_OP_PHASE = 1,    /* amplitude *= m[0..1] where the control predicate holds            */
+    B200K_OP_PARITY = 2,   /* amplitude *= (parity(idx & zmask) ? m[2..3] : m[0..1])            */
+    B200K_OP_PAULIROT = 3, /* exp(-i theta/2 P): m[0]=cos, m[1]=sin, x-part = tmask, z-part = a */
+    B200K_OP_DENSE = 4     /* 2^k x 2^k row-major matrix in global memory on k tile bits        */
+};
+
+#define B200K_MAX_OPS 32
+#define B200K_MAX_TILE_BITS 12
+#define B200K_MAX_HIGH 10
+#define B200K_TILE_THREADS 256
+
+typedef struct B200kTileOp {
+    uint32_t kind;
+    uint32_t k;       /* DENSE: number of target bits */
+    uint32_t tmask;   /* tile-local mask of the non-diagonal target bits */
+    uint32_t a, b;    /* PAIR: tile-local patterns; PARITY/PAULIROT: a = tile-local z mask */
+    uint32_t cmask, cval; /* control predicate on tile-local bits */
+    uint32_t ny;      /* PAULIROT: number of Y factors mod 4 */
+    uint64_t cmask_o, cval_o; /* control predicate on the bits outside the tile (incl. rank bits) */
+    uint64_t zmask_o;         /* PARITY/PAULIROT: z mask on the bits outside the tile */
+    union {
+        double m[8];
+        struct {
+            const double *mat; /* DENSE: device pointer, 2^k * 2^k complex, row-major */
+            uint8_t tb[16];    /* DENSE: tile-local target bits, most significant first */
+        } d;
+    } u;
+} B200kTileOp;
+
+typedef struct B200kTileProgram {
+    int32_t n_ops;
+    int32_t t;     /* tile bits (<= B200K_MAX_TILE_BITS, <= n_local) */
+    int32_t c;     /* contiguous low bits inside the tile */
+    int32_t nhigh; /* = t - c */
+    uint8_t high_pos[16]; /* index positions (>= c, ascending) of tile bits c..t-1 */
+    uint64_t rank_base;   /* rank << n_local */
+    B200kTileOp ops[B200K_MAX_OPS];
+} B200kTileProgram;
+
+int b200k_tile_program(double *psi, int n_local, const B200kTileProgram *prog, void *stream);
+
+/* ---- reductions (warp-shuffle tree -> per-block partials -> fixed-order final sum) -------------
+ * `scratch` must hold b200k_reduce_scratch_doubles() doubles; results land in `out` (device). */
+int64_t b200k_reduce_scratch_doubles(void);
+
+/* out[0..1] = sum_i conj(phi_i) * (P lam)_i over i with ((rank_base|i) & cmask) == cval, where
+ * (P v)_i = i^ny * (-1)^popc(j & zmask) * v_j, j = i ^ xmask.  xmask must be local bits. */
+int b200k_bilinear_pauli(const double *phi, const double *lam, int n_local, uint64_t rank_base,
+                         uint64_t xmask, uint64_t zmask, int ny, uint64_t cmask, uint64_t cval,
+                         double *scratch, double *out, void *stream);
+
+/* out[0..1] = sum over base indices i (tmask bits zero, control predicate true) of
+ * [phi_{i|a}, phi_{i|b}]^dagger * g(2x2, row-major complex) * [lam_{i|a}, lam_{i|b}]^T. */
+int b200k_bilinear_pair(const double *phi, const double *lam, int n_local, uint64_t rank_base,
+                        uint64_t tmask, uint64_t a, uint64_t b, const double *g8, uint64_t cmask,
+                        uint64_t cval, double *scratch, double *out, void *stream);
+
+/* out[0] = sum_i |psi_i|^2 * sum_t coef[t] * (-1)^popc((rank_base|i) & zmask[t]). */
+int b200k_expval_diag_batch(const double *psi, int n_local, uint64_t rank_base,
+                            const uint64_t *zmasks, const double *coefs, int nterms,
+                            double *scratch, double *out, void *stream);
+
+/* ---- probabilities ---------------------------------------------------------------------------- */
+int b200k_probs_all(const double *psi, double *out, int n_local, void *stream);
+/* out[o] = sum of |psi_i|^2 over i whose bits at tb[0..k) (most significant first) spell o.
+ * scratch: 2^k * b200k_probs_splits(n_local, k) doubles. */
+int b200k_probs_splits(int n_local, int k);
+int b200k_probs_partial(const double *psi, int n_local, const uint8_t *tb, int k, double *scratch,
+                        double *out, void *stream);
+
+/* ---- element-wise passes ---------------------------------------------------------------------- */
+/* psi_i = (bit `pos` of (rank_base|i) == keep) ? psi_i * scale : 0 */
+int b200k_collapse(double *psi, int n_local, uint64_t rank_base, int pos, int keep, double scale,
+                   void *stream);
+/* out_i = (accumulate ? out_i : 0) + coef * (P in)_i  (Pauli word as in b200k_bilinear_pauli) */
+int b200k_pauli_apply(double *out, const double *in, int n_local, uint64_t rank_base,
+                      uint64_t xmask, uint64_t zmask, int ny, double coef_re, double coef_im,
+                      int accumulate, void *stream);
+/* acc += coef * x */
+int b200k_axpy(double *acc, const double *x, double coef, int n_local, void *stream);
+/* psi = 0 everywhere, then psi[index] = 1 if index >= 0 */
+int b200k_set_basis(double *psi, int n_local, int64_t local_index, void *stream);
+/* psi = 0, then psi[index whose bits at tb[0..k) (most significant first) spell r] = vals[r] */
+int b200k_scatter_state(double *psi, const double *vals, int n_local, const uint8_t *tb, int k,
+                        void *stream);
+/* new[(i << 1)] = old[i], new[(i << 1) | 1] = 0  — append one qubit in |0> as the new bit 0 */
+int b200k_append_qubit(double *dst, const double *src, int n_local_old, void *stream);
+
+/* ---- alias-method sampler on device (reference algorithm: Walker alias table with LIFO pairing,
+ * SURVEY.md Appendix A.4; restated as prefix sums so that no sequential pass over 2^n is needed) */
+int64_t b200k_sampler_scratch_doubles(int64_t nbins);
+int b200k_sampler_prepare(const double *probs, int64_t nbins, double *scratch, void *stream);
+/* u: 2*nshots uniforms (u1,u2 per shot) on device; out_idx: nshots int64 on device */
+int b200k_sampler_draw(const double *probs, int64_t nbins, const double *scratch, const double *u,
+                       int64_t nshots, int64_t *out_idx, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

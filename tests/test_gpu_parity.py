@@ -1,0 +1,354 @@
+"""Parity of the CUDA device (through the C ABI of include/b200sv.h) against the CPU oracle and
+against the reference's own known-answer vectors.  Tolerance: 1e-12 on amplitudes, expectation
+values and gradients (BASELINE.json north_star); bit-exact for seeded mid-circuit measurement
+outcomes and sample bitstrings."""
+import numpy as np
+import pytest
+
+from dsl import (apply_ops, build_obs, random_circuit, random_op, random_pauli_obs, random_state)
+from golden import reference_cases as G
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-12
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    from catalyst_b200 import capi
+    return capi
+
+
+# ---- reference known-answer vectors ------------------------------------------------------------
+@pytest.mark.parametrize("case", G.CASES, ids=[c[0] for c in G.CASES])
+def test_expval_var_constants(gpu, case):
+    _, _, n, ops, kind, obs, expected = case
+    dev = gpu.B200Device(n)
+    apply_ops(dev, ops)
+    key = build_obs(dev, obs)
+    got = dev.expval(key) if kind == "expval" else dev.var(key)
+    assert np.isclose(got, expected, rtol=1e-5, atol=1e-8), (got, expected)
+
+
+@pytest.mark.parametrize("case", G.STATE_CASES, ids=[c[0] for c in G.STATE_CASES])
+def test_state_constants(gpu, case):
+    _, _, n, ops, expected = case
+    dev = gpu.B200Device(n)
+    apply_ops(dev, ops)
+    assert np.allclose(dev.state(), expected)
+
+
+@pytest.mark.parametrize("case", G.PROBS_CASES, ids=[c[0] for c in G.PROBS_CASES])
+def test_probs_constants(gpu, case):
+    _, _, n, ops, wires, expected = case
+    dev = gpu.B200Device(n)
+    apply_ops(dev, ops)
+    assert np.allclose(dev.probs(wires), expected)
+
+
+@pytest.mark.parametrize("case", G.SAMPLE_CASES, ids=[c[0] for c in G.SAMPLE_CASES])
+def test_sample_deterministic(gpu, case):
+    _, _, n, ops, shots, row = case
+    dev = gpu.B200Device(n)
+    apply_ops(dev, ops)
+    s = dev.sample(shots)
+    assert np.array_equal(s, np.array([row] * shots, dtype=float))
+
+
+@pytest.mark.parametrize("case", G.COUNTS_CASES, ids=[c[0] for c in G.COUNTS_CASES])
+def test_counts_deterministic(gpu, case):
+    _, _, n, ops, shots, expected = case
+    dev = gpu.B200Device(n)
+    apply_ops(dev, ops)
+    eig, cnt = dev.counts(shots)
+    assert np.array_equal(eig, np.arange(1 << n))
+    assert np.array_equal(cnt, expected)
+
+
+def _seeded_program(dev, x, terminal):
+    out = []
+    for _ in range(4):
+        dev.reset(1)
+        dev.named_op("RX", [x], [0])
+        if dev.measure(0):
+            dev.named_op("Hadamard", [], [0])
+        out.append(terminal(dev))
+    return out
+
+
+def test_seeded_mcm_changelog_0_8_0(gpu):
+    g = G.SEEDED_MCM
+    dev = gpu.B200Device(1, seed=g["seed"])
+    rows = _seeded_program(dev, g["x"], lambda d: d.probs())
+    assert np.allclose(np.array(rows), np.array(g["probs"]))
+
+
+def test_seeded_sample_changelog_0_9_0(gpu):
+    g = G.SEEDED_SAMPLE
+    dev = gpu.B200Device(1, seed=g["seed"])
+    rows = _seeded_program(dev, g["x"], lambda d: d.sample(g["shots"])[:, 0])
+    assert np.array_equal(np.array(rows, dtype=int), np.array(g["samples"]))
+
+
+# ---- random circuits vs the oracle --------------------------------------------------------------
+CONFIGS = [dict(), dict(fuse=False), dict(tile_bits=4, min_row_bits=2), dict(tile_bits=6, min_row_bits=0),
+           dict(tile_bits=12, min_row_bits=7)]
+
+
+@pytest.mark.parametrize("cfg", range(len(CONFIGS)))
+@pytest.mark.parametrize("n,seed", [(1, 0), (2, 1), (3, 2), (5, 3), (7, 4), (9, 5), (11, 6), (12, 7),
+                                    (13, 8), (14, 9), (16, 10)])
+def test_random_circuit_state(gpu, oracle_mod, n, seed, cfg):
+    ops = random_circuit(seed, n, 60)
+    init = random_state(seed + 500, n)
+    o = oracle_mod.OracleDevice(n)
+    d = gpu.B200Device(n, **CONFIGS[cfg])
+    o.set_state(init, list(range(n)))
+    d.set_state(init, list(range(n)))
+    apply_ops(o, ops)
+    apply_ops(d, ops)
+    a, b = o.state(), d.state()
+    assert np.max(np.abs(a - b)) < TOL
+    assert abs(np.linalg.norm(b) - 1) < 1e-12
+
+
+@pytest.mark.parametrize("n", [18, 20])
+def test_random_circuit_state_large(gpu, oracle_mod, n):
+    ops = random_circuit(n, n, 80)
+    o = oracle_mod.OracleDevice(n)
+    d = gpu.B200Device(n)
+    apply_ops(o, [("Hadamard", [], [w]) for w in range(n)] + ops)
+    apply_ops(d, [("Hadamard", [], [w]) for w in range(n)] + ops)
+    assert np.max(np.abs(o.state() - d.state())) < TOL
+
+
+@pytest.mark.parametrize("k", [2, 3, 4, 5, 6, 8])
+def test_matrix_operation_k_wires(gpu, oracle_mod, k):
+    from dsl import random_unitary
+    n = 12
+    rng = np.random.default_rng(k)
+    init = random_state(k, n)
+    o, d = oracle_mod.OracleDevice(n), gpu.B200Device(n)
+    o.set_state(init, list(range(n)))
+    d.set_state(init, list(range(n)))
+    for trial in range(3):
+        perm = [int(w) for w in rng.permutation(n)]
+        U = random_unitary(rng, k)
+        kw = dict(inverse=bool(trial & 1))
+        if trial == 2:
+            kw.update(ctrl_wires=perm[k:k + 2], ctrl_values=[True, False])
+        o.matrix_op(U, perm[:k], **kw)
+        d.matrix_op(U, perm[:k], **kw)
+    assert np.max(np.abs(o.state() - d.state())) < TOL
+
+
+def test_state_prep_and_wire_order(gpu, oracle_mod):
+    d = gpu.B200Device(3)
+    d.named_op("PauliX", [], [0])
+    assert np.argmax(np.abs(d.state())) == 4
+    assert np.allclose(d.probs([2, 0]), [0, 1, 0, 0])
+    sub = random_state(3, 2)
+    o = oracle_mod.OracleDevice(5)
+    d = gpu.B200Device(5)
+    o.set_state(sub, [3, 1])
+    d.set_state(sub, [3, 1])
+    assert np.allclose(o.state(), d.state(), atol=0)
+    o.set_basis_state([1, 0, 1], [4, 2, 0])
+    d.set_basis_state([1, 0, 1], [4, 2, 0])
+    assert np.array_equal(o.state(), d.state())
+
+
+# ---- measurements ------------------------------------------------------------------------------
+def _prepared(gpu, oracle_mod, n, seed, depth=40, **kw):
+    ops = random_circuit(seed, n, depth)
+    o = oracle_mod.OracleDevice(n, seed=kw.pop("rng_seed", None))
+    d = gpu.B200Device(n, **kw)
+    apply_ops(o, ops)
+    apply_ops(d, ops)
+    return o, d
+
+
+@pytest.mark.parametrize("n,seed", [(3, 0), (6, 1), (10, 2), (13, 3), (17, 4)])
+def test_expval_var_random_observables(gpu, oracle_mod, n, seed):
+    o, d = _prepared(gpu, oracle_mod, n, seed)
+    rng = np.random.default_rng(seed)
+    herm = rng.normal(size=(4, 4)) + 1j * rng.normal(size=(4, 4))
+    herm = herm + herm.conj().T
+    obs_list = [("N", "PauliZ", 0), ("N", "PauliX", n - 1), ("N", "PauliY", n // 2),
+                ("N", "Hadamard", 0), ("N", "Identity", 0)]
+    obs_list += [random_pauli_obs(rng, n) for _ in range(6)]
+    ham_terms = [random_pauli_obs(rng, n) for _ in range(12)]
+    obs_list.append(("Ham", list(rng.normal(size=12)), ham_terms))
+    if n >= 3:
+        obs_list.append(("H", herm, [n - 1, 0]))
+        obs_list.append(("T", [("H", herm, [0, 2]), ("N", "PauliX", 1)]))
+        obs_list.append(("Ham", [0.3, -1.2, 0.5], [("H", herm, [1, 0]), ("N", "Hadamard", 2),
+                                                   ("T", [("N", "PauliZ", 0), ("N", "Hadamard", 1)])]))
+        # all-Z Hamiltonian (one fused read pass)
+        obs_list.append(("Ham", list(rng.normal(size=n - 1)),
+                         [("T", [("N", "PauliZ", i), ("N", "PauliZ", i + 1)]) for i in range(n - 1)]))
+    for obs in obs_list:
+        ko, kd = build_obs(o, obs), build_obs(d, obs)
+        eo, ed = o.expval(ko), d.expval(kd)
+        assert abs(eo - ed) < TOL * max(1.0, abs(eo)), (obs, eo, ed)
+        vo, vd = o.var(ko), d.var(kd)
+        assert abs(vo - vd) < 1e-11 * max(1.0, abs(vo)), (obs, vo, vd)
+
+
+@pytest.mark.parametrize("n,seed", [(1, 0), (4, 1), (9, 2), (12, 3), (15, 4), (19, 5)])
+def test_probs_partial(gpu, oracle_mod, n, seed):
+    o, d = _prepared(gpu, oracle_mod, n, seed)
+    rng = np.random.default_rng(seed)
+    assert np.max(np.abs(o.probs() - d.probs())) < TOL
+    for _ in range(6):
+        k = int(rng.integers(1, n + 1))
+        wires = [int(w) for w in rng.permutation(n)[:k]]
+        po, pd = o.probs(wires), d.probs(wires)
+        assert np.max(np.abs(po - pd)) < TOL, wires
+    assert abs(d.probs().sum() - 1) < 1e-12
+
+
+@pytest.mark.parametrize("n,seed", [(2, 0), (5, 1), (8, 2), (11, 3), (14, 4)])
+def test_seeded_samples_bit_exact(gpu, oracle_mod, n, seed):
+    ops = random_circuit(seed, n, 30)
+    o = oracle_mod.OracleDevice(n, seed=1234 + seed)
+    d = gpu.B200Device(n, seed=1234 + seed)
+    apply_ops(o, ops)
+    apply_ops(d, ops)
+    assert np.array_equal(o.sample(2000), d.sample(2000))
+    wires = [n - 1, 0] if n > 1 else [0]
+    assert np.array_equal(o.sample(500, wires), d.sample(500, wires))
+    eo, co = o.counts(1000, wires)
+    ed, cd = d.counts(1000, wires)
+    assert np.array_equal(eo, ed) and np.array_equal(co, cd)
+    assert o.gen_peek() == d.gen_peek()  # same position in the runtime generator's stream
+
+
+def test_samples_sparse_distributions(gpu, oracle_mod):
+    # distributions with many exact zeros / ties stress the prefix-sum restatement of the alias table
+    for n, prep in [(6, [("Hadamard", [], [0])]),
+                    (10, [("Hadamard", [], [0])] + [("CNOT", [], [0, w]) for w in range(1, 10)]),
+                    (12, [("Hadamard", [], [w]) for w in (1, 5, 7)] + [("RY", [0.3], [2])]),
+                    (9, [("RY", [2.0], [w]) for w in range(9)])]:
+        o = oracle_mod.OracleDevice(n, seed=7)
+        d = gpu.B200Device(n, seed=7)
+        apply_ops(o, prep)
+        apply_ops(d, prep)
+        assert np.array_equal(o.sample(3000), d.sample(3000)), (n, prep)
+
+
+@pytest.mark.parametrize("n,seed", [(3, 0), (8, 1), (12, 2), (16, 3)])
+def test_seeded_mid_circuit_measurements(gpu, oracle_mod, n, seed):
+    rng = np.random.default_rng(seed)
+    o = oracle_mod.OracleDevice(n, seed=37)
+    d = gpu.B200Device(n, seed=37)
+    outcomes_o, outcomes_d = [], []
+    for layer in range(6):
+        ops = [random_op(rng, n) for _ in range(10)]
+        apply_ops(o, ops)
+        apply_ops(d, ops)
+        w = int(rng.integers(n))
+        outcomes_o.append(o.measure(w))
+        outcomes_d.append(d.measure(w))
+    assert outcomes_o == outcomes_d
+    assert np.max(np.abs(o.state() - d.state())) < TOL
+    # postselection
+    w = 0
+    p = o.probs([w])
+    ps = int(p[1] > p[0])
+    assert o.measure(w, ps) == d.measure(w, ps) == bool(ps)
+    assert np.max(np.abs(o.state() - d.state())) < 1e-11
+    with pytest.raises(RuntimeError):
+        d.measure(w, 1 - ps)  # probability of the other branch is now exactly 0
+
+
+# ---- adjoint gradient ----------------------------------------------------------------------------
+DIFF_GATES = ["RX", "RY", "RZ", "PhaseShift", "IsingXX", "IsingYY", "IsingXY", "IsingZZ",
+              "ControlledPhaseShift", "CRX", "CRY", "CRZ", "SingleExcitation", "DoubleExcitation",
+              "MultiRZ", "PauliRot", "GlobalPhase", "PSWAP"]
+
+
+@pytest.mark.parametrize("n,seed", [(4, 0), (5, 1), (8, 2), (12, 3), (14, 4)])
+def test_adjoint_gradient(gpu, oracle_mod, n, seed):
+    rng = np.random.default_rng(seed)
+    ops = []
+    for _ in range(30):
+        if rng.random() < 0.7:
+            ops.append(random_op(rng, n, names=[DIFF_GATES[rng.integers(len(DIFF_GATES))]]))
+        else:
+            ops.append(random_op(rng, n, names=["Hadamard", "CNOT", "S", "QubitUnitary", "Toffoli", "SWAP"]))
+    obs_list = [("N", "PauliZ", 0), ("T", [("N", "PauliX", 1), ("N", "PauliY", 3)]),
+                ("Ham", [0.3, -0.8], [("N", "PauliZ", 2), ("H", [[1, 2], [2, -1]], [n - 1])])]
+    devs = [oracle_mod.OracleDevice(n), gpu.B200Device(n)]
+    jacs = []
+    for dev in devs:
+        dev.set_state(random_state(99, n), list(range(n)))
+        dev.start_tape()
+        apply_ops(dev, ops)
+        vals = [dev.expval(build_obs(dev, ob)) for ob in obs_list]
+        dev.stop_tape()
+        jacs.append((np.array(vals), dev.gradient()))
+    assert np.max(np.abs(jacs[0][0] - jacs[1][0])) < TOL
+    assert jacs[0][1].shape == jacs[1][1].shape
+    assert np.max(np.abs(jacs[0][1] - jacs[1][1])) < TOL * 10
+    P = jacs[0][1].shape[1]
+    if P >= 3:
+        sub = [0, P // 2, P - 1]
+        assert np.max(np.abs(devs[1].gradient(sub) - jacs[0][1][:, sub])) < TOL * 10
+
+
+def test_gradient_rejects_var_and_multiparam(gpu):
+    d = gpu.B200Device(2)
+    d.start_tape()
+    d.named_op("RX", [0.3], [0])
+    d.var(d.obs_named("PauliZ", 0))
+    d.stop_tape()
+    with pytest.raises(RuntimeError):
+        d.gradient()
+    d = gpu.B200Device(2)
+    d.start_tape()
+    d.named_op("Rot", [0.3, 0.1, 0.2], [0])
+    d.expval(d.obs_named("PauliZ", 0))
+    d.stop_tape()
+    with pytest.raises(RuntimeError):
+        d.gradient()
+
+
+# ---- error behaviour + lifecycle -------------------------------------------------------------------
+def test_errors_and_reuse(gpu):
+    d = gpu.B200Device(3)
+    with pytest.raises(RuntimeError):
+        d.named_op("NotAGate", [], [0])
+    with pytest.raises(RuntimeError):
+        d.named_op("RX", [], [0])
+    with pytest.raises(RuntimeError):
+        d.named_op("CNOT", [], [0, 0])
+    with pytest.raises(RuntimeError):
+        d.named_op("PauliX", [], [3])
+    with pytest.raises(RuntimeError):
+        d.expval(17)
+    d.named_op("PauliX", [], [1])
+    d.release_qubits()
+    d.allocate_qubits(2)  # pooled-device reuse (ExecutionContext.hpp:355-361): clean |00>
+    assert np.array_equal(d.state(), [1, 0, 0, 0])
+    d.allocate_qubit()
+    d.named_op("PauliX", [], [2])
+    assert np.argmax(np.abs(d.state())) == 1 and d.num_qubits() == 3
+
+
+# ---- size-independent properties at a size the oracle does not reach in seconds --------------------
+def test_large_roundtrip_properties(gpu):
+    n = 26
+    d = gpu.B200Device(n)
+    ops = [("Hadamard", [], [w]) for w in range(n)] + random_circuit(5, n, 120)
+    apply_ops(d, ops)
+    inv = []
+    for op in reversed(ops):
+        kw = dict(op[3]) if len(op) > 3 else {}
+        kw["inverse"] = not kw.get("inverse", False)
+        inv.append((op[0], op[1], op[2], kw))
+    p = d.probs([0, 1, 2])
+    assert abs(p.sum() - 1) < 1e-12
+    apply_ops(d, inv)
+    # back to |0...0>: probability of the all-zero string is 1
+    assert abs(d.probs([n - 1])[0] - 1) < 1e-10
+    assert abs(d.expval(d.obs_named("PauliZ", 0)) - 1) < 1e-10
