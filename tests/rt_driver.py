@@ -179,7 +179,7 @@ class RuntimeDevice:
         elif name == "PCPhase":
             f(ps[0], C.c_int64(int(params[1])), mp, C.c_int64(len(qs)), *qs)
         elif name == "PauliRot":
-            f(pauli_word.encode(), ps[0], mp, C.c_bool(False), C.c_int64(len(qs)), *qs)
+            f(pauli_word.encode(), ps[0], mp, C.c_bool(True), C.c_int64(len(qs)), *qs)
         else:
             raise ValueError(name)
 
