@@ -36,7 +36,8 @@ SYMBOLS = [
 class Stats(C.Structure):
     _fields_ = [("gates_enqueued", C.c_int64), ("kernel_ops", C.c_int64),
                 ("tile_passes", C.c_int64), ("other_launches", C.c_int64),
-                ("gate_device_ms", C.c_double), ("algorithmic_bytes", C.c_double)]
+                ("gate_device_ms", C.c_double), ("algorithmic_bytes", C.c_double),
+                ("rounds", C.c_int64)]
 
 
 _lib = None

@@ -620,11 +620,16 @@ static int fit_rows(uint64_t req, int t)
     return c;
 }
 
+static inline bool is_pair1(const GateOp &g)
+{
+    return g.kind == GateOp::PAIR && g.a == 0 && g.b == g.xmask && __builtin_popcountll(g.xmask) == 1;
+}
+
 void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
 {
     const int t = (int)std::min<int64_t>(opt_.tile_bits, n_);
     const int cmin = std::min(opt_.min_row_bits, t);
-    const size_t LOOKAHEAD = 2048;
+    const size_t LOOKAHEAD = 4096;
     std::vector<char> done(ops.size(), 0);
     size_t first = 0, remaining = ops.size();
     std::vector<const GateOp *> pass;
@@ -632,13 +637,16 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
         uint64_t req = 0, blockedX = 0, blockedZ = 0;
         int c_cur = t;
         pass.clear();
-        for (size_t i = first; i < ops.size() && pass.size() < B200K_MAX_OPS && i - first < LOOKAHEAD;
-             i++) {
+        // a pass that starts with a DENSE op runs on the first-generation kernel (which knows
+        // DENSE); every other pass runs on the register-blocked kernel and defers DENSE ops
+        const bool dense_pass = ops[first].kind == GateOp::DENSE;
+        const size_t cap = dense_pass ? (size_t)B200K_MAX_OPS : (size_t)pass_op_cap_;
+        for (size_t i = first; i < ops.size() && pass.size() < cap && i - first < LOOKAHEAD; i++) {
             if (done[i]) continue;
             const GateOp &op = ops[i];
             const uint64_t xs = op.xmask, zs = op.zsupport();
             const bool commutes = !(xs & (blockedX | blockedZ)) && !(zs & blockedX);
-            if (commutes) {
+            if (commutes && (dense_pass || op.kind != GateOp::DENSE)) {
                 const uint64_t nreq = req | xs;
                 const int c = fit_rows(nreq, t);
                 B200_FAIL_IF(c < 0 && pass.empty(),
@@ -665,8 +673,221 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
         for (int p = c_cur; (int)high.size() < t - c_cur; p++)
             if (!((req >> p) & 1)) high.push_back(p);
         std::sort(high.begin(), high.end());
-        launch_pass(vec, pass, high, c_cur);
+        if (dense_pass) launch_pass(vec, pass, high, c_cur);
+        else launch_pass2(vec, pass, high, c_cur);
     }
+}
+
+// ---- second-generation pass: group the pass's ops into rounds ------------------------------------------
+// A register round holds three tile bits in each thread's registers; it takes every op that is
+// diagonal or a one-target PAIR on one of those bits.  Ops are taken greedily in order; an op that
+// does not fit is deferred to a later round and blocks the ops that do not commute with it.
+void Simulator::launch_pass2(double *vec, const std::vector<const GateOp *> &ops,
+                             const std::vector<int> &high, int c)
+{
+    const int t = c + (int)high.size();
+    B200_FAIL_IF((int)high.size() > B200K_MAX_HIGH, "too many scattered tile bits");
+    int loc[64];
+    for (int p = 0; p < 64; p++) loc[p] = p < c ? p : -1;
+    for (size_t h = 0; h < high.size(); h++) loc[high[h]] = c + (int)h;
+    auto split = [&](uint64_t mask, uint32_t &inside, uint64_t &outside) {
+        inside = 0;
+        outside = 0;
+        while (mask) {
+            const int p = __builtin_ctzll(mask);
+            mask &= mask - 1;
+            if (loc[p] >= 0) inside |= 1u << loc[p];
+            else outside |= 1ull << p;
+        }
+    };
+    auto inside_only = [&](uint64_t mask) -> uint32_t {
+        uint32_t in;
+        uint64_t outm;
+        split(mask, in, outm);
+        B200_FAIL_IF(outm != 0, "internal: target bit outside the tile");
+        return in;
+    };
+
+    std::vector<B200k2Round> rounds;
+    std::vector<B200k2Op> dops;
+    auto emit = [&]() {
+        if (rounds.empty()) return;
+        B200k2Header H;
+        std::memset(&H, 0, sizeof(H));
+        H.n_rounds = (int)rounds.size();
+        H.n_ops = (int)dops.size();
+        H.t = t;
+        H.c = c;
+        H.nhigh = (int)high.size();
+        for (size_t h = 0; h < high.size(); h++) H.high_pos[h] = (uint8_t)high[h];
+        H.rank_base = 0;
+        H.ntiles = 1ull << (n_ - t);
+        CUDA_CHECK(b200k_tile_program2(vec, (int)n_, &H, rounds.data(), dops.data(), stream_));
+        stats_.tile_passes++;
+        stats_.kernel_ops += (int64_t)dops.size();
+        stats_.rounds += (int64_t)rounds.size();
+        rounds.clear();
+        dops.clear();
+    };
+    auto base_op = [&](const GateOp &g, B200k2Op &o, uint32_t &ic, uint32_t &iv) {
+        std::memset(&o, 0, sizeof(o));
+        split(g.cmask, ic, o.co_mask);
+        split(g.cval, iv, o.co_val);
+    };
+
+    std::vector<const GateOp *> rem(ops.begin(), ops.end()), deferred, taken;
+    while (!rem.empty()) {
+        uint64_t blockedX = 0, blockedZ = 0;
+        uint32_t S = 0; // tile-local register bits of this round
+        bool smem_round = false;
+        deferred.clear();
+        taken.clear();
+        for (size_t i = 0; i < rem.size(); i++) {
+            const GateOp *g = rem[i];
+            const uint64_t xs = g->xmask, zs = g->zsupport();
+            bool fits = false;
+            if (!smem_round && !(xs & (blockedX | blockedZ)) && !(zs & blockedX)) {
+                const bool diag = g->kind == GateOp::PHASE || g->kind == GateOp::PARITY;
+                if (t >= 3 && diag) fits = true;
+                else if (t >= 3 && is_pair1(*g)) {
+                    const uint32_t b = inside_only(g->xmask);
+                    if ((S & b) || __builtin_popcount(S) < 3) {
+                        S |= b;
+                        fits = true;
+                    }
+                }
+                else if (taken.empty()) { // anything else: a shared-memory round of its own
+                    fits = true;
+                    smem_round = true;
+                }
+            }
+            if (fits) taken.push_back(g);
+            else {
+                deferred.push_back(g);
+                blockedX |= xs;
+                blockedZ |= zs;
+            }
+        }
+        if (dops.size() + taken.size() > (size_t)B200K2_LARGE_OPS || rounds.size() + 1 > (size_t)B200K2_LARGE_ROUNDS)
+            emit();
+        B200k2Round R;
+        std::memset(&R, 0, sizeof(R));
+        R.first = (uint16_t)dops.size();
+        R.count = (uint16_t)taken.size();
+        if (smem_round) {
+            R.kind = B200K2_ROUND_SMEM;
+            const GateOp &g = *taken[0];
+            B200k2Op o;
+            uint32_t ic, iv;
+            base_op(g, o, ic, iv);
+            o.tc_mask = ic;
+            o.tc_val = iv;
+            switch (g.kind) {
+            case GateOp::PAIR: {
+                o.kind = B200K2_PAIRG;
+                o.tmask = inside_only(g.xmask);
+                o.a = inside_only(g.a);
+                o.b = inside_only(g.b);
+                uint32_t m = o.tmask;
+                while (m) {
+                    B200_FAIL_IF(o.npos >= 4, "internal: PAIR on more than 4 bits");
+                    o.pos[o.npos++] = (uint32_t)__builtin_ctz(m);
+                    m &= m - 1;
+                }
+                for (int q = 0; q < 4; q++) {
+                    o.m[2 * q] = g.m[q].real();
+                    o.m[2 * q + 1] = g.m[q].imag();
+                }
+                break;
+            }
+            case GateOp::PAULIROT:
+                o.kind = B200K2_PAULIROT;
+                o.tmask = inside_only(g.xmask);
+                o.pos[0] = 31u - (uint32_t)__builtin_clz(o.tmask);
+                o.npos = 1;
+                split(g.zmask, o.tz_mask, o.zo_mask);
+                o.ny = (uint8_t)(g.ny & 3);
+                o.m[0] = g.m[0].real();
+                o.m[1] = g.m[0].imag();
+                break;
+            case GateOp::PHASE:
+                o.kind = B200K2_PHASE;
+                o.m[0] = g.m[0].real();
+                o.m[1] = g.m[0].imag();
+                break;
+            case GateOp::PARITY:
+                o.kind = B200K2_PARITY;
+                split(g.zmask, o.tz_mask, o.zo_mask);
+                o.m[0] = g.m[0].real(); o.m[1] = g.m[0].imag();
+                o.m[2] = g.m[1].real(); o.m[3] = g.m[1].imag();
+                break;
+            default: B200_FAIL("internal: DENSE op in a second-generation pass");
+            }
+            dops.push_back(o);
+        }
+        else {
+            R.kind = B200K2_ROUND_REG;
+            // pad the register bits to three with the highest free tile bits
+            for (int b = t - 1; b >= 0 && __builtin_popcount(S) < 3; b--)
+                if (!(S & (1u << b))) S |= 1u << b;
+            int rb[3], nrb = 0, ridx[32];
+            for (int b = 0; b < t; b++)
+                if (S & (1u << b)) {
+                    ridx[b] = nrb;
+                    rb[nrb++] = b;
+                }
+            R.rb0 = (uint8_t)rb[0];
+            R.rb1 = (uint8_t)rb[1];
+            R.rb2 = (uint8_t)rb[2];
+            auto regpart = [&](uint32_t m) -> uint8_t {
+                uint8_t r = 0;
+                for (int q = 0; q < 3; q++)
+                    if (m & (1u << rb[q])) r |= (uint8_t)(1u << q);
+                return r;
+            };
+            for (const GateOp *gp : taken) {
+                const GateOp &g = *gp;
+                B200k2Op o;
+                uint32_t ic, iv;
+                base_op(g, o, ic, iv);
+                o.rc_mask = regpart(ic);
+                o.rc_val = regpart(iv);
+                o.tc_mask = ic & ~S;
+                o.tc_val = iv & ~S;
+                if (g.kind == GateOp::PAIR) {
+                    o.kind = B200K2_PAIR1;
+                    o.j = (uint8_t)ridx[__builtin_ctz(inside_only(g.xmask))];
+                    bool real = true;
+                    for (int q = 0; q < 4; q++) {
+                        o.m[2 * q] = g.m[q].real();
+                        o.m[2 * q + 1] = g.m[q].imag();
+                        real = real && g.m[q].imag() == 0.0;
+                    }
+                    const bool swp = real && g.m[0].real() == 0.0 && g.m[3].real() == 0.0 &&
+                                     g.m[1].real() == 1.0 && g.m[2].real() == 1.0;
+                    o.mflag = swp ? B200K2_M_SWAP : (real ? B200K2_M_REAL : B200K2_M_GENERAL);
+                }
+                else if (g.kind == GateOp::PHASE) {
+                    o.kind = B200K2_PHASE;
+                    o.m[0] = g.m[0].real();
+                    o.m[1] = g.m[0].imag();
+                }
+                else {
+                    o.kind = B200K2_PARITY;
+                    uint32_t zi;
+                    split(g.zmask, zi, o.zo_mask);
+                    o.rz_mask = regpart(zi);
+                    o.tz_mask = zi & ~S;
+                    o.m[0] = g.m[0].real(); o.m[1] = g.m[0].imag();
+                    o.m[2] = g.m[1].real(); o.m[3] = g.m[1].imag();
+                }
+                dops.push_back(o);
+            }
+        }
+        rounds.push_back(R);
+        rem.swap(deferred);
+    }
+    emit();
 }
 
 const double *Simulator::upload_matrix(const CVec &m)

@@ -165,6 +165,9 @@ class Simulator {
     void run_ops(double *vec, std::vector<GateOp> &ops);
     void launch_pass(double *vec, const std::vector<const GateOp *> &ops,
                      const std::vector<int> &req_high, int c);
+    void launch_pass2(double *vec, const std::vector<const GateOp *> &ops,
+                      const std::vector<int> &req_high, int c);
+    int pass_op_cap_ = 160;
     const double *upload_matrix(const CVec &m);
 
     void flatten(int64_t key, std::vector<ObsTerm> &out) const;

@@ -117,6 +117,7 @@ typedef struct b200sv_stats {
     int64_t other_launches;   /* reductions, probs, collapse, sampler, copies */
     double gate_device_ms;    /* CUDA-event time of the tile passes since the last reset */
     double algorithmic_bytes; /* sum over gates of 2*16*2^(n-c) */
+    int64_t rounds;           /* shared-memory round trips inside the tile passes */
 } b200sv_stats;
 int b200sv_get_stats(b200sv_device *d, b200sv_stats *out);
 int b200sv_reset_stats(b200sv_device *d);

@@ -1,0 +1,15 @@
+import sys, os
+R = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, R); sys.path.insert(0, os.path.join(R, "tests"))
+from catalyst_b200 import capi, workloads
+from dsl import apply_ops
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 28
+kw = {}
+if len(sys.argv) > 2: kw["tile_bits"] = int(sys.argv[2])
+d = capi.B200Device(n, **kw)
+ops = workloads.random_layers(n, 10, 0)
+for rep in range(2):
+    d.set_basis_state([0]*n, list(range(n))); d.synchronize(); d.reset_stats(); d.set_timing(True)
+    apply_ops(d, ops); d.synchronize()
+    s = d.stats()
+    print("gates", s.gates_enqueued, "passes", s.tile_passes, "rounds", s.rounds, "ms %.2f" % s.gate_device_ms, flush=True)

@@ -11,7 +11,7 @@ for cfg in [dict(), dict(fuse=False), dict(tile_bits=12), dict(tile_bits=10)]:
         d.reset(n); d.synchronize(); d.reset_stats(); d.set_timing(True)
         t0 = time.time(); apply_ops(d, sub); d.synchronize(); t1 = time.time()
         s = d.stats()
-        print(cfg, name, "gates", s.gates_enqueued, "passes", s.tile_passes, "ops", s.kernel_ops, "dev_ms %.1f wall_ms %.1f" % (s.gate_device_ms, (t1-t0)*1e3),
+        print(cfg, name, "gates", s.gates_enqueued, "passes", s.tile_passes, "ops", s.kernel_ops, "rounds", s.rounds, "dev_ms %.1f wall_ms %.1f" % (s.gate_device_ms, (t1-t0)*1e3),
               "gates/s %.0f" % (s.gates_enqueued / (s.gate_device_ms*1e-3)), "alg GB/s %.0f" % (s.algorithmic_bytes/ (s.gate_device_ms*1e-3)/1e9),
               "pass GB/s %.0f" % (s.tile_passes * 32 * 2**n / (s.gate_device_ms*1e-3)/1e9), flush=True)
     t0=time.time(); p = d.expval(d.obs_named("PauliZ", 0)); print("expval", p, time.time()-t0)
