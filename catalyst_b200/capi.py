@@ -30,6 +30,7 @@ SYMBOLS = [
     "b200sv_stop_tape_recording", "b200sv_tape_num_params", "b200sv_tape_num_observables",
     "b200sv_gradient", "b200sv_get_stats", "b200sv_reset_stats", "b200sv_set_timing",
     "b200sv_flush", "b200sv_synchronize", "b200sv_device_pointer",
+    "b200sv_nccl_unique_id", "b200sv_world_size", "b200sv_rank", "b200sv_layout",
 ]
 
 
@@ -37,7 +38,7 @@ class Stats(C.Structure):
     _fields_ = [("gates_enqueued", C.c_int64), ("kernel_ops", C.c_int64),
                 ("tile_passes", C.c_int64), ("other_launches", C.c_int64),
                 ("gate_device_ms", C.c_double), ("algorithmic_bytes", C.c_double),
-                ("rounds", C.c_int64)]
+                ("rounds", C.c_int64), ("exchanges", C.c_int64), ("exchange_bytes", C.c_double)]
 
 
 _lib = None
@@ -59,12 +60,59 @@ def lib():
         L.b200sv_device_pointer.restype = C.c_void_p
         L.b200sv_device_pointer.argtypes = [C.c_void_p]
         L.b200sv_prng_peek.restype = C.c_uint32
+        L.b200sv_layout.restype = C.c_int64
+        L.b200sv_layout.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int64]
+        L.b200sv_world_size.argtypes = [C.c_void_p]
+        L.b200sv_rank.argtypes = [C.c_void_p]
         for name in ("b200sv_num_qubits", "b200sv_get_shots", "b200sv_observable",
                      "b200sv_tensor_observable", "b200sv_hamiltonian_observable",
                      "b200sv_tape_num_params", "b200sv_tape_num_observables"):
             getattr(L, name).restype = C.c_int64
         _lib = L
     return _lib
+
+
+def nccl_unique_id() -> str:
+    """256 hex digits of a fresh ncclUniqueId (rank 0 creates it, the host program distributes it)."""
+    L = lib()
+    buf = C.create_string_buffer(257)
+    if L.b200sv_nccl_unique_id(buf) != 0:
+        raise B200Error(L.b200sv_last_error().decode())
+    return buf.value.decode()
+
+
+def run_spmd(world: int, fn, group: str | None = None, **kwargs):
+    """Run ``fn(device, rank)`` on `world` ranks as threads of this process (comm 'local:<group>'):
+    the single-process form of the sharded device, also usable with all ranks on ONE GPU.
+    Returns the list of results in rank order; re-raises the first failure."""
+    import threading
+    import uuid
+    group = group or ("g" + uuid.uuid4().hex[:12])
+    out, err = [None] * world, [None] * world
+
+    def work(r):
+        d = None
+        try:
+            kw = dict(kwargs)
+            if world > 1:
+                kw.update(world_size=world, rank=r, comm=f"local:{group}")
+            d = B200Device(**kw)
+            out[r] = fn(d, r)
+        except BaseException as e:  # noqa: BLE001
+            err[r] = e
+        finally:
+            if d is not None:
+                d.close()
+
+    th = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    for e in err:
+        if e is not None:
+            raise e
+    return out
 
 
 def _i64(a):
@@ -300,6 +348,17 @@ class B200Device:
 
     def synchronize(self):
         self._chk(self.L.b200sv_synchronize(self.h))
+
+    def world_size(self) -> int:
+        return int(self.L.b200sv_world_size(self.h))
+
+    def rank(self) -> int:
+        return int(self.L.b200sv_rank(self.h))
+
+    def layout(self):
+        buf = (C.c_int32 * 64)()
+        k = int(self.L.b200sv_layout(self.h, buf, C.c_int64(64)))
+        return [int(buf[i]) for i in range(k)]
 
     def device_pointer(self) -> int:
         return int(self.L.b200sv_device_pointer(self.h) or 0)

@@ -5,6 +5,7 @@
 // the reference pins in-tree are cited where they are used.  The arithmetic runs only on the GPU:
 // there is no CPU code path for any amplitude.
 #include "simulator.hpp"
+#include "comm.hpp"
 
 #include <cuda_runtime.h>
 
@@ -86,9 +87,18 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "min_row_bits") o.min_row_bits = (int)as_int(o.min_row_bits);
         else if (k == "fuse") o.fuse = as_int(1) != 0;
         else if (k == "device") o.device = (int)as_int(-1);
+        else if (k == "world_size") o.world = (int)as_int(1);
+        else if (k == "rank") o.rank = (int)as_int(0);
+        else if (k == "stage_mib") o.stage_mib = as_int(o.stage_mib);
+        else if (k == "comm") o.comm = v;
     }
+    B200_FAIL_IF(o.world < 1 || (o.world & (o.world - 1)) || o.world > 64, "world_size must be a power of two (<= 64)");
+    B200_FAIL_IF(o.rank < 0 || o.rank >= o.world, "rank out of range");
+    B200_FAIL_IF(o.world > 1 && o.comm.empty(), "world_size > 1 needs a 'comm' kwarg (nccl:<id> or local:<group>)");
+    B200_FAIL_IF(o.stage_mib < 1, "stage_mib out of range");
     B200_FAIL_IF(o.tile_bits < 1 || o.tile_bits > B200K_MAX_TILE_BITS, "tile_bits out of range");
-    B200_FAIL_IF(o.min_row_bits < 0 || o.min_row_bits > o.tile_bits, "min_row_bits out of range");
+    B200_FAIL_IF(o.min_row_bits < 0, "min_row_bits out of range");
+    o.min_row_bits = std::min(o.min_row_bits, o.tile_bits);
     return o;
 }
 
@@ -122,6 +132,15 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
     CUDA_CHECK(cudaMallocHost((void **)&pinned_, pinned_doubles_ * sizeof(double)));
     scratch_ = std::make_unique<DeviceBuffer>((size_t)b200k_reduce_scratch_doubles() * sizeof(double));
     results_ = std::make_unique<DeviceBuffer>(4096 * sizeof(double));
+    while ((1 << g_) < opt_.world) g_++;
+    if (opt_.world > 1) {
+        try {
+            comm_ = make_comm(opt_.comm, opt_.world, opt_.rank, cuda_device_, stream_);
+        }
+        catch (const std::exception &e) {
+            B200_FAIL(std::string("b200sv: cannot join the rank group: ") + e.what());
+        }
+    }
 }
 
 Simulator::~Simulator()
@@ -131,6 +150,8 @@ Simulator::~Simulator()
     psi_.reset();
     tmp_.reset();
     acc_.reset();
+    stage_.reset();
+    comm_.reset();
     scratch_.reset();
     results_.reset();
     probs_buf_.reset();
@@ -155,17 +176,24 @@ void Simulator::allocate(int64_t n)
     CUDA_CHECK(cudaSetDevice(cuda_device_));
     B200_FAIL_IF(n < 0 || n > 40, "Invalid number of qubits");
     if (n_ > 0 || psi_) release();
+    B200_FAIL_IF(sharded() && n < 2 * g_,
+                 "AllocateQubits: a register sharded over " + std::to_string(opt_.world) +
+                     " ranks needs at least " + std::to_string(2 * g_) + " qubits");
     n_ = n;
-    const size_t bytes = sizeof(cplx) << n;
+    nl_ = n - g_;
+    rank_base_ = (uint64_t)opt_.rank << nl_;
+    pos_.resize((size_t)n);
+    for (int q = 0; q < (int)n; q++) pos_[q] = q;
+    const size_t bytes = sizeof(cplx) << nl_;
     try {
         psi_ = std::make_unique<DeviceBuffer>(bytes);
     }
     catch (const Error &e) {
-        n_ = 0;
+        n_ = nl_ = 0;
         throw Error(std::string("AllocateQubits: cannot allocate the state vector in HBM: ") +
                     e.what());
     }
-    CUDA_CHECK(b200k_set_basis(psi_->d(), (int)n_, 0, stream_));
+    CUDA_CHECK(b200k_set_basis(psi_->d(), (int)nl_, opt_.rank == 0 ? 0 : -1, stream_));
     note_launch();
 }
 
@@ -175,6 +203,7 @@ void Simulator::allocate_one()
         allocate(1);
         return;
     }
+    B200_FAIL_IF(sharded(), "AllocateQubit: dynamic allocation is not supported on a sharded register");
     flush();
     auto nb = std::make_unique<DeviceBuffer>(sizeof(cplx) << (n_ + 1));
     CUDA_CHECK(b200k_append_qubit(nb->d(), psi_->d(), (int)n_, stream_));
@@ -184,6 +213,8 @@ void Simulator::allocate_one()
     tmp_.reset();
     acc_.reset();
     n_ += 1;
+    nl_ = n_;
+    pos_.push_back((int)n_ - 1);
 }
 
 void Simulator::release()
@@ -194,7 +225,9 @@ void Simulator::release()
     tmp_.reset();
     acc_.reset();
     probs_buf_.reset();
-    n_ = 0;
+    n_ = nl_ = 0;
+    rank_base_ = 0;
+    pos_.clear();
     obs_.clear();
     tape_.clear();
     tape_obs_.clear();
@@ -565,7 +598,7 @@ void Simulator::named_op(const std::string &name, const std::vector<double> &par
     if (name != "Identity") {
         stats_.gates_enqueued++;
         if (name != "GlobalPhase" || !cw.empty())
-            stats_.algorithmic_bytes += 32.0 * std::ldexp(1.0, (int)(n_ - (int64_t)cw.size()));
+            stats_.algorithmic_bytes += 32.0 * std::ldexp(1.0, (int)(nl_ - (int64_t)cw.size()));
     }
     enqueue(std::move(ops));
     if (recording_) // reference tape model: runtime/lib/backend/common/CacheManager.hpp:89-103
@@ -579,7 +612,7 @@ void Simulator::matrix_op(const CVec &matrix, const std::vector<int64_t> &wires,
     std::vector<GateOp> ops;
     canonicalize_matrix(ops, matrix, wires, inverse, cw, cv);
     stats_.gates_enqueued++;
-    stats_.algorithmic_bytes += 32.0 * std::ldexp(1.0, (int)(n_ - (int64_t)cw.size()));
+    stats_.algorithmic_bytes += 32.0 * std::ldexp(1.0, (int)(nl_ - (int64_t)cw.size()));
     enqueue(std::move(ops));
     if (recording_) tape_.push_back({"QubitUnitary", {}, wires, inverse, matrix, cw, cv, ""});
 }
@@ -591,7 +624,7 @@ void Simulator::flush()
     std::vector<GateOp> ops;
     ops.swap(queue_);
     if (timing_) CUDA_CHECK(cudaEventRecord((cudaEvent_t)ev0_, (cudaStream_t)stream_));
-    run_ops(psi_->d(), ops);
+    execute({psi_->d()}, pos_, ops);
     if (timing_) {
         CUDA_CHECK(cudaEventRecord((cudaEvent_t)ev1_, (cudaStream_t)stream_));
         CUDA_CHECK(cudaEventSynchronize((cudaEvent_t)ev1_));
@@ -627,7 +660,7 @@ static inline bool is_pair1(const GateOp &g)
 
 void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
 {
-    const int t = (int)std::min<int64_t>(opt_.tile_bits, n_);
+    const int t = (int)std::min<int64_t>(opt_.tile_bits, nl_);
     const int cmin = std::min(opt_.min_row_bits, t);
     const size_t LOOKAHEAD = 4096;
     std::vector<char> done(ops.size(), 0);
@@ -678,6 +711,223 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
     }
 }
 
+// ---- sharded execution ----------------------------------------------------------------
+// Physical index = (rank << nl_) | local index.  `pos[q]` is the physical position of logical bit q.
+// Diagonal action and control wires on rank bits need no data movement (the kernels evaluate them
+// from rank_base); only a NON-diagonal target on a rank bit forces a global<->local qubit swap.
+uint64_t Simulator::to_phys(const std::vector<int> &pos, uint64_t m) const
+{
+    uint64_t r = 0;
+    while (m) {
+        const int q = __builtin_ctzll(m);
+        m &= m - 1;
+        r |= 1ull << pos[q];
+    }
+    return r;
+}
+
+GateOp Simulator::phys_op(const std::vector<int> &pos, const GateOp &g) const
+{
+    GateOp o = g;
+    o.xmask = to_phys(pos, g.xmask);
+    o.cmask = to_phys(pos, g.cmask);
+    o.cval = to_phys(pos, g.cval);
+    o.a = to_phys(pos, g.a);
+    o.b = to_phys(pos, g.b);
+    o.zmask = to_phys(pos, g.zmask);
+    for (auto &t : o.targets) t = pos[t];
+    return o;
+}
+
+void Simulator::execute(const std::vector<double *> &vecs, std::vector<int> &pos, std::vector<GateOp> &ops)
+{
+    if (!sharded()) { // identity layout: logical == physical
+        for (double *v : vecs) run_ops(v, ops);
+        return;
+    }
+    const uint64_t local_mask_all = nl_ >= 64 ? ~0ull : ((1ull << nl_) - 1ull);
+    const size_t LOOKAHEAD = 4096;
+    std::vector<char> done(ops.size(), 0);
+    size_t first = 0, remaining = ops.size();
+    std::vector<GateOp> seg;
+    while (remaining) {
+        // every op that can run under the current layout without overtaking an op it does not
+        // commute with (same rule as the tile planner: diagonal action commutes)
+        uint64_t blockedX = 0, blockedZ = 0;
+        seg.clear();
+        for (size_t i = first; i < ops.size() && i - first < LOOKAHEAD; i++) {
+            if (done[i]) continue;
+            const GateOp &op = ops[i];
+            const uint64_t xs = op.xmask, zs = op.zsupport();
+            const bool commutes = !(xs & (blockedX | blockedZ)) && !(zs & blockedX);
+            if (commutes && !(to_phys(pos, xs) & ~local_mask_all)) {
+                seg.push_back(phys_op(pos, op));
+                done[i] = 1;
+                remaining--;
+                continue;
+            }
+            blockedX |= xs;
+            blockedZ |= zs;
+        }
+        while (first < ops.size() && done[first]) first++;
+        if (!seg.empty())
+            for (double *v : vecs) run_ops(v, seg);
+        if (!remaining) break;
+        // ---- choose the swap: the first blocked op must become runnable -------------------------
+        const GateOp &head = ops[first];
+        B200_FAIL_IF(__builtin_popcountll(head.xmask) > nl_,
+                     "Operation acts non-diagonally on more qubits than one shard holds");
+        // next non-diagonal use of every logical qubit among the remaining ops
+        std::vector<size_t> next_use((size_t)n_, SIZE_MAX);
+        for (size_t i = first; i < ops.size() && i - first < LOOKAHEAD; i++) {
+            if (done[i]) continue;
+            uint64_t m = ops[i].xmask;
+            while (m) {
+                const int q = __builtin_ctzll(m);
+                m &= m - 1;
+                if (next_use[q] == SIZE_MAX) next_use[q] = i;
+            }
+        }
+        std::vector<int> inq, victims; // logical qubits: global ones to bring in, local candidates
+        for (int q = 0; q < (int)n_; q++) {
+            if (pos[q] >= nl_) {
+                if (next_use[q] != SIZE_MAX) inq.push_back(q);
+            }
+            else if (!((head.xmask >> q) & 1)) victims.push_back(q);
+        }
+        std::sort(inq.begin(), inq.end(), [&](int a, int b) { return next_use[a] < next_use[b]; });
+        std::sort(victims.begin(), victims.end(), [&](int a, int b) {
+            if (next_use[a] != next_use[b]) return next_use[a] > next_use[b]; // farthest use first
+            return pos[a] > pos[b];                                            // then high positions
+        });
+        std::vector<std::pair<int, int>> pairs;
+        size_t vi = 0;
+        for (int q : inq) {
+            if (vi >= victims.size()) break;
+            const int v = victims[vi];
+            const bool mandatory = (head.xmask >> q) & 1;
+            if (!mandatory && next_use[v] <= next_use[q]) continue; // evicting v would cost more
+            pairs.push_back({pos[q], pos[v]});
+            vi++;
+        }
+        B200_FAIL_IF(pairs.empty(), "internal: sharded planner found no swap to make progress");
+        swap_bits(vecs, pos, pairs);
+        B200_FAIL_IF(to_phys(pos, head.xmask) & ~local_mask_all,
+                     "internal: sharded planner could not localise an operation");
+    }
+}
+
+void Simulator::make_local(const std::vector<double *> &vecs, std::vector<int> &pos, uint64_t logical_mask)
+{
+    if (!sharded()) return;
+    std::vector<int> inq, victims;
+    for (int q = 0; q < (int)n_; q++) {
+        const bool wanted = (logical_mask >> q) & 1;
+        if (wanted && pos[q] >= nl_) inq.push_back(q);
+        if (!wanted && pos[q] < nl_) victims.push_back(q);
+    }
+    if (inq.empty()) return;
+    B200_FAIL_IF(inq.size() > victims.size(),
+                 "Operation acts non-diagonally on more qubits than one shard holds");
+    std::sort(victims.begin(), victims.end(), [&](int a, int b) { return pos[a] > pos[b]; });
+    std::vector<std::pair<int, int>> pairs;
+    for (size_t i = 0; i < inq.size(); i++) pairs.push_back({pos[inq[i]], pos[victims[i]]});
+    swap_bits(vecs, pos, pairs);
+}
+
+// Exchange m rank bits with m local bits: a personalised all-to-all inside groups of 2^m ranks.
+// Rank pattern a sends, to the rank with pattern b != a, its sub-block whose local bits spell b, and
+// receives that rank's sub-block (whose local bits spell a) into the same slots; chunked through a
+// bounded staging buffer (pack -> exchange -> unpack on one stream).
+void Simulator::swap_bits(const std::vector<double *> &vecs, std::vector<int> &pos,
+                          std::vector<std::pair<int, int>> pairs)
+{
+    const int m = (int)pairs.size();
+    if (m == 0) return;
+    B200_FAIL_IF(m > 8 || m > g_, "internal: too many bits in one swap");
+    std::sort(pairs.begin(), pairs.end(), [](auto &x, auto &y) { return x.second < y.second; });
+    uint8_t lpos[8];
+    int gsel[8];
+    for (int i = 0; i < m; i++) {
+        B200_FAIL_IF(pairs[i].first < nl_ || pairs[i].second >= nl_, "internal: malformed swap");
+        lpos[i] = (uint8_t)pairs[i].second;
+        gsel[i] = pairs[i].first - (int)nl_;
+    }
+    uint32_t mine = 0;
+    for (int i = 0; i < m; i++) mine |= (uint32_t)((opt_.rank >> gsel[i]) & 1) << i;
+    auto peer_of = [&](uint32_t b) {
+        int r = opt_.rank;
+        for (int i = 0; i < m; i++) r = (r & ~(1 << gsel[i])) | (int)((b >> i) & 1u) << gsel[i];
+        return r;
+    };
+    const uint32_t npat = 1u << m;
+    const uint64_t sub = 1ull << (nl_ - m); // amplitudes per sub-block
+    const uint64_t stage_amps = ((uint64_t)opt_.stage_mib << 20) / sizeof(cplx);
+    uint64_t chunk = stage_amps / (2ull * (npat - 1));
+    if (chunk > sub) chunk = sub;
+    B200_FAIL_IF(chunk == 0, "stage_mib too small for the qubit swap");
+    ensure_buffer(stage_, 2ull * (npat - 1) * chunk * sizeof(cplx));
+    cplx *stage = static_cast<cplx *>(stage_->p());
+    for (double *vec : vecs) {
+        for (uint64_t j0 = 0; j0 < sub; j0 += chunk) {
+            const uint64_t cnt = std::min(chunk, sub - j0);
+            std::vector<Xfer> sends, recvs;
+            uint32_t slot = 0;
+            for (uint32_t b = 0; b < npat; b++) {
+                if (b == mine) continue;
+                cplx *sbuf = stage + (uint64_t)(2 * slot) * chunk, *rbuf = stage + (uint64_t)(2 * slot + 1) * chunk;
+                CUDA_CHECK(b200k_pack_bits(reinterpret_cast<double *>(sbuf), vec, lpos, m, b, j0, cnt, stream_));
+                note_launch();
+                sends.push_back({peer_of(b), sbuf, cnt * sizeof(cplx)});
+                recvs.push_back({peer_of(b), rbuf, cnt * sizeof(cplx)});
+                slot++;
+            }
+            try {
+                comm_->exchange(sends, recvs, stream_);
+            }
+            catch (const std::exception &e) {
+                B200_FAIL(std::string("qubit swap failed: ") + e.what());
+            }
+            slot = 0;
+            for (uint32_t b = 0; b < npat; b++) {
+                if (b == mine) continue;
+                const cplx *rbuf = stage + (uint64_t)(2 * slot + 1) * chunk;
+                CUDA_CHECK(b200k_unpack_bits(vec, reinterpret_cast<const double *>(rbuf), lpos, m, b, j0, cnt, stream_));
+                note_launch();
+                slot++;
+            }
+            stats_.exchange_bytes += (double)(npat - 1) * (double)cnt * sizeof(cplx);
+        }
+    }
+    stats_.exchanges++;
+    // layout: the logical qubits at the exchanged positions trade places
+    for (int i = 0; i < m; i++) {
+        int qg = -1, ql = -1;
+        for (int q = 0; q < (int)n_; q++) {
+            if (pos[q] == pairs[i].first) qg = q;
+            if (pos[q] == pairs[i].second) ql = q;
+        }
+        std::swap(pos[qg], pos[ql]);
+    }
+}
+
+void Simulator::reduce_results(std::vector<double> &host)
+{
+    if (!sharded() || host.empty()) return;
+    std::vector<double> all(host.size() * (size_t)opt_.world);
+    try {
+        comm_->allgather_host(host.data(), all.data(), host.size());
+    }
+    catch (const std::exception &e) {
+        B200_FAIL(std::string("reduction across ranks failed: ") + e.what());
+    }
+    for (size_t i = 0; i < host.size(); i++) {
+        double s = 0.0;
+        for (int r = 0; r < opt_.world; r++) s += all[(size_t)r * host.size() + i];
+        host[i] = s;
+    }
+}
+
 // ---- second-generation pass: group the pass's ops into rounds ------------------------------------------
 // A register round holds three tile bits in each thread's registers; it takes every op that is
 // diagonal or a one-target PAIR on one of those bits.  Ops are taken greedily in order; an op that
@@ -720,9 +970,9 @@ void Simulator::launch_pass2(double *vec, const std::vector<const GateOp *> &ops
         H.c = c;
         H.nhigh = (int)high.size();
         for (size_t h = 0; h < high.size(); h++) H.high_pos[h] = (uint8_t)high[h];
-        H.rank_base = 0;
-        H.ntiles = 1ull << (n_ - t);
-        CUDA_CHECK(b200k_tile_program2(vec, (int)n_, &H, rounds.data(), dops.data(), stream_));
+        H.rank_base = rank_base_;
+        H.ntiles = 1ull << (nl_ - t);
+        CUDA_CHECK(b200k_tile_program2(vec, (int)nl_, &H, rounds.data(), dops.data(), stream_));
         stats_.tile_passes++;
         stats_.kernel_ops += (int64_t)dops.size();
         stats_.rounds += (int64_t)rounds.size();
@@ -918,7 +1168,7 @@ void Simulator::launch_pass(double *vec, const std::vector<const GateOp *> &ops,
     P.nhigh = (int)high.size();
     B200_FAIL_IF(P.nhigh > B200K_MAX_HIGH, "too many scattered tile bits");
     for (size_t h = 0; h < high.size(); h++) P.high_pos[h] = (uint8_t)high[h];
-    P.rank_base = 0;
+    P.rank_base = rank_base_;
     int loc[64];
     for (int p = 0; p < 64; p++) loc[p] = p < c ? p : -1;
     for (size_t h = 0; h < high.size(); h++) loc[high[h]] = c + (int)h;
@@ -986,7 +1236,7 @@ void Simulator::launch_pass(double *vec, const std::vector<const GateOp *> &ops,
             break;
         }
     }
-    CUDA_CHECK(b200k_tile_program(vec, (int)n_, &P, stream_));
+    CUDA_CHECK(b200k_tile_program(vec, (int)nl_, &P, stream_));
     stats_.tile_passes++;
     stats_.kernel_ops += (int64_t)ops.size();
 }
@@ -1004,7 +1254,9 @@ void Simulator::set_basis_state(const std::vector<int8_t> &bits, const std::vect
         B200_FAIL_IF(bits[j] != 0 && bits[j] != 1, "BasisState parameter must consist of 0 or 1 integers.");
         if (bits[j]) idx |= bit_of(wires[j]);
     }
-    CUDA_CHECK(b200k_set_basis(psi_->d(), (int)n_, (int64_t)idx, stream_));
+    for (int q = 0; q < (int)n_; q++) pos_[q] = q; // fresh register: identity layout
+    const int64_t local = (idx >> nl_) == (uint64_t)opt_.rank ? (int64_t)(idx & ((1ull << nl_) - 1ull)) : -1;
+    CUDA_CHECK(b200k_set_basis(psi_->d(), (int)nl_, local, stream_));
     note_launch();
 }
 
@@ -1015,20 +1267,44 @@ void Simulator::set_state(const CVec &st, const std::vector<int64_t> &wires)
     const size_t k = wires.size();
     B200_FAIL_IF(st.size() != (size_t(1) << k), "Invalid state size: must be 2^len(wires)");
     queue_.clear();
+    for (int q = 0; q < (int)n_; q++) pos_[q] = q; // the register is overwritten: identity layout
     bool natural = (int64_t)k == n_;
     for (size_t j = 0; j < k && natural; j++) natural = wires[j] == (int64_t)j;
-    if (natural) {
-        CUDA_CHECK(cudaMemcpyAsync(psi_->p(), st.data(), st.size() * sizeof(cplx),
+    if (natural) { // each rank takes its contiguous slice
+        CUDA_CHECK(cudaMemcpyAsync(psi_->p(), st.data() + ((size_t)opt_.rank << nl_), sizeof(cplx) << nl_,
                                    cudaMemcpyHostToDevice, (cudaStream_t)stream_));
         CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
         return;
     }
-    ensure_buffer(misc_, st.size() * sizeof(cplx));
-    CUDA_CHECK(cudaMemcpyAsync(misc_->p(), st.data(), st.size() * sizeof(cplx), cudaMemcpyHostToDevice,
+    // wires on rank bits select a slice of `st`; a rank bit outside `wires` must be 0
+    std::vector<uint8_t> tb;
+    std::vector<size_t> local_j; // positions (in `wires`) of the wires that live on local bits
+    bool empty_shard = false;
+    uint64_t covered = 0;
+    size_t fixed = 0;
+    for (size_t j = 0; j < k; j++) {
+        const int b = lbit(wires[j]);
+        covered |= 1ull << b;
+        if (b < nl_) {
+            tb.push_back((uint8_t)b);
+            local_j.push_back(j);
+        }
+        else if ((rank_base_ >> b) & 1) fixed |= size_t(1) << (k - 1 - j);
+    }
+    for (int b = (int)nl_; b < (int)n_; b++)
+        if (!((covered >> b) & 1) && ((rank_base_ >> b) & 1)) empty_shard = true;
+    const size_t kl = tb.size();
+    CVec part(size_t(1) << kl);
+    for (size_t r = 0; r < part.size(); r++) {
+        size_t src = fixed;
+        for (size_t i = 0; i < kl; i++)
+            if ((r >> (kl - 1 - i)) & 1) src |= size_t(1) << (k - 1 - local_j[i]);
+        part[r] = empty_shard ? cplx(0.0, 0.0) : st[src];
+    }
+    ensure_buffer(misc_, part.size() * sizeof(cplx));
+    CUDA_CHECK(cudaMemcpyAsync(misc_->p(), part.data(), part.size() * sizeof(cplx), cudaMemcpyHostToDevice,
                                (cudaStream_t)stream_));
-    std::vector<uint8_t> tb(k);
-    for (size_t j = 0; j < k; j++) tb[j] = (uint8_t)lbit(wires[j]);
-    CUDA_CHECK(b200k_scatter_state(psi_->d(), misc_->d(), (int)n_, tb.data(), (int)k, stream_));
+    CUDA_CHECK(b200k_scatter_state(psi_->d(), misc_->d(), (int)nl_, tb.data(), (int)kl, stream_));
     note_launch();
     CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
 }
@@ -1183,29 +1459,52 @@ void Simulator::read_results(int nslots, std::vector<double> &host)
     CUDA_CHECK(cudaMemcpyAsync(host.data(), results_->p(), host.size() * sizeof(double),
                                cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
     CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    reduce_results(host);
 }
 
 cplx Simulator::inner(const double *a, const double *b)
 {
-    CUDA_CHECK(b200k_bilinear_pauli(a, b, (int)n_, 0, 0, 0, 0, 0, 0, scratch_->d(), result_slot(0), stream_));
+    CUDA_CHECK(b200k_bilinear_pauli(a, b, (int)nl_, rank_base_, 0, 0, 0, 0, 0, scratch_->d(), result_slot(0), stream_));
     note_launch();
     std::vector<double> h;
     read_results(1, h);
     return {h[0], h[1]};
 }
 
-void Simulator::apply_observable(int64_t key, const double *vin, double *vout)
+uint64_t Simulator::observable_xmask(int64_t key) const
+{
+    std::vector<ObsTerm> terms;
+    flatten(key, terms);
+    uint64_t m = 0;
+    for (auto &t : terms) {
+        std::vector<PauliTerm> pts;
+        if (term_to_paulis(t, pts)) {
+            for (auto &p : pts) m |= p.xmask;
+            continue;
+        }
+        for (auto &f : t.factors) {
+            if (f.named_id == 0 || f.named_id == 3) continue; // Identity, PauliZ: diagonal
+            for (auto w : f.wires) m |= bit_of(w);
+        }
+    }
+    return m;
+}
+
+// vout = O vin; both vectors share the layout `pos`, under which every non-diagonal target of O
+// must already be local (callers run make_local(observable_xmask(key)) first).
+void Simulator::apply_observable(int64_t key, const double *vin, double *vout, const std::vector<int> &pos)
 {
     std::vector<ObsTerm> terms;
     flatten(key, terms);
     bool first = true;
-    const size_t bytes = sizeof(cplx) << n_;
+    const size_t bytes = sizeof(cplx) << nl_;
     for (auto &t : terms) {
         std::vector<PauliTerm> pts;
         if (term_to_paulis(t, pts)) {
             for (auto &p : pts) {
-                CUDA_CHECK(b200k_pauli_apply(vout, vin, (int)n_, 0, p.xmask, p.zmask, p.ny,
-                                             p.coef.real(), p.coef.imag(), first ? 0 : 1, stream_));
+                CUDA_CHECK(b200k_pauli_apply(vout, vin, (int)nl_, rank_base_, to_phys(pos, p.xmask),
+                                             to_phys(pos, p.zmask), p.ny, p.coef.real(), p.coef.imag(),
+                                             first ? 0 : 1, stream_));
                 note_launch();
                 first = false;
             }
@@ -1215,12 +1514,16 @@ void Simulator::apply_observable(int64_t key, const double *vin, double *vout)
         CUDA_CHECK(cudaMemcpyAsync(tmp_->p(), vin, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
         std::vector<GateOp> ops;
         for (auto &f : t.factors) factor_ops(f, ops);
-        if (!ops.empty()) run_ops(tmp_->d(), ops);
+        if (!ops.empty()) {
+            std::vector<int> lay = pos; // no swap can happen: targets are local
+            execute({tmp_->d()}, lay, ops);
+            B200_FAIL_IF(lay != pos, "internal: observable application changed the layout");
+        }
         if (first) {
-            CUDA_CHECK(b200k_pauli_apply(vout, tmp_->d(), (int)n_, 0, 0, 0, 0, t.coef, 0.0, 0, stream_));
+            CUDA_CHECK(b200k_pauli_apply(vout, tmp_->d(), (int)nl_, rank_base_, 0, 0, 0, t.coef, 0.0, 0, stream_));
         }
         else {
-            CUDA_CHECK(b200k_axpy(vout, tmp_->d(), t.coef, (int)n_, stream_));
+            CUDA_CHECK(b200k_axpy(vout, tmp_->d(), t.coef, (int)nl_, stream_));
         }
         note_launch();
         first = false;
@@ -1250,14 +1553,14 @@ double Simulator::expval(int64_t key)
     const int nslots = ndiag_slots + (int)offd.size() + (int)generic.size();
     ensure_buffer(results_, std::max<size_t>(4096, 2 * (size_t)nslots) * sizeof(double));
     int slot = 0;
-    // all-diagonal words: one read pass per batch
+    // all-diagonal words: one read pass per batch (rank bits enter through rank_base)
     if (!diag.empty()) {
         const size_t nt = diag.size();
         ensure_buffer(misc_, nt * 16);
         std::vector<uint64_t> zm(nt);
         std::vector<double> cf(nt);
         for (size_t i = 0; i < nt; i++) {
-            zm[i] = diag[i].zmask;
+            zm[i] = to_phys(pos_, diag[i].zmask);
             cf[i] = diag[i].coef.real();
         }
         uint64_t *dz = static_cast<uint64_t *>(misc_->p());
@@ -1266,26 +1569,39 @@ double Simulator::expval(int64_t key)
         CUDA_CHECK(cudaMemcpyAsync(dc, cf.data(), nt * 8, cudaMemcpyHostToDevice, (cudaStream_t)stream_));
         for (size_t o = 0; o < nt; o += BATCH) {
             const int cnt = (int)std::min<size_t>(BATCH, nt - o);
-            CUDA_CHECK(b200k_expval_diag_batch(psi_->d(), (int)n_, 0, dz + o, dc + o, cnt, scratch_->d(),
-                                               result_slot(slot++), stream_));
+            CUDA_CHECK(b200k_expval_diag_batch(psi_->d(), (int)nl_, rank_base_, dz + o, dc + o, cnt,
+                                               scratch_->d(), result_slot(slot++), stream_));
             note_launch();
         }
         CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_)); // zm/cf are stack-owned
     }
+    // the layout may change between terms (a word with X/Y on a rank bit pulls that qubit in), so
+    // masks are translated term by term
     for (auto &p : offd) {
-        CUDA_CHECK(b200k_bilinear_pauli(psi_->d(), psi_->d(), (int)n_, 0, p.xmask, p.zmask, p.ny, 0, 0,
-                                        scratch_->d(), result_slot(slot++), stream_));
+        make_local({psi_->d()}, pos_, p.xmask);
+        CUDA_CHECK(b200k_bilinear_pauli(psi_->d(), psi_->d(), (int)nl_, rank_base_, to_phys(pos_, p.xmask),
+                                        to_phys(pos_, p.zmask), p.ny, 0, 0, scratch_->d(),
+                                        result_slot(slot++), stream_));
         note_launch();
     }
-    const size_t bytes = sizeof(cplx) << n_;
+    const size_t bytes = sizeof(cplx) << nl_;
     for (auto *t : generic) {
+        uint64_t xm = 0;
+        for (auto &f : t->factors)
+            if (f.named_id != 0 && f.named_id != 3)
+                for (auto w : f.wires) xm |= bit_of(w);
+        make_local({psi_->d()}, pos_, xm);
         ensure_buffer(tmp_, bytes);
         CUDA_CHECK(cudaMemcpyAsync(tmp_->p(), psi_->p(), bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
         std::vector<GateOp> ops;
         for (auto &f : t->factors) factor_ops(f, ops);
-        if (!ops.empty()) run_ops(tmp_->d(), ops);
-        CUDA_CHECK(b200k_bilinear_pauli(psi_->d(), tmp_->d(), (int)n_, 0, 0, 0, 0, 0, 0, scratch_->d(),
-                                        result_slot(slot++), stream_));
+        if (!ops.empty()) {
+            std::vector<int> lay = pos_;
+            execute({tmp_->d()}, lay, ops);
+            B200_FAIL_IF(lay != pos_, "internal: observable application changed the layout");
+        }
+        CUDA_CHECK(b200k_bilinear_pauli(psi_->d(), tmp_->d(), (int)nl_, rank_base_, 0, 0, 0, 0, 0,
+                                        scratch_->d(), result_slot(slot++), stream_));
         note_launch();
     }
     std::vector<double> h;
@@ -1304,12 +1620,13 @@ double Simulator::var(int64_t key)
     B200_FAIL_IF(key < 0 || (size_t)key >= obs_.size(), "Invalid key for cached observables");
     if (recording_) tape_obs_.push_back({key, 2});
     flush();
-    const size_t bytes = sizeof(cplx) << n_;
+    const size_t bytes = sizeof(cplx) << nl_;
+    make_local({psi_->d()}, pos_, observable_xmask(key));
     ensure_buffer(acc_, bytes);
-    apply_observable(key, psi_->d(), acc_->d());
-    CUDA_CHECK(b200k_bilinear_pauli(psi_->d(), acc_->d(), (int)n_, 0, 0, 0, 0, 0, 0, scratch_->d(),
+    apply_observable(key, psi_->d(), acc_->d(), pos_);
+    CUDA_CHECK(b200k_bilinear_pauli(psi_->d(), acc_->d(), (int)nl_, rank_base_, 0, 0, 0, 0, 0, scratch_->d(),
                                     result_slot(0), stream_));
-    CUDA_CHECK(b200k_bilinear_pauli(acc_->d(), acc_->d(), (int)n_, 0, 0, 0, 0, 0, 0, scratch_->d(),
+    CUDA_CHECK(b200k_bilinear_pauli(acc_->d(), acc_->d(), (int)nl_, rank_base_, 0, 0, 0, 0, 0, scratch_->d(),
                                     result_slot(1), stream_));
     note_launch();
     note_launch();
@@ -1346,7 +1663,30 @@ void Simulator::state(double *out_ri, int64_t stride)
 {
     B200_FAIL_IF(!psi_, "No qubits allocated");
     flush();
-    d2h_strided(stream_, psi_->p(), sizeof(cplx), size_t(1) << n_, out_ri, stride);
+    if (!sharded()) {
+        d2h_strided(stream_, psi_->p(), sizeof(cplx), size_t(1) << n_, out_ri, stride);
+        return;
+    }
+    // SPMD contract: every rank returns the whole vector.  Shards are gathered through the host and
+    // the layout is undone there; meant for the register sizes a host can hold anyway.
+    const size_t nloc = size_t(1) << nl_;
+    std::vector<double> mine(2 * nloc), all(2 * nloc * (size_t)opt_.world);
+    CUDA_CHECK(cudaMemcpyAsync(mine.data(), psi_->p(), nloc * sizeof(cplx), cudaMemcpyDeviceToHost,
+                               (cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    try {
+        comm_->allgather_host(mine.data(), all.data(), mine.size());
+    }
+    catch (const std::exception &e) {
+        B200_FAIL(std::string("State: gather across ranks failed: ") + e.what());
+    }
+    const size_t N = size_t(1) << n_;
+    for (size_t phys = 0; phys < N; phys++) {
+        size_t logical = 0;
+        for (int q = 0; q < (int)n_; q++) logical |= ((phys >> pos_[q]) & 1) << q;
+        out_ri[2 * (int64_t)logical * stride] = all[2 * phys];
+        out_ri[2 * (int64_t)logical * stride + 1] = all[2 * phys + 1];
+    }
 }
 
 void Simulator::probs(const std::vector<int64_t> &wires_in, double *out, int64_t stride)
@@ -1361,19 +1701,80 @@ void Simulator::probs(const std::vector<int64_t> &wires_in, double *out, int64_t
     }
     const size_t k = wires_in.empty() ? (size_t)n_ : wires_in.size();
     ensure_buffer(probs_buf_, sizeof(double) << k);
-    if (all) {
-        CUDA_CHECK(b200k_probs_all(psi_->d(), probs_buf_->d(), (int)n_, stream_));
+    if (!sharded()) {
+        if (all) {
+            CUDA_CHECK(b200k_probs_all(psi_->d(), probs_buf_->d(), (int)n_, stream_));
+        }
+        else {
+            std::vector<uint8_t> tb(k);
+            for (size_t j = 0; j < k; j++) tb[j] = (uint8_t)lbit(wires_in[j]);
+            const size_t sp = (size_t)b200k_probs_splits((int)n_, (int)k);
+            ensure_buffer(misc_, (sizeof(double) << k) * sp);
+            CUDA_CHECK(b200k_probs_partial(psi_->d(), (int)n_, tb.data(), (int)k, misc_->d(),
+                                           probs_buf_->d(), stream_));
+        }
+        note_launch();
+        if (out) d2h_strided(stream_, probs_buf_->p(), sizeof(double), size_t(1) << k, out, stride);
+        return;
+    }
+    // sharded: marginal over the wires that sit on local bits (kernel), wires on rank bits select the
+    // output slots; partials are gathered and summed in rank order on every rank
+    std::vector<int64_t> wires = wires_in;
+    if (wires.empty())
+        for (int64_t w = 0; w < n_; w++) wires.push_back(w);
+    std::vector<uint8_t> tb;
+    std::vector<size_t> local_j;
+    for (size_t j = 0; j < k; j++) {
+        const int p = pos_[lbit(wires[j])];
+        if (p < nl_) {
+            tb.push_back((uint8_t)p);
+            local_j.push_back(j);
+        }
+    }
+    const size_t kl = tb.size(), nl_bins = size_t(1) << kl;
+    B200_FAIL_IF(((double)nl_bins * opt_.world) * 8.0 > 64.0 * 1073741824.0,
+                 "Probs: the requested marginal is too large to gather on every rank of a sharded register");
+    ensure_buffer(tmp_probs_, sizeof(double) << kl);
+    if (kl == 0) { // every requested wire is a rank bit: this shard's total mass
+        CUDA_CHECK(b200k_bilinear_pauli(psi_->d(), psi_->d(), (int)nl_, rank_base_, 0, 0, 0, 0, 0,
+                                        scratch_->d(), result_slot(0), stream_));
+        CUDA_CHECK(cudaMemcpyAsync(tmp_probs_->p(), result_slot(0), sizeof(double), cudaMemcpyDeviceToDevice,
+                                   (cudaStream_t)stream_));
     }
     else {
-        std::vector<uint8_t> tb(k);
-        for (size_t j = 0; j < k; j++) tb[j] = (uint8_t)lbit(wires_in[j]);
-        const size_t sp = (size_t)b200k_probs_splits((int)n_, (int)k);
-        ensure_buffer(misc_, (sizeof(double) << k) * sp);
-        CUDA_CHECK(b200k_probs_partial(psi_->d(), (int)n_, tb.data(), (int)k, misc_->d(),
-                                       probs_buf_->d(), stream_));
+        const size_t sp = (size_t)b200k_probs_splits((int)nl_, (int)kl);
+        ensure_buffer(misc_, (sizeof(double) << kl) * sp);
+        CUDA_CHECK(b200k_probs_partial(psi_->d(), (int)nl_, tb.data(), (int)kl, misc_->d(), tmp_probs_->d(), stream_));
     }
     note_launch();
-    if (out) d2h_strided(stream_, probs_buf_->p(), sizeof(double), size_t(1) << k, out, stride);
+    std::vector<double> mine(nl_bins), gathered(nl_bins * (size_t)opt_.world), full(size_t(1) << k, 0.0);
+    CUDA_CHECK(cudaMemcpyAsync(mine.data(), tmp_probs_->p(), nl_bins * sizeof(double), cudaMemcpyDeviceToHost,
+                               (cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    try {
+        comm_->allgather_host(mine.data(), gathered.data(), nl_bins);
+    }
+    catch (const std::exception &e) {
+        B200_FAIL(std::string("Probs: gather across ranks failed: ") + e.what());
+    }
+    for (int r = 0; r < opt_.world; r++) {
+        size_t fixed = 0;
+        for (size_t j = 0; j < k; j++) {
+            const int p = pos_[lbit(wires[j])];
+            if (p >= nl_ && ((r >> (p - nl_)) & 1)) fixed |= size_t(1) << (k - 1 - j);
+        }
+        for (size_t jl = 0; jl < nl_bins; jl++) {
+            size_t o = fixed;
+            for (size_t i = 0; i < kl; i++)
+                if ((jl >> (kl - 1 - i)) & 1) o |= size_t(1) << (k - 1 - local_j[i]);
+            full[o] += gathered[(size_t)r * nl_bins + jl];
+        }
+    }
+    CUDA_CHECK(cudaMemcpyAsync(probs_buf_->p(), full.data(), full.size() * sizeof(double), cudaMemcpyHostToDevice,
+                               (cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    if (out)
+        for (size_t i = 0; i < full.size(); i++) out[(int64_t)i * stride] = full[i];
 }
 
 // ---- Sample -------------------------------------------------------------------------------------------
@@ -1443,7 +1844,7 @@ bool Simulator::measure(int64_t wire, int postselect)
         res = draw > p[0];
     }
     const double scale = 1.0 / std::sqrt(p[res ? 1 : 0]);
-    CUDA_CHECK(b200k_collapse(psi_->d(), (int)n_, 0, lbit(wire), res ? 1 : 0, scale, stream_));
+    CUDA_CHECK(b200k_collapse(psi_->d(), (int)nl_, rank_base_, pos_[lbit(wire)], res ? 1 : 0, scale, stream_));
     note_launch();
     return res;
 }
@@ -1501,14 +1902,22 @@ std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
                                     "differentiation method only supports expectation return type");
     B200_FAIL_IF(!std::is_sorted(train.begin(), train.end()), "trainable parameters must be sorted");
     flush();
-    const size_t bytes = sizeof(cplx) << n_;
+    const size_t bytes = sizeof(cplx) << nl_;
     cudaStream_t st = (cudaStream_t)stream_;
+    // sharded: psi_ keeps its own layout pos_; lambda and the phi_k share the working layout `lay`
+    // (they are swapped together when an adjoint gate or a generator needs a rank-bit qubit)
+    uint64_t obs_x = 0;
+    for (size_t k = 0; k < K; k++) obs_x |= observable_xmask(tape_obs_[k].first);
+    make_local({psi_->d()}, pos_, obs_x);
+    std::vector<int> lay = pos_;
     DeviceBuffer lambda(bytes);
     std::vector<std::unique_ptr<DeviceBuffer>> phi;
     CUDA_CHECK(cudaMemcpyAsync(lambda.p(), psi_->p(), bytes, cudaMemcpyDeviceToDevice, st));
+    std::vector<double *> vecs{lambda.d()};
     for (size_t k = 0; k < K; k++) {
         phi.push_back(std::make_unique<DeviceBuffer>(bytes));
-        apply_observable(tape_obs_[k].first, psi_->d(), phi[k]->d());
+        apply_observable(tape_obs_[k].first, psi_->d(), phi[k]->d(), pos_);
+        vecs.push_back(phi[k]->d());
     }
     ensure_buffer(results_, std::max<size_t>(4096, 2 * K * T) * sizeof(double));
 
@@ -1558,8 +1967,7 @@ std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
     std::vector<GateOp> pending; // adjoint ops not yet applied to lambda / phi
     auto apply_pending = [&]() {
         if (pending.empty()) return;
-        run_ops(lambda.d(), pending);
-        for (size_t k = 0; k < K; k++) run_ops(phi[k]->d(), pending);
+        execute(vecs, lay, pending);
         pending.clear();
     };
 
@@ -1579,15 +1987,19 @@ std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
                     cmask |= bit_of(op.ctrl_wires[i]);
                     if (op.ctrl_values[i]) cval |= bit_of(op.ctrl_wires[i]);
                 }
+                make_local(vecs, lay, g.is_pair ? g.tmask : g.xmask);
                 for (size_t k = 0; k < K; k++) {
                     double *slot = result_slot((int)(k * T + (size_t)tp));
                     if (g.is_pair)
-                        CUDA_CHECK(b200k_bilinear_pair(phi[k]->d(), lambda.d(), (int)n_, 0, g.tmask, g.a,
-                                                       g.b, g.g, cmask, cval, scratch_->d(), slot, stream_));
+                        CUDA_CHECK(b200k_bilinear_pair(phi[k]->d(), lambda.d(), (int)nl_, rank_base_,
+                                                       to_phys(lay, g.tmask), to_phys(lay, g.a),
+                                                       to_phys(lay, g.b), g.g, to_phys(lay, cmask),
+                                                       to_phys(lay, cval), scratch_->d(), slot, stream_));
                     else
-                        CUDA_CHECK(b200k_bilinear_pauli(phi[k]->d(), lambda.d(), (int)n_, 0, g.xmask,
-                                                        g.zmask, g.ny, cmask, cval, scratch_->d(), slot,
-                                                        stream_));
+                        CUDA_CHECK(b200k_bilinear_pauli(phi[k]->d(), lambda.d(), (int)nl_, rank_base_,
+                                                        to_phys(lay, g.xmask), to_phys(lay, g.zmask), g.ny,
+                                                        to_phys(lay, cmask), to_phys(lay, cval),
+                                                        scratch_->d(), slot, stream_));
                     note_launch();
                     sig[k * T + (size_t)tp] = g.sigma;
                 }
@@ -1804,5 +2216,31 @@ int b200sv_set_timing(b200sv_device *d, int on) { B200_TRY(d->sim->set_timing(on
 int b200sv_flush(b200sv_device *d) { B200_TRY(d->sim->flush()) }
 int b200sv_synchronize(b200sv_device *d) { B200_TRY(d->sim->synchronize()) }
 void *b200sv_device_pointer(b200sv_device *d) { return d->sim->device_pointer(); }
+
+int b200sv_nccl_unique_id(char hex_out[257])
+{
+    unsigned char id[128];
+    std::string err;
+    if (b200::nccl_unique_id(id, err) != 0) {
+        g_err = err;
+        return 1;
+    }
+    static const char *H = "0123456789abcdef";
+    for (int i = 0; i < 128; i++) {
+        hex_out[2 * i] = H[id[i] >> 4];
+        hex_out[2 * i + 1] = H[id[i] & 15];
+    }
+    hex_out[256] = 0;
+    return 0;
+}
+int b200sv_world_size(b200sv_device *d) { return d->sim->world(); }
+int b200sv_rank(b200sv_device *d) { return d->sim->rank(); }
+int64_t b200sv_layout(b200sv_device *d, int32_t *layout, int64_t cap)
+{
+    const std::vector<int> l = d->sim->layout();
+    int64_t i = 0;
+    for (; i < (int64_t)l.size() && i < cap; i++) layout[i] = l[(size_t)i];
+    return i;
+}
 
 } // extern "C"

@@ -88,9 +88,15 @@ struct Options {
     int min_row_bits = 7;
     bool fuse = true;
     int device = -1; // -1: LOCAL_RANK or 0
+    // sharding: this object owns the amplitudes whose top log2(world) index bits
+    // equal `rank`; `comm` = "local:<group>" (threads of one process) or "nccl:<hex unique id>"
+    int world = 1, rank = 0;
+    std::string comm;
+    int64_t stage_mib = 1024; // staging memory of the global<->local qubit swap
 };
 
 class DeviceBuffer;
+class Comm;
 
 class Simulator {
   public:
@@ -147,6 +153,10 @@ class Simulator {
     void flush();
     void synchronize();
     void *device_pointer();
+    int world() const { return opt_.world; }
+    int rank() const { return opt_.rank; }
+    int64_t num_local_bits() const { return nl_; }
+    std::vector<int> layout() const { return pos_; } // logical bit -> physical index position
 
   private:
     // --- helpers -------------------------------------------------------------------------------
@@ -161,7 +171,19 @@ class Simulator {
                              const std::vector<int64_t> &wires, bool inverse,
                              const std::vector<int64_t> &cw, const std::vector<bool> &cv) const;
     void enqueue(std::vector<GateOp> &&ops);
-    // plan + launch a list of canonical ops on an arbitrary device vector of 2^n amplitudes
+    // sharded execution: `ops` are in LOGICAL bit space, `pos` maps logical bits to physical index
+    // positions (>= nl_ means a rank bit).  Runs every op on every vector of `vecs` (which share the
+    // layout), inserting global<->local qubit swaps where an op acts non-diagonally on a rank bit.
+    void execute(const std::vector<double *> &vecs, std::vector<int> &pos, std::vector<GateOp> &ops);
+    void make_local(const std::vector<double *> &vecs, std::vector<int> &pos, uint64_t logical_mask);
+    void swap_bits(const std::vector<double *> &vecs, std::vector<int> &pos,
+                   std::vector<std::pair<int, int>> pairs); // (global position, local position)
+    uint64_t to_phys(const std::vector<int> &pos, uint64_t logical_mask) const;
+    GateOp phys_op(const std::vector<int> &pos, const GateOp &g) const;
+    bool sharded() const { return opt_.world > 1; }
+    void reduce_results(std::vector<double> &host); // sum over ranks, fixed order
+    // plan + launch a list of canonical ops (PHYSICAL bit space, non-diagonal targets all local) on a
+    // device vector holding this rank's 2^nl_ amplitudes
     void run_ops(double *vec, std::vector<GateOp> &ops);
     void launch_pass(double *vec, const std::vector<const GateOp *> &ops,
                      const std::vector<int> &req_high, int c);
@@ -173,7 +195,8 @@ class Simulator {
     void flatten(int64_t key, std::vector<ObsTerm> &out) const;
     bool term_to_paulis(const ObsTerm &t, std::vector<PauliTerm> &out) const;
     // vec_out = O vec_in  (vec_out != vec_in); uses tmp_ for non-Pauli terms
-    void apply_observable(int64_t key, const double *vec_in, double *vec_out);
+    void apply_observable(int64_t key, const double *vec_in, double *vec_out, const std::vector<int> &pos);
+    uint64_t observable_xmask(int64_t key) const; // logical bits any term touches non-diagonally
     void factor_ops(const ObsFactor &f, std::vector<GateOp> &ops) const;
     cplx inner(const double *a, const double *b);
     void read_results(int nslots, std::vector<double> &host);
@@ -187,6 +210,12 @@ class Simulator {
 
     Options opt_;
     int64_t n_ = 0;
+    int64_t nl_ = 0;         // local index bits = n_ - g_
+    int g_ = 0;              // rank bits = log2(world)
+    uint64_t rank_base_ = 0; // rank << nl_
+    std::vector<int> pos_;   // layout of psi_: logical bit -> physical position
+    std::unique_ptr<Comm> comm_;
+    std::unique_ptr<DeviceBuffer> stage_, tmp_probs_;
     int cuda_device_ = 0;
     void *stream_ = nullptr;
     std::unique_ptr<DeviceBuffer> psi_, tmp_, acc_, scratch_, results_, probs_buf_, misc_;

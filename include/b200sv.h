@@ -36,7 +36,8 @@ const char *b200sv_version(void);
 
 /* <Name>Factory(kwargs) — QuantumDevice.hpp:30-33; kwargs is the Python str(dict) the frontend
  * bakes into quantum.device (runtime/lib/backend/common/Utils.hpp:107-156).  Recognised keys:
- * shots, tile_bits, min_row_bits, fuse (0/1), device (CUDA ordinal).  Unknown keys are ignored
+ * shots, tile_bits, min_row_bits, fuse (0/1), device (CUDA ordinal), world_size, rank, comm,
+ * stage_mib (see "sharding" below).  Unknown keys are ignored
  * like lightning's mcmc/num_burnin/kernel_name. Returns NULL on error. */
 b200sv_device *b200sv_create(const char *kwargs);
 void b200sv_destroy(b200sv_device *d);
@@ -118,6 +119,8 @@ typedef struct b200sv_stats {
     double gate_device_ms;    /* CUDA-event time of the tile passes since the last reset */
     double algorithmic_bytes; /* sum over gates of 2*16*2^(n-c) */
     int64_t rounds;           /* shared-memory round trips inside the tile passes */
+    int64_t exchanges;        /* global<->local qubit swaps (each = one personalised all-to-all) */
+    double exchange_bytes;    /* bytes this rank sent over NVLink in those swaps */
 } b200sv_stats;
 int b200sv_get_stats(b200sv_device *d, b200sv_stats *out);
 int b200sv_reset_stats(b200sv_device *d);
@@ -126,6 +129,22 @@ int b200sv_flush(b200sv_device *d);              /* launch everything queued (no
 int b200sv_synchronize(b200sv_device *d);        /* flush + wait */
 /* device pointer of the local shard (for benchmarks / zero-copy consumers) */
 void *b200sv_device_pointer(b200sv_device *d);
+
+/* ---- sharding across GPUs ------------------------------------------------------
+ * The register is sharded by its high-order index bits: rank r of `world_size` (a power of two)
+ * owns the amplitudes whose top log2(world_size) bits equal r.  Every rank runs the SAME call
+ * sequence (SPMD: one process per GPU under torchrun/mpirun, or one thread per rank); scalar and
+ * array results are identical on every rank.  Configured through the factory kwargs:
+ *   'world_size': G, 'rank': r, 'comm': 'nccl:<256 hex digits>' | 'local:<group name>'
+ * where the hex digits are an ncclUniqueId created once by b200sv_nccl_unique_id() and distributed
+ * by the host program (any out-of-band channel: torch.distributed, MPI, a file).  'local:' joins the
+ * ranks of one process by name (threads; several ranks may share a GPU — used by the tests). */
+int b200sv_nccl_unique_id(char hex_out[257]);
+int b200sv_world_size(b200sv_device *d);
+int b200sv_rank(b200sv_device *d);
+/* layout[q] = physical index position of logical bit q (bit n-1-w for wire w); positions >=
+ * n - log2(world_size) are rank bits.  Returns the number of entries written (<= cap). */
+int64_t b200sv_layout(b200sv_device *d, int32_t *layout, int64_t cap);
 
 #ifdef __cplusplus
 }

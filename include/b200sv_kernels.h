@@ -172,6 +172,15 @@ int b200k_scatter_state(double *psi, const double *vals, int n_local, const uint
 /* new[(i << 1)] = old[i], new[(i << 1) | 1] = 0  — append one qubit in |0> as the new bit 0 */
 int b200k_append_qubit(double *dst, const double *src, int n_local_old, void *stream);
 
+/* ---- global<->local qubit swap (shard.cu) --------------------------------------------------------
+ * staged[j] = state[expand(j0 + j)], j in [0, count): expand() inserts, at the m ascending local bit
+ * positions lpos[], the bits of `val` (bit i of val -> position lpos[i]).  unpack is the inverse
+ * scatter into the same slots.  m <= 8. */
+int b200k_pack_bits(double *staged, const double *state, const uint8_t *lpos, int m, uint32_t val,
+                    uint64_t j0, uint64_t count, void *stream);
+int b200k_unpack_bits(double *state, const double *staged, const uint8_t *lpos, int m, uint32_t val,
+                      uint64_t j0, uint64_t count, void *stream);
+
 /* ---- alias-method sampler on device (reference algorithm: Walker alias table with LIFO pairing,
  * SURVEY.md Appendix A.4; restated as prefix sums so that no sequential pass over 2^n is needed) */
 int64_t b200k_sampler_scratch_doubles(int64_t nbins);

@@ -1,0 +1,197 @@
+"""Parity of the SHARDED device against the CPU oracle, on ONE GPU: the ranks run as
+threads of this process joined by the 'local:' rank group ("virtual shards"), which exercises the
+same planner, pack/exchange/unpack swap path, rank-bit predicates and cross-rank reductions as the
+NCCL build — only the transport differs.  Every rank must return the same, oracle-equal results."""
+import numpy as np
+import pytest
+
+from dsl import apply_ops, build_obs, random_circuit, random_pauli_obs, random_state
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-12
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    from catalyst_b200 import capi
+    return capi
+
+
+def _oracle(oracle_mod, n, ops, seed=None):
+    o = oracle_mod.OracleDevice(n, seed=seed)
+    apply_ops(o, ops)
+    return o
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("n,depth,seed", [(7, 40, 1), (8, 80, 2), (10, 120, 3), (12, 150, 4)])
+def test_state_random_circuits(gpu, oracle_mod, world, n, depth, seed):
+    ops = random_circuit(seed * 100 + world, n, depth)
+    want = _oracle(oracle_mod, n, ops).state()
+
+    def prog(d, r):
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        return d.state(), d.stats().exchanges
+
+    res = gpu.run_spmd(world, prog)
+    for st, _ in res:
+        assert np.max(np.abs(st - want)) < TOL
+    assert res[0][1] > 0, "no global<->local swap was exercised"
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_swap_chunking_small_stage(gpu, oracle_mod, world):
+    """stage_mib=1 at n=18 forces many chunks per swap."""
+    n = 18
+    ops = random_circuit(77, n, 60, names=["RX", "RY", "Hadamard", "CNOT", "CZ", "RZ", "SWAP"])
+    want = _oracle(oracle_mod, n, ops).state()
+
+    def prog(d, r):
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        return d.state()
+
+    for st in gpu.run_spmd(world, prog, stage_mib=1):
+        assert np.max(np.abs(st - want)) < TOL
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_expval_var_probs(gpu, oracle_mod, world):
+    n = 9
+    rng = np.random.default_rng(5)
+    ops = random_circuit(11, n, 60)
+    obs_list = [random_pauli_obs(rng, n) for _ in range(6)]
+    obs_list.append(("Ham", [0.3, -1.2, 0.7], [obs_list[0], obs_list[1], ("N", "Hadamard", 0)]))
+    herm = rng.normal(size=(4, 4)) + 1j * rng.normal(size=(4, 4))
+    herm = herm + herm.conj().T
+    obs_list.append(("H", herm, [0, n - 1]))
+    obs_list.append(("T", [("H", herm, [1, 0]), ("N", "PauliZ", 5)]))
+    o = _oracle(oracle_mod, n, ops)
+    want_e = [o.expval(build_obs(o, ob)) for ob in obs_list]
+    want_v = [o.var(build_obs(o, ob)) for ob in obs_list]
+    wire_sets = [[0], [n - 1], [0, 1, 2], [3, 0, 8], list(range(n)), [8, 7, 6, 5, 4, 3, 2, 1, 0]]
+    want_p = [o.probs(w) for w in wire_sets] + [o.probs()]
+
+    def prog(d, r):
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        e = [d.expval(build_obs(d, ob)) for ob in obs_list]
+        v = [d.var(build_obs(d, ob)) for ob in obs_list]
+        p = [d.probs(w) for w in wire_sets] + [d.probs()]
+        return e, v, p, d.state()
+
+    for e, v, p, st in gpu.run_spmd(world, prog, tile_bits=5):
+        assert np.max(np.abs(np.array(e) - want_e)) < TOL
+        assert np.max(np.abs(np.array(v) - want_v)) < 1e-11
+        for a, b in zip(p, want_p):
+            assert np.max(np.abs(a - b)) < TOL
+        assert np.max(np.abs(st - o.state())) < TOL  # swaps made by the measurements are consistent
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_state_prep(gpu, oracle_mod, world):
+    n = 7
+    full = random_state(3, n)
+    sub = random_state(4, 3)
+    ops = random_circuit(21, n, 30)
+
+    def prog(d, r):
+        out = []
+        d.allocate_qubits(n)
+        d.set_state(full, list(range(n)))
+        apply_ops(d, ops)
+        out.append(d.state())
+        d.set_basis_state([1, 0, 1], [0, 3, 6])
+        apply_ops(d, ops)
+        out.append(d.state())
+        d.set_state(sub, [6, 0, 2])
+        apply_ops(d, ops)
+        out.append(d.state())
+        return out
+
+    want = []
+    o = oracle_mod.OracleDevice(n)
+    o.set_state(full, list(range(n))); apply_ops(o, ops); want.append(o.state())
+    o.set_basis_state([1, 0, 1], [0, 3, 6]); apply_ops(o, ops); want.append(o.state())
+    o.set_state(sub, [6, 0, 2]); apply_ops(o, ops); want.append(o.state())
+    for got in gpu.run_spmd(world, prog, tile_bits=4):
+        for a, b in zip(got, want):
+            assert np.max(np.abs(a - b)) < TOL
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_measure_and_sample_bit_exact(gpu, oracle_mod, world):
+    n = 8
+    ops = random_circuit(31, n, 50)
+    o = _oracle(oracle_mod, n, ops, seed=37)
+    want_m = [o.measure(w) for w in (0, 5, 7)]
+    want_s = o.sample(500)
+    want_sp = o.sample(300, [6, 0])
+    want_c = o.counts(200, [1, 7, 0])
+    want_state = o.state()
+
+    def prog(d, r):
+        d.seed(37)
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        m = [d.measure(w) for w in (0, 5, 7)]
+        return m, d.sample(500), d.sample(300, [6, 0]), d.counts(200, [1, 7, 0]), d.state()
+
+    for m, s, sp, c, st in gpu.run_spmd(world, prog, tile_bits=5):
+        assert m == want_m
+        assert np.array_equal(s, want_s)
+        assert np.array_equal(sp, want_sp)
+        assert np.array_equal(c[0], want_c[0]) and np.array_equal(c[1], want_c[1])
+        assert np.max(np.abs(st - want_state)) < TOL
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_adjoint_gradient(gpu, oracle_mod, world):
+    n = 8
+    names = ["RX", "RY", "RZ", "PhaseShift", "IsingXX", "IsingYY", "IsingZZ", "IsingXY", "CRX", "CRY",
+             "CRZ", "ControlledPhaseShift", "SingleExcitation", "DoubleExcitation", "MultiRZ",
+             "CNOT", "Hadamard", "CZ", "SWAP", "Toffoli", "PSWAP"]
+    ops = random_circuit(41, n, 45, names=names, allow_ctrl=False)
+    rng = np.random.default_rng(9)
+    obs_list = [random_pauli_obs(rng, n), ("N", "PauliZ", 0),
+                ("Ham", [0.5, -0.25], [random_pauli_obs(rng, n), random_pauli_obs(rng, n)])]
+
+    def run(d):
+        d.start_tape()
+        apply_ops(d, ops)
+        e = [d.expval(build_obs(d, ob)) for ob in obs_list]
+        d.stop_tape()
+        return e, d.gradient()
+
+    o = oracle_mod.OracleDevice(n)
+    want_e, want_g = run(o)
+
+    def prog(d, r):
+        d.allocate_qubits(n)
+        e, g = run(d)
+        return e, g, d.state()
+
+    for e, g, st in gpu.run_spmd(world, prog, tile_bits=5):
+        assert np.max(np.abs(np.array(e) - want_e)) < TOL
+        assert np.max(np.abs(g - want_g)) < 1e-11
+        assert np.max(np.abs(st - o.state())) < TOL
+
+
+def test_sharded_errors(gpu):
+    with pytest.raises(gpu.B200Error):
+        gpu.B200Device(world_size=3, rank=0, comm="local:x")
+    with pytest.raises(gpu.B200Error):
+        gpu.B200Device(world_size=2, rank=0)  # no comm
+    with pytest.raises(gpu.B200Error):
+        gpu.B200Device(world_size=2, rank=2, comm="local:x")
+
+    def prog(d, r):
+        with pytest.raises(gpu.B200Error):
+            d.allocate_qubits(3)  # 8 ranks need >= 6 qubits
+        d.allocate_qubits(6)
+        with pytest.raises(gpu.B200Error):
+            d.allocate_qubit()
+        return True
+
+    assert all(gpu.run_spmd(8, prog))
