@@ -1,0 +1,76 @@
+"""The NCCL transport of the sharded device: one PROCESS per GPU (the torchrun model), ncclUniqueId
+handed over by the parent.  Needs >= 2 GPUs; on a single-GPU box these tests skip and the same
+logic is covered by tests/test_gpu_sharded.py (threads + 'local:' group)."""
+import multiprocessing as mp
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from dsl import apply_ops, build_obs, random_circuit, random_pauli_obs
+
+pytestmark = pytest.mark.gpu
+
+
+def _ngpus():
+    try:
+        import subprocess
+        out = subprocess.run(["nvidia-smi", "-L"], capture_output=True, text=True, timeout=30).stdout
+        return sum(1 for l in out.splitlines() if l.startswith("GPU "))
+    except Exception:
+        return 0
+
+
+def _worker(rank, world, uid, n, ops, obs_list, q):
+    try:
+        root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+        sys.path[:0] = [root, os.path.join(root, "tests")]
+        from catalyst_b200 import capi
+        d = capi.B200Device(world_size=world, rank=rank, comm="nccl:" + uid, device=rank, seed=37)
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        e = [d.expval(build_obs(d, ob)) for ob in obs_list]
+        p = d.probs([0, n - 1, 3])
+        m = d.measure(0)
+        smp = d.sample(200, [1, 2, n - 1])
+        st = d.state()
+        q.put((rank, e, p, m, smp, st, d.stats().exchanges, None))
+        d.close()
+    except BaseException as ex:  # noqa: BLE001
+        q.put((rank, None, None, None, None, None, 0, repr(ex)))
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_nccl_ranks_match_oracle(oracle_mod, world):
+    if _ngpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    from catalyst_b200 import capi
+    n = 14
+    ops = random_circuit(500 + world, n, 150)
+    rng = np.random.default_rng(3)
+    obs_list = [random_pauli_obs(rng, n) for _ in range(4)]
+    o = oracle_mod.OracleDevice(n, seed=37)
+    apply_ops(o, ops)
+    want_e = [o.expval(build_obs(o, ob)) for ob in obs_list]
+    want_p = o.probs([0, n - 1, 3])
+    want_m = o.measure(0)
+    want_s = o.sample(200, [1, 2, n - 1])
+    want_st = o.state()
+    uid = capi.nccl_unique_id()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, uid, n, ops, obs_list, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, e, p, m, smp, st, nx, err in res:
+        assert err is None, f"rank {rank}: {err}"
+        assert np.max(np.abs(np.array(e) - want_e)) < 1e-12
+        assert np.max(np.abs(p - want_p)) < 1e-12
+        assert m == want_m
+        assert np.array_equal(smp, want_s)
+        assert np.max(np.abs(st - want_st)) < 1e-12
+        assert nx > 0
