@@ -34,13 +34,16 @@ try:  # pragma: no cover - exercised only where PennyLane is installed
         name = "b200.statevector"
         config_filepath = CONFIG_FILEPATH
 
-        def __init__(self, wires=None, shots=None, tile_bits=None, fuse=True, cuda_device=None):
+        def __init__(self, wires=None, shots=None, tile_bits=None, fuse=True, cuda_device=None,
+                     world_size=1, rank=0, comm=None):
             super().__init__(wires=wires, shots=shots)
             self.device_kwargs = {"fuse": bool(fuse)}
             if tile_bits is not None:
                 self.device_kwargs["tile_bits"] = int(tile_bits)
             if cuda_device is not None:
                 self.device_kwargs["device"] = int(cuda_device)
+            if world_size > 1:  # SPMD sharding over GPUs: see include/b200sv.h, "sharding"
+                self.device_kwargs.update(world_size=int(world_size), rank=int(rank), comm=str(comm))
 
         @staticmethod
         def get_c_interface():
