@@ -171,6 +171,8 @@ class Plumbing:
 
     def __init__(self, world):
         self.dist = None
+        # NCCL's own banner / debug lines must not land on stdout next to the JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         if world > 1:
             import torch.distributed as dist
             dist.init_process_group("gloo")

@@ -91,6 +91,7 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "rank") o.rank = (int)as_int(0);
         else if (k == "stage_mib") o.stage_mib = as_int(o.stage_mib);
         else if (k == "comm") o.comm = v;
+        else if (k == "kernel_gen") o.kernel_gen = (int)as_int(o.kernel_gen);
     }
     B200_FAIL_IF(o.world < 1 || (o.world & (o.world - 1)) || o.world > 64, "world_size must be a power of two (<= 64)");
     B200_FAIL_IF(o.rank < 0 || o.rank >= o.world, "rank out of range");
@@ -707,7 +708,8 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
             if (!((req >> p) & 1)) high.push_back(p);
         std::sort(high.begin(), high.end());
         if (dense_pass) launch_pass(vec, pass, high, c_cur);
-        else launch_pass2(vec, pass, high, c_cur);
+        else if (opt_.kernel_gen == 2) launch_pass2(vec, pass, high, c_cur);
+        else launch_pass3(vec, pass, high, c_cur);
     }
 }
 
@@ -1133,6 +1135,288 @@ void Simulator::launch_pass2(double *vec, const std::vector<const GateOp *> &ops
                 }
                 dops.push_back(o);
             }
+        }
+        rounds.push_back(R);
+        rem.swap(deferred);
+    }
+    emit();
+}
+
+// ---- third-generation pass (tile3.cu): rounds with host-precomputed slot masks -------------------------
+// Same round formation as launch_pass2, plus: two-target PAIRs (01<->10, 00<->11) whose two bits are both
+// register bits run in registers; every op carries masks over the thread's 8 register slots.
+namespace {
+// kind of a PAIR op for the register rounds: 1 = one target (a = 0, b = bit), 2 = two targets
+// exchanging 01 <-> 10, 3 = two targets exchanging 00 <-> 11, 0 = none of these
+int reg_pair_kind(const GateOp &g)
+{
+    if (g.kind != GateOp::PAIR) return 0;
+    const int k = __builtin_popcountll(g.xmask);
+    if (k == 1 && g.a == 0 && g.b == g.xmask) return 1;
+    if (k == 2 && (g.a ^ g.b) == g.xmask) {
+        if (g.a != 0 && g.b != 0) return 2;
+        return 3;
+    }
+    return 0;
+}
+} // namespace
+
+void Simulator::launch_pass3(double *vec, const std::vector<const GateOp *> &ops,
+                             const std::vector<int> &high, int c)
+{
+    const int t = c + (int)high.size();
+    B200_FAIL_IF((int)high.size() > B200K_MAX_HIGH, "too many scattered tile bits");
+    int loc[64];
+    for (int p = 0; p < 64; p++) loc[p] = p < c ? p : -1;
+    for (size_t h = 0; h < high.size(); h++) loc[high[h]] = c + (int)h;
+    auto split = [&](uint64_t mask, uint32_t &inside, uint64_t &outside) {
+        inside = 0;
+        outside = 0;
+        while (mask) {
+            const int p = __builtin_ctzll(mask);
+            mask &= mask - 1;
+            if (loc[p] >= 0) inside |= 1u << loc[p];
+            else outside |= 1ull << p;
+        }
+    };
+    auto inside_only = [&](uint64_t mask) -> uint32_t {
+        uint32_t in;
+        uint64_t outm;
+        split(mask, in, outm);
+        B200_FAIL_IF(outm != 0, "internal: target bit outside the tile");
+        return in;
+    };
+
+    std::vector<B200k3Round> rounds;
+    std::vector<B200k3Op> dops;
+    auto emit = [&]() {
+        if (rounds.empty()) return;
+        B200k2Header H;
+        std::memset(&H, 0, sizeof(H));
+        H.n_rounds = (int)rounds.size();
+        H.n_ops = (int)dops.size();
+        H.t = t;
+        H.c = c;
+        H.nhigh = (int)high.size();
+        for (size_t h = 0; h < high.size(); h++) H.high_pos[h] = (uint8_t)high[h];
+        H.rank_base = rank_base_;
+        H.ntiles = 1ull << (nl_ - t);
+        CUDA_CHECK(b200k_tile_program3(vec, (int)nl_, &H, rounds.data(), dops.data(), stream_));
+        stats_.tile_passes++;
+        stats_.kernel_ops += (int64_t)dops.size();
+        stats_.rounds += (int64_t)rounds.size();
+        rounds.clear();
+        dops.clear();
+    };
+    auto base_op = [&](const GateOp &g, B200k3Op &o, uint32_t &ic, uint32_t &iv) {
+        std::memset(&o, 0, sizeof(o));
+        split(g.cmask, ic, o.co_mask);
+        split(g.cval, iv, o.co_val);
+        if (o.co_mask) o.flags |= B200K3_F_CO;
+    };
+    auto put_matrix = [&](B200k3Op &o, const cplx *m) {
+        for (int q = 0; q < 4; q++) {
+            o.m[2 * q] = m[q].real();
+            o.m[2 * q + 1] = m[q].imag();
+        }
+    };
+
+    std::vector<const GateOp *> rem(ops.begin(), ops.end()), deferred, taken;
+    while (!rem.empty()) {
+        uint64_t blockedX = 0, blockedZ = 0;
+        uint32_t S = 0; // tile-local register bits of this round
+        bool smem_round = false;
+        deferred.clear();
+        taken.clear();
+        for (size_t i = 0; i < rem.size(); i++) {
+            const GateOp *g = rem[i];
+            const uint64_t xs = g->xmask, zs = g->zsupport();
+            bool fits = false;
+            if (!smem_round && !(xs & (blockedX | blockedZ)) && !(zs & blockedX)) {
+                const bool diag = g->kind == GateOp::PHASE || g->kind == GateOp::PARITY;
+                const int rk = t >= 3 ? reg_pair_kind(*g) : 0;
+                if (t >= 3 && diag) fits = true;
+                else if (rk) {
+                    const uint32_t b = inside_only(g->xmask);
+                    if (__builtin_popcount(S | b) <= 3) {
+                        S |= b;
+                        fits = true;
+                    }
+                }
+                else if (taken.empty()) { // anything else: a shared-memory round of its own
+                    fits = true;
+                    smem_round = true;
+                }
+            }
+            if (fits) taken.push_back(g);
+            else {
+                deferred.push_back(g);
+                blockedX |= xs;
+                blockedZ |= zs;
+            }
+        }
+        if (dops.size() + taken.size() > (size_t)B200K3_LARGE_OPS || rounds.size() + 1 > (size_t)B200K3_LARGE_ROUNDS)
+            emit();
+        B200k3Round R;
+        std::memset(&R, 0, sizeof(R));
+        R.first = (uint16_t)dops.size();
+        R.count = (uint16_t)taken.size();
+        if (smem_round) {
+            R.kind = B200K2_ROUND_SMEM;
+            const GateOp &g = *taken[0];
+            B200k3Op o;
+            uint32_t ic, iv;
+            base_op(g, o, ic, iv);
+            o.tc_mask = ic;
+            o.tc_val = iv;
+            switch (g.kind) {
+            case GateOp::PAIR: {
+                o.kind = B200K3_PAIRG;
+                o.tmask = inside_only(g.xmask);
+                o.a = inside_only(g.a);
+                o.b = inside_only(g.b);
+                uint32_t m = o.tmask;
+                while (m) {
+                    B200_FAIL_IF(o.npos >= 4, "internal: PAIR on more than 4 bits");
+                    o.pos[o.npos++] = (uint8_t)__builtin_ctz(m);
+                    m &= m - 1;
+                }
+                put_matrix(o, g.m);
+                break;
+            }
+            case GateOp::PAULIROT:
+                o.kind = B200K3_PAULIROT;
+                o.tmask = inside_only(g.xmask);
+                o.pos[0] = (uint8_t)(31 - __builtin_clz(o.tmask));
+                o.npos = 1;
+                split(g.zmask, o.tz_mask, o.zo_mask);
+                o.ny = (uint8_t)(g.ny & 3);
+                o.m[0] = g.m[0].real();
+                o.m[1] = g.m[0].imag();
+                break;
+            case GateOp::PHASE:
+                o.kind = B200K3_PHASE;
+                o.m[0] = g.m[0].real();
+                o.m[1] = g.m[0].imag();
+                break;
+            case GateOp::PARITY:
+                o.kind = B200K3_PARITY;
+                split(g.zmask, o.tz_mask, o.zo_mask);
+                o.m[0] = g.m[0].real(); o.m[1] = g.m[0].imag();
+                o.m[2] = g.m[1].real(); o.m[3] = g.m[1].imag();
+                break;
+            default: B200_FAIL("internal: DENSE op in a register-blocked pass");
+            }
+            dops.push_back(o);
+        }
+        else {
+            R.kind = B200K2_ROUND_REG;
+            // pad the register bits to three with the highest free tile bits
+            for (int b = t - 1; b >= 0 && __builtin_popcount(S) < 3; b--)
+                if (!(S & (1u << b))) S |= 1u << b;
+            int rb[3], nrb = 0, ridx[32];
+            for (int b = 0; b < t; b++)
+                if (S & (1u << b)) {
+                    ridx[b] = nrb;
+                    rb[nrb++] = b;
+                }
+            R.rb0 = (uint8_t)rb[0];
+            R.rb1 = (uint8_t)rb[1];
+            R.rb2 = (uint8_t)rb[2];
+            for (int a = 0; a < 8; a++) {
+                uint32_t idx = 0;
+                for (int q = 0; q < 3; q++)
+                    if (a & (1 << q)) idx |= 1u << rb[q];
+                R.swz[a] = (uint16_t)(idx ^ ((idx >> 3) & 7u));
+            }
+            auto regpart = [&](uint32_t m) -> uint32_t {
+                uint32_t r = 0;
+                for (int q = 0; q < 3; q++)
+                    if (m & (1u << rb[q])) r |= 1u << q;
+                return r;
+            };
+            for (const GateOp *gp : taken) {
+                const GateOp &g = *gp;
+                B200k3Op o;
+                uint32_t ic, iv;
+                base_op(g, o, ic, iv);
+                const uint32_t rcm = regpart(ic), rcv = regpart(iv);
+                o.tc_mask = ic & ~S;
+                o.tc_val = iv & ~S;
+                if (o.tc_mask) o.flags |= B200K3_F_TC;
+                uint32_t slots = 0; // register slots where the control predicate holds
+                for (uint32_t a = 0; a < 8; a++)
+                    if ((a & rcm) == rcv) slots |= 1u << a;
+                if (g.kind == GateOp::PAIR) {
+                    o.kind = B200K3_PAIR;
+                    const int rk = reg_pair_kind(g);
+                    cplx m[4] = {g.m[0], g.m[1], g.m[2], g.m[3]};
+                    uint32_t lo[4];
+                    int npairs;
+                    if (rk == 1) {
+                        const int j = ridx[__builtin_ctz(inside_only(g.xmask))];
+                        o.j = (uint8_t)j;
+                        npairs = 4;
+                        static const uint32_t LO[3][4] = {{0, 2, 4, 6}, {0, 1, 4, 5}, {0, 1, 2, 3}};
+                        for (int p = 0; p < 4; p++) lo[p] = LO[j][p];
+                    }
+                    else {
+                        uint32_t A = regpart(inside_only(g.a)), B = regpart(inside_only(g.b));
+                        const uint32_t tm = A | B;
+                        const int pairsel = tm == 3 ? 0 : (tm == 5 ? 1 : 2);
+                        if (rk == 2 && A > B) { // kernel convention: first pattern = lower bit set
+                            std::swap(A, B);
+                            const cplx sw[4] = {m[3], m[2], m[1], m[0]};
+                            for (int q = 0; q < 4; q++) m[q] = sw[q];
+                        }
+                        if (rk == 3 && A != 0) { // first pattern = 00
+                            std::swap(A, B);
+                            const cplx sw[4] = {m[3], m[2], m[1], m[0]};
+                            for (int q = 0; q < 4; q++) m[q] = sw[q];
+                        }
+                        o.j = (uint8_t)((rk == 2 ? 3 : 6) + pairsel);
+                        npairs = 2;
+                        const uint32_t freebit = 7u & ~tm;
+                        lo[0] = A;
+                        lo[1] = A | freebit;
+                    }
+                    uint32_t pm = 0;
+                    for (int p = 0; p < npairs; p++)
+                        if (slots & (1u << lo[p])) pm |= 1u << p;
+                    o.amask = (uint8_t)pm;
+                    bool real = true, rx = true;
+                    for (int q = 0; q < 4; q++) real = real && m[q].imag() == 0.0;
+                    rx = m[0].imag() == 0.0 && m[3].imag() == 0.0 && m[1].real() == 0.0 && m[2].real() == 0.0;
+                    const bool swp = real && m[0].real() == 0.0 && m[3].real() == 0.0 && m[1].real() == 1.0 &&
+                                     m[2].real() == 1.0;
+                    o.mclass = swp ? B200K3_M_SWAP : (real ? B200K3_M_REAL : (rx ? B200K3_M_RX : B200K3_M_GENERAL));
+                    put_matrix(o, m);
+                    if (pm == 0) continue; // predicate can never hold on these slots
+                }
+                else if (g.kind == GateOp::PHASE) {
+                    o.kind = B200K3_PHASE;
+                    o.amask = (uint8_t)slots;
+                    o.m[0] = g.m[0].real();
+                    o.m[1] = g.m[0].imag();
+                }
+                else {
+                    o.kind = B200K3_PARITY;
+                    o.amask = (uint8_t)slots;
+                    uint32_t zi;
+                    split(g.zmask, zi, o.zo_mask);
+                    const uint32_t rz = regpart(zi);
+                    uint32_t rp = 0;
+                    for (uint32_t a = 0; a < 8; a++)
+                        if (__builtin_popcount(a & rz) & 1) rp |= 1u << a;
+                    o.rpar = (uint8_t)rp;
+                    o.tz_mask = zi & ~S;
+                    if (o.tz_mask || o.zo_mask) o.flags |= B200K3_F_TZ;
+                    o.m[0] = g.m[0].real(); o.m[1] = g.m[0].imag();
+                    o.m[2] = g.m[1].real(); o.m[3] = g.m[1].imag();
+                }
+                dops.push_back(o);
+            }
+            R.count = (uint16_t)(dops.size() - R.first);
         }
         rounds.push_back(R);
         rem.swap(deferred);

@@ -93,6 +93,7 @@ struct Options {
     int world = 1, rank = 0;
     std::string comm;
     int64_t stage_mib = 1024; // staging memory of the global<->local qubit swap
+    int kernel_gen = 3;       // tile kernel generation (2 = k_tile2, 3 = k_tile3)
 };
 
 class DeviceBuffer;
@@ -188,6 +189,8 @@ class Simulator {
     void launch_pass(double *vec, const std::vector<const GateOp *> &ops,
                      const std::vector<int> &req_high, int c);
     void launch_pass2(double *vec, const std::vector<const GateOp *> &ops,
+                      const std::vector<int> &req_high, int c);
+    void launch_pass3(double *vec, const std::vector<const GateOp *> &ops,
                       const std::vector<int> &req_high, int c);
     int pass_op_cap_ = 160;
     const double *upload_matrix(const CVec &m);

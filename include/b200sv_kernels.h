@@ -125,6 +125,59 @@ typedef struct B200k2Header {
 int b200k_tile_program2(double *psi, int n_local, const B200k2Header *hdr, const B200k2Round *rounds,
                         const B200k2Op *ops, void *stream);
 
+/* ---- fused tile pass, third generation (tile3.cu) ------------------------------------------------
+ * Same tile geometry and round structure as the second generation; what changed follows the ncu
+ * reading of k_tile2 (profiles/README.md: issue-bound on per-op decode, not on HBM or FP64):
+ *   - tile load/store offsets are precomputed once per thread (persistent CTAs), not per amplitude;
+ *   - a round's eight shared-memory slots are SW(thread base) ^ swz[a] (the XOR swizzle is linear),
+ *   - every op carries host-precomputed SLOT MASKS over the thread's 8 registers instead of
+ *     per-amplitude predicates, and a matrix class (general / real / real-diagonal+imaginary-off-
+ *     diagonal / permutation) that halves or removes the FP64 work of H, RX, RY, X, CNOT;
+ *   - two-pattern PAIRs whose two target bits are both register bits (SWAP, ISWAP, PSWAP, IsingXY,
+ *     SingleExcitation, CSWAP) run in registers too. */
+enum { B200K3_PAIR = 0, B200K3_PHASE = 1, B200K3_PARITY = 2, B200K3_PAIRG = 3, B200K3_PAULIROT = 4 };
+enum { B200K3_M_GENERAL = 0, B200K3_M_REAL = 1, B200K3_M_RX = 2, B200K3_M_SWAP = 3 };
+enum { B200K3_F_CO = 1, B200K3_F_TC = 2, B200K3_F_TZ = 4 };
+
+typedef struct B200k3Op { /* 128 bytes */
+    uint8_t kind;
+    uint8_t j;       /* PAIR: 0..2 = one-target on register bit j (pairs a <-> a|bit j);
+                        3..5 = two-target 01<->10 on register bits (0,1), (0,2), (1,2) (first
+                        pattern = lower bit set); 6..8 = two-target 00<->11 on the same bit pairs */
+    uint8_t mclass;  /* PAIR: B200K3_M_*                                                       */
+    uint8_t amask;   /* PAIR: mask over the op's 4 (or 2) register pairs; PHASE/PARITY: mask over
+                        the 8 register slots (control predicate restricted to the register bits) */
+    uint8_t rpar;    /* PARITY: bit a = parity(a & z mask over the register bits)               */
+    uint8_t flags;   /* B200K3_F_CO: outside predicate present; _TC: thread predicate present;
+                        _TZ: parity has a thread-bit or outside z part                          */
+    uint8_t ny, npos; /* shared-memory rounds (PAULIROT / PAIRG)                                 */
+    uint32_t tc_mask, tc_val; /* control predicate over the non-register tile bits (shared-memory
+                                 rounds: over all tile bits)                                    */
+    uint32_t tz_mask;         /* z mask over the non-register tile bits (shared-memory rounds: all) */
+    uint32_t tmask;           /* shared-memory rounds: tile-local target mask                   */
+    uint32_t a, b;            /* shared-memory rounds: patterns                                 */
+    uint8_t pos[4];           /* shared-memory rounds: ascending positions of tmask bits        */
+    uint32_t pad;
+    uint64_t co_mask, co_val; /* control predicate on the bits outside the tile (incl. rank bits) */
+    uint64_t zo_mask;         /* z mask outside the tile                                        */
+    double m[8];
+} B200k3Op;
+
+typedef struct B200k3Round { /* 24 bytes */
+    uint8_t kind, rb0, rb1, rb2;
+    uint16_t first, count;
+    uint16_t swz[8]; /* SW(pattern a spread over rb0..rb2), a = 0..7 */
+} B200k3Round;
+
+#define B200K3_SMALL_OPS 24
+#define B200K3_SMALL_ROUNDS 16
+#define B200K3_LARGE_OPS 216
+#define B200K3_LARGE_ROUNDS 128
+
+/* header is shared with the second generation (B200k2Header) */
+int b200k_tile_program3(double *psi, int n_local, const struct B200k2Header *hdr, const B200k3Round *rounds,
+                        const B200k3Op *ops, void *stream);
+
 /* ---- reductions (warp-shuffle tree -> per-block partials -> fixed-order final sum) -------------
  * `scratch` must hold b200k_reduce_scratch_doubles() doubles; results land in `out` (device). */
 int64_t b200k_reduce_scratch_doubles(void);

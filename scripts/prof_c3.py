@@ -6,7 +6,10 @@ from catalyst_b200 import capi, workloads
 from dsl import apply_ops
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 30
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 1
-d = capi.B200Device(n)
+kw = {}
+if len(sys.argv) > 3: kw["kernel_gen"] = int(sys.argv[3])
+if len(sys.argv) > 4: kw["tile_bits"] = int(sys.argv[4])
+d = capi.B200Device(n, **kw)
 ops = workloads.c3_qft_random(n)
 for rep in range(reps):
     d.set_basis_state([0] * n, list(range(n))); d.synchronize(); d.reset_stats(); d.set_timing(True)
