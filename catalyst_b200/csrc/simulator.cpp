@@ -1389,15 +1389,27 @@ void Simulator::launch_pass3(double *vec, const std::vector<const GateOp *> &ops
                     rx = m[0].imag() == 0.0 && m[3].imag() == 0.0 && m[1].real() == 0.0 && m[2].real() == 0.0;
                     const bool swp = real && m[0].real() == 0.0 && m[3].real() == 0.0 && m[1].real() == 1.0 &&
                                      m[2].real() == 1.0;
-                    o.mclass = swp ? B200K3_M_SWAP : (real ? B200K3_M_REAL : (rx ? B200K3_M_RX : B200K3_M_GENERAL));
+                    // permutations (X, CNOT, SWAP) run as REAL: explicit register exchanges made the
+                    // compiler keep two copies of the thread's 8 amplitudes (32 moves per op); 8 FP64
+                    // ops per pair on an idle FP64 pipe are cheaper
+                    (void)swp;
+                    o.mclass = real ? B200K3_M_REAL : (rx ? B200K3_M_RX : B200K3_M_GENERAL);
                     put_matrix(o, m);
                     if (pm == 0) continue; // predicate can never hold on these slots
+                    const bool full = pm == (npairs == 4 ? 15u : 3u);
+                    o.code = (uint32_t)((o.mclass * 9 + o.j) * 2 + (full ? 1 : 0));
                 }
                 else if (g.kind == GateOp::PHASE) {
                     o.kind = B200K3_PHASE;
                     o.amask = (uint8_t)slots;
                     o.m[0] = g.m[0].real();
                     o.m[1] = g.m[0].imag();
+                    static const uint32_t SPECIAL[10] = {0xff, 0xaa, 0x55, 0xcc, 0x33, 0xf0, 0x0f, 0x88, 0xa0, 0xc0};
+                    uint32_t idx = 10;
+                    for (uint32_t q = 0; q < 10; q++)
+                        if (SPECIAL[q] == slots) idx = q;
+                    o.code = B200K3_CODE_PHASE + idx;
+                    if (slots == 0) continue;
                 }
                 else {
                     o.kind = B200K3_PARITY;
@@ -1413,6 +1425,12 @@ void Simulator::launch_pass3(double *vec, const std::vector<const GateOp *> &ops
                     if (o.tz_mask || o.zo_mask) o.flags |= B200K3_F_TZ;
                     o.m[0] = g.m[0].real(); o.m[1] = g.m[0].imag();
                     o.m[2] = g.m[1].real(); o.m[3] = g.m[1].imag();
+                    static const uint32_t RPARS[8] = {0x00, 0xaa, 0xcc, 0xf0, 0x66, 0x5a, 0x3c, 0x96};
+                    uint32_t idx = 0;
+                    for (uint32_t q = 0; q < 8; q++)
+                        if (RPARS[q] == rp) idx = q;
+                    o.code = B200K3_CODE_PARITY + 2 * idx + (slots == 0xffu ? 1 : 0);
+                    if (slots == 0) continue;
                 }
                 dops.push_back(o);
             }

@@ -1,12 +1,19 @@
 // tile3.cu — third-generation fused tile pass (see include/b200sv_kernels.h, "third generation").
 //
-// Evidence that shaped it (profiles/README.md, ncu --set full of k_tile2 at 30 qubits): DRAM traffic
-// at the algorithmic minimum (34.4 GB per launch) but 33-64 ms per launch; issue slots 57 % busy,
-// FP64 pipe 11 %, ~630 thread-instructions per amplitude per pass of which ~60 FP64.  The cost was
-// the per-op interpreter: field loads, per-amplitude predicate loops whose predicated-off complex
-// multiplies still issue, 64-bit index arithmetic per amplitude in the tile load/store.  Here every
-// decision that is uniform over the CTA is taken once per op on host-precomputed slot masks, and
-// everything that does not depend on the tile is computed once per thread.
+// Evidence that shaped it (profiles/README.md):
+//  * ncu --set full of k_tile2 at 30 qubits: DRAM traffic at the algorithmic minimum (34.4 GB per
+//    launch) but 33-64 ms per launch; issue slots 57 % busy, FP64 pipe 11 %, ~630 thread-instructions
+//    per amplitude per pass of which ~60 FP64.  The cost was the per-op interpreter: field loads,
+//    per-amplitude predicate loops whose predicated-off complex multiplies still issue, 64-bit index
+//    arithmetic per amplitude in the tile load/store.  Here every decision that is uniform over the
+//    CTA is taken once per op on host-precomputed slot masks, everything that does not depend on the
+//    tile is computed once per thread.
+//  * SASS-level profile of the first k_tile3: explicit register exchanges for permutation gates made
+//    the compiler keep two copies of the thread's 8 amplitudes (32 moves per op, 29 % of all issued
+//    instructions) -> permutations run as real 2x2 matrices; the compare chain that selected an op
+//    body cost ~45 instructions per op -> one dense dispatch code per op (jump table); 30 % of the
+//    stall samples sat on the tile's global loads -> the next tile is prefetched with cp.async into
+//    a second shared-memory buffer while the current one is processed.
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -39,16 +46,28 @@ __device__ __forceinline__ cplx ipow3(cplx a, int k)
     default: return make_double2(a.y, -a.x);
     }
 }
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src)
+{
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait()
+{
+    asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
+
+// register pairs of a PAIR op, by op.j (see B200k3Op): lo slot, hi slot (2 pairs for j >= 3)
+__device__ constexpr int PLO[9][4] = {{0, 2, 4, 6}, {0, 1, 4, 5}, {0, 1, 2, 3}, {1, 5, 0, 0}, {1, 3, 0, 0},
+                                      {2, 3, 0, 0}, {0, 4, 0, 0}, {0, 2, 0, 0}, {0, 1, 0, 0}};
+__device__ constexpr int PHI[9][4] = {{1, 3, 5, 7}, {2, 3, 6, 7}, {4, 5, 6, 7}, {2, 6, 0, 0}, {4, 6, 0, 0},
+                                      {4, 5, 0, 0}, {3, 7, 0, 0}, {5, 7, 0, 0}, {6, 7, 0, 0}};
 
 // one 2x2 block on the register pair (x, y); MC selects how much FP64 work the matrix needs
 template <int MC> __device__ __forceinline__ void pair2x2(cplx &x, cplx &y, const double (&m)[8])
 {
     const cplx a = x, b = y;
-    if (MC == B200K3_M_SWAP) {
-        x = b;
-        y = a;
-    }
-    else if (MC == B200K3_M_REAL) { // all entries real: H, RY, X-like with signs
+    if (MC == B200K3_M_REAL) { // all entries real: H, RY, X, CNOT, SWAP
         x = make_double2(fma(m[0], a.x, m[2] * b.x), fma(m[0], a.y, m[2] * b.y));
         y = make_double2(fma(m[4], a.x, m[6] * b.x), fma(m[4], a.y, m[6] * b.y));
     }
@@ -64,81 +83,112 @@ template <int MC> __device__ __forceinline__ void pair2x2(cplx &x, cplx &y, cons
     }
 }
 
-template <int MC, int L0, int H0, int L1, int H1, int L2, int H2, int L3, int H3>
-__device__ __forceinline__ void apply4(cplx (&v)[8], const double (&m)[8], uint32_t pm)
-{
-    if (pm == 15u) {
-        pair2x2<MC>(v[L0], v[H0], m);
-        pair2x2<MC>(v[L1], v[H1], m);
-        pair2x2<MC>(v[L2], v[H2], m);
-        pair2x2<MC>(v[L3], v[H3], m);
-    }
-    else { // controls on register bits: CTA-uniform branches
-        if (pm & 1u) pair2x2<MC>(v[L0], v[H0], m);
-        if (pm & 2u) pair2x2<MC>(v[L1], v[H1], m);
-        if (pm & 4u) pair2x2<MC>(v[L2], v[H2], m);
-        if (pm & 8u) pair2x2<MC>(v[L3], v[H3], m);
-    }
-}
-template <int MC, int L0, int H0, int L1, int H1>
-__device__ __forceinline__ void apply2(cplx (&v)[8], const double (&m)[8], uint32_t pm)
-{
-    if (pm & 1u) pair2x2<MC>(v[L0], v[H0], m);
-    if (pm & 2u) pair2x2<MC>(v[L1], v[H1], m);
-}
-
-template <int MC> __device__ __forceinline__ void pair_op(cplx (&v)[8], const B200k3Op &op)
+template <int MC, int J, bool FULL> __device__ __forceinline__ void pair_case(cplx (&v)[8], const B200k3Op &op)
 {
     double m[8];
-#pragma unroll
-    for (int q = 0; q < 8; q++) m[q] = op.m[q];
-    const uint32_t pm = op.amask;
-    switch (op.j) {
-    case 0: apply4<MC, 0, 1, 2, 3, 4, 5, 6, 7>(v, m, pm); break;
-    case 1: apply4<MC, 0, 2, 1, 3, 4, 6, 5, 7>(v, m, pm); break;
-    case 2: apply4<MC, 0, 4, 1, 5, 2, 6, 3, 7>(v, m, pm); break;
-    // two-target 01 <-> 10: first pattern = lower register bit set, second = higher bit set
-    case 3: apply2<MC, 1, 2, 5, 6>(v, m, pm); break; // bits (0,1), free bit 2
-    case 4: apply2<MC, 1, 4, 3, 6>(v, m, pm); break; // bits (0,2), free bit 1
-    case 5: apply2<MC, 2, 4, 3, 5>(v, m, pm); break; // bits (1,2), free bit 0
-    // two-target 00 <-> 11
-    case 6: apply2<MC, 0, 3, 4, 7>(v, m, pm); break; // bits (0,1)
-    case 7: apply2<MC, 0, 5, 2, 7>(v, m, pm); break; // bits (0,2)
-    default: apply2<MC, 0, 6, 1, 7>(v, m, pm); break; // bits (1,2)
+    if (MC == B200K3_M_REAL) {
+        m[0] = op.m[0]; m[2] = op.m[2]; m[4] = op.m[4]; m[6] = op.m[6];
+        m[1] = m[3] = m[5] = m[7] = 0.0;
     }
+    else if (MC == B200K3_M_RX) {
+        m[0] = op.m[0]; m[3] = op.m[3]; m[5] = op.m[5]; m[6] = op.m[6];
+        m[1] = m[2] = m[4] = m[7] = 0.0;
+    }
+    else {
+#pragma unroll
+        for (int q = 0; q < 8; q++) m[q] = op.m[q];
+    }
+    constexpr int NP = J < 3 ? 4 : 2;
+    const uint32_t pm = FULL ? 0xfu : op.amask;
+#pragma unroll
+    for (int p = 0; p < NP; p++)
+        if (FULL || (pm & (1u << p))) pair2x2<MC>(v[PLO[J][p]], v[PHI[J][p]], m);
 }
 
-template <int MASK> __device__ __forceinline__ void phase_slots(cplx (&v)[8], cplx e)
+template <int MASK> __device__ __forceinline__ void phase_slots(cplx (&v)[8], const B200k3Op &op)
 {
+    const cplx e = make_double2(op.m[0], op.m[1]);
 #pragma unroll
     for (int a = 0; a < 8; a++)
         if (MASK & (1 << a)) v[a] = cmul3(v[a], e);
 }
 
-// v[a] *= ((RPAR >> a) & 1) ? eB : eA on the slots of `am`
-template <int RPAR> __device__ __forceinline__ void parity_slots(cplx (&v)[8], cplx eA, cplx eB, uint32_t am)
+// v[a] *= ((RPAR >> a) & 1) ? eB : eA on the slots of amask; eA/eB = (e0, e1) ordered by the parity of
+// the thread's non-register index bits and of the tile's outside bits
+template <int RPAR, bool FULL>
+__device__ __forceinline__ void parity_case(cplx (&v)[8], const B200k3Op &op, uint32_t ib, uint64_t obase)
 {
-    if (am == 0xffu) {
+    uint32_t p0 = 0;
+    if (op.flags & B200K3_F_TZ) p0 = (__popc(ib & op.tz_mask) + __popcll(obase & op.zo_mask)) & 1u;
+    const cplx e0 = make_double2(op.m[0], op.m[1]);
+    const cplx e1 = make_double2(op.m[2], op.m[3]);
+    const cplx eA = p0 ? e1 : e0, eB = p0 ? e0 : e1;
+    const uint32_t am = FULL ? 0xffu : op.amask;
 #pragma unroll
-        for (int a = 0; a < 8; a++) v[a] = cmul3(v[a], ((RPAR >> a) & 1) ? eB : eA);
-    }
-    else {
+    for (int a = 0; a < 8; a++)
+        if (FULL || (am & (1u << a))) v[a] = cmul3(v[a], ((RPAR >> a) & 1) ? eB : eA);
+}
+
+// every register-round op body, selected by the host-computed dense code (jump table)
+__device__ __forceinline__ void run_op(cplx (&v)[8], const B200k3Op &op, uint32_t ib, uint64_t obase)
+{
+#define PAIR_J(MC, J)                                                                              \
+    case ((MC * 9 + J) * 2 + 1): pair_case<MC, J, true>(v, op); break;                             \
+    case ((MC * 9 + J) * 2 + 0): pair_case<MC, J, false>(v, op); break;
+#define PAIR_MC(MC)                                                                                \
+    PAIR_J(MC, 0) PAIR_J(MC, 1) PAIR_J(MC, 2) PAIR_J(MC, 3) PAIR_J(MC, 4) PAIR_J(MC, 5) PAIR_J(MC, 6)   \
+    PAIR_J(MC, 7) PAIR_J(MC, 8)
+#define PARITY_R(IDX, RPAR)                                                                        \
+    case (B200K3_CODE_PARITY + 2 * IDX + 1): parity_case<RPAR, true>(v, op, ib, obase); break;     \
+    case (B200K3_CODE_PARITY + 2 * IDX + 0): parity_case<RPAR, false>(v, op, ib, obase); break;
+    switch (op.code) {
+        PAIR_MC(B200K3_M_GENERAL)
+        PAIR_MC(B200K3_M_REAL)
+        PAIR_MC(B200K3_M_RX)
+    case B200K3_CODE_PHASE + 0: phase_slots<0xff>(v, op); break;
+    case B200K3_CODE_PHASE + 1: phase_slots<0xaa>(v, op); break;
+    case B200K3_CODE_PHASE + 2: phase_slots<0x55>(v, op); break;
+    case B200K3_CODE_PHASE + 3: phase_slots<0xcc>(v, op); break;
+    case B200K3_CODE_PHASE + 4: phase_slots<0x33>(v, op); break;
+    case B200K3_CODE_PHASE + 5: phase_slots<0xf0>(v, op); break;
+    case B200K3_CODE_PHASE + 6: phase_slots<0x0f>(v, op); break;
+    case B200K3_CODE_PHASE + 7: phase_slots<0x88>(v, op); break;
+    case B200K3_CODE_PHASE + 8: phase_slots<0xa0>(v, op); break;
+    case B200K3_CODE_PHASE + 9: phase_slots<0xc0>(v, op); break;
+    case B200K3_CODE_PHASE + 10: {
+        const cplx e = make_double2(op.m[0], op.m[1]);
+        const uint32_t am = op.amask;
 #pragma unroll
         for (int a = 0; a < 8; a++)
-            if (am & (1u << a)) v[a] = cmul3(v[a], ((RPAR >> a) & 1) ? eB : eA);
+            if (am & (1u << a)) v[a] = cmul3(v[a], e);
+        break;
     }
+        PARITY_R(0, 0x00)
+        PARITY_R(1, 0xaa)
+        PARITY_R(2, 0xcc)
+        PARITY_R(3, 0xf0)
+        PARITY_R(4, 0x66)
+        PARITY_R(5, 0x5a)
+        PARITY_R(6, 0x3c)
+        PARITY_R(7, 0x96)
+    default: break;
+    }
+#undef PAIR_J
+#undef PAIR_MC
+#undef PARITY_R
 }
 
 template <int NOPS, int NROUNDS>
 __global__ void __launch_bounds__(TT, 3)
 k_tile3(cplx *__restrict__ psi, const __grid_constant__ Prog3<NOPS, NROUNDS> P)
 {
-    extern __shared__ cplx s[];
+    extern __shared__ cplx smem[]; // one tile, or two when the launch double-buffers (P.h.pad != 0)
     __shared__ uint64_t s_offk[32];
     const int t = P.h.t, c = P.h.c, nhigh = P.h.nhigh;
     const uint32_t nelem = 1u << t;
     const uint32_t lowmask = (1u << c) - 1u;
     const uint32_t tid = threadIdx.x;
+    const bool dbuf = P.h.pad != 0;
 
     // tile-independent part of the global offset of element e: off(e) = (e & lowmask) | scatter(e >> c)
     // is an OR over disjoint bit sets of e, so off(tid + 256 k) = off(tid) | off(256 k)
@@ -148,23 +198,47 @@ k_tile3(cplx *__restrict__ psi, const __grid_constant__ Prog3<NOPS, NROUNDS> P)
         for (int h = 0; h < nhigh; h++) o |= (uint64_t)((r >> h) & 1u) << P.h.high_pos[h];
         return o;
     };
+    auto base_of = [&](uint64_t tile) -> uint64_t {
+        uint64_t base = tile << c;
+        for (int h = 0; h < nhigh; h++) {
+            const int p = P.h.high_pos[h];
+            base = ((base >> p) << (p + 1)) | (base & ((1ull << p) - 1ull));
+        }
+        return base;
+    };
     const uint32_t niter = nelem > TT ? nelem / TT : 1u; // <= 16 for t <= 12
     if (tid < niter) s_offk[tid] = off_of(tid * TT);
     const uint64_t off_tid = off_of(tid);
     const uint32_t sw_tid = SW(tid);
     __syncthreads();
 
-    for (uint64_t tile = blockIdx.x; tile < P.h.ntiles; tile += gridDim.x) {
-        uint64_t base = tile << c;
-        for (int h = 0; h < nhigh; h++) {
-            const int p = P.h.high_pos[h];
-            base = ((base >> p) << (p + 1)) | (base & ((1ull << p) - 1ull));
+    auto prefetch = [&](uint64_t tile, cplx *buf) {
+        if (tid < nelem) {
+            const cplx *src = psi + (base_of(tile) | off_tid);
+#pragma unroll 8
+            for (uint32_t k = 0; k < niter; k++) cp_async16(&buf[sw_tid + k * TT], &src[s_offk[k]]);
         }
+        cp_async_commit();
+    };
+
+    uint32_t cur = 0;
+    if (dbuf && blockIdx.x < P.h.ntiles) prefetch(blockIdx.x, smem);
+    for (uint64_t tile = blockIdx.x; tile < P.h.ntiles; tile += gridDim.x) {
+        const uint64_t base = base_of(tile);
         const uint64_t obase = base | P.h.rank_base;
         cplx *__restrict__ tp = psi + (base | off_tid);
+        cplx *__restrict__ s = smem + (dbuf ? cur * nelem : 0u);
 
         // ---- load ---------------------------------------------------------------------------
-        if (tid < nelem) {
+        if (dbuf) {
+            const uint64_t next = tile + gridDim.x;
+            if (next < P.h.ntiles) {
+                prefetch(next, smem + (cur ^ 1u) * nelem);
+                cp_async_wait<1>(); // the current tile's group is complete, the next one may be in flight
+            }
+            else cp_async_wait<0>();
+        }
+        else if (tid < nelem) {
 #pragma unroll 8
             for (uint32_t k = 0; k < niter; k++) s[sw_tid + k * TT] = tp[s_offk[k]];
         }
@@ -186,53 +260,7 @@ k_tile3(cplx *__restrict__ psi, const __grid_constant__ Prog3<NOPS, NROUNDS> P)
                         const uint32_t fl = op.flags;
                         if ((fl & B200K3_F_CO) && (obase & op.co_mask) != op.co_val) continue;
                         if ((fl & B200K3_F_TC) && (ib & op.tc_mask) != op.tc_val) continue;
-                        if (op.kind == B200K3_PAIR) {
-                            switch (op.mclass) {
-                            case B200K3_M_SWAP: pair_op<B200K3_M_SWAP>(v, op); break;
-                            case B200K3_M_REAL: pair_op<B200K3_M_REAL>(v, op); break;
-                            case B200K3_M_RX: pair_op<B200K3_M_RX>(v, op); break;
-                            default: pair_op<B200K3_M_GENERAL>(v, op); break;
-                            }
-                        }
-                        else if (op.kind == B200K3_PHASE) {
-                            const cplx e = make_double2(op.m[0], op.m[1]);
-                            switch (op.amask) {
-                            case 0xff: phase_slots<0xff>(v, e); break;
-                            case 0xaa: phase_slots<0xaa>(v, e); break;
-                            case 0x55: phase_slots<0x55>(v, e); break;
-                            case 0xcc: phase_slots<0xcc>(v, e); break;
-                            case 0x33: phase_slots<0x33>(v, e); break;
-                            case 0xf0: phase_slots<0xf0>(v, e); break;
-                            case 0x0f: phase_slots<0x0f>(v, e); break;
-                            case 0x88: phase_slots<0x88>(v, e); break;
-                            case 0xa0: phase_slots<0xa0>(v, e); break;
-                            case 0xc0: phase_slots<0xc0>(v, e); break;
-                            default: {
-                                const uint32_t am = op.amask;
-#pragma unroll
-                                for (int a = 0; a < 8; a++)
-                                    if (am & (1u << a)) v[a] = cmul3(v[a], e);
-                            }
-                            }
-                        }
-                        else { // PARITY
-                            uint32_t p0 = 0;
-                            if (fl & B200K3_F_TZ) p0 = (__popc(ib & op.tz_mask) + __popcll(obase & op.zo_mask)) & 1u;
-                            const cplx e0 = make_double2(op.m[0], op.m[1]);
-                            const cplx e1 = make_double2(op.m[2], op.m[3]);
-                            const cplx eA = p0 ? e1 : e0, eB = p0 ? e0 : e1;
-                            const uint32_t am = op.amask;
-                            switch (op.rpar) {
-                            case 0x00: parity_slots<0x00>(v, eA, eB, am); break;
-                            case 0xaa: parity_slots<0xaa>(v, eA, eB, am); break;
-                            case 0xcc: parity_slots<0xcc>(v, eA, eB, am); break;
-                            case 0xf0: parity_slots<0xf0>(v, eA, eB, am); break;
-                            case 0x66: parity_slots<0x66>(v, eA, eB, am); break;
-                            case 0x5a: parity_slots<0x5a>(v, eA, eB, am); break;
-                            case 0x3c: parity_slots<0x3c>(v, eA, eB, am); break;
-                            default: parity_slots<0x96>(v, eA, eB, am); break;
-                            }
-                        }
+                        run_op(v, op, ib, obase);
                     }
 #pragma unroll
                     for (int a = 0; a < 8; a++) s[sb ^ R.swz[a]] = v[a];
@@ -293,7 +321,8 @@ k_tile3(cplx *__restrict__ psi, const __grid_constant__ Prog3<NOPS, NROUNDS> P)
 #pragma unroll 8
             for (uint32_t k = 0; k < niter; k++) tp[s_offk[k]] = s[sw_tid + k * TT];
         }
-        __syncthreads();
+        __syncthreads(); // the buffer is refilled by the next iteration's prefetch (or load)
+        cur ^= 1u;
     }
 }
 
@@ -301,31 +330,40 @@ template <int NOPS, int NROUNDS>
 static int launch3(double *psi, const B200k2Header *hdr, const B200k3Round *rounds, const B200k3Op *ops,
                    cudaStream_t st)
 {
-    static int grid_per_sm[B200K_MAX_TILE_BITS + 1];
+    // resident CTAs per SM for [double-buffered?][tile bits]
+    static int grid_per_sm[2][B200K_MAX_TILE_BITS + 1];
     static int sm_count = 0;
     static bool attr_set = false;
     auto kern = k_tile3<NOPS, NROUNDS>;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)(sizeof(cplx) << B200K_MAX_TILE_BITS));
+                                             (int)(2 * sizeof(cplx) << B200K_MAX_TILE_BITS));
         if (e != cudaSuccess) return (int)e;
         int dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
-        for (int t = 0; t <= B200K_MAX_TILE_BITS; t++) {
-            int nb = 0;
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, TT, sizeof(cplx) << t);
-            grid_per_sm[t] = nb > 0 ? nb : 1;
-        }
+        for (int d = 0; d < 2; d++)
+            for (int t = 0; t <= B200K_MAX_TILE_BITS; t++) {
+                int nb = 0;
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, TT, (size_t)(d + 1) * (sizeof(cplx) << t));
+                grid_per_sm[d][t] = nb;
+            }
         attr_set = true;
     }
     Prog3<NOPS, NROUNDS> P;
     P.h = *hdr;
     for (int i = 0; i < hdr->n_rounds; i++) P.rounds[i] = rounds[i];
     for (int i = 0; i < hdr->n_ops; i++) P.ops[i] = ops[i];
-    uint64_t grid = (uint64_t)sm_count * grid_per_sm[hdr->t];
+    // double-buffer when it costs no residency and every CTA handles several tiles
+    const int t = hdr->t;
+    int dbuf = grid_per_sm[1][t] >= grid_per_sm[0][t] && grid_per_sm[1][t] > 0 &&
+               hdr->ntiles >= 2ull * (uint64_t)sm_count * (uint64_t)grid_per_sm[1][t] && t >= 8;
+    if (hdr->pad == 2) dbuf = 0; // caller override (benchmarking the plain path)
+    const int per_sm = grid_per_sm[dbuf][t] > 0 ? grid_per_sm[dbuf][t] : 1;
+    P.h.pad = dbuf;
+    uint64_t grid = (uint64_t)sm_count * per_sm;
     if (grid > hdr->ntiles) grid = hdr->ntiles;
-    kern<<<(unsigned)grid, TT, sizeof(cplx) << hdr->t, st>>>(reinterpret_cast<cplx *>(psi), P);
+    kern<<<(unsigned)grid, TT, (size_t)(dbuf + 1) * (sizeof(cplx) << t), st>>>(reinterpret_cast<cplx *>(psi), P);
     return (int)cudaGetLastError();
 }
 

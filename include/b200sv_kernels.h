@@ -136,8 +136,9 @@ int b200k_tile_program2(double *psi, int n_local, const B200k2Header *hdr, const
  *   - two-pattern PAIRs whose two target bits are both register bits (SWAP, ISWAP, PSWAP, IsingXY,
  *     SingleExcitation, CSWAP) run in registers too. */
 enum { B200K3_PAIR = 0, B200K3_PHASE = 1, B200K3_PARITY = 2, B200K3_PAIRG = 3, B200K3_PAULIROT = 4 };
-enum { B200K3_M_GENERAL = 0, B200K3_M_REAL = 1, B200K3_M_RX = 2, B200K3_M_SWAP = 3 };
+enum { B200K3_M_GENERAL = 0, B200K3_M_REAL = 1, B200K3_M_RX = 2 };
 enum { B200K3_F_CO = 1, B200K3_F_TC = 2, B200K3_F_TZ = 4 };
+enum { B200K3_CODE_PHASE = 54, B200K3_CODE_PARITY = 65, B200K3_NCODES = 81 };
 
 typedef struct B200k3Op { /* 128 bytes */
     uint8_t kind;
@@ -157,7 +158,13 @@ typedef struct B200k3Op { /* 128 bytes */
     uint32_t tmask;           /* shared-memory rounds: tile-local target mask                   */
     uint32_t a, b;            /* shared-memory rounds: patterns                                 */
     uint8_t pos[4];           /* shared-memory rounds: ascending positions of tmask bits        */
-    uint32_t pad;
+    uint32_t code;            /* register rounds: dense dispatch code (one straight-line body per
+                                 code, reached through a jump table):
+                                 PAIR   : ((mclass * 9 + j) * 2 + full), full = all pairs active
+                                 PHASE  : B200K3_CODE_PHASE + index of amask in the special-mask list
+                                          {ff,aa,55,cc,33,f0,0f,88,a0,c0}, 10 = any other mask
+                                 PARITY : B200K3_CODE_PARITY + 2 * index of rpar in
+                                          {00,aa,cc,f0,66,5a,3c,96} + (amask == ff)                */
     uint64_t co_mask, co_val; /* control predicate on the bits outside the tile (incl. rank bits) */
     uint64_t zo_mask;         /* z mask outside the tile                                        */
     double m[8];
