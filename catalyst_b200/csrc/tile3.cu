@@ -31,7 +31,8 @@ template <int NOPS, int NROUNDS> struct Prog3 {
 
 __device__ __forceinline__ cplx cmul3(cplx a, cplx b)
 {
-    return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+    // multiplies on a.x first, FMAs on a.y last: both results can be written over their own inputs
+    return make_double2(fma(-a.y, b.y, a.x * b.x), fma(a.y, b.x, a.x * b.y));
 }
 __device__ __forceinline__ uint32_t ins0(uint32_t g, uint32_t b)
 {
@@ -68,11 +69,11 @@ template <int MC> __device__ __forceinline__ void pair2x2(cplx &x, cplx &y, cons
 {
     const cplx a = x, b = y;
     if (MC == B200K3_M_REAL) { // all entries real: H, RY, X, CNOT, SWAP
-        x = make_double2(fma(m[0], a.x, m[2] * b.x), fma(m[0], a.y, m[2] * b.y));
-        y = make_double2(fma(m[4], a.x, m[6] * b.x), fma(m[4], a.y, m[6] * b.y));
+        x = make_double2(fma(m[2], b.x, m[0] * a.x), fma(m[2], b.y, m[0] * a.y));
+        y = make_double2(fma(m[6], b.x, m[4] * a.x), fma(m[6], b.y, m[4] * a.y));
     }
     else if (MC == B200K3_M_RX) { // real diagonal, imaginary off-diagonal: RX, IsingXX blocks
-        x = make_double2(fma(m[0], a.x, -m[3] * b.y), fma(m[0], a.y, m[3] * b.x));
+        x = make_double2(fma(-m[3], b.y, m[0] * a.x), fma(m[3], b.x, m[0] * a.y));
         y = make_double2(fma(m[6], b.x, -m[5] * a.y), fma(m[6], b.y, m[5] * a.x));
     }
     else {
