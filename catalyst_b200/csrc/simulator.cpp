@@ -1338,7 +1338,7 @@ void Simulator::launch_pass3(double *vec, const std::vector<const GateOp *> &ops
             for (const GateOp *gp : taken) {
                 const GateOp &g = *gp;
                 B200k3Op o;
-                uint32_t ic, iv;
+                uint32_t ic, iv, code = 0;
                 base_op(g, o, ic, iv);
                 const uint32_t rcm = regpart(ic), rcv = regpart(iv);
                 o.tc_mask = ic & ~S;
@@ -1397,7 +1397,7 @@ void Simulator::launch_pass3(double *vec, const std::vector<const GateOp *> &ops
                     put_matrix(o, m);
                     if (pm == 0) continue; // predicate can never hold on these slots
                     const bool full = pm == (npairs == 4 ? 15u : 3u);
-                    o.code = (uint32_t)((o.mclass * 9 + o.j) * 2 + (full ? 1 : 0));
+                    code = (uint32_t)((o.mclass * 9 + o.j) * 2 + (full ? 1 : 0));
                 }
                 else if (g.kind == GateOp::PHASE) {
                     o.kind = B200K3_PHASE;
@@ -1408,7 +1408,7 @@ void Simulator::launch_pass3(double *vec, const std::vector<const GateOp *> &ops
                     uint32_t idx = 10;
                     for (uint32_t q = 0; q < 10; q++)
                         if (SPECIAL[q] == slots) idx = q;
-                    o.code = B200K3_CODE_PHASE + idx;
+                    code = B200K3_CODE_PHASE + idx;
                     if (slots == 0) continue;
                 }
                 else {
@@ -1429,9 +1429,10 @@ void Simulator::launch_pass3(double *vec, const std::vector<const GateOp *> &ops
                     uint32_t idx = 0;
                     for (uint32_t q = 0; q < 8; q++)
                         if (RPARS[q] == rp) idx = q;
-                    o.code = B200K3_CODE_PARITY + 2 * idx + (slots == 0xffu ? 1 : 0);
+                    code = B200K3_CODE_PARITY + 2 * idx + (slots == 0xffu ? 1 : 0);
                     if (slots == 0) continue;
                 }
+                o.ctl = code | (uint32_t)o.amask << 8 | (uint32_t)o.flags << 16 | (uint32_t)o.rpar << 24;
                 dops.push_back(o);
             }
             R.count = (uint16_t)(dops.size() - R.first);

@@ -26,7 +26,7 @@ typedef double2 cplx;
 template <int NOPS, int NROUNDS> struct Prog3 {
     B200k2Header h;
     B200k3Round rounds[NROUNDS];
-    B200k3Op ops[NOPS];
+    B200k3Op ops[NOPS + 1]; // + one readable entry for the control-word prefetch
 };
 
 __device__ __forceinline__ cplx cmul3(cplx a, cplx b)
@@ -84,7 +84,8 @@ template <int MC> __device__ __forceinline__ void pair2x2(cplx &x, cplx &y, cons
     }
 }
 
-template <int MC, int J, bool FULL> __device__ __forceinline__ void pair_case(cplx (&v)[8], const B200k3Op &op)
+template <int MC, int J, bool FULL>
+__device__ __forceinline__ void pair_case(cplx (&v)[8], const B200k3Op &op, uint32_t ctl)
 {
     double m[8];
     if (MC == B200K3_M_REAL) {
@@ -100,7 +101,7 @@ template <int MC, int J, bool FULL> __device__ __forceinline__ void pair_case(cp
         for (int q = 0; q < 8; q++) m[q] = op.m[q];
     }
     constexpr int NP = J < 3 ? 4 : 2;
-    const uint32_t pm = FULL ? 0xfu : op.amask;
+    const uint32_t pm = FULL ? 0xfu : ((ctl >> 8) & 0xffu);
 #pragma unroll
     for (int p = 0; p < NP; p++)
         if (FULL || (pm & (1u << p))) pair2x2<MC>(v[PLO[J][p]], v[PHI[J][p]], m);
@@ -117,32 +118,33 @@ template <int MASK> __device__ __forceinline__ void phase_slots(cplx (&v)[8], co
 // v[a] *= ((RPAR >> a) & 1) ? eB : eA on the slots of amask; eA/eB = (e0, e1) ordered by the parity of
 // the thread's non-register index bits and of the tile's outside bits
 template <int RPAR, bool FULL>
-__device__ __forceinline__ void parity_case(cplx (&v)[8], const B200k3Op &op, uint32_t ib, uint64_t obase)
+__device__ __forceinline__ void parity_case(cplx (&v)[8], const B200k3Op &op, uint4 ctl, uint32_t ib,
+                                            uint64_t obase)
 {
     uint32_t p0 = 0;
-    if (op.flags & B200K3_F_TZ) p0 = (__popc(ib & op.tz_mask) + __popcll(obase & op.zo_mask)) & 1u;
+    if (ctl.x & (B200K3_F_TZ << 16)) p0 = (__popc(ib & ctl.w) + __popcll(obase & op.zo_mask)) & 1u;
     const cplx e0 = make_double2(op.m[0], op.m[1]);
     const cplx e1 = make_double2(op.m[2], op.m[3]);
     const cplx eA = p0 ? e1 : e0, eB = p0 ? e0 : e1;
-    const uint32_t am = FULL ? 0xffu : op.amask;
+    const uint32_t am = FULL ? 0xffu : ((ctl.x >> 8) & 0xffu);
 #pragma unroll
     for (int a = 0; a < 8; a++)
         if (FULL || (am & (1u << a))) v[a] = cmul3(v[a], ((RPAR >> a) & 1) ? eB : eA);
 }
 
 // every register-round op body, selected by the host-computed dense code (jump table)
-__device__ __forceinline__ void run_op(cplx (&v)[8], const B200k3Op &op, uint32_t ib, uint64_t obase)
+__device__ __forceinline__ void run_op(cplx (&v)[8], const B200k3Op &op, uint4 ctl, uint32_t ib, uint64_t obase)
 {
 #define PAIR_J(MC, J)                                                                              \
-    case ((MC * 9 + J) * 2 + 1): pair_case<MC, J, true>(v, op); break;                             \
-    case ((MC * 9 + J) * 2 + 0): pair_case<MC, J, false>(v, op); break;
+    case ((MC * 9 + J) * 2 + 1): pair_case<MC, J, true>(v, op, ctl.x); break;                      \
+    case ((MC * 9 + J) * 2 + 0): pair_case<MC, J, false>(v, op, ctl.x); break;
 #define PAIR_MC(MC)                                                                                \
     PAIR_J(MC, 0) PAIR_J(MC, 1) PAIR_J(MC, 2) PAIR_J(MC, 3) PAIR_J(MC, 4) PAIR_J(MC, 5) PAIR_J(MC, 6)   \
     PAIR_J(MC, 7) PAIR_J(MC, 8)
 #define PARITY_R(IDX, RPAR)                                                                        \
-    case (B200K3_CODE_PARITY + 2 * IDX + 1): parity_case<RPAR, true>(v, op, ib, obase); break;     \
-    case (B200K3_CODE_PARITY + 2 * IDX + 0): parity_case<RPAR, false>(v, op, ib, obase); break;
-    switch (op.code) {
+    case (B200K3_CODE_PARITY + 2 * IDX + 1): parity_case<RPAR, true>(v, op, ctl, ib, obase); break; \
+    case (B200K3_CODE_PARITY + 2 * IDX + 0): parity_case<RPAR, false>(v, op, ctl, ib, obase); break;
+    switch (ctl.x & 0xffu) {
         PAIR_MC(B200K3_M_GENERAL)
         PAIR_MC(B200K3_M_REAL)
         PAIR_MC(B200K3_M_RX)
@@ -158,7 +160,7 @@ __device__ __forceinline__ void run_op(cplx (&v)[8], const B200k3Op &op, uint32_
     case B200K3_CODE_PHASE + 9: phase_slots<0xc0>(v, op); break;
     case B200K3_CODE_PHASE + 10: {
         const cplx e = make_double2(op.m[0], op.m[1]);
-        const uint32_t am = op.amask;
+        const uint32_t am = (ctl.x >> 8) & 0xffu;
 #pragma unroll
         for (int a = 0; a < 8; a++)
             if (am & (1u << a)) v[a] = cmul3(v[a], e);
@@ -256,12 +258,16 @@ k_tile3(cplx *__restrict__ psi, const __grid_constant__ Prog3<NOPS, NROUNDS> P)
                     cplx v[8];
 #pragma unroll
                     for (int a = 0; a < 8; a++) v[a] = s[sb ^ R.swz[a]];
+                    // the next op's 16-byte control word is fetched while the current op runs (the op
+                    // array has one readable entry past the last op)
+                    uint4 nxt = *reinterpret_cast<const uint4 *>(&P.ops[o0]);
                     for (int o = o0; o < o1; o++) {
                         const B200k3Op &op = P.ops[o];
-                        const uint32_t fl = op.flags;
-                        if ((fl & B200K3_F_CO) && (obase & op.co_mask) != op.co_val) continue;
-                        if ((fl & B200K3_F_TC) && (ib & op.tc_mask) != op.tc_val) continue;
-                        run_op(v, op, ib, obase);
+                        const uint4 ctl = nxt;
+                        nxt = *reinterpret_cast<const uint4 *>(&P.ops[o + 1]);
+                        if ((ctl.x & (B200K3_F_CO << 16)) && (obase & op.co_mask) != op.co_val) continue;
+                        if ((ctl.x & (B200K3_F_TC << 16)) && (ib & ctl.y) != ctl.z) continue;
+                        run_op(v, op, ctl, ib, obase);
                     }
 #pragma unroll
                     for (int a = 0; a < 8; a++) s[sb ^ R.swz[a]] = v[a];

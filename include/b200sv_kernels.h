@@ -140,7 +140,20 @@ enum { B200K3_M_GENERAL = 0, B200K3_M_REAL = 1, B200K3_M_RX = 2 };
 enum { B200K3_F_CO = 1, B200K3_F_TC = 2, B200K3_F_TZ = 4 };
 enum { B200K3_CODE_PHASE = 54, B200K3_CODE_PARITY = 65, B200K3_NCODES = 81 };
 
-typedef struct B200k3Op { /* 128 bytes */
+typedef struct B200k3Op { /* 128 bytes; the first 16 are the CONTROL WORD the kernel prefetches */
+    uint32_t ctl;             /* register rounds: code | amask << 8 | flags << 16 | rpar << 24, where
+                                 code is the dense dispatch code (one straight-line body per code,
+                                 reached through a jump table):
+                                 PAIR   : ((mclass * 9 + j) * 2 + full), full = all pairs active
+                                 PHASE  : B200K3_CODE_PHASE + index of amask in the special-mask list
+                                          {ff,aa,55,cc,33,f0,0f,88,a0,c0}, 10 = any other mask
+                                 PARITY : B200K3_CODE_PARITY + 2 * index of rpar in
+                                          {00,aa,cc,f0,66,5a,3c,96} + (amask == ff)                */
+    uint32_t tc_mask, tc_val; /* control predicate over the non-register tile bits (shared-memory
+                                 rounds: over all tile bits)                                    */
+    uint32_t tz_mask;         /* z mask over the non-register tile bits (shared-memory rounds: all) */
+    uint64_t co_mask, co_val; /* control predicate on the bits outside the tile (incl. rank bits) */
+    uint64_t zo_mask;         /* z mask outside the tile                                        */
     uint8_t kind;
     uint8_t j;       /* PAIR: 0..2 = one-target on register bit j (pairs a <-> a|bit j);
                         3..5 = two-target 01<->10 on register bits (0,1), (0,2), (1,2) (first
@@ -152,21 +165,9 @@ typedef struct B200k3Op { /* 128 bytes */
     uint8_t flags;   /* B200K3_F_CO: outside predicate present; _TC: thread predicate present;
                         _TZ: parity has a thread-bit or outside z part                          */
     uint8_t ny, npos; /* shared-memory rounds (PAULIROT / PAIRG)                                 */
-    uint32_t tc_mask, tc_val; /* control predicate over the non-register tile bits (shared-memory
-                                 rounds: over all tile bits)                                    */
-    uint32_t tz_mask;         /* z mask over the non-register tile bits (shared-memory rounds: all) */
     uint32_t tmask;           /* shared-memory rounds: tile-local target mask                   */
     uint32_t a, b;            /* shared-memory rounds: patterns                                 */
     uint8_t pos[4];           /* shared-memory rounds: ascending positions of tmask bits        */
-    uint32_t code;            /* register rounds: dense dispatch code (one straight-line body per
-                                 code, reached through a jump table):
-                                 PAIR   : ((mclass * 9 + j) * 2 + full), full = all pairs active
-                                 PHASE  : B200K3_CODE_PHASE + index of amask in the special-mask list
-                                          {ff,aa,55,cc,33,f0,0f,88,a0,c0}, 10 = any other mask
-                                 PARITY : B200K3_CODE_PARITY + 2 * index of rpar in
-                                          {00,aa,cc,f0,66,5a,3c,96} + (amask == ff)                */
-    uint64_t co_mask, co_val; /* control predicate on the bits outside the tile (incl. rank bits) */
-    uint64_t zo_mask;         /* z mask outside the tile                                        */
     double m[8];
 } B200k3Op;
 
@@ -178,7 +179,7 @@ typedef struct B200k3Round { /* 24 bytes */
 
 #define B200K3_SMALL_OPS 24
 #define B200K3_SMALL_ROUNDS 16
-#define B200K3_LARGE_OPS 216
+#define B200K3_LARGE_OPS 215 /* + 1 readable pad entry for the control-word prefetch */
 #define B200K3_LARGE_ROUNDS 128
 
 /* header is shared with the second generation (B200k2Header) */
