@@ -263,7 +263,7 @@ def run_ours(args, rank, world, local_rank):
         traffic = json.load(open(os.path.join(ROOT, "profiles", "tile_kernel_traffic.json")))["bytes_per_launch"]
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "k_tile2", "achieved": achieved, "peak": peak,
+    roofline = {"bound": "hbm", "kernel": "k_tile3", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "per": "GPU", "launches": int(s.tile_passes),
                 "avg_launch_ms": s.gate_device_ms / max(1, s.tile_passes),
