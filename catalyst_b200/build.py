@@ -43,8 +43,8 @@ def reference_runtime_dir() -> str | None:
 def build_sv(force: bool = False, verbose: bool = False) -> str:
     srcs = [os.path.join(CSRC, "kernels.cu"), os.path.join(CSRC, "tile2.cu"),
             os.path.join(CSRC, "tile3.cu"), os.path.join(CSRC, "shard.cu"), os.path.join(CSRC, "simulator.cpp"),
-            os.path.join(CSRC, "comm.cpp")]
-    deps = srcs + [os.path.join(CSRC, "simulator.hpp"), os.path.join(CSRC, "comm.hpp"),
+            os.path.join(CSRC, "simulator_jit.cpp"), os.path.join(CSRC, "jit.cpp"), os.path.join(CSRC, "comm.cpp")]
+    deps = srcs + [os.path.join(CSRC, "simulator.hpp"), os.path.join(CSRC, "comm.hpp"), os.path.join(CSRC, "jit.hpp"),
                    os.path.join(INCLUDE, "b200sv.h"),
                    os.path.join(INCLUDE, "b200sv_kernels.h")]
     if not force and not _stale(LIB_SV, deps):

@@ -29,7 +29,7 @@ SYMBOLS = [
     "b200sv_sample", "b200sv_counts", "b200sv_measure", "b200sv_start_tape_recording",
     "b200sv_stop_tape_recording", "b200sv_tape_num_params", "b200sv_tape_num_observables",
     "b200sv_gradient", "b200sv_get_stats", "b200sv_reset_stats", "b200sv_set_timing",
-    "b200sv_flush", "b200sv_synchronize", "b200sv_device_pointer",
+    "b200sv_flush", "b200sv_synchronize", "b200sv_jit_wait", "b200sv_device_pointer",
     "b200sv_nccl_unique_id", "b200sv_world_size", "b200sv_rank", "b200sv_layout",
 ]
 
@@ -38,7 +38,9 @@ class Stats(C.Structure):
     _fields_ = [("gates_enqueued", C.c_int64), ("kernel_ops", C.c_int64),
                 ("tile_passes", C.c_int64), ("other_launches", C.c_int64),
                 ("gate_device_ms", C.c_double), ("algorithmic_bytes", C.c_double),
-                ("rounds", C.c_int64), ("exchanges", C.c_int64), ("exchange_bytes", C.c_double)]
+                ("rounds", C.c_int64), ("exchanges", C.c_int64), ("exchange_bytes", C.c_double),
+                ("jit_passes", C.c_int64), ("jit_compiled", C.c_int64), ("jit_pending", C.c_int64),
+                ("jit_compile_ms", C.c_double)]
 
 
 _lib = None
@@ -348,6 +350,10 @@ class B200Device:
 
     def synchronize(self):
         self._chk(self.L.b200sv_synchronize(self.h))
+
+    def jit_wait(self):
+        """Block until no specialised tile pass is being compiled in the background."""
+        self._chk(self.L.b200sv_jit_wait(self.h))
 
     def world_size(self) -> int:
         return int(self.L.b200sv_world_size(self.h))

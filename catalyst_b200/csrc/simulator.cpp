@@ -92,6 +92,16 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "stage_mib") o.stage_mib = as_int(o.stage_mib);
         else if (k == "comm") o.comm = v;
         else if (k == "kernel_gen") o.kernel_gen = (int)as_int(o.kernel_gen);
+        else if (k == "jit") {
+            if (v == "off") o.jit = 0;
+            else if (v == "auto") o.jit = 1;
+            else if (v == "always") o.jit = 2;
+            else o.jit = (int)as_int(o.jit);
+        }
+        else if (k == "jit_threshold") o.jit_threshold = (int)as_int(o.jit_threshold);
+        else if (k == "jit_regbits") o.jit_regbits = (int)as_int(o.jit_regbits);
+        else if (k == "jit_min_qubits") o.jit_min_qubits = (int)as_int(o.jit_min_qubits);
+        else if (k == "jit_dbuf") o.jit_dbuf = (int)as_int(o.jit_dbuf);
     }
     B200_FAIL_IF(o.world < 1 || (o.world & (o.world - 1)) || o.world > 64, "world_size must be a power of two (<= 64)");
     B200_FAIL_IF(o.rank < 0 || o.rank >= o.world, "rank out of range");
@@ -99,6 +109,9 @@ Options parse_kwargs(const char *kwargs)
     B200_FAIL_IF(o.stage_mib < 1, "stage_mib out of range");
     B200_FAIL_IF(o.tile_bits < 1 || o.tile_bits > B200K_MAX_TILE_BITS, "tile_bits out of range");
     B200_FAIL_IF(o.min_row_bits < 0, "min_row_bits out of range");
+    B200_FAIL_IF(o.jit < 0 || o.jit > 2, "jit must be 0/off, 1/auto or 2/always");
+    B200_FAIL_IF(o.jit_regbits < 1 || o.jit_regbits > 5, "jit_regbits out of range (1..5)");
+    B200_FAIL_IF(o.jit_threshold < 1, "jit_threshold out of range");
     o.min_row_bits = std::min(o.min_row_bits, o.tile_bits);
     return o;
 }
@@ -120,6 +133,13 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
     }
     B200_FAIL_IF(dev >= count, "b200sv: CUDA device ordinal out of range");
     cuda_device_ = dev;
+    jit_mode_ = opt_.jit;
+    if (const char *e = std::getenv("B200SV_JIT")) { // test / benchmark override of the kwarg
+        const std::string v(e);
+        jit_mode_ = v == "off" || v == "0" ? 0 : (v == "always" || v == "2" ? 2 : 1);
+    }
+    if (const char *e = std::getenv("B200SV_JIT_DBUF")) opt_.jit_dbuf = std::atoi(e);
+    if (const char *e = std::getenv("B200SV_JIT_REGBITS")) opt_.jit_regbits = std::max(1, std::min(5, std::atoi(e)));
     CUDA_CHECK(cudaSetDevice(dev));
     cudaStream_t st;
     CUDA_CHECK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
@@ -708,6 +728,7 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
             if (!((req >> p) & 1)) high.push_back(p);
         std::sort(high.begin(), high.end());
         if (dense_pass) launch_pass(vec, pass, high, c_cur);
+        else if (launch_pass_jit(vec, pass, high, c_cur)) {}
         else if (opt_.kernel_gen == 2) launch_pass2(vec, pass, high, c_cur);
         else launch_pass3(vec, pass, high, c_cur);
     }
@@ -2518,6 +2539,7 @@ int b200sv_reset_stats(b200sv_device *d) { B200_TRY(d->sim->reset_stats()) }
 int b200sv_set_timing(b200sv_device *d, int on) { B200_TRY(d->sim->set_timing(on != 0)) }
 int b200sv_flush(b200sv_device *d) { B200_TRY(d->sim->flush()) }
 int b200sv_synchronize(b200sv_device *d) { B200_TRY(d->sim->synchronize()) }
+int b200sv_jit_wait(b200sv_device *d) { B200_TRY(d->sim->jit_wait()) }
 void *b200sv_device_pointer(b200sv_device *d) { return d->sim->device_pointer(); }
 
 int b200sv_nccl_unique_id(char hex_out[257])

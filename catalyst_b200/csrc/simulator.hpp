@@ -94,6 +94,14 @@ struct Options {
     std::string comm;
     int64_t stage_mib = 1024; // staging memory of the global<->local qubit swap
     int kernel_gen = 3;       // tile kernel generation (2 = k_tile2, 3 = k_tile3)
+    // run-time specialised tile passes (jit.hpp): 0 = off, 1 = auto (a pass structure seen
+    // `jit_threshold` times is compiled in the background, the interpreter runs it until the
+    // kernel is ready), 2 = always (compile synchronously at first sight; tests)
+    int jit = 1;
+    int jit_threshold = 2;
+    int jit_regbits = 4;      // a thread owns 2^jit_regbits amplitudes in a specialised pass
+    int jit_min_qubits = 22;  // smaller local states stay on the interpreter
+    int jit_dbuf = 1;         // cp.async double-buffered tiles in specialised passes
 };
 
 class DeviceBuffer;
@@ -148,11 +156,12 @@ class Simulator {
     std::vector<double> gradient(const std::vector<int64_t> &train); // K x T row-major
 
     // instrumentation
-    b200sv_stats stats() const { return stats_; }
+    b200sv_stats stats() const; // simulator_jit.cpp (adds the process-wide JIT counters)
     void reset_stats();
     void set_timing(bool on) { timing_ = on; }
     void flush();
     void synchronize();
+    void jit_wait(); // block until no specialised pass is being compiled
     void *device_pointer();
     int world() const { return opt_.world; }
     int rank() const { return opt_.rank; }
@@ -192,6 +201,9 @@ class Simulator {
                       const std::vector<int> &req_high, int c);
     void launch_pass3(double *vec, const std::vector<const GateOp *> &ops,
                       const std::vector<int> &req_high, int c);
+    bool launch_pass_jit(double *vec, const std::vector<const GateOp *> &ops,
+                         const std::vector<int> &req_high, int c);
+    int jit_mode_ = 0;
     int pass_op_cap_ = 160;
     const double *upload_matrix(const CVec &m);
 

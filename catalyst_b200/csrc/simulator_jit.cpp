@@ -1,0 +1,574 @@
+// simulator_jit.cpp — plans one tile pass for the specialised (run-time compiled) kernel and emits its
+// CUDA source.  Same tile geometry, commutation rule and round structure as launch_pass3
+// (simulator.cpp); what differs is that a thread owns 2^NR amplitudes (NR = 4 by default instead of
+// 3, the interpreter's limit), every op whose non-diagonal bits fit the register bits runs in
+// registers (incl. 4-bit PAIRs such as DoubleExcitation and general Pauli rotations), and all
+// structure is folded into the instruction stream (jit.hpp explains why).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstring>
+#include <sstream>
+
+#include "jit.hpp"
+#include "simulator.hpp"
+
+namespace b200 {
+
+#define B200_FAIL_IF(cond, msg)                                                                    \
+    do {                                                                                           \
+        if (cond) throw ::b200::Error(std::string(msg));                                           \
+    } while (0)
+
+namespace {
+
+enum { CLS_ZERO = 0, CLS_ONE = 1, CLS_MONE = 2, CLS_GEN = 3 };
+
+struct JOp {
+    int kind = 0;               // GateOp::Kind
+    uint32_t x = 0, a = 0, b = 0; // tile-local target mask / patterns
+    uint32_t cin_m = 0, cin_v = 0; // control predicate inside the tile
+    uint64_t co_m = 0, co_v = 0;   // control predicate outside the tile (incl. rank bits)
+    uint32_t zin = 0;              // z mask inside the tile
+    uint64_t zo = 0;               // z mask outside the tile
+    int ny = 0;
+    int nm = 0, moff = 0;          // doubles in the parameter block
+    uint32_t cls = 0;              // 2 bits per double
+    double vals[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+};
+
+struct JRound {
+    uint32_t S = 0; // tile-local register bits
+    std::vector<JOp> ops;
+};
+
+struct JPlan {
+    int t = 0, c = 0, nr = 0, nl = 0, dbuf = 0;
+    std::vector<int> high;
+    uint64_t rank_base = 0;
+    std::vector<JRound> rounds;
+    int nm = 0;
+};
+
+inline int cls_of(double v) { return v == 0.0 ? CLS_ZERO : (v == 1.0 ? CLS_ONE : (v == -1.0 ? CLS_MONE : CLS_GEN)); }
+
+inline uint32_t fold3(uint32_t i) { return ((i >> 3) ^ (i >> 6) ^ (i >> 9) ^ (i >> 12)) & 7u; }
+inline uint32_t swz(uint32_t i) { return i ^ fold3(i); }
+
+template <typename T> void put(std::string &s, const T &v) { s.append(reinterpret_cast<const char *>(&v), sizeof(T)); }
+
+std::string hex32(uint32_t v)
+{
+    char b[16];
+    snprintf(b, sizeof b, "0x%xu", v);
+    return b;
+}
+std::string hex64(uint64_t v)
+{
+    char b[32];
+    snprintf(b, sizeof b, "0x%llxull", (unsigned long long)v);
+    return b;
+}
+
+// ---- expression builder: sum of sign * coef * operand with coefficient classes ---------------------
+struct Term {
+    int cls;
+    std::string coef; // expression of a GEN coefficient
+    std::string opnd;
+    bool neg;
+};
+
+std::string lin(const std::vector<Term> &terms)
+{
+    std::string acc;
+    // operands with coefficient +-1 first: they start the FMA chain for free
+    std::vector<const Term *> ord;
+    for (auto &t : terms)
+        if (t.cls == CLS_ONE || t.cls == CLS_MONE) ord.push_back(&t);
+    for (auto &t : terms)
+        if (t.cls == CLS_GEN) ord.push_back(&t);
+    for (const Term *t : ord) {
+        bool neg = t->neg;
+        if (t->cls == CLS_MONE) neg = !neg;
+        if (t->cls != CLS_GEN) {
+            if (acc.empty()) acc = neg ? "(-" + t->opnd + ")" : t->opnd;
+            else acc = "(" + acc + (neg ? " - " : " + ") + t->opnd + ")";
+        }
+        else {
+            if (acc.empty()) acc = neg ? "(-" + t->coef + " * " + t->opnd + ")" : "(" + t->coef + " * " + t->opnd + ")";
+            else acc = "fma(" + std::string(neg ? "-" : "") + t->coef + ", " + t->opnd + ", " + acc + ")";
+        }
+    }
+    return acc.empty() ? "0.0" : acc;
+}
+
+struct Coef { // a complex coefficient: literal classes + expressions
+    int cr, ci;
+    std::string er, ei;
+};
+
+// (re, im) of coef * (xr, xi) [+ coef2 * (yr, yi)]
+void cmul_terms(std::vector<Term> &re, std::vector<Term> &im, const Coef &k, const std::string &xr, const std::string &xi)
+{
+    re.push_back({k.cr, k.er, xr, false});
+    re.push_back({k.ci, k.ei, xi, true});
+    im.push_back({k.cr, k.er, xi, false});
+    im.push_back({k.ci, k.ei, xr, false});
+}
+
+// ---- CUDA source of one pass ---------------------------------------------------------------------
+std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
+{
+    const int t = P.t, c = P.c, nr = P.nr;
+    const int tbits = t - nr;          // log2(threads)
+    const uint32_t TT = 1u << tbits;
+    const uint32_t nelem = 1u << t;
+    const uint32_t niter = nelem / TT; // = 2^nr
+    const uint32_t nslots = 1u << nr;
+    const uint64_t ntiles = 1ull << (P.nl - t);
+    std::ostringstream o;
+    auto mref = [&](int k) { return "P.m[" + std::to_string(k) + "]"; };
+    // global offset of tile-local index e (an OR over disjoint bit sets)
+    auto off_of = [&](uint32_t e) -> uint64_t {
+        uint64_t r = e & ((1u << c) - 1u);
+        for (size_t h = 0; h < P.high.size(); h++)
+            if ((e >> (c + h)) & 1u) r |= 1ull << P.high[h];
+        return r;
+    };
+
+    o << "// generated by catalyst_b200/csrc/simulator_jit.cpp: t=" << t << " c=" << c << " nr=" << nr
+      << " rounds=" << P.rounds.size() << "\n";
+    o << "typedef double2 cplx;\n";
+    o << "struct Params { double m[" << std::max(1, P.nm) << "]; };\n";
+    o << "__device__ __forceinline__ void cpa16(void *d, const void *s) {\n"
+         "  const unsigned a = (unsigned)__cvta_generic_to_shared(d);\n"
+         "  asm volatile(\"cp.async.cg.shared.global [%0], [%1], 16;\\n\" :: \"r\"(a), \"l\"(s) : \"memory\");\n}\n";
+    o << "__device__ __forceinline__ unsigned long long base_of(unsigned long long tile) {\n"
+         "  unsigned long long b = tile << "
+      << c << ";\n";
+    for (size_t h = 0; h < P.high.size(); h++) {
+        const int p = P.high[h];
+        // insert a zero at position p unless the positions so far are contiguous from c (then the
+        // shift by c already made room)
+        if (p == c + (int)h) {
+            // contiguous with the low block: make room by shifting everything above
+            o << "  b = ((b >> " << p << ") << " << (p + 1) << ") | (b & " << hex64((1ull << p) - 1ull) << ");\n";
+        }
+        else
+            o << "  b = ((b >> " << p << ") << " << (p + 1) << ") | (b & " << hex64((1ull << p) - 1ull) << ");\n";
+    }
+    o << "  return b;\n}\n";
+    const int minb = P.dbuf ? std::max(1, std::min(8, (227 * 1024) / (int)(2 * 16 * nelem + 1024)))
+                            : std::max(1, std::min(8, (227 * 1024) / (int)(16 * nelem + 1024)));
+    // register budget: leave the compiler room for 2^nr amplitudes (4 registers each) + temporaries
+    int minb_regs = (int)(65536 / (TT * (uint32_t)(4 * nslots + 56)));
+    const int launch_minb = std::max(1, std::min(minb, std::max(1, minb_regs)));
+    o << "extern \"C\" __global__ void __launch_bounds__(" << TT << ", " << launch_minb << ") " << name
+      << "(cplx *__restrict__ psi, const __grid_constant__ Params P)\n{\n";
+    o << "  extern __shared__ __align__(16) cplx smem[];\n";
+    o << "  const unsigned tid = threadIdx.x;\n";
+    // off_tid: tid covers tile-local bits 0..tbits-1
+    {
+        o << "  const unsigned long long off_tid = (unsigned long long)(tid & " << hex32((1u << std::min(c, tbits)) - 1u) << ")";
+        for (int bpos = c; bpos < tbits; bpos++)
+            o << " | ((unsigned long long)((tid >> " << bpos << ") & 1u) << " << P.high[bpos - c] << ")";
+        o << ";\n";
+    }
+    o << "  const unsigned swtid = tid ^ (((tid >> 3) ^ (tid >> 6) ^ (tid >> 9) ^ (tid >> 12)) & 7u);\n";
+    auto slot_expr = [&](const std::string &sw, uint32_t pat) { // smem index of (thread base | pattern)
+        const uint32_t k = swz(pat), kl = k & 7u, kh = k & ~7u;
+        std::string e = kl ? "(" + sw + " ^ " + std::to_string(kl) + "u)" : sw;
+        if (kh) e = "(" + e + " + " + std::to_string(kh) + "u)";
+        return e;
+    };
+    if (P.dbuf) {
+        o << "  auto prefetch = [&](unsigned long long tile, cplx *buf) {\n"
+             "    const cplx *src = psi + (base_of(tile) | off_tid);\n";
+        for (uint32_t k = 0; k < niter; k++)
+            o << "    cpa16(&buf[" << slot_expr("swtid", k * TT) << "], src + " << hex64(off_of(k * TT)) << ");\n";
+        o << "    asm volatile(\"cp.async.commit_group;\\n\" ::: \"memory\");\n  };\n";
+        o << "  unsigned cur = 0;\n";
+        o << "  if (blockIdx.x < " << hex64(ntiles) << ") prefetch(blockIdx.x, smem);\n";
+    }
+    o << "  for (unsigned long long tile = blockIdx.x; tile < " << hex64(ntiles) << "; tile += gridDim.x) {\n";
+    o << "    const unsigned long long base = base_of(tile);\n";
+    o << "    const unsigned long long obase = base | " << hex64(P.rank_base) << ";\n";
+    o << "    cplx *__restrict__ tp = psi + (base | off_tid);\n";
+    if (P.dbuf) {
+        o << "    cplx *__restrict__ s = smem + cur * " << nelem << "u;\n";
+        o << "    { const unsigned long long next = tile + gridDim.x;\n"
+             "      if (next < "
+          << hex64(ntiles) << ") { prefetch(next, smem + (cur ^ 1u) * " << nelem
+          << "u); asm volatile(\"cp.async.wait_group 1;\\n\" ::: \"memory\"); }\n"
+             "      else asm volatile(\"cp.async.wait_group 0;\\n\" ::: \"memory\"); }\n";
+    }
+    else {
+        o << "    cplx *__restrict__ s = smem;\n";
+        for (uint32_t k = 0; k < niter; k++)
+            o << "    s[" << slot_expr("swtid", k * TT) << "] = tp[" << hex64(off_of(k * TT)) << "];\n";
+    }
+    o << "    __syncthreads();\n";
+
+
+    // ---- rounds ------------------------------------------------------------------------------------
+    int rix = 0;
+    for (const JRound &R : P.rounds) {
+        std::vector<int> rb, q;
+        for (int b = 0; b < t; b++) ((R.S >> b) & 1u ? rb : q).push_back(b);
+        // thread bit k -> tile-local position qq[k]; the three lowest thread bits go to positions that
+        // are distinct mod 3 where possible, so that the 8 threads of a quarter warp hit 8 different
+        // 16-byte bank groups under the XOR-fold swizzle
+        std::vector<int> qq;
+        {
+            std::vector<char> used(q.size(), 0);
+            bool res[3] = {false, false, false};
+            for (size_t i = 0; i < q.size() && qq.size() < 3; i++)
+                if (!res[q[i] % 3]) {
+                    res[q[i] % 3] = true;
+                    used[i] = 1;
+                    qq.push_back(q[i]);
+                }
+            std::sort(qq.begin(), qq.end());
+            for (size_t i = 0; i < q.size(); i++)
+                if (!used[i]) qq.push_back(q[i]);
+        }
+        std::vector<uint32_t> pat(nslots, 0);
+        for (uint32_t k = 0; k < nslots; k++)
+            for (int j = 0; j < nr; j++)
+                if ((k >> j) & 1u) pat[k] |= 1u << rb[j];
+        auto slot_of = [&](uint32_t p) -> uint32_t { // register pattern (subset of S) -> slot number
+            uint32_t k = 0;
+            for (int j = 0; j < nr; j++)
+                if ((p >> rb[j]) & 1u) k |= 1u << j;
+            return k;
+        };
+        o << "    { // round " << rix++ << ": register bits";
+        for (int b : rb) o << " " << b;
+        o << "\n";
+        // ib: deposit the thread bits (runs of consecutive positions move together)
+        o << "      const unsigned ib = 0u";
+        for (int k = 0; k < (int)qq.size();) {
+            int len = 1;
+            while (k + len < (int)qq.size() && qq[k + len] == qq[k] + len) len++;
+            const uint32_t m = ((1u << len) - 1u) << k;
+            const int sh = qq[k] - k;
+            o << " | ((tid & " << hex32(m) << ")" << (sh > 0 ? " << " + std::to_string(sh) : (sh < 0 ? " >> " + std::to_string(-sh) : "")) << ")";
+            k += len;
+        }
+        o << ";\n";
+        o << "      const unsigned sb = ib ^ (((ib >> 3) ^ (ib >> 6) ^ (ib >> 9) ^ (ib >> 12)) & 7u);\n";
+        for (uint32_t k = 0; k < nslots; k++) {
+            o << "      double v" << k << "r, v" << k << "i; { const cplx q_ = s[" << slot_expr("sb", pat[k]) << "]; v" << k
+              << "r = q_.x; v" << k << "i = q_.y; }\n";
+        }
+        auto V = [&](uint32_t k, char part) { return "v" + std::to_string(k) + part; };
+        for (const JOp &g : R.ops) {
+            // run-time condition: outside-the-tile controls (uniform per tile) and thread-bit controls
+            std::string cond;
+            if (g.co_m) cond = "((obase & " + hex64(g.co_m) + ") == " + hex64(g.co_v) + ")";
+            const uint32_t tcm = g.cin_m & ~R.S, tcv = g.cin_v & ~R.S;
+            if (tcm) cond += std::string(cond.empty() ? "" : " && ") + "((ib & " + hex32(tcm) + ") == " + hex32(tcv) + ")";
+            const uint32_t rcm = g.cin_m & R.S, rcv = g.cin_v & R.S;
+            auto slot_on = [&](uint32_t k) { return (pat[k] & rcm) == rcv; };
+            auto coef = [&](int idx) -> Coef { // complex coefficient idx of the op's parameter doubles
+                return Coef{(int)((g.cls >> (4 * idx)) & 3u), (int)((g.cls >> (4 * idx + 2)) & 3u),
+                            mref(g.moff + 2 * idx), mref(g.moff + 2 * idx + 1)};
+            };
+            std::ostringstream b; // op body
+            if (g.kind == GateOp::PAIR) {
+                const Coef m00 = coef(0), m01 = coef(1), m10 = coef(2), m11 = coef(3);
+                for (uint32_t k = 0; k < nslots; k++) {
+                    if ((pat[k] & g.x) || !slot_on(k)) continue;
+                    const uint32_t A = slot_of(pat[k] | g.a), B = slot_of(pat[k] | g.b);
+                    std::vector<Term> xr, xi, yr, yi;
+                    cmul_terms(xr, xi, m00, "ar", "ai");
+                    cmul_terms(xr, xi, m01, "br", "bi");
+                    cmul_terms(yr, yi, m10, "ar", "ai");
+                    cmul_terms(yr, yi, m11, "br", "bi");
+                    b << "        { const double ar = " << V(A, 'r') << ", ai = " << V(A, 'i') << ", br = " << V(B, 'r')
+                      << ", bi = " << V(B, 'i') << ";\n";
+                    b << "          " << V(A, 'r') << " = " << lin(xr) << "; " << V(A, 'i') << " = " << lin(xi) << ";\n";
+                    b << "          " << V(B, 'r') << " = " << lin(yr) << "; " << V(B, 'i') << " = " << lin(yi) << "; }\n";
+                }
+            }
+            else if (g.kind == GateOp::PHASE) {
+                const Coef e = coef(0);
+                for (uint32_t k = 0; k < nslots; k++) {
+                    if (!slot_on(k)) continue;
+                    std::vector<Term> re, im;
+                    cmul_terms(re, im, e, "ar", "ai");
+                    b << "        { const double ar = " << V(k, 'r') << ", ai = " << V(k, 'i') << "; " << V(k, 'r') << " = "
+                      << lin(re) << "; " << V(k, 'i') << " = " << lin(im) << "; }\n";
+                }
+            }
+            else if (g.kind == GateOp::PARITY) {
+                const uint32_t tz = g.zin & ~R.S, rz = g.zin & R.S;
+                Coef e[2] = {coef(0), coef(1)};
+                if (tz || g.zo) {
+                    b << "        const bool pz_ = ((";
+                    if (tz) b << "__popc(ib & " << hex32(tz) << ")";
+                    if (tz && g.zo) b << " + ";
+                    if (g.zo) b << "__popcll(obase & " << hex64(g.zo) << ")";
+                    b << ") & 1) != 0;\n";
+                    b << "        const double ear = pz_ ? " << mref(g.moff + 2) << " : " << mref(g.moff) << ", eai = pz_ ? "
+                      << mref(g.moff + 3) << " : " << mref(g.moff + 1) << ", ebr = pz_ ? " << mref(g.moff) << " : "
+                      << mref(g.moff + 2) << ", ebi = pz_ ? " << mref(g.moff + 1) << " : " << mref(g.moff + 3) << ";\n";
+                    e[0] = Coef{CLS_GEN, CLS_GEN, "ear", "eai"};
+                    e[1] = Coef{CLS_GEN, CLS_GEN, "ebr", "ebi"};
+                }
+                for (uint32_t k = 0; k < nslots; k++) {
+                    if (!slot_on(k)) continue;
+                    const Coef &ek = e[__builtin_popcount(pat[k] & rz) & 1];
+                    std::vector<Term> re, im;
+                    cmul_terms(re, im, ek, "ar", "ai");
+                    b << "        { const double ar = " << V(k, 'r') << ", ai = " << V(k, 'i') << "; " << V(k, 'r') << " = "
+                      << lin(re) << "; " << V(k, 'i') << " = " << lin(im) << "; }\n";
+                }
+            }
+            else { // PAULIROT with all non-diagonal bits in registers
+                const uint32_t tz = g.zin & ~R.S, rz = g.zin & R.S;
+                const uint32_t top = 1u << (31 - __builtin_clz(g.x));
+                std::string sn = mref(g.moff + 1);
+                if (tz || g.zo) {
+                    b << "        const bool pz_ = ((";
+                    if (tz) b << "__popc(ib & " << hex32(tz) << ")";
+                    if (tz && g.zo) b << " + ";
+                    if (g.zo) b << "__popcll(obase & " << hex64(g.zo) << ")";
+                    b << ") & 1) != 0;\n";
+                    b << "        const double sn_ = pz_ ? -" << sn << " : " << sn << ";\n";
+                    sn = "sn_";
+                }
+                const std::string cs = mref(g.moff);
+                // W(v, e) = -i * i^e * v, as (re, im) expressions with sign
+                auto W = [&](const char *r, const char *i_, int e, std::string &wr, bool &nr_, std::string &wi, bool &ni_) {
+                    switch ((e + 3) & 3) {
+                    case 0: wr = r; nr_ = false; wi = i_; ni_ = false; break;
+                    case 1: wr = i_; nr_ = true; wi = r; ni_ = false; break;
+                    case 2: wr = r; nr_ = true; wi = i_; ni_ = true; break;
+                    default: wr = i_; nr_ = false; wi = r; ni_ = true; break;
+                    }
+                };
+                for (uint32_t k = 0; k < nslots; k++) {
+                    if ((pat[k] & top) || !slot_on(k)) continue;
+                    const uint32_t A = k, B = slot_of((pat[k] ^ g.x) & R.S);
+                    const int eA = g.ny + 2 * (__builtin_popcount(pat[A] & rz) & 1);
+                    const int eB = g.ny + 2 * (__builtin_popcount(pat[B] & rz) & 1);
+                    std::string wr, wi;
+                    bool nr_, ni_;
+                    b << "        { const double ar = " << V(A, 'r') << ", ai = " << V(A, 'i') << ", br = " << V(B, 'r')
+                      << ", bi = " << V(B, 'i') << ";\n";
+                    W("br", "bi", eB, wr, nr_, wi, ni_); // new_A = cs * A + sn * W(B, eB)
+                    b << "          " << V(A, 'r') << " = fma(" << (nr_ ? "-" : "") << sn << ", " << wr << ", " << cs << " * ar); "
+                      << V(A, 'i') << " = fma(" << (ni_ ? "-" : "") << sn << ", " << wi << ", " << cs << " * ai);\n";
+                    W("ar", "ai", eA, wr, nr_, wi, ni_);
+                    b << "          " << V(B, 'r') << " = fma(" << (nr_ ? "-" : "") << sn << ", " << wr << ", " << cs << " * br); "
+                      << V(B, 'i') << " = fma(" << (ni_ ? "-" : "") << sn << ", " << wi << ", " << cs << " * bi); }\n";
+                }
+            }
+            const std::string body = b.str();
+            if (body.empty()) continue;
+            if (!cond.empty()) o << "      if (" << cond << ") {\n" << body << "      }\n";
+            else o << "      {\n" << body << "      }\n";
+        }
+        for (uint32_t k = 0; k < nslots; k++)
+            o << "      s[" << slot_expr("sb", pat[k]) << "] = make_double2(v" << k << "r, v" << k << "i);\n";
+        o << "    }\n    __syncthreads();\n";
+    }
+    // ---- store -------------------------------------------------------------------------------------
+    for (uint32_t k = 0; k < niter; k++)
+        o << "    tp[" << hex64(off_of(k * TT)) << "] = s[" << slot_expr("swtid", k * TT) << "];\n";
+    o << "    __syncthreads();\n";
+    if (P.dbuf) o << "    cur ^= 1u;\n";
+    o << "  }\n}\n";
+
+    K.name = name;
+    K.threads = (int)TT;
+    K.smem_bytes = (int)((P.dbuf ? 2 : 1) * 16 * nelem);
+    K.param_doubles = std::max(1, P.nm);
+    return o.str();
+}
+
+} // namespace
+
+// Returns false when the pass must stay on the interpreted kernel (JIT off or unavailable, kernel not
+// compiled yet, an op that does not fit a register round, tile too small).
+bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &ops, const std::vector<int> &high, int c)
+{
+    if (jit_mode_ == 0) return false;
+    const int t = c + (int)high.size();
+    // 'always' (tests) specialises every pass, however small; 'auto' only where it can pay off
+    const bool always = jit_mode_ == 2;
+    const int nr = std::min(opt_.jit_regbits, always ? t - 1 : t - 5);
+    if (nr < (always ? 1 : 3) || t > 13 || (!always && nl_ < opt_.jit_min_qubits)) return false;
+    jit::Engine &E = jit::Engine::get();
+    if (!E.available()) {
+        B200_FAIL_IF(jit_mode_ == 2, "jit='always' but NVRTC / the driver API could not be loaded");
+        return false;
+    }
+    int loc[64];
+    for (int p = 0; p < 64; p++) loc[p] = p < c ? p : -1;
+    for (size_t h = 0; h < high.size(); h++) loc[high[h]] = c + (int)h;
+    auto split = [&](uint64_t mask, uint32_t &inside, uint64_t &outside) {
+        inside = 0;
+        outside = 0;
+        while (mask) {
+            const int p = __builtin_ctzll(mask);
+            mask &= mask - 1;
+            if (loc[p] >= 0) inside |= 1u << loc[p];
+            else outside |= 1ull << p;
+        }
+    };
+
+    JPlan P;
+    P.t = t;
+    P.c = c;
+    P.nr = nr;
+    P.nl = (int)nl_;
+    P.high = high;
+    P.rank_base = rank_base_;
+    {
+        const uint64_t ntiles = 1ull << (nl_ - t);
+        const int per_sm = std::max(1, (227 * 1024) / (2 * 16 * (1 << t) + 1024));
+        P.dbuf = opt_.jit_dbuf == 2 || // 2 = forced (tests)
+                 (opt_.jit_dbuf && ntiles >= 2ull * (uint64_t)E.sm_count(cuda_device_) * (uint64_t)per_sm);
+    }
+    std::vector<double> mvals;
+    std::vector<const GateOp *> rem(ops.begin(), ops.end()), deferred, taken;
+    while (!rem.empty()) {
+        uint64_t blockedX = 0, blockedZ = 0;
+        uint32_t S = 0;
+        deferred.clear();
+        taken.clear();
+        for (const GateOp *g : rem) {
+            const uint64_t xs = g->xmask, zs = g->zsupport();
+            bool fits = false;
+            if (!(xs & (blockedX | blockedZ)) && !(zs & blockedX)) {
+                if (g->kind == GateOp::DENSE) return false;
+                uint32_t xin;
+                uint64_t xout;
+                split(xs, xin, xout);
+                if (xout) return false;
+                if (__builtin_popcount(xin) > nr) return false;
+                if (__builtin_popcount(S | xin) <= nr) {
+                    S |= xin;
+                    fits = true;
+                }
+            }
+            if (fits) taken.push_back(g);
+            else {
+                deferred.push_back(g);
+                blockedX |= xs;
+                blockedZ |= zs;
+            }
+        }
+        for (int b = t - 1; b >= 0 && __builtin_popcount(S) < nr; b--) // pad with the highest free tile bits
+            if (!(S & (1u << b))) S |= 1u << b;
+        JRound R;
+        R.S = S;
+        for (const GateOp *gp : taken) {
+            const GateOp &g = *gp;
+            JOp o;
+            o.kind = (int)g.kind;
+            uint64_t dummy;
+            split(g.xmask, o.x, dummy);
+            split(g.a, o.a, dummy);
+            split(g.b, o.b, dummy);
+            split(g.cmask, o.cin_m, o.co_m);
+            split(g.cval, o.cin_v, o.co_v);
+            if (g.kind == GateOp::PARITY || g.kind == GateOp::PAULIROT) split(g.zmask, o.zin, o.zo);
+            o.ny = g.ny & 3;
+            switch (g.kind) {
+            case GateOp::PAIR:
+                o.nm = 8;
+                for (int q = 0; q < 4; q++) {
+                    o.vals[2 * q] = g.m[q].real();
+                    o.vals[2 * q + 1] = g.m[q].imag();
+                }
+                break;
+            case GateOp::PHASE:
+                o.nm = 2;
+                o.vals[0] = g.m[0].real();
+                o.vals[1] = g.m[0].imag();
+                break;
+            case GateOp::PARITY:
+                o.nm = 4;
+                o.vals[0] = g.m[0].real(); o.vals[1] = g.m[0].imag();
+                o.vals[2] = g.m[1].real(); o.vals[3] = g.m[1].imag();
+                break;
+            default: // PAULIROT: (cos, sin)
+                o.nm = 2;
+                o.vals[0] = g.m[0].real();
+                o.vals[1] = g.m[0].imag();
+                break;
+            }
+            o.cls = 0;
+            const bool literal = g.kind == GateOp::PAIR || g.kind == GateOp::PHASE ||
+                                 (g.kind == GateOp::PARITY && !(o.zin & ~S) && !o.zo);
+            for (int q = 0; q < o.nm; q++) o.cls |= (uint32_t)(literal ? cls_of(o.vals[q]) : CLS_GEN) << (2 * q);
+            o.moff = (int)mvals.size();
+            for (int q = 0; q < o.nm; q++) mvals.push_back(o.vals[q]);
+            R.ops.push_back(o);
+        }
+        P.rounds.push_back(std::move(R));
+        rem.swap(deferred);
+    }
+    P.nm = (int)mvals.size();
+    if (P.nm * 8 + 16 > 32000) return false; // kernel parameter block limit
+
+    // structural key
+    std::string key;
+    key.reserve(64 + 64 * ops.size());
+    put(key, (int)3); // generator version
+    put(key, P.t); put(key, P.c); put(key, P.nr); put(key, P.nl); put(key, P.dbuf); put(key, P.rank_base);
+    for (int h : P.high) put(key, (uint8_t)h);
+    for (const JRound &R : P.rounds) {
+        put(key, (uint32_t)0xffffffffu);
+        put(key, R.S);
+        for (const JOp &o : R.ops) {
+            put(key, (uint8_t)o.kind); put(key, (uint8_t)o.ny);
+            put(key, o.x); put(key, o.a); put(key, o.b); put(key, o.cin_m); put(key, o.cin_v);
+            put(key, o.co_m); put(key, o.co_v); put(key, o.zin); put(key, o.zo); put(key, o.cls);
+        }
+    }
+    const jit::Kernel *K = E.lookup(cuda_device_, key, jit_mode_ == 2 ? 1 : opt_.jit_threshold, jit_mode_ == 2,
+                                    [&](jit::Kernel &k) {
+                                        const uint64_t h = std::hash<std::string>{}(key);
+                                        char name[64];
+                                        snprintf(name, sizeof name, "k_pass_%016llx", (unsigned long long)h);
+                                        return generate(P, k, name);
+                                    });
+    if (!K) {
+        B200_FAIL_IF(jit_mode_ == 2, "jit='always': specialised pass failed to compile (set B200SV_JIT_VERBOSE=1)");
+        return false;
+    }
+    const uint64_t ntiles = 1ull << (nl_ - t);
+    uint64_t grid = (uint64_t)E.sm_count(cuda_device_) * (uint64_t)K->ctas_per_sm;
+    if (grid > ntiles) grid = ntiles;
+    if (mvals.empty()) mvals.push_back(0.0);
+    const int rc = E.launch(*K, (unsigned)grid, vec, mvals.data(), stream_);
+    B200_FAIL_IF(rc != 0, "cuLaunchKernel of a specialised pass failed with driver error " + std::to_string(rc));
+    stats_.tile_passes++;
+    stats_.jit_passes++;
+    stats_.kernel_ops += (int64_t)ops.size();
+    stats_.rounds += (int64_t)P.rounds.size();
+    return true;
+}
+
+b200sv_stats Simulator::stats() const
+{
+    b200sv_stats s = stats_;
+    if (jit_mode_ != 0) {
+        const jit::Counters c = jit::Engine::get().counters();
+        s.jit_compiled = c.compiled;
+        s.jit_pending = c.pending;
+        s.jit_compile_ms = c.compile_ms;
+    }
+    return s;
+}
+
+void Simulator::jit_wait()
+{
+    if (jit_mode_ != 0) jit::Engine::get().wait_all();
+}
+
+} // namespace b200

@@ -121,12 +121,20 @@ typedef struct b200sv_stats {
     int64_t rounds;           /* shared-memory round trips inside the tile passes */
     int64_t exchanges;        /* global<->local qubit swaps (each = one personalised all-to-all) */
     double exchange_bytes;    /* bytes this rank sent over NVLink in those swaps */
+    int64_t jit_passes;       /* tile passes that ran on a run-time specialised kernel */
+    int64_t jit_compiled;     /* process-wide: specialised kernels compiled so far */
+    int64_t jit_pending;      /* process-wide: compilations still running in the background */
+    double jit_compile_ms;    /* process-wide: NVRTC time spent so far (sum over pool threads) */
 } b200sv_stats;
 int b200sv_get_stats(b200sv_device *d, b200sv_stats *out);
 int b200sv_reset_stats(b200sv_device *d);
 int b200sv_set_timing(b200sv_device *d, int on); /* record CUDA events around each flush */
 int b200sv_flush(b200sv_device *d);              /* launch everything queued (no host sync) */
 int b200sv_synchronize(b200sv_device *d);        /* flush + wait */
+/* Tile passes whose structure recurs are compiled at run time into specialised kernels (kwarg
+ * 'jit': 'off' | 'auto' (default) | 'always'; catalyst_b200/csrc/jit.hpp).  In 'auto' mode the
+ * compilation runs in the background; this call blocks until none is pending (benchmarks). */
+int b200sv_jit_wait(b200sv_device *d);
 /* device pointer of the local shard (for benchmarks / zero-copy consumers) */
 void *b200sv_device_pointer(b200sv_device *d);
 

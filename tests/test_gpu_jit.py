@@ -1,0 +1,155 @@
+"""Run-time specialised tile passes (catalyst_b200/csrc/jit.hpp, simulator_jit.cpp) against the CPU
+oracle: every pass of these circuits is compiled by NVRTC into a straight-line sm_100a kernel
+(`jit='always'`), and the statistics prove that the specialised kernels, not the interpreted one,
+produced the result.  Same tolerance as the interpreted path: 1e-12 on amplitudes."""
+import numpy as np
+import pytest
+
+from dsl import apply_ops, build_obs, random_circuit, random_state
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-12
+
+NO_DENSE = ["PauliX", "PauliY", "PauliZ", "Hadamard", "S", "T", "PhaseShift", "RX", "RY", "RZ", "Rot", "CNOT",
+            "CY", "CZ", "SWAP", "ISWAP", "PSWAP", "IsingXX", "IsingYY", "IsingXY", "IsingZZ", "SingleExcitation",
+            "DoubleExcitation", "ControlledPhaseShift", "CRX", "CRY", "CRZ", "CRot", "CSWAP", "Toffoli", "MultiRZ",
+            "GlobalPhase", "PCPhase", "PauliRot"]
+
+
+FIT2 = [g for g in NO_DENSE if g not in ("DoubleExcitation", "PauliRot")]
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    from catalyst_b200 import capi
+    return capi
+
+
+def _run(gpu, oracle_mod, n, ops, init=None, **kw):
+    o = oracle_mod.OracleDevice(n)
+    d = gpu.B200Device(n, jit="always", **kw)
+    if init is not None:
+        o.set_state(init, list(range(n)))
+        d.set_state(init, list(range(n)))
+    apply_ops(o, ops)
+    apply_ops(d, ops)
+    a, b = o.state(), d.state()
+    return d, float(np.max(np.abs(a - b)))
+
+
+CFG = [dict(), dict(jit_regbits=3), dict(jit_regbits=5), dict(jit_dbuf=2), dict(tile_bits=6, min_row_bits=2),
+       dict(tile_bits=12, jit_dbuf=2), dict(tile_bits=9, jit_regbits=2, min_row_bits=3, jit_dbuf=2)]
+
+
+@pytest.mark.parametrize("cfg", range(len(CFG)))
+@pytest.mark.parametrize("n,seed", [(3, 1), (6, 2), (9, 3), (12, 4), (14, 5), (16, 6)])
+def test_jit_random_circuit_state(gpu, oracle_mod, n, seed, cfg):
+    # gates with at most two non-diagonal bits fit the register rounds of every configuration:
+    # every pass must run on a specialised kernel
+    ops = random_circuit(seed, n, 50, names=FIT2)
+    d, err = _run(gpu, oracle_mod, n, ops, init=random_state(seed + 900, n), **CFG[cfg])
+    s = d.stats()
+    assert err < TOL
+    assert s.jit_passes == s.tile_passes > 0, (s.jit_passes, s.tile_passes)
+
+
+@pytest.mark.parametrize("cfg", range(len(CFG)))
+@pytest.mark.parametrize("n,seed", [(6, 2), (9, 3), (12, 4), (15, 5)])
+def test_jit_random_circuit_all_gates(gpu, oracle_mod, n, seed, cfg):
+    # a pass holding an op with more non-diagonal bits than register bits (DoubleExcitation, long
+    # Pauli words) legitimately stays on the interpreter: parity must hold either way
+    ops = random_circuit(seed, n, 60, names=NO_DENSE)
+    d, err = _run(gpu, oracle_mod, n, ops, init=random_state(seed + 900, n), **CFG[cfg])
+    assert err < TOL
+
+
+def test_jit_mixed_with_dense(gpu, oracle_mod):
+    # MatrixOperation (k >= 2) passes stay on the generic kernel, everything else is specialised
+    n = 13
+    ops = random_circuit(11, n, 80)
+    d, err = _run(gpu, oracle_mod, n, ops, init=random_state(3, n))
+    assert err < TOL
+    assert d.stats().jit_passes > 0
+
+
+@pytest.mark.parametrize("n", [18, 21])
+def test_jit_qft_random_layers(gpu, oracle_mod, n):
+    from catalyst_b200 import workloads
+    ops = workloads.c3_qft_random(n, layers=3)
+    d, err = _run(gpu, oracle_mod, n, ops)
+    s = d.stats()
+    assert err < TOL
+    assert s.jit_passes == s.tile_passes > 0
+
+
+@pytest.mark.skipif("B200SV_JIT" in __import__("os").environ, reason="the environment overrides the jit kwarg")
+def test_jit_auto_mode_switches_over(gpu, oracle_mod):
+    """'auto': the first sightings run interpreted, the structure is compiled in the background, later
+    runs use the specialised kernels; the results never change beyond rounding."""
+    from catalyst_b200 import workloads
+    n = 16
+    ops = workloads.c3_qft_random(n, layers=2)
+    o = oracle_mod.OracleDevice(n)
+    apply_ops(o, ops)
+    ref = o.state()
+    d = gpu.B200Device(n, jit="auto", jit_min_qubits=10, jit_threshold=2)
+    seen = []
+    for rep in range(4):
+        d.set_basis_state([0] * n, list(range(n)))
+        d.reset_stats()
+        apply_ops(d, ops)
+        assert np.max(np.abs(d.state() - ref)) < TOL
+        seen.append(int(d.stats().jit_passes))
+        d.jit_wait()
+    assert seen[0] == 0 and seen[-1] > 0, seen
+
+
+def test_jit_new_parameters_reuse_kernels(gpu, oracle_mod):
+    n = 12
+    rng = np.random.default_rng(5)
+    d = gpu.B200Device(n, jit="always")
+    compiled = []
+    for rep in range(3):
+        th = rng.uniform(-3, 3, size=3 * n)
+        ops = [("RX", [th[w]], [w]) for w in range(n)] + [("CNOT", [], [w, (w + 1) % n]) for w in range(n)]
+        ops += [("RZ", [th[n + w]], [w]) for w in range(n)] + [("IsingXY", [th[2 * n + w]], [w, (w + 5) % n]) for w in range(n)]
+        o = oracle_mod.OracleDevice(n)
+        apply_ops(o, ops)
+        d.set_basis_state([0] * n, list(range(n)))
+        apply_ops(d, ops)
+        assert np.max(np.abs(d.state() - o.state())) < TOL
+        compiled.append(int(d.stats().jit_compiled))
+    assert compiled[1] == compiled[0] and compiled[2] == compiled[0], compiled
+
+
+def test_jit_gradient_and_expval(gpu, oracle_mod):
+    n = 12
+    from catalyst_b200 import workloads
+    ops, obs = workloads.c2_qaoa_maxcut(n=n, layers=2, seed=3)
+    d = gpu.B200Device(n, jit="always")
+    o = oracle_mod.OracleDevice(n)
+    d.start_tape(); o.start_tape()
+    apply_ops(d, ops); apply_ops(o, ops)
+    ed, eo = d.expval(build_obs(d, obs)), o.expval(build_obs(o, obs))
+    d.stop_tape(); o.stop_tape()
+    assert abs(ed - eo) < 1e-12
+    assert np.max(np.abs(d.gradient() - o.gradient())) < 1e-11
+    assert d.stats().jit_passes > 0
+
+
+def test_jit_sharded_virtual_ranks(gpu, oracle_mod):
+    n, world = 12, 4
+    ops = random_circuit(21, n, 60, names=NO_DENSE)
+    o = oracle_mod.OracleDevice(n)
+    apply_ops(o, ops)
+    ref = o.state()
+
+    def body(d, r):
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        return d.state(), int(d.stats().jit_passes)
+
+    res = gpu.run_spmd(world, body, jit="always")
+    for st, jp in res:
+        assert np.max(np.abs(st - ref)) < TOL
+        assert jp > 0
