@@ -102,6 +102,7 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "jit_regbits") o.jit_regbits = (int)as_int(o.jit_regbits);
         else if (k == "jit_min_qubits") o.jit_min_qubits = (int)as_int(o.jit_min_qubits);
         else if (k == "jit_dbuf") o.jit_dbuf = (int)as_int(o.jit_dbuf);
+        else if (k == "jit_fuse_diag") o.jit_fuse_diag = (int)as_int(o.jit_fuse_diag);
     }
     B200_FAIL_IF(o.world < 1 || (o.world & (o.world - 1)) || o.world > 64, "world_size must be a power of two (<= 64)");
     B200_FAIL_IF(o.rank < 0 || o.rank >= o.world, "rank out of range");

@@ -102,6 +102,7 @@ struct Options {
     int jit_regbits = 4;      // a thread owns 2^jit_regbits amplitudes in a specialised pass
     int jit_min_qubits = 22;  // smaller local states stay on the interpreter
     int jit_dbuf = 1;         // cp.async double-buffered tiles in specialised passes
+    int jit_fuse_diag = 1;    // fuse runs of diagonal ops inside a register round
 };
 
 class DeviceBuffer;

@@ -43,7 +43,7 @@ struct JRound {
 };
 
 struct JPlan {
-    int t = 0, c = 0, nr = 0, nl = 0, dbuf = 0;
+    int t = 0, c = 0, nr = 0, nl = 0, dbuf = 0, fuse_diag = 1;
     std::vector<int> high;
     uint64_t rank_base = 0;
     std::vector<JRound> rounds;
@@ -262,7 +262,142 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
               << "r = q_.x; v" << k << "i = q_.y; }\n";
         }
         auto V = [&](uint32_t k, char part) { return "v" + std::to_string(k) + part; };
-        for (const JOp &g : R.ops) {
+        // ---- a run of consecutive diagonal ops (PHASE / PARITY) is fused: each op multiplies a
+        // per-thread accumulator (one per distinct register-bit signature) instead of its 4..2^nr
+        // register slots, run-time conditions become selects (no branches), and every slot is
+        // multiplied once by the product of the accumulators that apply to it.  The QFT's fans of
+        // controlled phases and QAOA's ZZ layers collapse from ~8 complex multiplies per op to ~1.
+        auto cond_of = [&](const JOp &g) {
+            std::string cond;
+            if (g.co_m) cond = "((obase & " + hex64(g.co_m) + ") == " + hex64(g.co_v) + ")";
+            const uint32_t tcm = g.cin_m & ~R.S, tcv = g.cin_v & ~R.S;
+            if (tcm) cond += std::string(cond.empty() ? "" : " && ") + "((ib & " + hex32(tcm) + ") == " + hex32(tcv) + ")";
+            return cond;
+        };
+        auto emit_diag_run = [&](size_t i0, size_t i1) {
+            struct Acc {
+                int type; // 0 PHASE, 1 PARITY
+                uint32_t rcm, rcv, rz;
+                Coef a, b; // current value (literal coefficient or variable)
+                int id;
+            };
+            std::vector<Acc> accs;
+            int uid = 0;
+            o << "      { // fused run of " << (i1 - i0) << " diagonal ops\n";
+            auto mul_into = [&](Coef &acc, const Coef &f, const std::string &name) {
+                // acc = acc * f, result in fresh variables name{r,i}
+                std::vector<Term> re, im;
+                cmul_terms(re, im, f, acc.er, acc.ei);
+                // cmul_terms treats f as the coefficient with classes and acc as operands: acc must be a variable or
+                // GEN literal expression; classes of acc are ignored (operands), which is correct but not minimal
+                o << "        const double " << name << "r = " << lin(re) << ", " << name << "i = " << lin(im) << ";\n";
+                acc = Coef{CLS_GEN, CLS_GEN, name + "r", name + "i"};
+            };
+            for (size_t i = i0; i < i1; i++) {
+                const JOp &g = R.ops[i];
+                const std::string cond = cond_of(g);
+                const uint32_t rcm = g.cin_m & R.S, rcv = g.cin_v & R.S;
+                const int u = uid++;
+                const std::string un = "f" + std::to_string(u);
+                if (g.kind == GateOp::PHASE) {
+                    Coef f{(int)(g.cls & 3u), (int)((g.cls >> 2) & 3u), mref(g.moff), mref(g.moff + 1)};
+                    if (!cond.empty()) {
+                        o << "        const bool " << un << "c = " << cond << ";\n";
+                        o << "        const double " << un << "r = " << un << "c ? " << mref(g.moff) << " : 1.0, " << un << "i = " << un
+                          << "c ? " << mref(g.moff + 1) << " : 0.0;\n";
+                        f = Coef{CLS_GEN, CLS_GEN, un + "r", un + "i"};
+                    }
+                    Acc *A = nullptr;
+                    for (auto &a : accs)
+                        if (a.type == 0 && a.rcm == rcm && a.rcv == rcv) A = &a;
+                    if (!A) {
+                        accs.push_back(Acc{0, rcm, rcv, 0, f, f, (int)accs.size()});
+                        continue;
+                    }
+                    if (A->a.cr != CLS_GEN || A->a.ci != CLS_GEN) std::swap(A->a, f); // keep the literal as the coefficient
+                    mul_into(A->a, f, "g" + std::to_string(A->id) + "_" + std::to_string(u));
+                }
+                else { // PARITY: factor e0 on even parity of the z bits, e1 on odd
+                    const uint32_t tz = g.zin & ~R.S, rz = g.zin & R.S;
+                    Coef fa{(int)(g.cls & 3u), (int)((g.cls >> 2) & 3u), mref(g.moff), mref(g.moff + 1)};
+                    Coef fb{(int)((g.cls >> 4) & 3u), (int)((g.cls >> 6) & 3u), mref(g.moff + 2), mref(g.moff + 3)};
+                    if (tz || g.zo || !cond.empty()) {
+                        std::string pz = "false";
+                        if (tz || g.zo) {
+                            pz = "(((";
+                            if (tz) pz += "__popc(ib & " + hex32(tz) + ")";
+                            if (tz && g.zo) pz += " + ";
+                            if (g.zo) pz += "__popcll(obase & " + hex64(g.zo) + ")";
+                            pz += ") & 1) != 0)";
+                        }
+                        o << "        const bool " << un << "p = " << pz << ";\n";
+                        const std::string c1 = cond.empty() ? "" : "!(" + cond + ") ? 1.0 : ";
+                        const std::string c0 = cond.empty() ? "" : "!(" + cond + ") ? 0.0 : ";
+                        o << "        const double " << un << "ar = " << c1 << "(" << un << "p ? " << mref(g.moff + 2) << " : " << mref(g.moff)
+                          << "), " << un << "ai = " << c0 << "(" << un << "p ? " << mref(g.moff + 3) << " : " << mref(g.moff + 1) << ");\n";
+                        o << "        const double " << un << "br = " << c1 << "(" << un << "p ? " << mref(g.moff) << " : " << mref(g.moff + 2)
+                          << "), " << un << "bi = " << c0 << "(" << un << "p ? " << mref(g.moff + 1) << " : " << mref(g.moff + 3) << ");\n";
+                        fa = Coef{CLS_GEN, CLS_GEN, un + "ar", un + "ai"};
+                        fb = Coef{CLS_GEN, CLS_GEN, un + "br", un + "bi"};
+                    }
+                    Acc *A = nullptr;
+                    for (auto &a : accs)
+                        if (a.type == 1 && a.rcm == rcm && a.rcv == rcv && a.rz == rz) A = &a;
+                    if (!A) {
+                        accs.push_back(Acc{1, rcm, rcv, rz, fa, fb, (int)accs.size()});
+                        continue;
+                    }
+                    if (A->a.cr != CLS_GEN || A->a.ci != CLS_GEN) std::swap(A->a, fa);
+                    if (A->b.cr != CLS_GEN || A->b.ci != CLS_GEN) std::swap(A->b, fb);
+                    mul_into(A->a, fa, "ga" + std::to_string(A->id) + "_" + std::to_string(u));
+                    if (rz) mul_into(A->b, fb, "gb" + std::to_string(A->id) + "_" + std::to_string(u));
+                }
+            }
+            // every slot times the product of the accumulators that apply to it (products are shared)
+            std::vector<std::pair<std::vector<int>, Coef>> memo; // factor list (acc id * 2 + odd) -> value
+            auto factor_of = [&](int code) -> Coef { return (code & 1) ? accs[code >> 1].b : accs[code >> 1].a; };
+            for (uint32_t k = 0; k < nslots; k++) {
+                std::vector<int> fl;
+                for (auto &a : accs)
+                    if ((pat[k] & a.rcm) == a.rcv)
+                        fl.push_back(a.id * 2 + (a.type == 1 ? (__builtin_popcount(pat[k] & a.rz) & 1) : 0));
+                if (fl.empty()) continue;
+                Coef F = factor_of(fl[0]);
+                std::vector<int> pre{fl[0]};
+                for (size_t q = 1; q < fl.size(); q++) {
+                    pre.push_back(fl[q]);
+                    const Coef *hit = nullptr;
+                    for (auto &m : memo)
+                        if (m.first == pre) hit = &m.second;
+                    if (hit) {
+                        F = *hit;
+                        continue;
+                    }
+                    Coef f = factor_of(fl[q]);
+                    if (F.cr != CLS_GEN || F.ci != CLS_GEN) std::swap(F, f);
+                    std::string nm = "p";
+                    for (int c_ : pre) nm += "_" + std::to_string(c_);
+                    mul_into(F, f, nm);
+                    memo.push_back({pre, F});
+                }
+                std::vector<Term> re, im;
+                cmul_terms(re, im, F, "ar", "ai");
+                o << "        { const double ar = v" << k << "r, ai = v" << k << "i; v" << k << "r = " << lin(re) << "; v" << k
+                  << "i = " << lin(im) << "; }\n";
+            }
+            o << "      }\n";
+        };
+        for (size_t oi = 0; oi < R.ops.size(); oi++) {
+            const JOp &g = R.ops[oi];
+            if (P.fuse_diag && (g.kind == GateOp::PHASE || g.kind == GateOp::PARITY)) {
+                size_t oj = oi;
+                while (oj < R.ops.size() && (R.ops[oj].kind == GateOp::PHASE || R.ops[oj].kind == GateOp::PARITY)) oj++;
+                if (oj - oi >= 2) {
+                    emit_diag_run(oi, oj);
+                    oi = oj - 1;
+                    continue;
+                }
+            }
             // run-time condition: outside-the-tile controls (uniform per tile) and thread-bit controls
             std::string cond;
             if (g.co_m) cond = "((obase & " + hex64(g.co_m) + ") == " + hex64(g.co_v) + ")";
@@ -426,6 +561,7 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
     P.nl = (int)nl_;
     P.high = high;
     P.rank_base = rank_base_;
+    P.fuse_diag = opt_.jit_fuse_diag;
     {
         const uint64_t ntiles = 1ull << (nl_ - t);
         const int per_sm = std::max(1, (227 * 1024) / (2 * 16 * (1 << t) + 1024));
@@ -518,7 +654,8 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
     // structural key
     std::string key;
     key.reserve(64 + 64 * ops.size());
-    put(key, (int)3); // generator version
+    put(key, (int)4); // generator version
+    put(key, P.fuse_diag);
     put(key, P.t); put(key, P.c); put(key, P.nr); put(key, P.nl); put(key, P.dbuf); put(key, P.rank_base);
     for (int h : P.high) put(key, (uint8_t)h);
     for (const JRound &R : P.rounds) {
