@@ -26,7 +26,7 @@ SYMBOLS = [
     "b200sv_named_operation", "b200sv_matrix_operation", "b200sv_set_state",
     "b200sv_set_basis_state", "b200sv_observable", "b200sv_tensor_observable",
     "b200sv_hamiltonian_observable", "b200sv_expval", "b200sv_var", "b200sv_state", "b200sv_probs",
-    "b200sv_sample", "b200sv_counts", "b200sv_measure", "b200sv_start_tape_recording",
+    "b200sv_sample", "b200sv_counts", "b200sv_measure", "b200sv_pauli_measure", "b200sv_start_tape_recording",
     "b200sv_stop_tape_recording", "b200sv_tape_num_params", "b200sv_tape_num_observables",
     "b200sv_gradient", "b200sv_get_stats", "b200sv_reset_stats", "b200sv_set_timing",
     "b200sv_flush", "b200sv_synchronize", "b200sv_jit_wait", "b200sv_device_pointer",
@@ -309,6 +309,14 @@ class B200Device:
         self._chk(self.L.b200sv_measure(self.h, C.c_int64(wire),
                                         -1 if postselect is None else int(postselect),
                                         C.byref(out)))
+        return bool(out.value)
+
+    def pauli_measure(self, word, wires, postselect=None):
+        """PauliMeasure (QuantumDevice.hpp:531): False <-> eigenvalue +1 of the Pauli product."""
+        out = C.c_int()
+        w = (C.c_int64 * len(wires))(*wires)
+        self._chk(self.L.b200sv_pauli_measure(self.h, word.encode(), w, C.c_int64(len(wires)),
+                                              -1 if postselect is None else int(postselect), C.byref(out)))
         return bool(out.value)
 
     # -- tape / gradient (QuantumDevice.hpp:564-581) --------------------------------------------

@@ -264,6 +264,14 @@ class B200StateVector final : public Catalyst::Runtime::QuantumDevice {
         return out ? &static_true_ : &static_false_;
     }
 
+    auto PauliMeasure(const std::string &pauli_word, const std::vector<QubitIdType> &wires) -> Result override
+    {
+        const auto w = dev_wires(wires);
+        int out = 0;
+        B200_RT_CHECK(b200sv_pauli_measure(dev_, pauli_word.c_str(), w.data(), (int64_t)w.size(), -1, &out));
+        return out ? &static_true_ : &static_false_;
+    }
+
     // ---- differentiation (QuantumDevice.hpp:564-581) -----------------------------------------------
     void StartTapeRecording() override { B200_RT_CHECK(b200sv_start_tape_recording(dev_)); }
     void StopTapeRecording() override { B200_RT_CHECK(b200sv_stop_tape_recording(dev_)); }

@@ -2142,35 +2142,105 @@ std::vector<int64_t> Simulator::sample_indices(const std::vector<int64_t> &wires
 // Draw semantics: runtime/lib/backend/common/Utils.hpp:312-338 (float cast of the draw and one
 // extra discarded generator output are part of the stream; verified against
 // doc/releases/changelog-0.8.0.md:70-108).
+bool Simulator::draw_outcome(const double p[2], int postselect)
+{
+    // simulateDraw (reference: runtime/lib/backend/common/Utils.hpp:312-338): one float draw from
+    // the borrowed mt19937 compared with p0, then one more engine call
+    if (postselect != -1) {
+        B200_FAIL_IF(postselect < 0 || postselect > 1, "Invalid postselect value");
+        B200_FAIL_IF(p[postselect] == 0, "Probability of postselect value is 0");
+        return postselect == 1;
+    }
+    std::uniform_real_distribution<> dis(0., 1.);
+    float draw;
+    if (rng_fn_ || own_seeded_) {
+        BorrowedEngine eng{[this] { return rng_next(); }};
+        draw = (float)dis(eng);
+        (void)rng_next();
+    }
+    else {
+        std::random_device rd;
+        std::mt19937 g(rd());
+        draw = (float)dis(g);
+    }
+    return draw > p[0];
+}
+
 bool Simulator::measure(int64_t wire, int postselect)
 {
     B200_FAIL_IF(!psi_, "No qubits allocated");
     double p[2];
     probs({wire}, p, 1);
-    bool res;
-    if (postselect != -1) {
-        B200_FAIL_IF(postselect < 0 || postselect > 1, "Invalid postselect value");
-        B200_FAIL_IF(p[postselect] == 0, "Probability of postselect value is 0");
-        res = postselect == 1;
-    }
-    else {
-        std::uniform_real_distribution<> dis(0., 1.);
-        float draw;
-        if (rng_fn_ || own_seeded_) {
-            BorrowedEngine eng{[this] { return rng_next(); }};
-            draw = (float)dis(eng);
-            (void)rng_next();
-        }
-        else {
-            std::random_device rd;
-            std::mt19937 g(rd());
-            draw = (float)dis(g);
-        }
-        res = draw > p[0];
-    }
+    const bool res = draw_outcome(p, postselect);
     const double scale = 1.0 / std::sqrt(p[res ? 1 : 0]);
     CUDA_CHECK(b200k_collapse(psi_->d(), (int)nl_, rank_base_, pos_[lbit(wire)], res ? 1 : 0, scale, stream_));
     note_launch();
+    return res;
+}
+
+// PauliMeasure (reference: runtime/include/QuantumDevice.hpp:531, caller RuntimeCAPI.cpp:962-993):
+// projective measurement of the Pauli product `word` on `wires`; result 0 <-> eigenvalue +1.
+// The word is rotated to the Z basis (X: H; Y: H S^dagger), the parity expectation is one read pass,
+// the projector (1 +- Z..Z)/2 with its renormalisation is ONE diagonal PARITY op, and the rotation
+// is undone; rotation, projector and un-rotation fuse into the surrounding tile passes.
+bool Simulator::pauli_measure(const std::string &word, const std::vector<int64_t> &wires, int postselect)
+{
+    B200_FAIL_IF(!psi_, "No qubits allocated");
+    B200_FAIL_IF(word.size() != wires.size(), "The length of the pauli string must be equal to the number of wires.");
+    check_wires(wires, {});
+    uint64_t zmask = 0;
+    std::vector<GateOp> pre, post;
+    for (size_t k = 0; k < wires.size(); k++) {
+        const std::vector<int64_t> w{wires[k]};
+        switch (word[k]) {
+        case 'I': break;
+        case 'Z': zmask |= bit_of(wires[k]); break;
+        case 'X':
+            canonicalize(pre, "Hadamard", {}, w, false, {}, {}, "");
+            canonicalize(post, "Hadamard", {}, w, false, {}, {}, "");
+            zmask |= bit_of(wires[k]);
+            break;
+        case 'Y':
+            canonicalize(pre, "S", {}, w, true, {}, {}, "");
+            canonicalize(pre, "Hadamard", {}, w, false, {}, {}, "");
+            canonicalize(post, "Hadamard", {}, w, false, {}, {}, "");
+            canonicalize(post, "S", {}, w, false, {}, {}, "");
+            zmask |= bit_of(wires[k]);
+            break;
+        default: B200_FAIL("Invalid Pauli word '" + word + "'");
+        }
+    }
+    double p[2] = {1.0, 0.0};
+    if (zmask) {
+        enqueue(std::move(pre));
+        flush();
+        const uint64_t zm = to_phys(pos_, zmask);
+        const double one = 1.0;
+        ensure_buffer(misc_, 16);
+        uint64_t *dz = static_cast<uint64_t *>(misc_->p());
+        double *dc = reinterpret_cast<double *>(dz + 1);
+        CUDA_CHECK(cudaMemcpyAsync(dz, &zm, 8, cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+        CUDA_CHECK(cudaMemcpyAsync(dc, &one, 8, cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+        CUDA_CHECK(b200k_expval_diag_batch(psi_->d(), (int)nl_, rank_base_, dz, dc, 1, scratch_->d(), result_slot(0),
+                                           stream_));
+        note_launch();
+        std::vector<double> h;
+        read_results(1, h); // synchronises; sums over ranks in fixed order
+        const double ev = h[0];
+        p[0] = std::min(1.0, std::max(0.0, 0.5 * (1.0 + ev)));
+        p[1] = std::min(1.0, std::max(0.0, 0.5 * (1.0 - ev)));
+    }
+    const bool res = draw_outcome(p, postselect);
+    if (!zmask) return res; // identity word: eigenvalue +1 with certainty, state untouched
+    GateOp proj;
+    proj.kind = GateOp::PARITY;
+    proj.zmask = zmask;
+    const double nrm = 1.0 / std::sqrt(p[res ? 1 : 0]);
+    proj.m[0] = res ? cplx(0.0) : cplx(nrm);
+    proj.m[1] = res ? cplx(nrm) : cplx(0.0);
+    std::vector<GateOp> ops{proj};
+    enqueue(std::move(ops));
+    enqueue(std::move(post));
     return res;
 }
 
@@ -2510,6 +2580,11 @@ int b200sv_counts(b200sv_device *d, const int64_t *wires, int64_t nwires, int64_
                  counts[i * cnt_stride] = 0;
              }
              for (auto i : idx) counts[i * cnt_stride] += 1)
+}
+int b200sv_pauli_measure(b200sv_device *d, const char *word, const int64_t *wires, int64_t nwires, int postselect,
+                         int *out)
+{
+    B200_TRY(*out = d->sim->pauli_measure(std::string(word ? word : ""), wv(wires, nwires), postselect) ? 1 : 0)
 }
 int b200sv_measure(b200sv_device *d, int64_t wire, int postselect, int *out)
 {

@@ -148,6 +148,7 @@ class Simulator {
     void probs(const std::vector<int64_t> &wires, double *out, int64_t stride);
     std::vector<int64_t> sample_indices(const std::vector<int64_t> &wires, int64_t shots);
     bool measure(int64_t wire, int postselect);
+    bool pauli_measure(const std::string &word, const std::vector<int64_t> &wires, int postselect);
 
     // tape / gradient
     void start_tape();
@@ -218,6 +219,7 @@ class Simulator {
     void read_results(int nslots, std::vector<double> &host);
     double *result_slot(int slot);
 
+    bool draw_outcome(const double p[2], int postselect);
     double uniform01();
     uint32_t rng_next();
 

@@ -99,6 +99,11 @@ int b200sv_counts(b200sv_device *d, const int64_t *wires, int64_t nwires, int64_
                   double *eigvals, int64_t eig_stride, int64_t *counts, int64_t cnt_stride);
 /* Measure :234 — postselect -1 = none (RuntimeCAPI.cpp:950-960); *out = 0/1 */
 int b200sv_measure(b200sv_device *d, int64_t wire, int postselect, int *out);
+/* PauliMeasure :531 (caller RuntimeCAPI.cpp:962-993) — joint measurement of the Pauli product `word`
+ * (one of I/X/Y/Z per wire); *out = 0 for eigenvalue +1, 1 for eigenvalue -1; the state collapses onto
+ * that eigenspace.  Same draw as Measure; postselect -1 = none. */
+int b200sv_pauli_measure(b200sv_device *d, const char *word, const int64_t *wires, int64_t nwires,
+                         int postselect, int *out);
 
 /* StartTapeRecording :574 / StopTapeRecording :581 / Gradient :564-567 (caller RuntimeCAPI.cpp:386-447).
  * grad_rows[k] receives d<O_k>/d theta_j for the recorded expvals k, j over `train` (ntrain == 0 =>

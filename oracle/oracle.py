@@ -200,6 +200,13 @@ class OracleDevice:
                                      -1 if postselect is None else int(postselect), C.byref(out)))
         return bool(out.value)
 
+    def pauli_measure(self, word, wires, postselect=None):
+        out = C.c_int()
+        w = (C.c_int64 * len(wires))(*wires)
+        self._chk(self.L.orc_pauli_measure(self.h, word.encode(), w, len(wires),
+                                           -1 if postselect is None else int(postselect), C.byref(out)))
+        return bool(out.value)
+
     # -- tape / gradient ------------------------------------------------------------------------
     def start_tape(self):
         self._chk(self.L.orc_start_tape(self.h))

@@ -671,6 +671,65 @@ class Oracle {
         return res;
     }
 
+    // ---- PauliMeasure (QuantumDevice.hpp:531; caller RuntimeCAPI.cpp:962-993): projective measurement
+    //      of the Pauli product P = word on `wires`.  Result 0 <-> eigenvalue +1, 1 <-> eigenvalue -1;
+    //      p(1) = (1 - <P>)/2; post-measurement state (1 +- P)/2 psi, renormalised.  The draw follows
+    //      Measure (Utils.hpp:312-338).  Restated directly from the projector (no basis rotations), so
+    //      that it cross-checks the device, which rotates to the Z basis.
+    bool pauli_measure(const std::string &word, const std::vector<size_t> &wires, int postselect /* -1 = none */)
+    {
+        ORC_FAIL_IF(word.size() != wires.size(), "The length of the pauli string must be equal to the number of wires.");
+        uint64_t xm = 0, zm = 0;
+        int ny = 0;
+        for (size_t k = 0; k < wires.size(); k++) {
+            ORC_FAIL_IF(wires[k] >= n, "Invalid wire");
+            const uint64_t b = uint64_t(1) << bit_of(wires[k]);
+            ORC_FAIL_IF((xm | zm) & b, "Repeated wire in PauliMeasure");
+            switch (word[k]) {
+            case 'I': break;
+            case 'X': xm |= b; break;
+            case 'Y': xm |= b; zm |= b; ny++; break;
+            case 'Z': zm |= b; break;
+            default: ORC_FAIL_IF(true, "Invalid Pauli word");
+            }
+        }
+        // (P psi)_i = i^ny * (-1)^popc(j & zm) * psi_j,  j = i ^ xm
+        const int64_t N = int64_t(1) << n;
+        static const cplx IP[4] = {{1, 0}, {0, 1}, {-1, 0}, {0, -1}};
+        CVec pv(static_cast<size_t>(N), cplx(0));
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < N; i++) {
+            const uint64_t j = uint64_t(i) ^ xm;
+            const int sgn = __builtin_popcountll(j & zm) & 1;
+            pv[i] = IP[ny & 3] * (sgn ? -psi[j] : psi[j]);
+        }
+        const double ev = inner(psi, pv).real();
+        double p[2] = {0.5 * (1.0 + ev), 0.5 * (1.0 - ev)};
+        for (double &q : p) q = std::min(1.0, std::max(0.0, q));
+        bool res;
+        if (postselect == 0 || postselect == 1) {
+            ORC_FAIL_IF(p[postselect] == 0, "Probability of postselect value is 0");
+            res = postselect == 1;
+        }
+        else {
+            std::uniform_real_distribution<> dis(0., 1.);
+            float draw;
+            if (gen) {
+                draw = dis(*gen);
+                (*gen)();
+            }
+            else {
+                std::mt19937 g(std::random_device{}());
+                draw = dis(g);
+            }
+            res = draw > p[0];
+        }
+        const double sgn = res ? -1.0 : 1.0, nrm = 0.5 / std::sqrt(p[res ? 1 : 0]);
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < N; i++) psi[i] = (psi[i] + sgn * pv[i]) * nrm;
+        return res;
+    }
+
     // ---- Tape + adjoint Jacobian (QuantumDevice.hpp:540-581) -------------
     void start_tape()
     {

@@ -188,6 +188,11 @@ int orc_measure(void *h, int64_t wire, int postselect, int *out)
 {
     ORC_TRY(*out = static_cast<Oracle *>(h)->measure(size_t(wire), postselect) ? 1 : 0)
 }
+int orc_pauli_measure(void *h, const char *word, const int64_t *wires, int nw, int postselect, int *out)
+{
+    ORC_TRY(std::vector<size_t> w; for (int i = 0; i < nw; i++) w.push_back(size_t(wires[i]));
+            *out = static_cast<Oracle *>(h)->pauli_measure(std::string(word), w, postselect) ? 1 : 0)
+}
 int orc_start_tape(void *h) { ORC_TRY(static_cast<Oracle *>(h)->start_tape()) }
 int orc_stop_tape(void *h) { ORC_TRY(static_cast<Oracle *>(h)->stop_tape()) }
 int orc_tape_num_params(void *h)

@@ -92,6 +92,7 @@ class RuntimeDevice:
         L.rt__array_get_element_ptr_1d.restype = C.POINTER(C.c_void_p)
         L.rt__num_qubits.restype = C.c_int64
         L.qis__Measure.restype = C.POINTER(C.c_bool)
+        L.qis__PauliMeasure.restype = C.POINTER(C.c_bool)
         L.qis__Expval.restype = C.c_double
         L.qis__Variance.restype = C.c_double
         for s in ("NamedObs", "HermitianObs", "TensorObs", "HamiltonianObs"):
@@ -272,6 +273,12 @@ class RuntimeDevice:
 
     def measure(self, wire, postselect=None):
         r = self.L.qis__Measure(self.q[wire], C.c_int32(-1 if postselect is None else postselect))
+        return bool(r[0])
+
+    def pauli_measure(self, word, wires, negated=False):
+        # RuntimeCAPI.cpp:962-993: (pauliStr, negated, pauliStrAlt, negatedAlt, selectSwitch, numQubits, qubits...)
+        r = self.L.qis__PauliMeasure(word.encode(), C.c_bool(negated), word.encode(), C.c_bool(negated),
+                                     C.c_bool(True), C.c_int64(len(wires)), *[self.q[w] for w in wires])
         return bool(r[0])
 
     # -- gradient (lowering: mlir/lib/Gradient/Transforms/ConversionPatterns.cpp:198-274) ---------

@@ -261,6 +261,56 @@ def test_seeded_mid_circuit_measurements(gpu, oracle_mod, n, seed):
         d.measure(w, 1 - ps)  # probability of the other branch is now exactly 0
 
 
+# ---- PauliMeasure (QuantumDevice.hpp:531): outcomes bit-exact under the seeded stream, states 1e-12 ----
+def _random_word(rng, n):
+    k = int(rng.integers(1, min(n, 5) + 1))
+    wires = [int(w) for w in rng.permutation(n)[:k]]
+    word = "".join(rng.choice(list("IXYZ"), size=k, p=[0.1, 0.3, 0.3, 0.3]))
+    return word, wires
+
+
+@pytest.mark.parametrize("cfg", [dict(), dict(jit="always"), dict(tile_bits=5, min_row_bits=2)])
+@pytest.mark.parametrize("n,seed", [(1, 0), (4, 1), (9, 2), (13, 3), (16, 4)])
+def test_seeded_pauli_measurements(gpu, oracle_mod, n, seed, cfg):
+    rng = np.random.default_rng(seed)
+    o = oracle_mod.OracleDevice(n, seed=37)
+    d = gpu.B200Device(n, seed=37, **cfg)
+    out_o, out_d = [], []
+    for layer in range(6):
+        ops = [random_op(rng, n) for _ in range(8)]
+        apply_ops(o, ops)
+        apply_ops(d, ops)
+        word, wires = _random_word(rng, n)
+        out_o.append(o.pauli_measure(word, wires))
+        out_d.append(d.pauli_measure(word, wires))
+        if layer % 2:   # interleave with ordinary measurements on the same stream
+            w = int(rng.integers(n))
+            out_o.append(o.measure(w))
+            out_d.append(d.measure(w))
+    assert out_o == out_d
+    assert np.max(np.abs(o.state() - d.state())) < 1e-11
+    assert abs(np.linalg.norm(d.state()) - 1) < 1e-12
+
+
+def test_pauli_measure_identities_and_errors(gpu):
+    d = gpu.B200Device(3, seed=5)
+    apply_ops(d, [("Hadamard", [], [0]), ("CNOT", [], [0, 1]), ("CNOT", [], [1, 2])])   # GHZ
+    ref = d.state()
+    assert [d.pauli_measure("XXX", [0, 1, 2]), d.pauli_measure("ZZ", [0, 1]), d.pauli_measure("ZIZ", [2, 1, 0]),
+            d.pauli_measure("II", [0, 2]), d.pauli_measure("YYX", [0, 1, 2])] == [False, False, False, False, True]
+    assert np.max(np.abs(d.state() - ref)) < TOL
+    r = d.pauli_measure("Z", [1])                      # collapses the GHZ state
+    want = np.zeros(8, dtype=complex); want[7 if r else 0] = 1
+    assert np.max(np.abs(d.state() - want)) < TOL
+    assert d.pauli_measure("ZZ", [0, 2], postselect=0) is False
+    with pytest.raises(RuntimeError):
+        d.pauli_measure("ZZ", [0, 2], postselect=1)
+    with pytest.raises(RuntimeError):
+        d.pauli_measure("XX", [0])
+    with pytest.raises(RuntimeError):
+        d.pauli_measure("A", [0])
+
+
 # ---- adjoint gradient ----------------------------------------------------------------------------
 DIFF_GATES = ["RX", "RY", "RZ", "PhaseShift", "IsingXX", "IsingYY", "IsingXY", "IsingZZ",
               "ControlledPhaseShift", "CRX", "CRY", "CRZ", "SingleExcitation", "DoubleExcitation",

@@ -110,6 +110,20 @@ def test_runtime_seeded_samples_and_counts(rt, oracle_mod, n, seed):
     assert o.measure(1) == d.measure(1)
 
 
+def test_runtime_pauli_measure(rt, oracle_mod):
+    """__catalyst__qis__PauliMeasure (RuntimeCAPI.cpp:962-993) -> QuantumDevice::PauliMeasure of the plugin,
+    incl. the runtime-side `negated` flip."""
+    n = 6
+    ops = random_circuit(9, n, 30)
+    o = oracle_mod.OracleDevice(n, seed=37)
+    d = rt(n, seed=37)
+    apply_ops(o, ops)
+    apply_ops(d, ops)
+    for word, wires, neg in [("XZ", [0, 3], False), ("YYX", [5, 1, 2], True), ("Z", [4], False), ("XIZY", [2, 0, 5, 3], True)]:
+        assert d.pauli_measure(word, wires, negated=neg) == (o.pauli_measure(word, wires) != neg)
+    assert np.max(np.abs(o.state() - d.state())) < 1e-11
+
+
 DIFF = ["RX", "RY", "RZ", "PhaseShift", "IsingXX", "IsingZZ", "CRX", "CRY", "CRZ", "ControlledPhaseShift",
         "SingleExcitation", "DoubleExcitation", "MultiRZ", "IsingXY", "IsingYY"]
 

@@ -188,3 +188,64 @@ def test_gradient_rejects_var_and_multiparam(oracle_mod):
     dev.stop_tape()
     with pytest.raises(RuntimeError):
         dev.gradient()
+
+
+# ---- PauliMeasure (QuantumDevice.hpp:531): joint Pauli-product measurement -------------------------
+def test_pauli_measure_stabilisers_are_deterministic(oracle_mod):
+    # Bell state |00> + |11>: stabilised by +XX, +ZZ, -YY; GHZ: +XXX, +ZZI, +IZZ
+    o = oracle_mod.OracleDevice(2, seed=11)
+    o.named_op("Hadamard", [], [0]); o.named_op("CNOT", [], [0, 1])
+    before = o.state()
+    assert [o.pauli_measure("ZZ", [0, 1]), o.pauli_measure("XX", [0, 1]), o.pauli_measure("YY", [0, 1])] == [False, False, True]
+    assert np.allclose(o.state(), before)
+    o = oracle_mod.OracleDevice(3, seed=11)
+    o.named_op("Hadamard", [], [0]); o.named_op("CNOT", [], [0, 1]); o.named_op("CNOT", [], [1, 2])
+    assert [o.pauli_measure("XXX", [0, 1, 2]), o.pauli_measure("ZZ", [0, 1]), o.pauli_measure("ZZ", [2, 1]),
+            o.pauli_measure("III", [0, 1, 2])] == [False] * 4
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_pauli_measure_z_equals_measure(oracle_mod, seed):
+    from dsl import apply_ops, random_circuit
+    n = 5
+    ops = random_circuit(seed, n, 25)
+    a, b = oracle_mod.OracleDevice(n, seed=seed), oracle_mod.OracleDevice(n, seed=seed)
+    apply_ops(a, ops); apply_ops(b, ops)
+    for w in (2, 0, 4):
+        assert a.pauli_measure("Z", [w]) == b.measure(w)
+        assert np.allclose(a.state(), b.state(), atol=1e-14)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_pauli_measure_projects_onto_eigenspace(oracle_mod, seed):
+    from dsl import apply_ops, build_obs, random_circuit
+    rng = np.random.default_rng(seed)
+    n = 6
+    o = oracle_mod.OracleDevice(n, seed=seed)
+    apply_ops(o, random_circuit(seed + 50, n, 30))
+    k = int(rng.integers(1, 5))
+    wires = [int(w) for w in rng.permutation(n)[:k]]
+    word = "".join(rng.choice(list("XYZ"), size=k))
+    names = {"X": "PauliX", "Y": "PauliY", "Z": "PauliZ"}
+    obs = ("T", [("N", names[c], w) for c, w in zip(word, wires)])
+    ev_before = o.expval(build_obs(o, obs))
+    r = o.pauli_measure(word, wires)
+    assert abs(np.linalg.norm(o.state()) - 1) < 1e-12
+    assert abs(o.expval(build_obs(o, obs)) - (-1.0 if r else 1.0)) < 1e-12
+    st = o.state()
+    assert o.pauli_measure(word, wires) == r and np.allclose(o.state(), st)   # idempotent
+    # postselecting the other branch of a fresh copy has probability (1 -+ <P>)/2 > 0 unless deterministic
+    if abs(abs(ev_before) - 1) > 1e-9:
+        o2 = oracle_mod.OracleDevice(n, seed=seed)
+        apply_ops(o2, random_circuit(seed + 50, n, 30))
+        assert o2.pauli_measure(word, wires, postselect=int(not r)) == (not r)
+
+
+def test_pauli_measure_errors(oracle_mod):
+    o = oracle_mod.OracleDevice(2)
+    with pytest.raises(RuntimeError):
+        o.pauli_measure("XX", [0])
+    with pytest.raises(RuntimeError):
+        o.pauli_measure("Q", [0])
+    with pytest.raises(RuntimeError):
+        o.pauli_measure("Z", [0], postselect=1)   # |0>: probability of -1 is 0
