@@ -103,6 +103,7 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "jit_min_qubits") o.jit_min_qubits = (int)as_int(o.jit_min_qubits);
         else if (k == "jit_dbuf") o.jit_dbuf = (int)as_int(o.jit_dbuf);
         else if (k == "jit_fuse_diag") o.jit_fuse_diag = (int)as_int(o.jit_fuse_diag);
+        else if (k == "lazy_adjoint") o.lazy_adjoint = as_int(1) != 0;
     }
     B200_FAIL_IF(o.world < 1 || (o.world & (o.world - 1)) || o.world > 64, "world_size must be a power of two (<= 64)");
     B200_FAIL_IF(o.rank < 0 || o.rank >= o.world, "rank out of range");
@@ -688,20 +689,31 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
     std::vector<char> done(ops.size(), 0);
     size_t first = 0, remaining = ops.size();
     std::vector<const GateOp *> pass;
+    const bool jit_on = jit_mode_ == 2 || (jit_mode_ == 1 && nl_ >= opt_.jit_min_qubits);
+    const int jit_k = std::min(opt_.jit_regbits, jit_mode_ == 2 ? t - 1 : t - 5);
+    auto jit_dense = [&](const GateOp &op) {
+        return jit_on && op.kind == GateOp::DENSE && (int)op.targets.size() <= jit_k &&
+               (int64_t)op.matrix->size() * 16 <= 8192;
+    };
     while (remaining) {
         uint64_t req = 0, blockedX = 0, blockedZ = 0;
         int c_cur = t;
+        int64_t pass_params = 0;
         pass.clear();
         // a pass that starts with a DENSE op runs on the first-generation kernel (which knows
         // DENSE); every other pass runs on the register-blocked kernel and defers DENSE ops
-        const bool dense_pass = ops[first].kind == GateOp::DENSE;
+        // (small DENSE blocks run in registers inside the specialised passes when those are enabled)
+        const bool dense_pass = ops[first].kind == GateOp::DENSE && !jit_dense(ops[first]);
         const size_t cap = dense_pass ? (size_t)B200K_MAX_OPS : (size_t)pass_op_cap_;
         for (size_t i = first; i < ops.size() && pass.size() < cap && i - first < LOOKAHEAD; i++) {
             if (done[i]) continue;
             const GateOp &op = ops[i];
             const uint64_t xs = op.xmask, zs = op.zsupport();
             const bool commutes = !(xs & (blockedX | blockedZ)) && !(zs & blockedX);
-            if (commutes && (dense_pass || op.kind != GateOp::DENSE)) {
+            // a specialised pass carries its matrices in the kernel parameter block (<= 32 KB)
+            const int64_t pcost = op.kind == GateOp::DENSE ? 2 * (int64_t)op.matrix->size() : 8;
+            const bool room = dense_pass || !jit_on || pass.empty() || pass_params + pcost <= 3800;
+            if (commutes && room && (dense_pass || op.kind != GateOp::DENSE || jit_dense(op))) {
                 const uint64_t nreq = req | xs;
                 const int c = fit_rows(nreq, t);
                 B200_FAIL_IF(c < 0 && pass.empty(),
@@ -710,6 +722,7 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
                     req = nreq;
                     c_cur = c;
                     pass.push_back(&op);
+                    pass_params += pcost;
                     done[i] = 1;
                     remaining--;
                     if (!opt_.fuse) break;
@@ -730,6 +743,21 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
         std::sort(high.begin(), high.end());
         if (dense_pass) launch_pass(vec, pass, high, c_cur);
         else if (launch_pass_jit(vec, pass, high, c_cur)) {}
+        else if (std::any_of(pass.begin(), pass.end(), [](const GateOp *g) { return g->kind == GateOp::DENSE; })) {
+            // the specialised kernel is not available (yet): DENSE ops one by one on the generic
+            // kernel, the runs between them on the interpreter, in program order
+            std::vector<const GateOp *> run;
+            for (const GateOp *g : pass) {
+                if (g->kind != GateOp::DENSE) {
+                    run.push_back(g);
+                    continue;
+                }
+                if (!run.empty()) launch_pass3(vec, run, high, c_cur);
+                run.clear();
+                launch_pass(vec, {g}, high, c_cur);
+            }
+            if (!run.empty()) launch_pass3(vec, run, high, c_cur);
+        }
         else if (opt_.kernel_gen == 2) launch_pass2(vec, pass, high, c_cur);
         else launch_pass3(vec, pass, high, c_cur);
     }
@@ -1864,6 +1892,11 @@ double Simulator::expval(int64_t key)
     flush();
     std::vector<ObsTerm> terms;
     flatten(key, terms);
+    if (opt_.shots > 0) { // sampled estimate
+        double e = 0.0;
+        for (auto &t : terms) e += t.coef * sampled_term_mean(t);
+        return e;
+    }
     std::vector<PauliTerm> diag, offd;
     std::vector<const ObsTerm *> generic;
     for (auto &t : terms) {
@@ -1945,6 +1978,13 @@ double Simulator::var(int64_t key)
     B200_FAIL_IF(key < 0 || (size_t)key >= obs_.size(), "Invalid key for cached observables");
     if (recording_) tape_obs_.push_back({key, 2});
     flush();
+    if (opt_.shots > 0) {
+        std::vector<ObsTerm> terms;
+        flatten(key, terms);
+        B200_FAIL_IF(terms.size() != 1, "Var of a sum of observables does not support finite shots");
+        const double m = sampled_term_mean(terms[0]); // eigenvalues are +-1: <O^2> = coef^2
+        return terms[0].coef * terms[0].coef * (1.0 - m * m);
+    }
     const size_t bytes = sizeof(cplx) << nl_;
     make_local({psi_->d()}, pos_, observable_xmask(key));
     ensure_buffer(acc_, bytes);
@@ -2012,6 +2052,61 @@ void Simulator::state(double *out_ri, int64_t stride)
         out_ri[2 * (int64_t)logical * stride] = all[2 * phys];
         out_ri[2 * (int64_t)logical * stride + 1] = all[2 * phys + 1];
     }
+}
+
+// ---- finite shots (reference: QuantumDevice.hpp:476-503) ------------------------------
+// Mean eigenvalue of one flattened term (a product of named Paulis / Hadamards) over `shots` samples:
+// the state is rotated IN PLACE to the term's eigenbasis (X: H; Y: H S^dagger; Hadamard: RY(-pi/4) —
+// the reference rotates a copy, which at 30 qubits would cost a second 16 GiB vector), the term's wires
+// are sampled with the alias sampler on the runtime's RNG stream (one seed draw per term), and the
+// rotation is undone; rotation and un-rotation of consecutive terms fuse into the same tile passes.
+double Simulator::sampled_term_mean(const ObsTerm &t)
+{
+    std::vector<GateOp> pre, post;
+    std::vector<int64_t> wires;
+    for (auto &f : t.factors) {
+        B200_FAIL_IF(f.named_id == 5, "Hermitian observables do not support finite shots");
+        if (f.named_id == 0) continue;
+        B200_FAIL_IF(f.wires.size() != 1, "Named observable acts on one wire");
+        for (auto w : wires) B200_FAIL_IF(w == f.wires[0], "Repeated wire in a tensor observable with finite shots");
+        wires.push_back(f.wires[0]);
+        const std::vector<int64_t> w{f.wires[0]};
+        if (f.named_id == 1) {
+            canonicalize(pre, "Hadamard", {}, w, false, {}, {}, "");
+            canonicalize(post, "Hadamard", {}, w, false, {}, {}, "");
+        }
+        else if (f.named_id == 2) {
+            canonicalize(pre, "S", {}, w, true, {}, {}, "");
+            canonicalize(pre, "Hadamard", {}, w, false, {}, {}, "");
+            canonicalize(post, "Hadamard", {}, w, false, {}, {}, "");
+            canonicalize(post, "S", {}, w, false, {}, {}, "");
+        }
+        else if (f.named_id == 4) {
+            canonicalize(pre, "RY", {-M_PI / 4}, w, false, {}, {}, "");
+            canonicalize(post, "RY", {M_PI / 4}, w, false, {}, {}, "");
+        }
+    }
+    if (wires.empty()) return 1.0;
+    enqueue(std::move(pre));
+    const auto idx = sample_indices(wires, opt_.shots); // flushes
+    enqueue(std::move(post));
+    double acc = 0.0;
+    for (auto i : idx) acc += (__builtin_popcountll((uint64_t)i) & 1) ? -1.0 : 1.0;
+    return acc / (double)opt_.shots;
+}
+
+// Probs / PartialProbs as the interface sees them: sampled frequencies when shots > 0
+void Simulator::probs_measured(const std::vector<int64_t> &wires_in, double *out, int64_t stride)
+{
+    if (opt_.shots <= 0) return probs(wires_in, out, stride);
+    B200_FAIL_IF(!psi_, "No qubits allocated");
+    check_wires(wires_in, {});
+    const size_t k = wires_in.empty() ? (size_t)n_ : wires_in.size();
+    B200_FAIL_IF(k > 30, "Sampled probabilities of more than 30 wires are not supported");
+    const auto idx = sample_indices(wires_in, opt_.shots);
+    std::vector<double> h(size_t(1) << k, 0.0);
+    for (auto i : idx) h[(size_t)i] += 1.0;
+    for (size_t i = 0; i < h.size(); i++) out[(int64_t)i * stride] = h[i] / (double)opt_.shots;
 }
 
 void Simulator::probs(const std::vector<int64_t> &wires_in, double *out, int64_t stride)
@@ -2359,11 +2454,19 @@ std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
         return g;
     };
 
-    std::vector<GateOp> pending; // adjoint ops not yet applied to lambda / phi
+    // Adjoint ops not yet applied to lambda / phi.  They are applied LAZILY: the overlap
+    // <phi_j| G |lambda_j> with phi_j = A phi', lambda_j = A lambda' (A = the pending unitaries) equals
+    // <phi'| G |lambda'> whenever G commutes with every pending op, i.e. on every shared bit both act
+    // diagonally.  A QAOA cost layer (42 ZZ rotations) or a layer of one-qubit rotations on distinct
+    // wires then needs ONE fused application instead of one per parameter: per parameter only the read
+    // pass of the overlap remains (2 x 16 x 2^n bytes instead of 6 x).
+    std::vector<GateOp> pending;
+    uint64_t pendX = 0, pendZ = 0;
     auto apply_pending = [&]() {
         if (pending.empty()) return;
         execute(vecs, lay, pending);
         pending.clear();
+        pendX = pendZ = 0;
     };
 
     int64_t tp = (int64_t)T - 1;
@@ -2375,12 +2478,16 @@ std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
                      "The operation is not supported using the adjoint differentiation method: " + op.name);
         if (!op.params.empty()) {
             if ((size_t)cur == train[tp]) {
-                apply_pending();
                 const Generator g = generator_of(op);
                 uint64_t cmask = g.extra_cmask, cval = g.extra_cmask;
                 for (size_t i = 0; i < op.ctrl_wires.size(); i++) {
                     cmask |= bit_of(op.ctrl_wires[i]);
                     if (op.ctrl_values[i]) cval |= bit_of(op.ctrl_wires[i]);
+                }
+                {
+                    const uint64_t gx = g.is_pair ? g.tmask : g.xmask;
+                    const uint64_t gz = (g.is_pair ? 0 : g.zmask) | cmask;
+                    if (!opt_.lazy_adjoint || (gx & (pendX | pendZ)) || (gz & pendX)) apply_pending();
                 }
                 make_local(vecs, lay, g.is_pair ? g.tmask : g.xmask);
                 for (size_t k = 0; k < K; k++) {
@@ -2402,11 +2509,16 @@ std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
             }
             cur--;
         }
+        const size_t before = pending.size();
         if (op.name == "QubitUnitary")
             canonicalize_matrix(pending, op.matrix, op.wires, !op.inverse, op.ctrl_wires, op.ctrl_values);
         else
             canonicalize(pending, op.name, op.params, op.wires, !op.inverse, op.ctrl_wires,
                          op.ctrl_values, op.pauli_word);
+        for (size_t q = before; q < pending.size(); q++) {
+            pendX |= pending[q].xmask;
+            pendZ |= pending[q].zsupport();
+        }
     }
     std::vector<double> h;
     read_results((int)(K * T), h);
@@ -2554,7 +2666,7 @@ int b200sv_var(b200sv_device *d, int64_t key, double *out) { B200_TRY(*out = d->
 int b200sv_state(b200sv_device *d, double *out_ri, int64_t stride) { B200_TRY(d->sim->state(out_ri, stride)) }
 int b200sv_probs(b200sv_device *d, const int64_t *wires, int64_t nwires, double *out, int64_t stride)
 {
-    B200_TRY(d->sim->probs(wv(wires, nwires), out, stride))
+    B200_TRY(d->sim->probs_measured(wv(wires, nwires), out, stride))
 }
 int b200sv_sample(b200sv_device *d, const int64_t *wires, int64_t nwires, int64_t shots, double *out,
                   int64_t stride0, int64_t stride1)

@@ -103,6 +103,7 @@ struct Options {
     int jit_min_qubits = 22;  // smaller local states stay on the interpreter
     int jit_dbuf = 1;         // cp.async double-buffered tiles in specialised passes
     int jit_fuse_diag = 1;    // fuse runs of diagonal ops inside a register round
+    bool lazy_adjoint = true; // adjoint gradient: apply U^dagger only when the next generator does not commute with it
 };
 
 class DeviceBuffer;
@@ -145,7 +146,8 @@ class Simulator {
     double expval(int64_t key);
     double var(int64_t key);
     void state(double *out_ri, int64_t stride);
-    void probs(const std::vector<int64_t> &wires, double *out, int64_t stride);
+    void probs(const std::vector<int64_t> &wires, double *out, int64_t stride); // analytic
+    void probs_measured(const std::vector<int64_t> &wires, double *out, int64_t stride); // sampled if shots > 0
     std::vector<int64_t> sample_indices(const std::vector<int64_t> &wires, int64_t shots);
     bool measure(int64_t wire, int postselect);
     bool pauli_measure(const std::string &word, const std::vector<int64_t> &wires, int postselect);
@@ -220,6 +222,7 @@ class Simulator {
     double *result_slot(int slot);
 
     bool draw_outcome(const double p[2], int postselect);
+    double sampled_term_mean(const ObsTerm &t);
     double uniform01();
     uint32_t rng_next();
 

@@ -35,6 +35,8 @@ struct JOp {
     int nm = 0, moff = 0;          // doubles in the parameter block
     uint32_t cls = 0;              // 2 bits per double
     double vals[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    std::vector<int> tg;           // DENSE: tile-local target positions, most significant first
+    std::vector<double> dvals;     // DENSE: 2 * 4^k doubles, row-major (re, im)
 };
 
 struct JRound {
@@ -460,6 +462,34 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
                       << lin(re) << "; " << V(k, 'i') << " = " << lin(im) << "; }\n";
                 }
             }
+            else if (g.kind == GateOp::DENSE) { // 2^k x 2^k matrix on k register bits
+                const int k = (int)g.tg.size(), dim = 1 << k;
+                auto spread = [&](int r) {
+                    uint32_t m = 0;
+                    for (int i = 0; i < k; i++)
+                        if ((r >> (k - 1 - i)) & 1) m |= 1u << g.tg[i];
+                    return m;
+                };
+                for (uint32_t s0 = 0; s0 < nslots; s0++) {
+                    if ((pat[s0] & g.x) || !slot_on(s0)) continue;
+                    b << "        {\n";
+                    for (int cc = 0; cc < dim; cc++) {
+                        const uint32_t sl = slot_of(pat[s0] | spread(cc));
+                        b << "          const double a" << cc << "r = " << V(sl, 'r') << ", a" << cc << "i = " << V(sl, 'i') << ";\n";
+                    }
+                    for (int r = 0; r < dim; r++) {
+                        std::vector<Term> re, im;
+                        for (int cc = 0; cc < dim; cc++) {
+                            const int mo = g.moff + 2 * (r * dim + cc);
+                            cmul_terms(re, im, Coef{CLS_GEN, CLS_GEN, mref(mo), mref(mo + 1)}, "a" + std::to_string(cc) + "r",
+                                       "a" + std::to_string(cc) + "i");
+                        }
+                        const uint32_t sl = slot_of(pat[s0] | spread(r));
+                        b << "          " << V(sl, 'r') << " = " << lin(re) << ";\n          " << V(sl, 'i') << " = " << lin(im) << ";\n";
+                    }
+                    b << "        }\n";
+                }
+            }
             else { // PAULIROT with all non-diagonal bits in registers
                 const uint32_t tz = g.zin & ~R.S, rz = g.zin & R.S;
                 const uint32_t top = 1u << (31 - __builtin_clz(g.x));
@@ -579,7 +609,7 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
             const uint64_t xs = g->xmask, zs = g->zsupport();
             bool fits = false;
             if (!(xs & (blockedX | blockedZ)) && !(zs & blockedX)) {
-                if (g->kind == GateOp::DENSE) return false;
+                if (g->kind == GateOp::DENSE && ((int)g->targets.size() > nr || !g->matrix)) return false;
                 uint32_t xin;
                 uint64_t xout;
                 split(xs, xin, xout);
@@ -614,6 +644,17 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
             if (g.kind == GateOp::PARITY || g.kind == GateOp::PAULIROT) split(g.zmask, o.zin, o.zo);
             o.ny = g.ny & 3;
             switch (g.kind) {
+            case GateOp::DENSE: {
+                const size_t dim = size_t(1) << g.targets.size();
+                for (int tb : g.targets) o.tg.push_back(loc[tb]);
+                o.nm = (int)(2 * dim * dim);
+                o.dvals.resize((size_t)o.nm);
+                for (size_t q = 0; q < dim * dim; q++) {
+                    o.dvals[2 * q] = (*g.matrix)[q].real();
+                    o.dvals[2 * q + 1] = (*g.matrix)[q].imag();
+                }
+                break;
+            }
             case GateOp::PAIR:
                 o.nm = 8;
                 for (int q = 0; q < 4; q++) {
@@ -640,9 +681,12 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
             o.cls = 0;
             const bool literal = g.kind == GateOp::PAIR || g.kind == GateOp::PHASE ||
                                  (g.kind == GateOp::PARITY && !(o.zin & ~S) && !o.zo);
-            for (int q = 0; q < o.nm; q++) o.cls |= (uint32_t)(literal ? cls_of(o.vals[q]) : CLS_GEN) << (2 * q);
             o.moff = (int)mvals.size();
-            for (int q = 0; q < o.nm; q++) mvals.push_back(o.vals[q]);
+            if (g.kind == GateOp::DENSE) mvals.insert(mvals.end(), o.dvals.begin(), o.dvals.end());
+            else {
+                for (int q = 0; q < o.nm; q++) o.cls |= (uint32_t)(literal ? cls_of(o.vals[q]) : CLS_GEN) << (2 * q);
+                for (int q = 0; q < o.nm; q++) mvals.push_back(o.vals[q]);
+            }
             R.ops.push_back(o);
         }
         P.rounds.push_back(std::move(R));
@@ -654,7 +698,7 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
     // structural key
     std::string key;
     key.reserve(64 + 64 * ops.size());
-    put(key, (int)4); // generator version
+    put(key, (int)5); // generator version
     put(key, P.fuse_diag);
     put(key, P.t); put(key, P.c); put(key, P.nr); put(key, P.nl); put(key, P.dbuf); put(key, P.rank_base);
     for (int h : P.high) put(key, (uint8_t)h);
@@ -665,6 +709,7 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
             put(key, (uint8_t)o.kind); put(key, (uint8_t)o.ny);
             put(key, o.x); put(key, o.a); put(key, o.b); put(key, o.cin_m); put(key, o.cin_v);
             put(key, o.co_m); put(key, o.co_v); put(key, o.zin); put(key, o.zo); put(key, o.cls);
+            for (int tb : o.tg) put(key, (uint8_t)tb);
         }
     }
     const jit::Kernel *K = E.lookup(cuda_device_, key, jit_mode_ == 2 ? 1 : opt_.jit_threshold, jit_mode_ == 2,

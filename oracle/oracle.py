@@ -94,6 +94,10 @@ class OracleDevice:
     def seed(self, s):
         self.L.orc_seed(self.h, C.c_uint32(s))
 
+    def set_shots(self, shots):
+        """SetDeviceShots (QuantumDevice.hpp:164): > 0 turns Expval / Var / Probs into sampled estimates."""
+        self.L.orc_set_shots(self.h, C.c_int64(shots))
+
     def gen_peek(self) -> int:
         return int(self.L.orc_gen_peek(self.h))
 

@@ -521,13 +521,99 @@ class Oracle {
         if (seed_every_measurement && gen) (void)(*gen)();
     }
 
-    // Expval / Var (QuantumDevice.hpp:488,503).  Analytic only (shots-based estimates are a
-    // "next" row).
+    // ---- finite shots (QuantumDevice.hpp:476-503): with shots > 0, Expval / Var /
+    //      Probs are estimated from samples.  Per flattened term coef * (x) P_w: a COPY of the state
+    //      is rotated to the term's eigenbasis (PennyLane diagonalizing gates: X -> H, Y -> H S^dagger,
+    //      Hadamard -> RY(-pi/4)), `shots` basis states of the term's wires are drawn with the sampler
+    //      below (one generateSeed() per term, terms in flattening order), and the eigenvalues
+    //      (-1)^popcount are averaged.  Hermitian observables are analytic-only here.  The RNG stream of
+    //      the reference for this path is not pinned by any in-tree vector (SURVEY 8(c) iii): what the
+    //      tests pin is determinism, convergence to the analytic value, and device == oracle.
+    struct ShotTerm {
+        double coef = 1.0;
+        std::vector<std::pair<int, size_t>> f; // (named id, wire), identities dropped
+    };
+    void flatten_shots(int64_t key, std::vector<ShotTerm> &out) const
+    {
+        ORC_FAIL_IF(key < 0 || size_t(key) >= obs.size(), "Invalid key for cached observables");
+        const Obs &o = obs[key];
+        switch (o.kind) {
+        case OBS_NAMED: {
+            ShotTerm t;
+            if (o.named_id != ID_Identity) {
+                ORC_FAIL_IF(o.wires.size() != 1, "Named observable acts on one wire");
+                t.f.push_back({o.named_id, o.wires[0]});
+            }
+            out.push_back(t);
+            return;
+        }
+        case OBS_HERMITIAN: ORC_FAIL_IF(true, "Hermitian observables do not support finite shots"); return;
+        case OBS_TENSOR: {
+            std::vector<ShotTerm> acc(1);
+            for (auto c : o.children) {
+                std::vector<ShotTerm> sub, next;
+                flatten_shots(c, sub);
+                for (auto &a : acc)
+                    for (auto &b : sub) {
+                        ShotTerm t = a;
+                        t.coef *= b.coef;
+                        t.f.insert(t.f.end(), b.f.begin(), b.f.end());
+                        next.push_back(t);
+                    }
+                acc.swap(next);
+            }
+            for (auto &t : acc) out.push_back(t);
+            return;
+        }
+        case OBS_HAMILTONIAN:
+            for (size_t i = 0; i < o.children.size(); i++) {
+                std::vector<ShotTerm> sub;
+                flatten_shots(o.children[i], sub);
+                for (auto &t : sub) {
+                    t.coef *= o.coeffs[i];
+                    out.push_back(t);
+                }
+            }
+            return;
+        }
+    }
+    // mean eigenvalue of one Pauli/Hadamard product over `shots` samples
+    double sampled_term_mean(const ShotTerm &t)
+    {
+        if (t.f.empty()) return 1.0;
+        CVec keep = psi; // the reference rotates a copy; psi is restored below
+        std::vector<size_t> wires;
+        for (auto &fw : t.f) {
+            const std::vector<size_t> w{fw.second};
+            for (auto x : wires) ORC_FAIL_IF(x == fw.second, "Repeated wire in a tensor observable with finite shots");
+            wires.push_back(fw.second);
+            if (fw.first == ID_PauliX) apply_named(psi, "Hadamard", {}, w, false, {}, {}, "");
+            else if (fw.first == ID_PauliY) {
+                apply_named(psi, "S", {}, w, true, {}, {}, "");
+                apply_named(psi, "Hadamard", {}, w, false, {}, {}, "");
+            }
+            else if (fw.first == ID_Hadamard) apply_named(psi, "RY", {-M_PI / 4}, w, false, {}, {}, "");
+        }
+        const auto idx = sample_indices(wires, shots);
+        psi.swap(keep);
+        double acc = 0.0;
+        for (auto i : idx) acc += (__builtin_popcountll(i) & 1) ? -1.0 : 1.0;
+        return acc / double(shots);
+    }
+
+    // Expval / Var (QuantumDevice.hpp:488,503)
     double expval(int64_t key)
     {
         ORC_FAIL_IF(key < 0 || size_t(key) >= obs.size(), "Invalid key for cached observables");
         if (recording) tape_obs.push_back({key, 1}); // CacheManager.hpp:111-114
         maybe_draw_seed();
+        if (shots > 0) {
+            std::vector<ShotTerm> terms;
+            flatten_shots(key, terms);
+            double e = 0.0;
+            for (auto &t : terms) e += t.coef * sampled_term_mean(t);
+            return e;
+        }
         CVec ov = psi;
         apply_obs(key, ov);
         return inner(psi, ov).real();
@@ -537,6 +623,13 @@ class Oracle {
         ORC_FAIL_IF(key < 0 || size_t(key) >= obs.size(), "Invalid key for cached observables");
         if (recording) tape_obs.push_back({key, 2});
         maybe_draw_seed();
+        if (shots > 0) {
+            std::vector<ShotTerm> terms;
+            flatten_shots(key, terms);
+            ORC_FAIL_IF(terms.size() != 1, "Var of a sum of observables does not support finite shots");
+            const double m = sampled_term_mean(terms[0]); // eigenvalues are +-1: <O^2> = coef^2
+            return terms[0].coef * terms[0].coef * (1.0 - m * m);
+        }
         CVec ov = psi;
         apply_obs(key, ov);
         const double e = inner(psi, ov).real();
@@ -567,6 +660,13 @@ class Oracle {
     std::vector<double> probs(const std::vector<size_t> &wires)
     {
         maybe_draw_seed();
+        if (shots > 0) { // sampled frequencies
+            const std::vector<size_t> w = wires.empty() ? all_wires() : wires;
+            std::vector<double> out(size_t(1) << w.size(), 0.0);
+            for (auto i : sample_indices(w, shots)) out[i] += 1.0;
+            for (auto &x : out) x /= double(shots);
+            return out;
+        }
         return probs_of(wires.empty() ? all_wires() : wires);
     }
 

@@ -79,6 +79,7 @@ int orc_reset(void *h, int n) { ORC_TRY(static_cast<Oracle *>(h)->reset(size_t(n
 int orc_num_qubits(void *h) { return int(static_cast<Oracle *>(h)->n); }
 void orc_seed(void *h, uint32_t s) { static_cast<Oracle *>(h)->seed(s); }
 void orc_unseed(void *h) { static_cast<Oracle *>(h)->unseed(); }
+void orc_set_shots(void *h, int64_t shots) { static_cast<Oracle *>(h)->shots = size_t(shots < 0 ? 0 : shots); }
 void orc_set_seed_every_measurement(void *h, int on)
 {
     static_cast<Oracle *>(h)->seed_every_measurement = on != 0;

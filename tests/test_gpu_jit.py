@@ -72,6 +72,31 @@ def test_jit_mixed_with_dense(gpu, oracle_mod):
     assert d.stats().jit_passes > 0
 
 
+@pytest.mark.parametrize("cfg", [dict(), dict(jit_regbits=5, tile_bits=12), dict(jit_dbuf=2, tile_bits=7, min_row_bits=3)])
+@pytest.mark.parametrize("n", [5, 10, 14])
+def test_jit_matrix_operation_in_registers(gpu, oracle_mod, n, cfg):
+    """MatrixOperation on k <= jit_regbits wires (with and without controls) is applied as a dense
+    2^k x 2^k block on the thread's registers inside the specialised pass."""
+    from dsl import random_unitary
+    rng = np.random.default_rng(n)
+    kmax = min(4, n - 1)
+    ops = [("Hadamard", [], [w]) for w in range(n)]
+    for i in range(24):
+        k = int(rng.integers(2, kmax + 1))
+        perm = [int(w) for w in rng.permutation(n)]
+        kw = {"matrix": random_unitary(rng, k), "inverse": bool(rng.integers(2))}
+        if i % 3 == 0 and n > k + 1:
+            kw["ctrl_wires"] = perm[k:k + 2][: n - k]
+            kw["ctrl_values"] = [bool(b) for b in rng.integers(0, 2, size=len(kw["ctrl_wires"]))]
+        ops.append(("QubitUnitary", [], perm[:k], kw))
+        ops.append(("RX", [float(rng.uniform(-3, 3))], [perm[-1]]))
+    d, err = _run(gpu, oracle_mod, n, ops, **cfg)
+    s = d.stats()
+    assert err < TOL
+    if cfg.get("tile_bits", 11) - 1 >= 4 and n - 1 >= 4:
+        assert s.jit_passes == s.tile_passes > 0, (s.jit_passes, s.tile_passes)
+
+
 @pytest.mark.parametrize("n", [18, 21])
 def test_jit_qft_random_layers(gpu, oracle_mod, n):
     from catalyst_b200 import workloads

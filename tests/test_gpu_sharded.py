@@ -221,3 +221,26 @@ def test_pauli_measure_sharded(gpu, oracle_mod, world):
     for m, st in gpu.run_spmd(world, prog, tile_bits=4, min_row_bits=2):
         assert m == want
         assert np.max(np.abs(st - want_state)) < 1e-11
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_shots_expval_sharded(gpu, oracle_mod, world):
+    n, shots = 8, 3000
+    ops = random_circuit(55, n, 40)
+    ham = ("Ham", [0.3, -0.8, 1.1], [("T", [("N", "PauliX", 0), ("N", "PauliY", 7)]), ("N", "Hadamard", 1),
+                                     ("T", [("N", "PauliZ", 0), ("N", "PauliX", 4)])])
+    o = _oracle(oracle_mod, n, ops, seed=37)
+    o.set_shots(shots)
+    want_e = o.expval(build_obs(o, ham))
+    want_p = o.probs([0, 6])
+
+    def prog(d, r):
+        d.seed(37)
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        d.set_shots(shots)
+        return d.expval(build_obs(d, ham)), d.probs([0, 6])
+
+    for e, p in gpu.run_spmd(world, prog, tile_bits=4, min_row_bits=2):
+        assert abs(e - want_e) < 1e-12
+        assert np.array_equal(p, want_p)

@@ -249,3 +249,49 @@ def test_pauli_measure_errors(oracle_mod):
         o.pauli_measure("Q", [0])
     with pytest.raises(RuntimeError):
         o.pauli_measure("Z", [0], postselect=1)   # |0>: probability of -1 is 0
+
+
+# ---- finite shots: sampled Expval / Var / Probs -----------------------------------
+def _shots_setup(mod, n, seed, shots, dev_seed=7):
+    from dsl import apply_ops, random_circuit
+    o = mod.OracleDevice(n, seed=dev_seed)
+    apply_ops(o, random_circuit(seed, n, 30))
+    o.set_shots(shots)
+    return o
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_shots_expval_converges_and_is_deterministic(oracle_mod, seed):
+    from dsl import build_obs
+    n, shots = 5, 200000
+    obs = ("Ham", [0.7, -1.3, 0.4, 2.0],
+           [("T", [("N", "PauliX", 0), ("N", "PauliY", 3)]), ("N", "PauliZ", 1), ("N", "Hadamard", 4),
+            ("T", [("N", "Identity", 2), ("N", "PauliZ", 2), ("N", "PauliX", 1)])])
+    a = _shots_setup(oracle_mod, n, seed, shots)
+    b = _shots_setup(oracle_mod, n, seed, shots)
+    ea, eb = a.expval(build_obs(a, obs)), b.expval(build_obs(b, obs))
+    assert ea == eb                                        # same seed, same stream, same estimate
+    a.set_shots(0)
+    exact = a.expval(build_obs(a, obs))
+    assert abs(ea - exact) < 5 * 4.4 / np.sqrt(shots)      # 5 sigma of the worst-case variance
+    # the state is untouched by a sampled expectation value
+    c = _shots_setup(oracle_mod, n, seed, 0)
+    assert np.allclose(a.state(), c.state(), atol=1e-14)
+
+
+def test_shots_var_and_probs(oracle_mod):
+    from dsl import build_obs
+    n, shots = 4, 100000
+    o = _shots_setup(oracle_mod, n, 3, shots)
+    obs = ("T", [("N", "PauliX", 0), ("N", "PauliZ", 2)])
+    v = o.var(build_obs(o, obs))
+    p = o.probs([2, 0])
+    assert abs(p.sum() - 1) < 1e-12 and np.all(p * shots == np.round(p * shots))
+    o.set_shots(0)
+    assert abs(v - o.var(build_obs(o, obs))) < 0.03
+    assert np.max(np.abs(p - o.probs([2, 0]))) < 0.01
+    o.set_shots(10)
+    with pytest.raises(RuntimeError):
+        o.var(build_obs(o, ("Ham", [1.0, 1.0], [("N", "PauliX", 0), ("N", "PauliZ", 1)])))
+    with pytest.raises(RuntimeError):
+        o.expval(build_obs(o, ("H", np.eye(2), [0])))
