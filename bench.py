@@ -222,7 +222,16 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         uid = plumb.bcast_obj(capi.nccl_unique_id() if rank == 0 else None)
         kw.update(world_size=world, rank=rank, comm="nccl:" + uid)
-    d = capi.B200Device(n, seed=37, **kw)   # raises if the CUDA library / device is missing
+    # NCCL prints its version banner on stdout at communicator creation: keep stdout for the JSON line
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        d = capi.B200Device(n, seed=37, **kw)   # raises if the CUDA library / device is missing
+    finally:
+        sys.stdout.flush()
+        os.dup2(saved, 1)
+        os.close(saved)
     zeros = [0] * n
     wires = list(range(n))
 
@@ -294,6 +303,7 @@ def run_ours(args, rank, world, local_rank):
     sharding = None
     if world > 1:
         sharding = {"exchanges_per_step": s.exchanges / args.steps,
+                    "peer_memory_exchanges_per_step": s.p2p_exchanges / args.steps,
                     "nvlink_bytes_sent_per_rank_per_step": s.exchange_bytes / args.steps,
                     "device_ms_per_step_incl_exchanges": s.gate_device_ms / args.steps}
 

@@ -40,7 +40,7 @@ class Stats(C.Structure):
                 ("gate_device_ms", C.c_double), ("algorithmic_bytes", C.c_double),
                 ("rounds", C.c_int64), ("exchanges", C.c_int64), ("exchange_bytes", C.c_double),
                 ("jit_passes", C.c_int64), ("jit_compiled", C.c_int64), ("jit_pending", C.c_int64),
-                ("jit_compile_ms", C.c_double)]
+                ("jit_compile_ms", C.c_double), ("p2p_exchanges", C.c_int64)]
 
 
 _lib = None
@@ -96,6 +96,9 @@ def run_spmd(world: int, fn, group: str | None = None, **kwargs):
         d = None
         try:
             kw = dict(kwargs)
+            devices = kw.pop("devices", None)   # one CUDA ordinal per rank: ranks on different GPUs
+            if devices is not None:
+                kw["device"] = int(devices[r])
             if world > 1:
                 kw.update(world_size=world, rank=r, comm=f"local:{group}")
             d = B200Device(**kw)

@@ -122,6 +122,47 @@ class LocalComm final : public Comm {
     }
     void barrier() override { grp_->barrier(); }
     const char *kind() const override { return "local"; }
+    bool map_peers(void *mine, std::vector<void *> &out) override
+    {
+        int my_dev = 0;
+        cuda_ok(cudaGetDevice(&my_dev), "LocalComm::map_peers");
+        grp_->ptrs[rank_] = mine;
+        grp_->barrier();
+        out.assign(world_, nullptr);
+        bool ok = true;
+        for (int r = 0; r < world_; r++) {
+            out[r] = const_cast<void *>(grp_->ptrs[r]);
+            cudaPointerAttributes at;
+            if (cudaPointerGetAttributes(&at, out[r]) != cudaSuccess) {
+                cudaGetLastError();
+                ok = false;
+                continue;
+            }
+            if (at.device != my_dev) { // another GPU of this process: needs peer access
+                int can = 0;
+                cudaDeviceCanAccessPeer(&can, my_dev, at.device);
+                if (!can) ok = false;
+                else {
+                    const cudaError_t e = cudaDeviceEnablePeerAccess(at.device, 0);
+                    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) ok = false;
+                    cudaGetLastError();
+                }
+            }
+        }
+        grp_->barrier();
+        // agree on the answer
+        double flag = ok ? 1.0 : 0.0;
+        std::vector<double> all(world_);
+        allgather_host(&flag, all.data(), 1);
+        for (double f : all) ok = ok && f > 0.5;
+        return ok;
+    }
+    void unmap_peers(void *) override {}
+    void stream_barrier(void *stream) override
+    {
+        cuda_ok(cudaStreamSynchronize((cudaStream_t)stream), "LocalComm::stream_barrier");
+        grp_->barrier();
+    }
 
   private:
     std::string name_;
@@ -241,8 +282,71 @@ class NcclComm final : public Comm {
         allgather_host(&x, r, 1);
     }
     const char *kind() const override { return "nccl"; }
+    bool map_peers(void *mine, std::vector<void *> &out) override
+    {
+        auto it = maps_.find(mine);
+        if (it != maps_.end()) {
+            out = it->second;
+            return true;
+        }
+        // CUDA IPC: export my allocation, gather every rank's 64-byte handle, import the peers'
+        static_assert(sizeof(cudaIpcMemHandle_t) == 64, "unexpected IPC handle size");
+        double mineh[9] = {0};
+        cudaIpcMemHandle_t h;
+        bool good = cudaIpcGetMemHandle(&h, mine) == cudaSuccess;
+        cudaGetLastError();
+        std::memcpy(mineh, &h, 64);
+        mineh[8] = good ? 1.0 : 0.0;
+        std::vector<double> all((size_t)world_ * 9);
+        allgather_host(mineh, all.data(), 9);
+        for (int r = 0; r < world_; r++) good = good && all[(size_t)r * 9 + 8] > 0.5;
+        std::vector<void *> ptrs(world_, nullptr);
+        ptrs[rank_] = mine;
+        if (good)
+            for (int r = 0; r < world_; r++) {
+                if (r == rank_) continue;
+                cudaIpcMemHandle_t hr;
+                std::memcpy(&hr, &all[(size_t)r * 9], 64);
+                if (cudaIpcOpenMemHandle(&ptrs[r], hr, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                    cudaGetLastError();
+                    ptrs[r] = nullptr;
+                    good = false;
+                }
+            }
+        double flag = good ? 1.0 : 0.0;
+        std::vector<double> flags(world_);
+        allgather_host(&flag, flags.data(), 1);
+        bool all_good = true;
+        for (double f : flags) all_good = all_good && f > 0.5;
+        if (!all_good) {
+            for (int r = 0; r < world_; r++)
+                if (r != rank_ && ptrs[r]) cudaIpcCloseMemHandle(ptrs[r]);
+            cudaGetLastError();
+            return false;
+        }
+        maps_[mine] = ptrs;
+        out = ptrs;
+        return true;
+    }
+    void unmap_peers(void *mine) override
+    {
+        auto it = maps_.find(mine);
+        if (it == maps_.end()) return;
+        for (int r = 0; r < world_; r++)
+            if (r != rank_ && it->second[r]) cudaIpcCloseMemHandle(it->second[r]);
+        cudaGetLastError();
+        maps_.erase(it);
+    }
+    void stream_barrier(void *stream) override
+    {
+        if (!sync_buf_) cuda_ok(cudaMalloc(&sync_buf_, (size_t)(world_ + 1) * sizeof(double)), "NcclComm sync buffer");
+        double *d = static_cast<double *>(sync_buf_);
+        ok(nccl_api().AllGather(d, d + 1, 1, NCCL_FLOAT64, comm_, (cudaStream_t)stream), "ncclAllGather (barrier)");
+    }
 
   private:
+    std::map<void *, std::vector<void *>> maps_;
+    void *sync_buf_ = nullptr;
     void ok(int rc, const char *what)
     {
         if (rc != 0) {

@@ -40,6 +40,16 @@ class Comm {
     virtual void allgather_host(const double *send, double *recv, size_t count) = 0;
     virtual void barrier() = 0;
     virtual const char *kind() const = 0;
+    // Peer-memory view of a device buffer that every rank holds in the same role (the state shard):
+    // out[r] = a pointer kernels of THIS rank can dereference to reach rank r's buffer (out[rank] = mine).
+    // Collective; every rank gets the same answer.  false = peer memory is not available (no P2P path
+    // between the GPUs, IPC refused): the caller falls back to the staged exchange.
+    virtual bool map_peers(void *mine, std::vector<void *> &out) = 0;
+    // closes this rank's imports of the peers' buffers (call before ANY rank frees its buffer)
+    virtual void unmap_peers(void *mine) = 0;
+    // stream-ordered rendezvous: work enqueued on `stream` after this call starts only after every
+    // rank's work enqueued before its own call has completed
+    virtual void stream_barrier(void *stream) = 0;
 
   protected:
     int rank_ = 0, world_ = 1;

@@ -224,13 +224,18 @@ extern "C" int b200k_tile_program(double *psi, int n_local, const B200kTileProgr
     if (prog->t > B200K_MAX_TILE_BITS || prog->t > n_local || prog->n_ops > B200K_MAX_OPS ||
         prog->nhigh > B200K_MAX_HIGH || prog->c + prog->nhigh != prog->t)
         return (int)cudaErrorInvalidValue;
-    static bool attr_set = false;
+    // function attributes are per device: one bit per CUDA ordinal (ranks of one process may sit on
+    // different GPUs)
+    static unsigned long long attr_mask = 0;
+    int cur_dev = 0;
+    cudaGetDevice(&cur_dev);
+    const bool attr_set = (attr_mask >> (cur_dev & 63)) & 1ull;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(k_tile_program,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)(sizeof(cplx) << B200K_MAX_TILE_BITS));
         if (e != cudaSuccess) return (int)e;
-        attr_set = true;
+        attr_mask |= 1ull << (cur_dev & 63);
     }
     const uint64_t ntiles = 1ull << (n_local - prog->t);
     if (ntiles > 0x7fffffffull) return (int)cudaErrorInvalidValue;

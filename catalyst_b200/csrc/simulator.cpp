@@ -104,6 +104,8 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "jit_dbuf") o.jit_dbuf = (int)as_int(o.jit_dbuf);
         else if (k == "jit_fuse_diag") o.jit_fuse_diag = (int)as_int(o.jit_fuse_diag);
         else if (k == "lazy_adjoint") o.lazy_adjoint = as_int(1) != 0;
+        else if (k == "p2p_swap") o.p2p_swap = as_int(1) != 0;
+        else if (k == "adaptive_rows") o.adaptive_rows = as_int(1) != 0;
     }
     B200_FAIL_IF(o.world < 1 || (o.world & (o.world - 1)) || o.world > 64, "world_size must be a power of two (<= 64)");
     B200_FAIL_IF(o.rank < 0 || o.rank >= o.world, "rank out of range");
@@ -170,7 +172,9 @@ Simulator::~Simulator()
 {
     cudaSetDevice(cuda_device_);
     if (stream_) cudaStreamSynchronize((cudaStream_t)stream_);
+    drop_psi_peers();
     psi_.reset();
+    psi_keep_.reset();
     tmp_.reset();
     acc_.reset();
     stage_.reset();
@@ -209,7 +213,14 @@ void Simulator::allocate(int64_t n)
     for (int q = 0; q < (int)n; q++) pos_[q] = q;
     const size_t bytes = sizeof(cplx) << nl_;
     try {
-        psi_ = std::make_unique<DeviceBuffer>(bytes);
+        // a shard whose peers hold a mapping of it (peer-to-peer qubit swap) is kept across
+        // release/allocate of the same size, so the mapping stays valid
+        if (psi_keep_ && psi_keep_->bytes() == bytes) psi_ = std::move(psi_keep_);
+        else {
+            drop_psi_peers();
+            psi_keep_.reset();
+            psi_ = std::make_unique<DeviceBuffer>(bytes);
+        }
     }
     catch (const Error &e) {
         n_ = nl_ = 0;
@@ -244,6 +255,7 @@ void Simulator::release()
 {
     if (stream_) cudaStreamSynchronize((cudaStream_t)stream_);
     queue_.clear();
+    if (psi_peers_ok_ && psi_) psi_keep_ = std::move(psi_); // peers still map this allocation
     psi_.reset();
     tmp_.reset();
     acc_.reset();
@@ -695,36 +707,37 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
         return jit_on && op.kind == GateOp::DENSE && (int)op.targets.size() <= jit_k &&
                (int64_t)op.matrix->size() * 16 <= 8192;
     };
-    while (remaining) {
+    // One candidate pass for a given minimum row width: the op indices it would take, the union of
+    // their non-diagonal bits and the resulting number of contiguous low bits.
+    struct Cand {
+        std::vector<size_t> idx;
+        uint64_t req = 0;
+        int c = 0;
+    };
+    auto build = [&](int cmin_try, bool dense_pass, Cand &out) {
         uint64_t req = 0, blockedX = 0, blockedZ = 0;
         int c_cur = t;
         int64_t pass_params = 0;
-        pass.clear();
-        // a pass that starts with a DENSE op runs on the first-generation kernel (which knows
-        // DENSE); every other pass runs on the register-blocked kernel and defers DENSE ops
-        // (small DENSE blocks run in registers inside the specialised passes when those are enabled)
-        const bool dense_pass = ops[first].kind == GateOp::DENSE && !jit_dense(ops[first]);
+        out.idx.clear();
         const size_t cap = dense_pass ? (size_t)B200K_MAX_OPS : (size_t)pass_op_cap_;
-        for (size_t i = first; i < ops.size() && pass.size() < cap && i - first < LOOKAHEAD; i++) {
+        for (size_t i = first; i < ops.size() && out.idx.size() < cap && i - first < LOOKAHEAD; i++) {
             if (done[i]) continue;
             const GateOp &op = ops[i];
             const uint64_t xs = op.xmask, zs = op.zsupport();
             const bool commutes = !(xs & (blockedX | blockedZ)) && !(zs & blockedX);
             // a specialised pass carries its matrices in the kernel parameter block (<= 32 KB)
             const int64_t pcost = op.kind == GateOp::DENSE ? 2 * (int64_t)op.matrix->size() : 8;
-            const bool room = dense_pass || !jit_on || pass.empty() || pass_params + pcost <= 3800;
+            const bool room = dense_pass || !jit_on || out.idx.empty() || pass_params + pcost <= 3800;
             if (commutes && room && (dense_pass || op.kind != GateOp::DENSE || jit_dense(op))) {
                 const uint64_t nreq = req | xs;
                 const int c = fit_rows(nreq, t);
-                B200_FAIL_IF(c < 0 && pass.empty(),
+                B200_FAIL_IF(c < 0 && out.idx.empty(),
                              "Operation acts non-diagonally on more qubits than one tile holds");
-                if (c >= 0 && (c >= cmin || pass.empty())) {
+                if (c >= 0 && (c >= cmin_try || out.idx.empty())) {
                     req = nreq;
                     c_cur = c;
-                    pass.push_back(&op);
+                    out.idx.push_back(i);
                     pass_params += pcost;
-                    done[i] = 1;
-                    remaining--;
                     if (!opt_.fuse) break;
                     continue;
                 }
@@ -733,6 +746,39 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
             blockedX |= xs;
             blockedZ |= zs;
         }
+        out.req = req;
+        out.c = c_cur;
+    };
+    // Relative duration of a pass by row width 2^c amplitudes (measured at 30 qubits, specialised
+    // passes: 5.9 ms at c >= 7, 6.6 / 7.1 / 7.7 / 8.1 ms at c = 6 / 5 / 4 / 3): shorter rows cost DRAM
+    // efficiency but free tile bits for the high qubits, so fewer passes are needed.
+    auto pass_cost = [](int c) { return c >= 7 ? 1.0 : (c == 6 ? 1.12 : (c == 5 ? 1.2 : (c == 4 ? 1.3 : (c == 3 ? 1.38 : 1.6)))); };
+    while (remaining) {
+        // a pass that starts with a DENSE op runs on the first-generation kernel (which knows
+        // DENSE); every other pass runs on the register-blocked kernel and defers DENSE ops
+        // (small DENSE blocks run in registers inside the specialised passes when those are enabled)
+        const bool dense_pass = ops[first].kind == GateOp::DENSE && !jit_dense(ops[first]);
+        Cand best, cand;
+        build(cmin, dense_pass, best);
+        if (opt_.adaptive_rows && opt_.fuse && !dense_pass) {
+            double best_score = (double)best.idx.size() / pass_cost(best.c);
+            for (int cm = cmin + 1; cm <= std::min(7, t); cm++) {
+                build(cm, dense_pass, cand);
+                const double sc = (double)cand.idx.size() / pass_cost(cand.c);
+                if (sc > best_score * 1.0001) {
+                    best_score = sc;
+                    std::swap(best, cand);
+                }
+            }
+        }
+        pass.clear();
+        for (size_t i : best.idx) {
+            pass.push_back(&ops[i]);
+            done[i] = 1;
+            remaining--;
+        }
+        const uint64_t req = best.req;
+        const int c_cur = best.c;
         while (first < ops.size() && done[first]) first++;
         // high tile bits: required positions >= c, padded with the lowest free positions
         std::vector<int> high;
@@ -914,6 +960,37 @@ void Simulator::swap_bits(const std::vector<double *> &vecs, std::vector<int> &p
     };
     const uint32_t npat = 1u << m;
     const uint64_t sub = 1ull << (nl_ - m); // amplitudes per sub-block
+    // Peer-to-peer path (the state shard only; gradient work vectors use the staged path): every
+    // pairwise sub-block exchange runs as ONE kernel over the peer's mapped shard, bracketed by two
+    // stream-ordered rendezvous.  No staging buffer, no pack/unpack pass, no host synchronisation.
+    if (opt_.p2p_swap && vecs.size() == 1 && psi_ && vecs[0] == psi_->d() && sub >= 2 && ensure_psi_peers()) {
+        try {
+            comm_->stream_barrier(stream_);
+            for (uint32_t b = 0; b < npat; b++) {
+                if (b == mine) continue;
+                const bool lower = mine < b;
+                CUDA_CHECK(b200k_swap_p2p(vecs[0], static_cast<double *>(psi_peers_[(size_t)peer_of(b)]), lpos, m, mine,
+                                          b, lower ? 0 : sub / 2, lower ? sub / 2 : sub, stream_));
+                note_launch();
+                stats_.exchange_bytes += (double)sub * sizeof(cplx);
+            }
+            comm_->stream_barrier(stream_);
+        }
+        catch (const std::exception &e) {
+            B200_FAIL(std::string("peer-to-peer qubit swap failed: ") + e.what());
+        }
+        stats_.exchanges++;
+        stats_.p2p_exchanges++;
+        for (int i = 0; i < m; i++) {
+            int qg = -1, ql = -1;
+            for (int q = 0; q < (int)n_; q++) {
+                if (pos[q] == pairs[i].first) qg = q;
+                if (pos[q] == pairs[i].second) ql = q;
+            }
+            std::swap(pos[qg], pos[ql]);
+        }
+        return;
+    }
     const uint64_t stage_amps = ((uint64_t)opt_.stage_mib << 20) / sizeof(cplx);
     uint64_t chunk = stage_amps / (2ull * (npat - 1));
     if (chunk > sub) chunk = sub;
@@ -961,6 +1038,29 @@ void Simulator::swap_bits(const std::vector<double *> &vecs, std::vector<int> &p
         }
         std::swap(pos[qg], pos[ql]);
     }
+}
+
+bool Simulator::ensure_psi_peers()
+{
+    if (!psi_peers_tried_) {
+        psi_peers_tried_ = true;
+        psi_peers_ptr_ = psi_->p();
+        try {
+            psi_peers_ok_ = comm_->map_peers(psi_peers_ptr_, psi_peers_);
+        }
+        catch (const std::exception &) {
+            psi_peers_ok_ = false;
+        }
+    }
+    return psi_peers_ok_ && psi_peers_ptr_ == psi_->p();
+}
+
+void Simulator::drop_psi_peers()
+{
+    if (psi_peers_ok_ && comm_) comm_->unmap_peers(psi_peers_ptr_);
+    psi_peers_ok_ = psi_peers_tried_ = false;
+    psi_peers_ptr_ = nullptr;
+    psi_peers_.clear();
 }
 
 void Simulator::reduce_results(std::vector<double> &host)

@@ -85,7 +85,8 @@ struct PauliTerm {
 struct Options {
     int64_t shots = 0;
     int tile_bits = 11;
-    int min_row_bits = 7;
+    int min_row_bits = 3;     // shortest contiguous row of a tile: 2^3 amplitudes = 128 B (one cache line)
+    bool adaptive_rows = true; // per pass, pick the row width that maximises gates per unit of pass time
     bool fuse = true;
     int device = -1; // -1: LOCAL_RANK or 0
     // sharding: this object owns the amplitudes whose top log2(world) index bits
@@ -103,6 +104,7 @@ struct Options {
     int jit_min_qubits = 22;  // smaller local states stay on the interpreter
     int jit_dbuf = 1;         // cp.async double-buffered tiles in specialised passes
     int jit_fuse_diag = 1;    // fuse runs of diagonal ops inside a register round
+    bool p2p_swap = true;     // global<->local qubit swap over mapped peer memory (NVLink P2P / CUDA IPC)
     bool lazy_adjoint = true; // adjoint gradient: apply U^dagger only when the next generator does not commute with it
 };
 
@@ -195,6 +197,12 @@ class Simulator {
     uint64_t to_phys(const std::vector<int> &pos, uint64_t logical_mask) const;
     GateOp phys_op(const std::vector<int> &pos, const GateOp &g) const;
     bool sharded() const { return opt_.world > 1; }
+    bool ensure_psi_peers(); // collective: map every rank's state shard into this GPU's address space
+    void drop_psi_peers();
+    std::vector<void *> psi_peers_;
+    void *psi_peers_ptr_ = nullptr;
+    bool psi_peers_tried_ = false, psi_peers_ok_ = false;
+    std::unique_ptr<DeviceBuffer> psi_keep_;
     void reduce_results(std::vector<double> &host); // sum over ranks, fixed order
     // plan + launch a list of canonical ops (PHYSICAL bit space, non-diagonal targets all local) on a
     // device vector holding this rank's 2^nl_ amplitudes

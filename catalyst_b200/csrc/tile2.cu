@@ -220,7 +220,12 @@ static int launch2(double *psi, const B200k2Header *hdr, const B200k2Round *roun
 {
     static int grid_per_sm[B200K_MAX_TILE_BITS + 1];
     static int sm_count = 0;
-    static bool attr_set = false;
+    // function attributes are per device: one bit per CUDA ordinal (ranks of one process may sit on
+    // different GPUs)
+    static unsigned long long attr_mask = 0;
+    int cur_dev = 0;
+    cudaGetDevice(&cur_dev);
+    const bool attr_set = (attr_mask >> (cur_dev & 63)) & 1ull;
     auto kern = k_tile2<NOPS, NROUNDS>;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -234,7 +239,7 @@ static int launch2(double *psi, const B200k2Header *hdr, const B200k2Round *roun
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, TT, sizeof(cplx) << t);
             grid_per_sm[t] = nb > 0 ? nb : 1;
         }
-        attr_set = true;
+        attr_mask |= 1ull << (cur_dev & 63);
     }
     Prog2<NOPS, NROUNDS> P;
     P.h = *hdr;

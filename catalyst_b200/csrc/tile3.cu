@@ -340,7 +340,12 @@ static int launch3(double *psi, const B200k2Header *hdr, const B200k3Round *roun
     // resident CTAs per SM for [double-buffered?][tile bits]
     static int grid_per_sm[2][B200K_MAX_TILE_BITS + 1];
     static int sm_count = 0;
-    static bool attr_set = false;
+    // function attributes are per device: one bit per CUDA ordinal (ranks of one process may sit on
+    // different GPUs)
+    static unsigned long long attr_mask = 0;
+    int cur_dev = 0;
+    cudaGetDevice(&cur_dev);
+    const bool attr_set = (attr_mask >> (cur_dev & 63)) & 1ull;
     auto kern = k_tile3<NOPS, NROUNDS>;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -355,7 +360,7 @@ static int launch3(double *psi, const B200k2Header *hdr, const B200k3Round *roun
                 cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, TT, (size_t)(d + 1) * (sizeof(cplx) << t));
                 grid_per_sm[d][t] = nb;
             }
-        attr_set = true;
+        attr_mask |= 1ull << (cur_dev & 63);
     }
     Prog3<NOPS, NROUNDS> P;
     P.h = *hdr;

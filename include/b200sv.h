@@ -130,6 +130,7 @@ typedef struct b200sv_stats {
     int64_t jit_compiled;     /* process-wide: specialised kernels compiled so far */
     int64_t jit_pending;      /* process-wide: compilations still running in the background */
     double jit_compile_ms;    /* process-wide: NVRTC time spent so far (sum over pool threads) */
+    int64_t p2p_exchanges;    /* qubit swaps that ran as in-place kernels over mapped peer memory */
 } b200sv_stats;
 int b200sv_get_stats(b200sv_device *d, b200sv_stats *out);
 int b200sv_reset_stats(b200sv_device *d);

@@ -241,6 +241,11 @@ int b200k_pack_bits(double *staged, const double *state, const uint8_t *lpos, in
                     uint64_t j0, uint64_t count, void *stream);
 int b200k_unpack_bits(double *state, const double *staged, const uint8_t *lpos, int m, uint32_t val,
                       uint64_t j0, uint64_t count, void *stream);
+/* In-place pairwise swap over peer memory (NVLink/NVSwitch; `peer` = the other rank's shard mapped into
+ * this GPU's address space): for j in [j_begin, j_end), mine[expand(j) | bits(peer_pat)] <->
+ * peer[expand(j) | bits(my_pat)].  Each rank of a pair calls it for its half of the sub-block. */
+int b200k_swap_p2p(double *mine, double *peer, const uint8_t *lpos, int m, uint32_t my_pat, uint32_t peer_pat,
+                   uint64_t j_begin, uint64_t j_end, void *stream);
 
 /* ---- alias-method sampler on device (reference algorithm: Walker alias table with LIFO pairing,
  * SURVEY.md Appendix A.4; restated as prefix sums so that no sequential pass over 2^n is needed) */

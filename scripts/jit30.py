@@ -1,5 +1,5 @@
 """C3 at n qubits on the specialised (JIT) tile passes: `python scripts/jit30.py [n] [cfg ...]`,
-cfg = regbits:tile_bits:dbuf, e.g. 4:11:1.  Prints per-run device time of the circuit."""
+cfg = regbits:tile_bits:dbuf[:min_row_bits], e.g. 4:11:1:7.  Prints per-run device time of the circuit."""
 import sys, time, os
 R = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, R); sys.path.insert(0, os.path.join(R, "tests"))
@@ -9,8 +9,10 @@ n = int(sys.argv[1]) if len(sys.argv) > 1 else 30
 cfgs = sys.argv[2:] or ["4:11:1"]
 ops = workloads.c3_qft_random(n)
 for cfg in cfgs:
-    rb, tb, db = (int(x) for x in cfg.split(":"))
-    d = capi.B200Device(n, jit="auto", jit_regbits=rb, tile_bits=tb, jit_dbuf=db, jit_threshold=1)
+    f = [int(x) for x in cfg.split(":")]
+    rb, tb, db = f[:3]
+    mr = f[3] if len(f) > 3 else 7
+    d = capi.B200Device(n, jit="auto", jit_regbits=rb, tile_bits=tb, jit_dbuf=db, jit_threshold=1, min_row_bits=mr)
     for rep in range(4):
         d.set_basis_state([0] * n, list(range(n))); d.synchronize(); d.reset_stats(); d.set_timing(True)
         t0 = time.time(); apply_ops(d, ops); d.synchronize(); t1 = time.time()

@@ -244,3 +244,31 @@ def test_shots_expval_sharded(gpu, oracle_mod, world):
     for e, p in gpu.run_spmd(world, prog, tile_bits=4, min_row_bits=2):
         assert abs(e - want_e) < 1e-12
         assert np.array_equal(p, want_p)
+
+
+@pytest.mark.parametrize("p2p", [True, False])
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_swap_paths_peer_memory_and_staged(gpu, oracle_mod, world, p2p):
+    """The global<->local qubit swap has two transports: in-place kernels over the peers' mapped shards
+    (default) and pack -> exchange -> unpack through a staging buffer (`p2p_swap=False`, also used for
+    gradient work vectors).  Both must give the oracle's state; the statistics say which one ran."""
+    n = 11
+    ops = random_circuit(500 + world, n, 120)
+    want = _oracle(oracle_mod, n, ops).state()
+
+    def prog(d, r):
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        st = d.state()
+        s = d.stats()
+        # release / allocate of the same size keeps the mapping; run once more
+        d.release_qubits()
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        return st, int(s.exchanges), int(s.p2p_exchanges), d.state()
+
+    for st, ex, p2, st2 in gpu.run_spmd(world, prog, p2p_swap=p2p, tile_bits=5, min_row_bits=2):
+        assert np.max(np.abs(st - want)) < TOL
+        assert np.max(np.abs(st2 - want)) < TOL
+        assert ex > 0
+        assert (p2 == ex) if p2p else (p2 == 0)
