@@ -40,7 +40,8 @@ class Stats(C.Structure):
                 ("gate_device_ms", C.c_double), ("algorithmic_bytes", C.c_double),
                 ("rounds", C.c_int64), ("exchanges", C.c_int64), ("exchange_bytes", C.c_double),
                 ("jit_passes", C.c_int64), ("jit_compiled", C.c_int64), ("jit_pending", C.c_int64),
-                ("jit_compile_ms", C.c_double), ("p2p_exchanges", C.c_int64)]
+                ("jit_compile_ms", C.c_double), ("p2p_exchanges", C.c_int64),
+                ("relabelled_swaps", C.c_int64)]
 
 
 _lib = None

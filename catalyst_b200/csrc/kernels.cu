@@ -14,6 +14,7 @@
 //   k_sampler_* ........... Sample :384 / Counts :433 (alias sampler of SURVEY.md Appendix A.4)
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <string.h>
 
 #include "b200sv_kernels.h"
 
@@ -489,6 +490,100 @@ extern "C" int b200k_probs_all(const double *psi, double *out, int n_local, void
     uint64_t nb = (N / 2 + 255) / 256;
     if (nb > 148 * 32) nb = 148 * 32;
     k_probs_all<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>((const cplx *)psi, out, N);
+    return (int)cudaGetLastError();
+}
+
+// |psi|^2 written through a BIT PERMUTATION of the index: out[dst(i)] = |psi_i|^2 where source bit b
+// lands on destination bit perm[b] (the host's wire relabelling — SWAP gates executed as renames — is
+// undone on the way out, so Probs()/Sample() of all wires see canonical wire order at the cost of the
+// plain pass).  A tile = the low C source bits plus the source bits that become the low C destination
+// bits: loads are contiguous in the source, stores contiguous in the destination, the transposition
+// happens in shared memory.
+#define PP_C 5
+struct PermTile {
+    uint8_t nt;          // tile bits (C .. 2C)
+    uint8_t n;
+    uint8_t src_pos[2 * PP_C];   // tile bit j (source order, ascending) -> source position
+    uint8_t dst_rank[2 * PP_C];  // tile bit in destination order j' -> its index j in source order
+    uint8_t dst_pos[2 * PP_C];   // tile bit in destination order j' -> destination position
+    uint8_t rest_src[64];        // non-tile source positions (ascending)
+    uint8_t rest_dst[64];        // their destination positions
+    uint8_t nrest;
+};
+__global__ void __launch_bounds__(256)
+k_probs_all_perm(const cplx *__restrict__ psi, double *__restrict__ out, PermTile T)
+{
+    __shared__ double sm[1 << (2 * PP_C)];
+    const uint32_t nel = 1u << T.nt;
+    const uint64_t ntiles = 1ull << T.nrest;
+    for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        uint64_t sbase = 0, dbase = 0;
+        for (int q = 0; q < T.nrest; q++) {
+            const uint64_t bit = (tile >> q) & 1ull;
+            sbase |= bit << T.rest_src[q];
+            dbase |= bit << T.rest_dst[q];
+        }
+        for (uint32_t e = threadIdx.x; e < nel; e += blockDim.x) {
+            uint64_t off = 0;
+            for (int j = 0; j < T.nt; j++) off |= (uint64_t)((e >> j) & 1u) << T.src_pos[j];
+            const cplx a = psi[sbase | off];
+            sm[e] = a.x * a.x + a.y * a.y;
+        }
+        __syncthreads();
+        for (uint32_t e = threadIdx.x; e < nel; e += blockDim.x) { // e enumerates in destination order
+            uint64_t off = 0;
+            uint32_t se = 0;
+            for (int j = 0; j < T.nt; j++) {
+                const uint32_t bit = (e >> j) & 1u;
+                off |= (uint64_t)bit << T.dst_pos[j];
+                se |= bit << T.dst_rank[j];
+            }
+            out[dbase | off] = sm[se];
+        }
+        __syncthreads();
+    }
+}
+
+extern "C" int b200k_probs_all_perm(const double *psi, double *out, int n, const uint8_t *perm, void *stream)
+{
+    if (n < 1 || n > 62) return (int)cudaErrorInvalidValue;
+    PermTile T;
+    memset(&T, 0, sizeof(T));
+    T.n = (uint8_t)n;
+    const int C = n < PP_C ? n : PP_C;
+    bool in_tile[64] = {false};
+    for (int b = 0; b < C; b++) in_tile[b] = true;                 // low source bits
+    for (int b = 0; b < n; b++)
+        if (perm[b] < C) in_tile[b] = true;                        // sources of the low destination bits
+    int nt = 0;
+    for (int b = 0; b < n; b++)
+        if (in_tile[b]) T.src_pos[nt++] = (uint8_t)b;
+    T.nt = (uint8_t)nt;
+    // destination order: tile bits sorted by destination position
+    int order[2 * PP_C];
+    for (int j = 0; j < nt; j++) order[j] = j;
+    for (int i = 0; i < nt; i++)
+        for (int j = i + 1; j < nt; j++)
+            if (perm[T.src_pos[order[j]]] < perm[T.src_pos[order[i]]]) {
+                const int tmp = order[i];
+                order[i] = order[j];
+                order[j] = tmp;
+            }
+    for (int j = 0; j < nt; j++) {
+        T.dst_rank[j] = (uint8_t)order[j];
+        T.dst_pos[j] = perm[T.src_pos[order[j]]];
+    }
+    int nr = 0;
+    for (int b = 0; b < n; b++)
+        if (!in_tile[b]) {
+            T.rest_src[nr] = (uint8_t)b;
+            T.rest_dst[nr] = perm[b];
+            nr++;
+        }
+    T.nrest = (uint8_t)nr;
+    uint64_t nb = 1ull << nr;
+    if (nb > 148 * 16) nb = 148 * 16;
+    k_probs_all_perm<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>((const cplx *)psi, out, T);
     return (int)cudaGetLastError();
 }
 

@@ -106,6 +106,7 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "lazy_adjoint") o.lazy_adjoint = as_int(1) != 0;
         else if (k == "p2p_swap") o.p2p_swap = as_int(1) != 0;
         else if (k == "adaptive_rows") o.adaptive_rows = as_int(1) != 0;
+        else if (k == "virtual_swap") o.virtual_swap = as_int(1) != 0;
     }
     B200_FAIL_IF(o.world < 1 || (o.world & (o.world - 1)) || o.world > 64, "world_size must be a power of two (<= 64)");
     B200_FAIL_IF(o.rank < 0 || o.rank >= o.world, "rank out of range");
@@ -211,6 +212,8 @@ void Simulator::allocate(int64_t n)
     rank_base_ = (uint64_t)opt_.rank << nl_;
     pos_.resize((size_t)n);
     for (int q = 0; q < (int)n; q++) pos_[q] = q;
+    wire_bit_.resize((size_t)n);
+    for (int64_t w = 0; w < n; w++) wire_bit_[(size_t)w] = (int)(n - 1 - w);
     const size_t bytes = sizeof(cplx) << nl_;
     try {
         // a shard whose peers hold a mapping of it (peer-to-peer qubit swap) is kept across
@@ -249,6 +252,8 @@ void Simulator::allocate_one()
     n_ += 1;
     nl_ = n_;
     pos_.push_back((int)n_ - 1);
+    for (auto &b : wire_bit_) b += 1; // every existing index bit moved up by one
+    wire_bit_.push_back(0);           // the new wire is the new least significant bit
 }
 
 void Simulator::release()
@@ -313,7 +318,31 @@ struct BorrowedEngine { // same min/max as std::mt19937 => identical generate_ca
 int Simulator::lbit(int64_t wire) const
 {
     B200_FAIL_IF(wire < 0 || wire >= n_, "Invalid wire index " + std::to_string(wire));
-    return (int)(n_ - 1 - wire); // wire 0 = most significant bit
+    return wire_bit_[(size_t)wire]; // canonically n-1-wire (wire 0 = most significant bit); SWAPs relabel
+}
+
+bool Simulator::wire_identity() const
+{
+    for (int64_t w = 0; w < n_; w++)
+        if (wire_bit_[(size_t)w] != (int)(n_ - 1 - w)) return false;
+    return true;
+}
+
+// Turns the wire relabelling accumulated by SWAP gates back into data movement: after this call wire w
+// sits on logical bit n-1-w again (needed where the whole vector leaves in canonical order: State).
+void Simulator::restore_wire_order()
+{
+    for (int64_t w = 0; w < n_; w++) {
+        const int want = (int)(n_ - 1 - w);
+        if (wire_bit_[(size_t)w] == want) continue;
+        int64_t v = -1;
+        for (int64_t u = 0; u < n_; u++)
+            if (wire_bit_[(size_t)u] == want) v = u;
+        std::vector<GateOp> ops;
+        canonicalize(ops, "SWAP", {}, {w, v}, false, {}, {}, ""); // exchanges the contents of the two bits
+        enqueue(std::move(ops));
+        std::swap(wire_bit_[(size_t)w], wire_bit_[(size_t)v]);    // ... and the labels: the logical state is unchanged
+    }
 }
 uint64_t Simulator::bit_of(int64_t wire) const { return 1ull << lbit(wire); }
 
@@ -628,6 +657,17 @@ void Simulator::named_op(const std::string &name, const std::vector<double> &par
                          const std::string &pauli_word)
 {
     B200_FAIL_IF(!psi_, "No qubits allocated");
+    if (opt_.virtual_swap && !recording_ && cw.empty() && name == "SWAP") {
+        // an uncontrolled SWAP moves no data: the two wires trade index bits.  (While a tape is being
+        // recorded SWAPs stay real gates, so that the adjoint replay sees the labels it recorded.)
+        B200_FAIL_IF(wires.size() != 2, "Invalid number of wires for SWAP");
+        check_wires(wires, cw);
+        std::swap(wire_bit_[(size_t)wires[0]], wire_bit_[(size_t)wires[1]]);
+        stats_.gates_enqueued++;
+        stats_.relabelled_swaps++;
+        stats_.algorithmic_bytes += 32.0 * std::ldexp(1.0, (int)nl_);
+        return;
+    }
     std::vector<GateOp> ops;
     canonicalize(ops, name, params, wires, inverse, cw, cv, pauli_word);
     if (name != "Identity") {
@@ -1702,6 +1742,7 @@ void Simulator::set_basis_state(const std::vector<int8_t> &bits, const std::vect
                  "BasisState parameter and wires must be of equal length.");
     check_wires(wires, {});
     queue_.clear(); // the whole register is overwritten
+    for (int64_t w = 0; w < n_; w++) wire_bit_[(size_t)w] = (int)(n_ - 1 - w); // canonical wire order again
     uint64_t idx = 0;
     for (size_t j = 0; j < wires.size(); j++) {
         B200_FAIL_IF(bits[j] != 0 && bits[j] != 1, "BasisState parameter must consist of 0 or 1 integers.");
@@ -1721,6 +1762,7 @@ void Simulator::set_state(const CVec &st, const std::vector<int64_t> &wires)
     B200_FAIL_IF(st.size() != (size_t(1) << k), "Invalid state size: must be 2^len(wires)");
     queue_.clear();
     for (int q = 0; q < (int)n_; q++) pos_[q] = q; // the register is overwritten: identity layout
+    for (int64_t w = 0; w < n_; w++) wire_bit_[(size_t)w] = (int)(n_ - 1 - w); // ... and canonical wire order
     bool natural = (int64_t)k == n_;
     for (size_t j = 0; j < k && natural; j++) natural = wires[j] == (int64_t)j;
     if (natural) { // each rank takes its contiguous slice
@@ -2127,6 +2169,7 @@ static void d2h_strided(void *stream, const void *dsrc, size_t elem_bytes, size_
 void Simulator::state(double *out_ri, int64_t stride)
 {
     B200_FAIL_IF(!psi_, "No qubits allocated");
+    if (!wire_identity()) restore_wire_order();
     flush();
     if (!sharded()) {
         d2h_strided(stream_, psi_->p(), sizeof(cplx), size_t(1) << n_, out_ri, stride);
@@ -2222,8 +2265,13 @@ void Simulator::probs(const std::vector<int64_t> &wires_in, double *out, int64_t
     const size_t k = wires_in.empty() ? (size_t)n_ : wires_in.size();
     ensure_buffer(probs_buf_, sizeof(double) << k);
     if (!sharded()) {
-        if (all) {
+        if (all && wire_identity()) {
             CUDA_CHECK(b200k_probs_all(psi_->d(), probs_buf_->d(), (int)n_, stream_));
+        }
+        else if (all) { // wires were relabelled by SWAPs: undo the relabelling on the way out
+            uint8_t perm[64];
+            for (int64_t w = 0; w < n_; w++) perm[wire_bit_[(size_t)w]] = (uint8_t)(n_ - 1 - w);
+            CUDA_CHECK(b200k_probs_all_perm(psi_->d(), probs_buf_->d(), (int)n_, perm, stream_));
         }
         else {
             std::vector<uint8_t> tb(k);

@@ -104,6 +104,7 @@ struct Options {
     int jit_min_qubits = 22;  // smaller local states stay on the interpreter
     int jit_dbuf = 1;         // cp.async double-buffered tiles in specialised passes
     int jit_fuse_diag = 1;    // fuse runs of diagonal ops inside a register round
+    bool virtual_swap = true; // uncontrolled SWAP gates relabel wires instead of moving amplitudes
     bool p2p_swap = true;     // global<->local qubit swap over mapped peer memory (NVLink P2P / CUDA IPC)
     bool lazy_adjoint = true; // adjoint gradient: apply U^dagger only when the next generator does not commute with it
 };
@@ -178,6 +179,9 @@ class Simulator {
     // --- helpers -------------------------------------------------------------------------------
     uint64_t bit_of(int64_t wire) const;
     int lbit(int64_t wire) const;
+    bool wire_identity() const;
+    void restore_wire_order();
+    std::vector<int> wire_bit_; // wire -> logical index bit
     void check_wires(const std::vector<int64_t> &wires, const std::vector<int64_t> &cw) const;
     void canonicalize(std::vector<GateOp> &out, const std::string &name,
                       const std::vector<double> &params, const std::vector<int64_t> &wires,

@@ -131,6 +131,7 @@ typedef struct b200sv_stats {
     int64_t jit_pending;      /* process-wide: compilations still running in the background */
     double jit_compile_ms;    /* process-wide: NVRTC time spent so far (sum over pool threads) */
     int64_t p2p_exchanges;    /* qubit swaps that ran as in-place kernels over mapped peer memory */
+    int64_t relabelled_swaps; /* uncontrolled SWAP gates executed as wire relabelling (no data movement) */
 } b200sv_stats;
 int b200sv_get_stats(b200sv_device *d, b200sv_stats *out);
 int b200sv_reset_stats(b200sv_device *d);

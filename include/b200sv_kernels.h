@@ -209,6 +209,9 @@ int b200k_expval_diag_batch(const double *psi, int n_local, uint64_t rank_base,
 
 /* ---- probabilities ---------------------------------------------------------------------------- */
 int b200k_probs_all(const double *psi, double *out, int n_local, void *stream);
+/* out[dst(i)] = |psi_i|^2 with source index bit b landing on destination bit perm[b] (a permutation of
+ * 0..n-1): undoes the host's wire relabelling (SWAP gates executed as renames) on the way out. */
+int b200k_probs_all_perm(const double *psi, double *out, int n, const uint8_t *perm, void *stream);
 /* out[o] = sum of |psi_i|^2 over i whose bits at tb[0..k) (most significant first) spell o.
  * scratch: 2^k * b200k_probs_splits(n_local, k) doubles. */
 int b200k_probs_splits(int n_local, int k);

@@ -455,3 +455,63 @@ def test_large_roundtrip_properties(gpu):
     # back to |0...0>: probability of the all-zero string is 1
     assert abs(d.probs([n - 1])[0] - 1) < 1e-10
     assert abs(d.expval(d.obs_named("PauliZ", 0)) - 1) < 1e-10
+
+
+# ---- SWAP gates as wire relabelling ---------------------------------------------------------------
+@pytest.mark.parametrize("cfg", [dict(), dict(jit="always"), dict(virtual_swap=False)])
+@pytest.mark.parametrize("n,seed", [(2, 0), (5, 1), (9, 2), (12, 3), (15, 4)])
+def test_swap_relabelling(gpu, oracle_mod, n, seed, cfg):
+    """Uncontrolled SWAPs move no data (the wires trade index bits); every way of looking at the state
+    must still see the oracle's wire order: State, Probs (all wires: permuted on the way out), partial
+    probs, expval, seeded samples on all wires (bit-exact: the alias table is built over the canonical
+    bin order), Measure, and gates applied after the swaps."""
+    rng = np.random.default_rng(seed)
+    ops = []
+    for layer in range(6):
+        ops += [random_op(rng, n) for _ in range(6)]
+        for _ in range(3):
+            a, b = (int(x) for x in rng.permutation(n)[:2])
+            ops.append(("SWAP", [], [a, b]))
+    o = oracle_mod.OracleDevice(n, seed=37)
+    d = gpu.B200Device(n, seed=37, **cfg)
+    init = random_state(seed + 77, n)
+    o.set_state(init, list(range(n))); d.set_state(init, list(range(n)))
+    apply_ops(o, ops); apply_ops(d, ops)
+    s = d.stats()
+    assert (s.relabelled_swaps >= 18) if cfg.get("virtual_swap", True) else (s.relabelled_swaps == 0)
+    assert np.max(np.abs(o.probs() - d.probs())) < TOL                       # all wires, permuted output
+    w = [int(x) for x in rng.permutation(n)[:min(n, 3)]]
+    assert np.max(np.abs(o.probs(w) - d.probs(w))) < TOL
+    obs = random_pauli_obs(rng, n)
+    assert abs(o.expval(build_obs(o, obs)) - d.expval(build_obs(d, obs))) < TOL
+    assert np.array_equal(o.sample(2000), d.sample(2000))
+    assert o.measure(n - 1) == d.measure(n - 1)
+    more = [random_op(rng, n) for _ in range(10)]
+    apply_ops(o, more); apply_ops(d, more)
+    assert np.max(np.abs(o.state() - d.state())) < 1e-11                      # State restores the order
+    # after State the relabelling is gone and everything still agrees
+    assert np.max(np.abs(o.probs() - d.probs())) < 1e-11
+
+
+def test_swap_relabelling_with_tape_and_dynamic_qubits(gpu, oracle_mod):
+    n = 6
+    ops = [("RX", [0.3], [0]), ("SWAP", [], [0, 4]), ("RY", [0.7], [4]), ("CNOT", [], [4, 2]), ("SWAP", [], [2, 5]),
+           ("RZ", [1.1], [5]), ("IsingXX", [0.4], [1, 5])]
+    o, d = oracle_mod.OracleDevice(n), gpu.B200Device(n)
+    pre = [("Hadamard", [], [1]), ("SWAP", [], [1, 3]), ("CNOT", [], [3, 0])]      # relabelled before the tape starts
+    apply_ops(o, pre); apply_ops(d, pre)
+    o.start_tape(); d.start_tape()
+    apply_ops(o, ops); apply_ops(d, ops)
+    obs = ("Ham", [0.5, -1.0], [("N", "PauliZ", 5), ("T", [("N", "PauliX", 0), ("N", "PauliY", 3)])])
+    eo, ed = o.expval(build_obs(o, obs)), d.expval(build_obs(d, obs))
+    o.stop_tape(); d.stop_tape()
+    assert abs(eo - ed) < TOL
+    assert np.max(np.abs(o.gradient() - d.gradient())) < 1e-11
+    # dynamic allocation on a relabelled register
+    d2 = gpu.B200Device(3)
+    apply_ops(d2, [("Hadamard", [], [0]), ("SWAP", [], [0, 2]), ("CNOT", [], [2, 1])])
+    d2.allocate_qubit()
+    apply_ops(d2, [("CNOT", [], [1, 3])])
+    o2 = oracle_mod.OracleDevice(4)
+    apply_ops(o2, [("Hadamard", [], [0]), ("SWAP", [], [0, 2]), ("CNOT", [], [2, 1]), ("CNOT", [], [1, 3])])
+    assert np.max(np.abs(o2.state() - d2.state())) < TOL

@@ -272,3 +272,28 @@ def test_swap_paths_peer_memory_and_staged(gpu, oracle_mod, world, p2p):
         assert np.max(np.abs(st2 - want)) < TOL
         assert ex > 0
         assert (p2 == ex) if p2p else (p2 == 0)
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_swap_relabelling_sharded(gpu, oracle_mod, world):
+    n = 9
+    rng = np.random.default_rng(3)
+    ops = []
+    for layer in range(5):
+        ops += random_circuit(600 + layer, n, 8)
+        ops += [("SWAP", [], [int(x) for x in rng.permutation(n)[:2]]) for _ in range(3)]
+    o = _oracle(oracle_mod, n, ops, seed=37)
+    want_p, want_pp, want_s = o.probs(), o.probs([0, 8, 4]), o.sample(300)
+    want = o.state()
+
+    def prog(d, r):
+        d.seed(37)
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        return d.probs(), d.probs([0, 8, 4]), d.sample(300), d.state(), int(d.stats().relabelled_swaps)
+
+    for p, pp, s, st, rs in gpu.run_spmd(world, prog, tile_bits=4, min_row_bits=2):
+        assert rs >= 15
+        assert np.max(np.abs(p - want_p)) < TOL and np.max(np.abs(pp - want_pp)) < TOL
+        assert np.array_equal(s, want_s)
+        assert np.max(np.abs(st - want)) < TOL
