@@ -1035,3 +1035,160 @@ extern "C" int b200k_sampler_draw(const double *probs, int64_t nbins, const doub
         probs, nbins, nch, cumD, cumE, u, nshots, out_idx);
     return (int)cudaGetLastError();
 }
+
+// =================================================================================================
+// Batched bilinear forms <phi| P_g |lam> for up to B200K_BATCH_GENS Pauli-word generators in ONE read
+// pass over the two vectors (adjoint gradient: every parameter whose generator commutes with the
+// not-yet-applied adjoint gates is evaluated on the same pair of vectors).  Tile geometry as in the
+// gate passes: a tile of phi and the same tile of lam are staged in shared memory; a generator whose
+// X/Y bits all lie inside the tile pairs amplitude i with i ^ x inside the tile; Z factors, controls
+// and rank bits outside the tile enter through the tile's base index.  Per (generator, tile) every
+// warp reduces with shuffles into its own shared-memory slot; per-CTA partials go to `partial`, a
+// second kernel sums them in fixed order (run-to-run reproducible) and applies the i^ny factor.
+// =================================================================================================
+struct BatchParams {
+    B200k2Header h;
+    B200kBatchGen g[B200K_BATCH_GENS];
+    int ngen;
+};
+
+__global__ void __launch_bounds__(256, 3)
+k_bilinear_batch(const cplx *__restrict__ phi, const cplx *__restrict__ lam, const __grid_constant__ BatchParams P,
+                 double *__restrict__ partial)
+{
+    extern __shared__ cplx sm2[]; // phi tile, lam tile
+    __shared__ double wacc[B200K_BATCH_GENS][8][2];
+    const int t = P.h.t, c = P.h.c, nhigh = P.h.nhigh;
+    const uint32_t nelem = 1u << t, lowmask = (1u << c) - 1u, tid = threadIdx.x;
+    cplx *sA = sm2, *sB = sm2 + nelem;
+    for (int q = tid; q < P.ngen * 16; q += blockDim.x) (&wacc[0][0][0])[q] = 0.0;
+    auto off_of = [&](uint32_t e) -> uint64_t {
+        uint64_t o = e & lowmask;
+        const uint32_t r = e >> c;
+        for (int hh = 0; hh < nhigh; hh++) o |= (uint64_t)((r >> hh) & 1u) << P.h.high_pos[hh];
+        return o;
+    };
+    const bool same = phi == lam;
+    __syncthreads();
+    for (uint64_t tile = blockIdx.x; tile < P.h.ntiles; tile += gridDim.x) {
+        uint64_t base = tile << c;
+        for (int hh = 0; hh < nhigh; hh++) {
+            const int p = P.h.high_pos[hh];
+            base = ((base >> p) << (p + 1)) | (base & ((1ull << p) - 1ull));
+        }
+        const uint64_t obase = base | P.h.rank_base;
+        for (uint32_t e = tid; e < nelem; e += blockDim.x) {
+            const uint64_t o = base | off_of(e);
+            const cplx b = lam[o];
+            sB[e] = b;
+            sA[e] = same ? b : phi[o];
+        }
+        __syncthreads();
+        for (int g = 0; g < P.ngen; g++) {
+            const B200kBatchGen &G = P.g[g];
+            if ((obase & G.co_m) != G.co_v) continue; // uniform per tile
+            const uint32_t opar = __popcll(obase & G.zo) & 1u;
+            double ar = 0.0, ai = 0.0;
+            for (uint32_t e = tid; e < nelem; e += blockDim.x) {
+                if ((e & G.cin_m) != G.cin_v) continue;
+                const uint32_t j = e ^ G.xin;
+                const cplx a = sA[e], b = sB[j];
+                // conj(a) * b, signed by the parity of the Z factors at index j
+                double tr = a.x * b.x + a.y * b.y, ti = a.x * b.y - a.y * b.x;
+                if ((__popc(j & G.zin) + opar) & 1u) {
+                    tr = -tr;
+                    ti = -ti;
+                }
+                ar += tr;
+                ai += ti;
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                ar += __shfl_down_sync(0xffffffffu, ar, off);
+                ai += __shfl_down_sync(0xffffffffu, ai, off);
+            }
+            if ((tid & 31u) == 0) {
+                wacc[g][tid >> 5][0] += ar;
+                wacc[g][tid >> 5][1] += ai;
+            }
+        }
+        __syncthreads();
+    }
+    __syncthreads();
+    for (int q = tid; q < P.ngen * 2; q += blockDim.x) {
+        const int g = q >> 1, comp = q & 1;
+        double s = 0.0;
+        for (int w = 0; w < 8; w++) s += wacc[g][w][comp];
+        partial[((size_t)blockIdx.x * B200K_BATCH_GENS + g) * 2 + comp] = s;
+    }
+}
+
+struct BatchOut {
+    double *out[B200K_BATCH_GENS];
+    int ny[B200K_BATCH_GENS];
+};
+__global__ void __launch_bounds__(256)
+k_bilinear_batch_final(const double *__restrict__ partial, int nblocks, BatchOut O)
+{
+    const int g = blockIdx.x;
+    double v[2] = {0.0, 0.0};
+    for (int i = threadIdx.x; i < nblocks; i += 256) {
+        v[0] += partial[((size_t)i * B200K_BATCH_GENS + g) * 2];
+        v[1] += partial[((size_t)i * B200K_BATCH_GENS + g) * 2 + 1];
+    }
+    __shared__ double sh[2][8];
+#pragma unroll
+    for (int q = 0; q < 2; q++)
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) v[q] += __shfl_down_sync(0xffffffffu, v[q], off);
+    if ((threadIdx.x & 31) == 0) {
+        sh[0][threadIdx.x >> 5] = v[0];
+        sh[1][threadIdx.x >> 5] = v[1];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        for (int i = 0; i < 8; i++) {
+            a += sh[0][i];
+            b += sh[1][i];
+        }
+        cplx r = cmul_ipow(make_double2(a, b), O.ny[g]);
+        O.out[g][0] = r.x;
+        O.out[g][1] = r.y;
+    }
+}
+
+extern "C" int64_t b200k_bilinear_batch_scratch_doubles(void) { return (int64_t)148 * 3 * B200K_BATCH_GENS * 2; }
+
+extern "C" int b200k_bilinear_batch(const double *phi, const double *lam, int n_local, const B200k2Header *hdr,
+                                    const B200kBatchGen *gens, int ngen, double *const *outs, double *scratch,
+                                    void *stream)
+{
+    if (ngen < 1 || ngen > B200K_BATCH_GENS || hdr->t > 11 || hdr->t > n_local || hdr->c + hdr->nhigh != hdr->t ||
+        hdr->ntiles != (1ull << (n_local - hdr->t)))
+        return (int)cudaErrorInvalidValue;
+    static unsigned long long attr_mask = 0;
+    int cur_dev = 0;
+    cudaGetDevice(&cur_dev);
+    if (!((attr_mask >> (cur_dev & 63)) & 1ull)) {
+        cudaError_t e = cudaFuncSetAttribute(k_bilinear_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 16 * 2048);
+        if (e != cudaSuccess) return (int)e;
+        attr_mask |= 1ull << (cur_dev & 63);
+    }
+    BatchParams P;
+    memset(&P, 0, sizeof(P));
+    P.h = *hdr;
+    P.ngen = ngen;
+    BatchOut O;
+    for (int g = 0; g < ngen; g++) {
+        P.g[g] = gens[g];
+        O.out[g] = outs[g];
+        O.ny[g] = gens[g].ny;
+    }
+    uint64_t grid = 148 * 3;
+    if (grid > hdr->ntiles) grid = hdr->ntiles;
+    k_bilinear_batch<<<(unsigned)grid, 256, (size_t)2 * sizeof(cplx) << hdr->t, (cudaStream_t)stream>>>(
+        (const cplx *)phi, (const cplx *)lam, P, scratch);
+    k_bilinear_batch_final<<<ngen, 256, 0, (cudaStream_t)stream>>>(scratch, (int)grid, O);
+    return (int)cudaGetLastError();
+}

@@ -107,6 +107,7 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "p2p_swap") o.p2p_swap = as_int(1) != 0;
         else if (k == "adaptive_rows") o.adaptive_rows = as_int(1) != 0;
         else if (k == "virtual_swap") o.virtual_swap = as_int(1) != 0;
+        else if (k == "batch_overlaps") o.batch_overlaps = as_int(1) != 0;
     }
     B200_FAIL_IF(o.world < 1 || (o.world & (o.world - 1)) || o.world > 64, "world_size must be a power of two (<= 64)");
     B200_FAIL_IF(o.rank < 0 || o.rank >= o.world, "rank out of range");
@@ -2077,13 +2078,29 @@ double Simulator::expval(int64_t key)
     }
     // the layout may change between terms (a word with X/Y on a rank bit pulls that qubit in), so
     // masks are translated term by term
-    for (auto &p : offd) {
-        make_local({psi_->d()}, pos_, p.xmask);
-        CUDA_CHECK(b200k_bilinear_pauli(psi_->d(), psi_->d(), (int)nl_, rank_base_, to_phys(pos_, p.xmask),
-                                        to_phys(pos_, p.zmask), p.ny, 0, 0, scratch_->d(),
-                                        result_slot(slot++), stream_));
-        note_launch();
+    bool batched = false;
+    if (opt_.batch_overlaps && nl_ >= 3 && offd.size() > 1) { // many words per read pass
+        std::vector<OvTerm> ov;
+        bool ok = true;
+        int sl = slot;
+        for (auto &p : offd) {
+            ok = ok && __builtin_popcountll(p.xmask) <= std::min<int64_t>(11, nl_) - 3;
+            ov.push_back({p.xmask, p.zmask, 0, 0, p.ny, result_slot(sl++), 0});
+        }
+        if (ok) {
+            overlaps_batched(psi_->d(), psi_->d(), {psi_->d()}, pos_, ov);
+            slot = sl;
+            batched = true;
+        }
     }
+    if (!batched)
+        for (auto &p : offd) {
+            make_local({psi_->d()}, pos_, p.xmask);
+            CUDA_CHECK(b200k_bilinear_pauli(psi_->d(), psi_->d(), (int)nl_, rank_base_, to_phys(pos_, p.xmask),
+                                            to_phys(pos_, p.zmask), p.ny, 0, 0, scratch_->d(),
+                                            result_slot(slot++), stream_));
+            note_launch();
+        }
     const size_t bytes = sizeof(cplx) << nl_;
     for (auto *t : generic) {
         uint64_t xm = 0;
@@ -2520,6 +2537,102 @@ struct Generator {
 };
 } // namespace
 
+// <phi| P_t |lam> for a list of Pauli-word terms (logical masks; optional control predicate), written to
+// t.out as (re, im).  Terms are independent, so they are packed first-fit into batches of up to
+// B200K_BATCH_GENS whose X/Y bits fit one tile, and each batch costs ONE read pass over the two vectors
+// (k_bilinear_batch) instead of one pass per term.  `movable` / `lay`: the vectors that share the
+// layout of phi and lam (sharded registers: a term with an X/Y factor on a rank bit pulls that qubit in).
+void Simulator::overlaps_batched(const double *phi, const double *lam, const std::vector<double *> &movable,
+                                 std::vector<int> &lay, const std::vector<OvTerm> &terms)
+{
+    const int bt = (int)std::min<int64_t>(11, nl_);
+    const int cmin = std::min(3, bt);
+    struct Bin {
+        uint64_t req = 0;
+        std::vector<const OvTerm *> t;
+    };
+    auto launch = [&](const Bin &b) {
+        const int c = fit_rows(b.req, bt);
+        std::vector<int> high;
+        for (int p = c; p < 64; p++)
+            if ((b.req >> p) & 1) high.push_back(p);
+        for (int p = c; (int)high.size() < bt - c; p++)
+            if (!((b.req >> p) & 1)) high.push_back(p);
+        std::sort(high.begin(), high.end());
+        int loc[64];
+        for (int p = 0; p < 64; p++) loc[p] = p < c ? p : -1;
+        for (size_t h = 0; h < high.size(); h++) loc[high[h]] = c + (int)h;
+        auto split = [&](uint64_t mask, uint32_t &inside, uint64_t &outside) {
+            inside = 0;
+            outside = 0;
+            while (mask) {
+                const int p = __builtin_ctzll(mask);
+                mask &= mask - 1;
+                if (loc[p] >= 0) inside |= 1u << loc[p];
+                else outside |= 1ull << p;
+            }
+        };
+        B200k2Header H;
+        std::memset(&H, 0, sizeof(H));
+        H.t = bt;
+        H.c = c;
+        H.nhigh = (int)high.size();
+        for (size_t h = 0; h < high.size(); h++) H.high_pos[h] = (uint8_t)high[h];
+        H.rank_base = rank_base_;
+        H.ntiles = 1ull << (nl_ - bt);
+        std::vector<B200kBatchGen> gens(b.t.size());
+        std::vector<double *> outs(b.t.size());
+        for (size_t q = 0; q < b.t.size(); q++) {
+            const OvTerm &p = *b.t[q];
+            B200kBatchGen &G = gens[q];
+            std::memset(&G, 0, sizeof(G));
+            uint64_t out_x;
+            split(to_phys(lay, p.xmask), G.xin, out_x);
+            B200_FAIL_IF(out_x != 0, "internal: generator bit outside the batch tile");
+            split(to_phys(lay, p.zmask), G.zin, G.zo);
+            split(to_phys(lay, p.cmask), G.cin_m, G.co_m);
+            split(to_phys(lay, p.cval), G.cin_v, G.co_v);
+            G.ny = p.ny;
+            outs[q] = p.out;
+        }
+        ensure_buffer(batch_scratch_, (size_t)b200k_bilinear_batch_scratch_doubles() * sizeof(double));
+        CUDA_CHECK(b200k_bilinear_batch(phi, lam, (int)nl_, &H, gens.data(), (int)gens.size(), outs.data(),
+                                        batch_scratch_->d(), stream_));
+        note_launch();
+    };
+    std::vector<const OvTerm *> rest;
+    for (auto &t : terms) rest.push_back(&t);
+    while (!rest.empty()) {
+        // every term whose X/Y bits are local under the current layout, packed first-fit
+        std::vector<Bin> bins;
+        std::vector<const OvTerm *> later;
+        for (const OvTerm *t : rest) {
+            const uint64_t x = to_phys(lay, t->xmask);
+            if (x >> nl_) {
+                later.push_back(t);
+                continue;
+            }
+            B200_FAIL_IF(fit_rows(x, bt) < 0, "internal: a Pauli word acts non-diagonally on more qubits than a tile holds");
+            bool placed = false;
+            for (auto &b : bins)
+                if (b.t.size() < (size_t)B200K_BATCH_GENS && fit_rows(b.req | x, bt) >= cmin) {
+                    b.req |= x;
+                    b.t.push_back(t);
+                    placed = true;
+                    break;
+                }
+            if (!placed) {
+                bins.emplace_back();
+                bins.back().req = x;
+                bins.back().t.push_back(t);
+            }
+        }
+        for (auto &b : bins) launch(b);
+        if (!later.empty()) make_local(movable, lay, later[0]->xmask); // sharded: one more qubit comes in
+        rest.swap(later);
+    }
+}
+
 std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
 {
     B200_FAIL_IF(!psi_, "No qubits allocated");
@@ -2608,9 +2721,24 @@ std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
     // diagonally.  A QAOA cost layer (42 ZZ rotations) or a layer of one-qubit rotations on distinct
     // wires then needs ONE fused application instead of one per parameter: per parameter only the read
     // pass of the overlap remains (2 x 16 x 2^n bytes instead of 6 x).
+    // Overlaps whose generators commute with the pending gates all refer to the SAME pair of vectors, so
+    // they are collected and evaluated in batches: one read pass of (phi_k, lambda) per batch of up to
+    // B200K_BATCH_GENS Pauli-word generators whose X/Y bits fit one tile (k_bilinear_batch), instead of
+    // one read pass per parameter.
+    std::vector<OvTerm> pend_ov;
+    auto flush_overlaps = [&]() {
+        if (pend_ov.empty()) return;
+        for (size_t k = 0; k < K; k++) {
+            std::vector<OvTerm> terms = pend_ov;
+            for (auto &t : terms) t.out = result_slot((int)(k * T + t.tag));
+            overlaps_batched(phi[k]->d(), lambda.d(), vecs, lay, terms);
+        }
+        pend_ov.clear();
+    };
     std::vector<GateOp> pending;
     uint64_t pendX = 0, pendZ = 0;
     auto apply_pending = [&]() {
+        flush_overlaps();
         if (pending.empty()) return;
         execute(vecs, lay, pending);
         pending.clear();
@@ -2637,6 +2765,13 @@ std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
                     const uint64_t gz = (g.is_pair ? 0 : g.zmask) | cmask;
                     if (!opt_.lazy_adjoint || (gx & (pendX | pendZ)) || (gz & pendX)) apply_pending();
                 }
+                if (opt_.batch_overlaps && !g.is_pair) { // evaluated together with its neighbours, see flush_overlaps
+                    pend_ov.push_back({g.xmask, g.zmask, cmask, cval, g.ny, nullptr, (size_t)tp});
+                    for (size_t k = 0; k < K; k++) sig[k * T + (size_t)tp] = g.sigma;
+                    tp--;
+                    cur--;
+                    goto adjoint_of_this_op;
+                }
                 make_local(vecs, lay, g.is_pair ? g.tmask : g.xmask);
                 for (size_t k = 0; k < K; k++) {
                     double *slot = result_slot((int)(k * T + (size_t)tp));
@@ -2657,6 +2792,7 @@ std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
             }
             cur--;
         }
+    adjoint_of_this_op:
         const size_t before = pending.size();
         if (op.name == "QubitUnitary")
             canonicalize_matrix(pending, op.matrix, op.wires, !op.inverse, op.ctrl_wires, op.ctrl_values);
@@ -2668,6 +2804,7 @@ std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
             pendZ |= pending[q].zsupport();
         }
     }
+    flush_overlaps();
     std::vector<double> h;
     read_results((int)(K * T), h);
     for (size_t i = 0; i < K * T; i++) jac[i] = -2.0 * sig[i] * h[2 * i + 1];

@@ -106,6 +106,7 @@ struct Options {
     int jit_fuse_diag = 1;    // fuse runs of diagonal ops inside a register round
     bool virtual_swap = true; // uncontrolled SWAP gates relabel wires instead of moving amplitudes
     bool p2p_swap = true;     // global<->local qubit swap over mapped peer memory (NVLink P2P / CUDA IPC)
+    bool batch_overlaps = true; // adjoint gradient: evaluate commuting generators' overlaps in batched read passes
     bool lazy_adjoint = true; // adjoint gradient: apply U^dagger only when the next generator does not commute with it
 };
 
@@ -233,6 +234,14 @@ class Simulator {
     void read_results(int nslots, std::vector<double> &host);
     double *result_slot(int slot);
 
+    struct OvTerm { // one Pauli-word bilinear form <phi| P |lam> (logical masks)
+        uint64_t xmask, zmask, cmask, cval;
+        int ny;
+        double *out; // device, (re, im)
+        size_t tag;
+    };
+    void overlaps_batched(const double *phi, const double *lam, const std::vector<double *> &movable,
+                          std::vector<int> &lay, const std::vector<OvTerm> &terms);
     bool draw_outcome(const double p[2], int postselect);
     double sampled_term_mean(const ObsTerm &t);
     double uniform01();
@@ -252,7 +261,7 @@ class Simulator {
     int cuda_device_ = 0;
     void *stream_ = nullptr;
     std::unique_ptr<DeviceBuffer> psi_, tmp_, acc_, scratch_, results_, probs_buf_, misc_;
-    std::unique_ptr<DeviceBuffer> matrix_arena_;
+    std::unique_ptr<DeviceBuffer> matrix_arena_, batch_scratch_;
     size_t arena_used_ = 0;
     double *pinned_ = nullptr;
     size_t pinned_doubles_ = 0;

@@ -202,6 +202,23 @@ int b200k_bilinear_pair(const double *phi, const double *lam, int n_local, uint6
                         uint64_t tmask, uint64_t a, uint64_t b, const double *g8, uint64_t cmask,
                         uint64_t cval, double *scratch, double *out, void *stream);
 
+/* Batched version of b200k_bilinear_pauli: up to B200K_BATCH_GENS Pauli-word generators evaluated in
+ * ONE read pass over phi and lam (tile geometry of the gate passes: header fields t, c, nhigh, high_pos,
+ * rank_base, ntiles).  Masks are split like the gate ops: inside the tile (tile-local bit positions) and
+ * outside (physical positions, incl. rank bits).  outs[g] receives (re, im) of generator g. */
+#define B200K_BATCH_GENS 32
+typedef struct B200kBatchGen {
+    uint32_t xin;            /* X/Y bits (tile-local); all of them must lie inside the tile        */
+    uint32_t zin;            /* Z/Y bits inside the tile                                            */
+    uint32_t cin_m, cin_v;   /* control predicate inside the tile                                   */
+    uint64_t zo;             /* Z bits outside the tile                                             */
+    uint64_t co_m, co_v;     /* control predicate outside the tile                                  */
+    int32_t ny, pad;         /* number of Y factors (phase i^ny)                                    */
+} B200kBatchGen;
+int64_t b200k_bilinear_batch_scratch_doubles(void);
+int b200k_bilinear_batch(const double *phi, const double *lam, int n_local, const struct B200k2Header *hdr,
+                         const B200kBatchGen *gens, int ngen, double *const *outs, double *scratch, void *stream);
+
 /* out[0] = sum_i |psi_i|^2 * sum_t coef[t] * (-1)^popc((rank_base|i) & zmask[t]). */
 int b200k_expval_diag_batch(const double *psi, int n_local, uint64_t rank_base,
                             const uint64_t *zmasks, const double *coefs, int nterms,

@@ -8,13 +8,14 @@ import numpy as np
 from catalyst_b200 import capi, workloads
 from dsl import apply_ops, build_obs
 args = [a for a in sys.argv[1:] if not a.startswith("--")]
-reps = 3
+reps = int(os.environ.get("REPS", 3))
 which = args or ["c1", "c2", "c4"]
 n2 = int(os.environ.get("C2_QUBITS", 28)); n4 = int(os.environ.get("C4_QUBITS", 26))
 
 
 def run(name, n, ops, obs, grad, mcm=False):
-    d = capi.B200Device(n, seed=37)
+    kw = eval(os.environ.get("B200_KW", "{}"))
+    d = capi.B200Device(n, seed=37, **kw)
     for rep in range(reps):
         d.set_basis_state([0] * n, list(range(n))); d.synchronize(); d.reset_stats()
         t0 = time.perf_counter()
@@ -28,13 +29,13 @@ def run(name, n, ops, obs, grad, mcm=False):
             apply_ops(d, ops)
         d.synchronize(); t1 = time.perf_counter()
         e = d.expval(build_obs(d, obs)); t2 = time.perf_counter()
+        s = d.stats()
         g = None
         if grad:
             d.stop_tape()
             g = d.gradient(); t3 = time.perf_counter()
-        s = d.stats()
         line = f"{name} n={n} rep {rep}: circuit {1e3*(t1-t0):.1f} ms ({len(ops)} gates, {s.tile_passes} passes, {s.jit_passes} specialised)  expval {1e3*(t2-t1):.1f} ms = {e:.12f}"
-        if grad: line += f"  gradient {1e3*(t3-t2):.1f} ms ({g.size} entries, |g|={np.linalg.norm(g):.6f})"
+        if grad: line += f"  gradient {1e3*(t3-t2):.1f} ms ({g.size} entries, |g|={np.linalg.norm(g):.6f}, launches {d.stats().other_launches - s.other_launches}, passes {d.stats().tile_passes - s.tile_passes})"
         if mcm: line += f"  mcm {m}"
         print(line, flush=True)
         d.jit_wait()
