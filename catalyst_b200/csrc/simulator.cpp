@@ -1994,18 +1994,32 @@ void Simulator::apply_observable(int64_t key, const double *vin, double *vout, c
     flatten(key, terms);
     bool first = true;
     const size_t bytes = sizeof(cplx) << nl_;
+    // Pauli words are applied B200K_APPLY_WORDS at a time (one read+write of the accumulator per batch)
+    std::vector<uint64_t> bx, bz;
+    std::vector<int> bny;
+    std::vector<double> bc;
+    auto flush_words = [&]() {
+        if (bx.empty()) return;
+        CUDA_CHECK(b200k_pauli_apply_batch(vout, vin, (int)nl_, rank_base_, bx.data(), bz.data(), bny.data(), bc.data(),
+                                           (int)bx.size(), first ? 0 : 1, stream_));
+        note_launch();
+        first = false;
+        bx.clear(); bz.clear(); bny.clear(); bc.clear();
+    };
     for (auto &t : terms) {
         std::vector<PauliTerm> pts;
         if (term_to_paulis(t, pts)) {
             for (auto &p : pts) {
-                CUDA_CHECK(b200k_pauli_apply(vout, vin, (int)nl_, rank_base_, to_phys(pos, p.xmask),
-                                             to_phys(pos, p.zmask), p.ny, p.coef.real(), p.coef.imag(),
-                                             first ? 0 : 1, stream_));
-                note_launch();
-                first = false;
+                bx.push_back(to_phys(pos, p.xmask));
+                bz.push_back(to_phys(pos, p.zmask));
+                bny.push_back(p.ny);
+                bc.push_back(p.coef.real());
+                bc.push_back(p.coef.imag());
+                if (bx.size() == (size_t)B200K_APPLY_WORDS) flush_words();
             }
             continue;
         }
+        flush_words();
         ensure_buffer(tmp_, bytes);
         CUDA_CHECK(cudaMemcpyAsync(tmp_->p(), vin, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
         std::vector<GateOp> ops;
@@ -2024,6 +2038,7 @@ void Simulator::apply_observable(int64_t key, const double *vin, double *vout, c
         note_launch();
         first = false;
     }
+    flush_words();
     if (first) CUDA_CHECK(cudaMemsetAsync(vout, 0, bytes, (cudaStream_t)stream_));
 }
 

@@ -243,6 +243,12 @@ int b200k_collapse(double *psi, int n_local, uint64_t rank_base, int pos, int ke
 int b200k_pauli_apply(double *out, const double *in, int n_local, uint64_t rank_base,
                       uint64_t xmask, uint64_t zmask, int ny, double coef_re, double coef_im,
                       int accumulate, void *stream);
+/* out_i = (accumulate ? out_i : 0) + sum_t coef[t] * (P_t in)_i for nwords <= B200K_APPLY_WORDS words in one
+ * pass (coefs_ri = (re, im) per word) */
+#define B200K_APPLY_WORDS 16
+int b200k_pauli_apply_batch(double *out, const double *in, int n_local, uint64_t rank_base,
+                            const uint64_t *xmasks, const uint64_t *zmasks, const int *nys,
+                            const double *coefs_ri, int nwords, int accumulate, void *stream);
 /* acc += coef * x */
 int b200k_axpy(double *acc, const double *x, double coef, int n_local, void *stream);
 /* psi = 0 everywhere, then psi[index] = 1 if index >= 0 */
