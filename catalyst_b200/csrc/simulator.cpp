@@ -104,7 +104,7 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "jit_dbuf") o.jit_dbuf = (int)as_int(o.jit_dbuf);
         else if (k == "jit_fuse_diag") o.jit_fuse_diag = (int)as_int(o.jit_fuse_diag);
         else if (k == "lazy_adjoint") o.lazy_adjoint = as_int(1) != 0;
-        else if (k == "p2p_swap") o.p2p_swap = as_int(1) != 0;
+        else if (k == "p2p_swap") o.p2p_swap = (int)as_int(-1);
         else if (k == "adaptive_rows") o.adaptive_rows = as_int(1) != 0;
         else if (k == "virtual_swap") o.virtual_swap = as_int(1) != 0;
         else if (k == "batch_overlaps") o.batch_overlaps = as_int(1) != 0;
@@ -145,6 +145,8 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
         jit_mode_ = v == "off" || v == "0" ? 0 : (v == "always" || v == "2" ? 2 : 1);
     }
     if (const char *e = std::getenv("B200SV_JIT_DBUF")) opt_.jit_dbuf = std::atoi(e);
+    if (const char *e = std::getenv("B200SV_P2P_SWAP")) opt_.p2p_swap = std::atoi(e);
+    if (const char *e = std::getenv("B200SV_MIN_ROW_BITS")) opt_.min_row_bits = std::max(0, std::min(opt_.tile_bits, std::atoi(e)));
     if (const char *e = std::getenv("B200SV_JIT_REGBITS")) opt_.jit_regbits = std::max(1, std::min(5, std::atoi(e)));
     CUDA_CHECK(cudaSetDevice(dev));
     cudaStream_t st;
@@ -1004,7 +1006,10 @@ void Simulator::swap_bits(const std::vector<double *> &vecs, std::vector<int> &p
     // Peer-to-peer path (the state shard only; gradient work vectors use the staged path): every
     // pairwise sub-block exchange runs as ONE kernel over the peer's mapped shard, bracketed by two
     // stream-ordered rendezvous.  No staging buffer, no pack/unpack pass, no host synchronisation.
-    if (opt_.p2p_swap && vecs.size() == 1 && psi_ && vecs[0] == psi_->d() && sub >= 2 && ensure_psi_peers()) {
+    // auto (-1): on between threads of one process (where the staged path is a chain of memcpys), off over
+    // NCCL, whose grouped send/recv drives all peers at once and measured faster on 8 GPUs
+    const bool want_p2p = opt_.p2p_swap == 1 || (opt_.p2p_swap < 0 && std::string(comm_->kind()) == "local");
+    if (want_p2p && vecs.size() == 1 && psi_ && vecs[0] == psi_->d() && sub >= 2 && ensure_psi_peers()) {
         try {
             comm_->stream_barrier(stream_);
             for (uint32_t b = 0; b < npat; b++) {

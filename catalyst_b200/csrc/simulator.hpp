@@ -105,7 +105,7 @@ struct Options {
     int jit_dbuf = 1;         // cp.async double-buffered tiles in specialised passes
     int jit_fuse_diag = 1;    // fuse runs of diagonal ops inside a register round
     bool virtual_swap = true; // uncontrolled SWAP gates relabel wires instead of moving amplitudes
-    bool p2p_swap = true;     // global<->local qubit swap over mapped peer memory (NVLink P2P / CUDA IPC)
+    int p2p_swap = -1;        // qubit swap over mapped peer memory: 1 on, 0 off, -1 auto (on for 'local:' rank groups)
     bool batch_overlaps = true; // adjoint gradient: evaluate commuting generators' overlaps in batched read passes
     bool lazy_adjoint = true; // adjoint gradient: apply U^dagger only when the next generator does not commute with it
 };

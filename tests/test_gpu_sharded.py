@@ -267,7 +267,7 @@ def test_swap_paths_peer_memory_and_staged(gpu, oracle_mod, world, p2p):
         apply_ops(d, ops)
         return st, int(s.exchanges), int(s.p2p_exchanges), d.state()
 
-    for st, ex, p2, st2 in gpu.run_spmd(world, prog, p2p_swap=p2p, tile_bits=5, min_row_bits=2):
+    for st, ex, p2, st2 in gpu.run_spmd(world, prog, p2p_swap=int(p2p), tile_bits=5, min_row_bits=2):
         assert np.max(np.abs(st - want)) < TOL
         assert np.max(np.abs(st2 - want)) < TOL
         assert ex > 0
