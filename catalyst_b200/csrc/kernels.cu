@@ -499,7 +499,7 @@ extern "C" int b200k_probs_all(const double *psi, double *out, int n_local, void
 // plain pass).  A tile = the low C source bits plus the source bits that become the low C destination
 // bits: loads are contiguous in the source, stores contiguous in the destination, the transposition
 // happens in shared memory.
-#define PP_C 5
+#define PP_C 6
 struct PermTile {
     uint8_t nt;          // tile bits (C .. 2C)
     uint8_t n;
