@@ -605,6 +605,7 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
         uint32_t S = 0;
         deferred.clear();
         taken.clear();
+        int ctrl_votes[32] = {0};
         for (const GateOp *g : rem) {
             const uint64_t xs = g->xmask, zs = g->zsupport();
             bool fits = false;
@@ -620,12 +621,31 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
                     fits = true;
                 }
             }
-            if (fits) taken.push_back(g);
+            if (fits) {
+                taken.push_back(g);
+                if (g->kind != GateOp::PHASE && g->kind != GateOp::PARITY) { // controls of non-diagonal ops
+                    uint32_t cin;
+                    uint64_t cout_;
+                    split(g->cmask, cin, cout_);
+                    for (int b = 0; b < t; b++)
+                        if ((cin >> b) & 1u) ctrl_votes[b]++;
+                }
+            }
             else {
                 deferred.push_back(g);
                 blockedX |= xs;
                 blockedZ |= zs;
             }
+        }
+        // Free register slots go to the control bits of the round's non-diagonal ops first: a control on a
+        // register bit is a compile-time slot selection (CNOT/Toffoli become pure renames), a control on a
+        // thread bit is a run-time condition whose permutation costs ~6 register moves per amplitude.
+        while (__builtin_popcount(S) < nr) {
+            int best = -1;
+            for (int b = 0; b < t; b++)
+                if (!((S >> b) & 1u) && ctrl_votes[b] > 0 && (best < 0 || ctrl_votes[b] > ctrl_votes[best])) best = b;
+            if (best < 0) break;
+            S |= 1u << best;
         }
         for (int b = t - 1; b >= 0 && __builtin_popcount(S) < nr; b--) // pad with the highest free tile bits
             if (!(S & (1u << b))) S |= 1u << b;
@@ -698,7 +718,7 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
     // structural key
     std::string key;
     key.reserve(64 + 64 * ops.size());
-    put(key, (int)5); // generator version
+    put(key, (int)6); // generator version
     put(key, P.fuse_diag);
     put(key, P.t); put(key, P.c); put(key, P.nr); put(key, P.nl); put(key, P.dbuf); put(key, P.rank_base);
     for (int h : P.high) put(key, (uint8_t)h);
