@@ -104,6 +104,7 @@ struct Options {
     int jit_min_qubits = 22;  // smaller local states stay on the interpreter
     int jit_dbuf = 1;         // cp.async double-buffered tiles in specialised passes
     int jit_fuse_diag = 1;    // fuse runs of diagonal ops inside a register round
+    int jit_factor = 1;       // factor u00 out of uncontrolled one-qubit gates, fold the product into one op
     bool virtual_swap = true; // uncontrolled SWAP gates relabel wires instead of moving amplitudes
     int p2p_swap = -1;        // qubit swap over mapped peer memory: 1 on, 0 off, -1 auto (on for 'local:' rank groups)
     bool batch_overlaps = true; // adjoint gradient: evaluate commuting generators' overlaps in batched read passes

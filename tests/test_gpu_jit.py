@@ -129,6 +129,31 @@ def test_jit_auto_mode_switches_over(gpu, oracle_mod):
     assert seen[0] == 0 and seen[-1] > 0, seen
 
 
+@pytest.mark.parametrize("absorber", [False, True])
+@pytest.mark.parametrize("factor", [0, 1])
+def test_jit_scale_factoring(gpu, oracle_mod, factor, absorber):
+    """Uncontrolled one-qubit gates are divided by their u00 and the product of the scalars is folded
+    into one op of the pass (simulator_jit.cpp factor_scales): angles next to pi (tiny and vanishing
+    cos), Hadamard chains without and with a parity phase to absorb the product."""
+    n = 13
+    rng = np.random.default_rng(17)
+    near = [np.pi, np.pi - 1e-3, np.pi + 3e-5, -np.pi + 1e-7, 0.0, 1e-9, 2 * np.pi, 3.0]
+    ops = []
+    for layer in range(6):
+        for w in range(n):
+            th = near[(layer * n + w) % len(near)] if layer % 2 == 0 else float(rng.uniform(-3, 3))
+            ops.append((["RX", "RY", "Hadamard", "Rot"][(w + layer) % 4],
+                        [th] if (w + layer) % 4 < 2 else ([] if (w + layer) % 4 == 2 else [th, 0.3, -1.1]), [w]))
+        ops += [("CNOT", [], [w, (w + 1 + layer) % n]) for w in range(0, n, 2)]
+        if absorber:
+            ops.append(("RZ", [0.37 * (layer + 1)], [int(rng.integers(n))]))
+            ops.append(("IsingZZ", [0.11], [0, n - 1]))
+    d, err = _run(gpu, oracle_mod, n, ops, init=random_state(8, n), jit_factor=factor)
+    s = d.stats()
+    assert err < TOL
+    assert s.jit_passes == s.tile_passes > 0
+
+
 def test_jit_new_parameters_reuse_kernels(gpu, oracle_mod):
     n = 12
     rng = np.random.default_rng(5)
