@@ -191,6 +191,11 @@ Simulator::~Simulator()
     misc_.reset();
     matrix_arena_.reset();
     if (pinned_) cudaFreeHost(pinned_);
+    for (int h = 0; h < 2; h++) {
+        if (ev_packed_[h]) cudaEventDestroy((cudaEvent_t)ev_packed_[h]);
+        if (ev_moved_[h]) cudaEventDestroy((cudaEvent_t)ev_moved_[h]);
+    }
+    if (xfer_stream_) cudaStreamDestroy((cudaStream_t)xfer_stream_);
     if (ev0_) cudaEventDestroy((cudaEvent_t)ev0_);
     if (ev1_) cudaEventDestroy((cudaEvent_t)ev1_);
     if (stream_) cudaStreamDestroy((cudaStream_t)stream_);
@@ -1039,43 +1044,83 @@ void Simulator::swap_bits(const std::vector<double *> &vecs, std::vector<int> &p
         }
         return;
     }
+    // Staged path, software-pipelined over two halves of the staging buffer: the transfers run on their own
+    // stream, so that packing chunk k+1 and unpacking chunk k-1 (HBM passes on the compute stream) overlap
+    // the NVLink transfer of chunk k.  Order on the compute stream: pack 0, pack 1, unpack 0, pack 2,
+    // unpack 1, ...; a half is packed again only after the unpack that emptied it, and a transfer starts
+    // only after its pack (events), so no buffer is written while it is still being read.
     const uint64_t stage_amps = ((uint64_t)opt_.stage_mib << 20) / sizeof(cplx);
-    uint64_t chunk = stage_amps / (2ull * (npat - 1));
+    uint64_t chunk = stage_amps / (4ull * (npat - 1));
     if (chunk > sub) chunk = sub;
     B200_FAIL_IF(chunk == 0, "stage_mib too small for the qubit swap");
-    ensure_buffer(stage_, 2ull * (npat - 1) * chunk * sizeof(cplx));
+    ensure_buffer(stage_, 4ull * (npat - 1) * chunk * sizeof(cplx));
     cplx *stage = static_cast<cplx *>(stage_->p());
-    for (double *vec : vecs) {
-        for (uint64_t j0 = 0; j0 < sub; j0 += chunk) {
-            const uint64_t cnt = std::min(chunk, sub - j0);
-            std::vector<Xfer> sends, recvs;
-            uint32_t slot = 0;
-            for (uint32_t b = 0; b < npat; b++) {
-                if (b == mine) continue;
-                cplx *sbuf = stage + (uint64_t)(2 * slot) * chunk, *rbuf = stage + (uint64_t)(2 * slot + 1) * chunk;
-                CUDA_CHECK(b200k_pack_bits(reinterpret_cast<double *>(sbuf), vec, lpos, m, b, j0, cnt, stream_));
-                note_launch();
-                sends.push_back({peer_of(b), sbuf, cnt * sizeof(cplx)});
-                recvs.push_back({peer_of(b), rbuf, cnt * sizeof(cplx)});
-                slot++;
-            }
-            try {
-                comm_->exchange(sends, recvs, stream_);
-            }
-            catch (const std::exception &e) {
-                B200_FAIL(std::string("qubit swap failed: ") + e.what());
-            }
-            slot = 0;
-            for (uint32_t b = 0; b < npat; b++) {
-                if (b == mine) continue;
-                const cplx *rbuf = stage + (uint64_t)(2 * slot + 1) * chunk;
-                CUDA_CHECK(b200k_unpack_bits(vec, reinterpret_cast<const double *>(rbuf), lpos, m, b, j0, cnt, stream_));
-                note_launch();
-                slot++;
-            }
-            stats_.exchange_bytes += (double)(npat - 1) * (double)cnt * sizeof(cplx);
+    if (!xfer_stream_) {
+        cudaStream_t xs;
+        CUDA_CHECK(cudaStreamCreateWithFlags(&xs, cudaStreamNonBlocking));
+        xfer_stream_ = xs;
+        for (int h = 0; h < 2; h++) {
+            cudaEvent_t e0, e1;
+            CUDA_CHECK(cudaEventCreateWithFlags(&e0, cudaEventDisableTiming));
+            CUDA_CHECK(cudaEventCreateWithFlags(&e1, cudaEventDisableTiming));
+            ev_packed_[h] = e0;
+            ev_moved_[h] = e1;
         }
     }
+    cudaStream_t cs = (cudaStream_t)stream_, xs = (cudaStream_t)xfer_stream_;
+    const uint64_t half_amps = 2ull * (npat - 1) * chunk;
+    struct Job {
+        double *vec;
+        uint64_t j0, cnt;
+    };
+    std::vector<Job> jobs;
+    for (double *vec : vecs)
+        for (uint64_t j0 = 0; j0 < sub; j0 += chunk) jobs.push_back({vec, j0, std::min(chunk, sub - j0)});
+    auto pack_and_send = [&](size_t k) {
+        const Job &J = jobs[k];
+        const int h = (int)(k & 1);
+        cplx *hb = stage + (uint64_t)h * half_amps;
+        std::vector<Xfer> sends, recvs;
+        uint32_t slot = 0;
+        for (uint32_t b = 0; b < npat; b++) {
+            if (b == mine) continue;
+            cplx *sbuf = hb + (uint64_t)(2 * slot) * chunk, *rbuf = hb + (uint64_t)(2 * slot + 1) * chunk;
+            CUDA_CHECK(b200k_pack_bits(reinterpret_cast<double *>(sbuf), J.vec, lpos, m, b, J.j0, J.cnt, stream_));
+            note_launch();
+            sends.push_back({peer_of(b), sbuf, J.cnt * sizeof(cplx)});
+            recvs.push_back({peer_of(b), rbuf, J.cnt * sizeof(cplx)});
+            slot++;
+        }
+        CUDA_CHECK(cudaEventRecord((cudaEvent_t)ev_packed_[h], cs));
+        CUDA_CHECK(cudaStreamWaitEvent(xs, (cudaEvent_t)ev_packed_[h], 0));
+        try {
+            comm_->exchange(sends, recvs, xfer_stream_);
+        }
+        catch (const std::exception &e) {
+            B200_FAIL(std::string("qubit swap failed: ") + e.what());
+        }
+        CUDA_CHECK(cudaEventRecord((cudaEvent_t)ev_moved_[h], xs));
+        stats_.exchange_bytes += (double)(npat - 1) * (double)J.cnt * sizeof(cplx);
+    };
+    auto unpack = [&](size_t k) {
+        const Job &J = jobs[k];
+        const int h = (int)(k & 1);
+        const cplx *hb = stage + (uint64_t)h * half_amps;
+        CUDA_CHECK(cudaStreamWaitEvent(cs, (cudaEvent_t)ev_moved_[h], 0));
+        uint32_t slot = 0;
+        for (uint32_t b = 0; b < npat; b++) {
+            if (b == mine) continue;
+            const cplx *rbuf = hb + (uint64_t)(2 * slot + 1) * chunk;
+            CUDA_CHECK(b200k_unpack_bits(J.vec, reinterpret_cast<const double *>(rbuf), lpos, m, b, J.j0, J.cnt, stream_));
+            note_launch();
+            slot++;
+        }
+    };
+    for (size_t k = 0; k < jobs.size(); k++) {
+        pack_and_send(k);
+        if (k >= 1) unpack(k - 1);
+    }
+    unpack(jobs.size() - 1);
     stats_.exchanges++;
     // layout: the logical qubits at the exchanged positions trade places
     for (int i = 0; i < m; i++) {

@@ -93,7 +93,7 @@ struct Options {
     // equal `rank`; `comm` = "local:<group>" (threads of one process) or "nccl:<hex unique id>"
     int world = 1, rank = 0;
     std::string comm;
-    int64_t stage_mib = 1024; // staging memory of the global<->local qubit swap
+    int64_t stage_mib = 4096; // staging memory of the global<->local qubit swap (two pipelined halves)
     int kernel_gen = 3;       // tile kernel generation (2 = k_tile2, 3 = k_tile3)
     // run-time specialised tile passes (jit.hpp): 0 = off, 1 = auto (a pass structure seen
     // `jit_threshold` times is compiled in the background, the interpreter runs it until the
@@ -259,6 +259,8 @@ class Simulator {
     std::vector<int> pos_;   // layout of psi_: logical bit -> physical position
     std::unique_ptr<Comm> comm_;
     std::unique_ptr<DeviceBuffer> stage_, tmp_probs_;
+    void *xfer_stream_ = nullptr;                          // transfers of the staged qubit swap
+    void *ev_packed_[2] = {nullptr, nullptr}, *ev_moved_[2] = {nullptr, nullptr};
     int cuda_device_ = 0;
     void *stream_ = nullptr;
     std::unique_ptr<DeviceBuffer> psi_, tmp_, acc_, scratch_, results_, probs_buf_, misc_;
