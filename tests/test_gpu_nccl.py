@@ -22,12 +22,13 @@ def _ngpus():
         return 0
 
 
-def _worker(rank, world, uid, n, ops, obs_list, q):
+def _worker(rank, world, uid, n, ops, obs_list, q, kwargs=None):
     try:
         root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
         sys.path[:0] = [root, os.path.join(root, "tests")]
         from catalyst_b200 import capi
-        d = capi.B200Device(world_size=world, rank=rank, comm="nccl:" + uid, device=rank, seed=37)
+        d = capi.B200Device(world_size=world, rank=rank, comm="nccl:" + uid, device=rank, seed=37,
+                            **(kwargs or {}))
         d.allocate_qubits(n)
         apply_ops(d, ops)
         e = [d.expval(build_obs(d, ob)) for ob in obs_list]
@@ -41,12 +42,15 @@ def _worker(rank, world, uid, n, ops, obs_list, q):
         q.put((rank, None, None, None, None, None, 0, repr(ex)))
 
 
-@pytest.mark.parametrize("world", [2, 4, 8])
-def test_nccl_ranks_match_oracle(oracle_mod, world):
+@pytest.mark.parametrize("world,n,kwargs", [(2, 14, None), (4, 14, None), (8, 14, None),
+                                            # 1 MiB staging buffer at 18 qubits: every qubit swap runs as
+                                            # several pipelined chunks (pack k+1 / transfer k / unpack k-1)
+                                            (2, 18, {"stage_mib": 1, "p2p_swap": 0}),
+                                            (4, 18, {"stage_mib": 1, "p2p_swap": 0})])
+def test_nccl_ranks_match_oracle(oracle_mod, world, n, kwargs):
     if _ngpus() < world:
         pytest.skip(f"needs {world} GPUs")
     from catalyst_b200 import capi
-    n = 14
     ops = random_circuit(500 + world, n, 150)
     rng = np.random.default_rng(3)
     obs_list = [random_pauli_obs(rng, n) for _ in range(4)]
@@ -60,7 +64,7 @@ def test_nccl_ranks_match_oracle(oracle_mod, world):
     uid = capi.nccl_unique_id()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, world, uid, n, ops, obs_list, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, uid, n, ops, obs_list, q, kwargs)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q.get(timeout=300) for _ in range(world)]
