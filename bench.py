@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--qubits", type=int, default=0, help="override the register size (default: 30 at N=1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-sample-gates", type=int, default=16)
+    ap.add_argument("--cpu-sample-gates", type=int, default=32)
     ap.add_argument("--tile-bits", type=int, default=0)
     ap.add_argument("--depth", type=int, default=40, help="depth of the sharded C5 circuit (N > 1)")
     return ap.parse_args()
