@@ -21,7 +21,8 @@ OBS_IDS = {"Identity": 0, "PauliX": 1, "PauliY": 2, "PauliZ": 3, "Hadamard": 4, 
 # every symbol include/b200sv.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "b200sv_last_error", "b200sv_version", "b200sv_create", "b200sv_destroy",
-    "b200sv_allocate_qubits", "b200sv_allocate_qubit", "b200sv_release_qubits", "b200sv_num_qubits",
+    "b200sv_allocate_qubits", "b200sv_allocate_qubit", "b200sv_release_qubits", "b200sv_release_qubit",
+    "b200sv_num_qubits",
     "b200sv_set_shots", "b200sv_get_shots", "b200sv_set_prng", "b200sv_seed", "b200sv_prng_peek",
     "b200sv_named_operation", "b200sv_matrix_operation", "b200sv_set_state",
     "b200sv_set_basis_state", "b200sv_observable", "b200sv_tensor_observable",
@@ -174,6 +175,10 @@ class B200Device:
     def release_qubits(self):
         self._chk(self.L.b200sv_release_qubits(self.h))
         self.n = 0
+
+    def release_qubit(self, wire):
+        self._chk(self.L.b200sv_release_qubit(self.h, C.c_int64(wire)))
+        self.n = int(self.L.b200sv_num_qubits(self.h))
 
     def reset(self, n=None):
         n = self.n if n is None else n

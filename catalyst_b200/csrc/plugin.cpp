@@ -87,13 +87,17 @@ class B200StateVector final : public Catalyst::Runtime::QuantumDevice {
     }
     void ReleaseQubits(const std::vector<QubitIdType> &qubits) override
     {
-        // Releasing the full register returns the (pooled, reusable) object to a clean state
-        // (runtime/lib/capi/ExecutionContext.hpp:355-361).
         RT_FAIL_IF(!qubit_manager_.isValidQubitId(qubits), "Given wires do not refer to qubits");
-        RT_FAIL_IF(qubits.size() != (size_t)b200sv_num_qubits(dev_),
-                   "Releasing a subset of the register is not supported by this device");
-        B200_RT_CHECK(b200sv_release_qubits(dev_));
-        qubit_manager_.ReleaseAll();
+        if (qubits.size() == (size_t)b200sv_num_qubits(dev_)) {
+            // Releasing the full register returns the (pooled, reusable) object to a clean state
+            // (runtime/lib/capi/ExecutionContext.hpp:355-361).
+            B200_RT_CHECK(b200sv_release_qubits(dev_));
+            qubit_manager_.ReleaseAll();
+            return;
+        }
+        // a dynamically allocated sub-register (qml.allocate / deallocate): one wire at a time, each
+        // looked up again because the earlier releases moved the later device wires down
+        for (auto q : qubits) ReleaseQubit(q);
     }
     void ReleaseQubit(QubitIdType qubit) override
     {
@@ -103,7 +107,8 @@ class B200StateVector final : public Catalyst::Runtime::QuantumDevice {
             qubit_manager_.ReleaseAll();
             return;
         }
-        RT_FAIL("Releasing a single qubit of a larger register is not supported by this device");
+        B200_RT_CHECK(b200sv_release_qubit(dev_, (int64_t)qubit_manager_.getDeviceId(qubit)));
+        qubit_manager_.Release(qubit); // later device indices move down (QubitManager.hpp:124-126)
     }
     auto GetNumQubits() const -> size_t override { return (size_t)b200sv_num_qubits(dev_); }
 

@@ -266,6 +266,53 @@ void Simulator::allocate_one()
     wire_bit_.push_back(0);           // the new wire is the new least significant bit
 }
 
+// ReleaseQubit (reference: runtime/include/QuantumDevice.hpp:144; id bookkeeping of the caller:
+// runtime/lib/backend/common/QubitManager.hpp:124-126 -- the wire leaves, later device indices move down).
+// Composed from the paths the rest of the device already uses: marginal of the wire (read pass), collapse
+// onto its more probable branch with renormalisation (exact for a qubit in a basis state, which is what
+// deallocation requires; a tie keeps |0>), X if that branch was |1>, a SWAP that brings the wire's index
+// bit to the top, and the lower half of the vector is the (n-1)-qubit state.
+void Simulator::release_one(int64_t wire)
+{
+    B200_FAIL_IF(!psi_, "No qubits allocated");
+    B200_FAIL_IF(wire < 0 || wire >= n_, "Invalid wire index " + std::to_string(wire));
+    if (n_ == 1) {
+        release();
+        return;
+    }
+    B200_FAIL_IF(sharded(), "ReleaseQubit: dynamic release is not supported on a sharded register");
+    B200_FAIL_IF(recording_, "ReleaseQubit: not supported while the tape is recording");
+    double p[2];
+    probs({wire}, p, 1); // flushes the queue
+    const int keep = p[1] > 0.5 + 1e-9 ? 1 : 0;
+    CUDA_CHECK(b200k_collapse(psi_->d(), (int)nl_, rank_base_, pos_[lbit(wire)], keep, 1.0 / std::sqrt(p[keep]), stream_));
+    note_launch();
+    std::vector<GateOp> ops;
+    if (keep) canonicalize(ops, "PauliX", {}, {wire}, false, {}, {}, "");
+    const int top = (int)n_ - 1;
+    if (wire_bit_[(size_t)wire] != top) {
+        int64_t v = -1;
+        for (int64_t u = 0; u < n_; u++)
+            if (wire_bit_[(size_t)u] == top) v = u;
+        canonicalize(ops, "SWAP", {}, {wire, v}, false, {}, {}, ""); // exchanges the contents of the two bits
+        std::swap(wire_bit_[(size_t)wire], wire_bit_[(size_t)v]);    // ... and the labels
+    }
+    if (!ops.empty()) enqueue(std::move(ops));
+    flush();
+    const size_t bytes = sizeof(cplx) << (n_ - 1);
+    auto nb = std::make_unique<DeviceBuffer>(bytes);
+    CUDA_CHECK(cudaMemcpyAsync(nb->p(), psi_->p(), bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    psi_ = std::move(nb);
+    tmp_.reset();
+    acc_.reset();
+    probs_buf_.reset();
+    n_ -= 1;
+    nl_ = n_;
+    pos_.pop_back();
+    wire_bit_.erase(wire_bit_.begin() + wire); // held the top bit: the rest is a permutation of 0..n-2
+}
+
 void Simulator::release()
 {
     if (stream_) cudaStreamSynchronize((cudaStream_t)stream_);
@@ -2937,6 +2984,7 @@ void b200sv_destroy(b200sv_device *d) { delete d; }
 int b200sv_allocate_qubits(b200sv_device *d, int64_t n) { B200_TRY(d->sim->allocate(n)) }
 int b200sv_allocate_qubit(b200sv_device *d) { B200_TRY(d->sim->allocate_one()) }
 int b200sv_release_qubits(b200sv_device *d) { B200_TRY(d->sim->release()) }
+int b200sv_release_qubit(b200sv_device *d, int64_t wire) { B200_TRY(d->sim->release_one(wire)) }
 int64_t b200sv_num_qubits(b200sv_device *d) { return d->sim->num_qubits(); }
 int b200sv_set_shots(b200sv_device *d, int64_t shots) { B200_TRY(d->sim->set_shots(shots)) }
 int64_t b200sv_get_shots(b200sv_device *d) { return d->sim->shots(); }

@@ -124,6 +124,7 @@ class Simulator {
     // lifecycle
     void allocate(int64_t n);
     void allocate_one();
+    void release_one(int64_t wire);
     void release();
     int64_t num_qubits() const { return n_; }
     void set_shots(int64_t s) { opt_.shots = s; }

@@ -42,10 +42,14 @@ const char *b200sv_version(void);
 b200sv_device *b200sv_create(const char *kwargs);
 void b200sv_destroy(b200sv_device *d);
 
-/* AllocateQubits :88 / AllocateQubit :122 / ReleaseQubits :103 / GetNumQubits :110 */
+/* AllocateQubits :88 / AllocateQubit :122 / ReleaseQubits :103 / ReleaseQubit :144 / GetNumQubits :110 */
 int b200sv_allocate_qubits(b200sv_device *d, int64_t n);
 int b200sv_allocate_qubit(b200sv_device *d); /* appends one wire in |0> */
 int b200sv_release_qubits(b200sv_device *d); /* frees the state; object stays reusable */
+/* ReleaseQubit :144 -- device wire `wire` leaves the register and every later wire moves down by one
+ * (the caller's id map: runtime/lib/backend/common/QubitManager.hpp:124-126).  The qubit is expected in
+ * a basis state (deallocation contract); its more probable branch is kept and renormalised. */
+int b200sv_release_qubit(b200sv_device *d, int64_t wire);
 int64_t b200sv_num_qubits(b200sv_device *d);
 /* SetDeviceShots :164 / GetDeviceShots :171 */
 int b200sv_set_shots(b200sv_device *d, int64_t shots);

@@ -91,6 +91,16 @@ class OracleDevice:
         self.n = self.n if n is None else n
         self._chk(self.L.orc_reset(self.h, int(self.n)))
 
+    def allocate_qubit(self):
+        """AllocateQubit (QuantumDevice.hpp:122): appends one wire in |0>."""
+        self._chk(self.L.orc_allocate_qubit(self.h))
+        self.n += 1
+
+    def release_qubit(self, wire):
+        """ReleaseQubit (QuantumDevice.hpp:144): the wire leaves the register, later wires move down."""
+        self._chk(self.L.orc_release_qubit(self.h, C.c_int64(wire)))
+        self.n -= 1
+
     def seed(self, s):
         self.L.orc_seed(self.h, C.c_uint32(s))
 

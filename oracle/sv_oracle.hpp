@@ -200,6 +200,35 @@ class Oracle {
         tape.clear();
         tape_obs.clear();
     }
+    // ---- dynamic qubits (QuantumDevice.hpp:122 AllocateQubit / :144 ReleaseQubit; id bookkeeping:
+    //      runtime/lib/backend/common/QubitManager.hpp:110-126 -- a new qubit takes device index n, a release
+    //      removes the wire and every later device index moves down by one).  The arithmetic is lightning's
+    //      (out of tree, unpinned): the contract pinned here is the reference's own
+    //      frontend/test/pytest/test_dynamic_qubit_allocation.py, where every released qubit is in a basis
+    //      state and the probabilities of the remaining wires are asserted.
+    void allocate_qubit()
+    { // the new wire is the last one = the new least significant index bit, in |0>
+        CVec nv(size_t(2) << n, 0.0);
+        for (size_t i = 0; i < psi.size(); i++) nv[2 * i] = psi[i];
+        psi.swap(nv);
+        n += 1;
+    }
+    void release_qubit(size_t wire)
+    { // the wire leaves the register: its more probable branch is kept (exact for a qubit in a basis
+      // state, which is what deallocation requires; a tie keeps |0>) and renormalised
+        ORC_FAIL_IF(wire >= n, "Invalid wire");
+        ORC_FAIL_IF(recording, "ReleaseQubit while the tape is recording");
+        const auto p = probs_of({wire});
+        const uint64_t keep = p[1] > 0.5 + 1e-9 ? 1 : 0;
+        const double nrm = 1.0 / std::sqrt(p[keep]);
+        const size_t b = bit_of(wire);
+        const uint64_t lo = (uint64_t(1) << b) - 1;
+        CVec nv(psi.size() / 2);
+        for (uint64_t j = 0; j < nv.size(); j++)
+            nv[j] = psi[((j & ~lo) << 1) | (keep << b) | (j & lo)] * nrm;
+        psi.swap(nv);
+        n -= 1;
+    }
     void seed(uint32_t s)
     { // mirrors ExecutionContext(uint32_t* seed): gen = mt19937(*seed) (ExecutionContext.hpp:309-321)
         own_gen = std::mt19937(s);

@@ -76,6 +76,8 @@ void *orc_create(int n)
 }
 void orc_destroy(void *h) { delete static_cast<Oracle *>(h); }
 int orc_reset(void *h, int n) { ORC_TRY(static_cast<Oracle *>(h)->reset(size_t(n))) }
+int orc_allocate_qubit(void *h) { ORC_TRY(static_cast<Oracle *>(h)->allocate_qubit()) }
+int orc_release_qubit(void *h, int64_t wire) { ORC_TRY(static_cast<Oracle *>(h)->release_qubit(size_t(wire))) }
 int orc_num_qubits(void *h) { return int(static_cast<Oracle *>(h)->n); }
 void orc_seed(void *h, uint32_t s) { static_cast<Oracle *>(h)->seed(s); }
 void orc_unseed(void *h) { static_cast<Oracle *>(h)->unseed(); }

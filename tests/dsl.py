@@ -113,3 +113,46 @@ def random_pauli_obs(rng, n, p_identity=0.5):
     names = {"X": "PauliX", "Y": "PauliY", "Z": "PauliZ"}
     terms = [("N", names[c], int(w)) for w, c in enumerate(word) if c != "I"]
     return terms[0] if len(terms) == 1 else ("T", terms)
+
+
+# ---- dynamic qubits: the runtime's id bookkeeping over a device (QubitManager.hpp:110-126) -----------
+class DynamicRegister:
+    """Runs a program with `qml.allocate` / `deallocate` on a device object the way the runtime does:
+    qubit ids are never reused, a new qubit takes device wire n, a release removes the wire and every
+    later device wire moves down by one (reference: runtime/lib/backend/common/QubitManager.hpp:110-126;
+    callers runtime/lib/capi/RuntimeCAPI.cpp:305-372)."""
+
+    def __init__(self, dev, n_static):
+        self.dev = dev
+        self.ids = list(range(n_static))        # position in this list = device wire
+        self.next_id = n_static
+
+    def wires(self, ids):
+        return [self.ids.index(i) for i in ids]
+
+    def allocate(self, k=1):
+        out = []
+        for _ in range(k):
+            self.dev.allocate_qubit()
+            self.ids.append(self.next_id)
+            out.append(self.next_id)
+            self.next_id += 1
+        return out
+
+    def release(self, ids):
+        for i in ids:
+            self.dev.release_qubit(self.ids.index(i))
+            self.ids.remove(i)
+
+    def op(self, name, params, ids, ctrl=(), ctrl_values=(), inverse=False):
+        self.dev.named_op(name, params, self.wires(ids), inverse=inverse, ctrl_wires=self.wires(ctrl),
+                          ctrl_values=list(ctrl_values))
+
+    def measure(self, i, postselect=None, reset=False):
+        m = self.dev.measure(self.ids.index(i), postselect)
+        if reset and m:                          # catalyst.measure(reset=True): X on outcome 1
+            self.op("PauliX", [], [i])
+        return m
+
+    def probs(self, ids):
+        return self.dev.probs(self.wires(ids))

@@ -151,6 +151,31 @@ class RuntimeDevice:
     def num_qubits(self):
         return int(self.L.rt__num_qubits())
 
+    # -- dynamic qubits (RuntimeCAPI.cpp:305-372): self.q[w] stays the id of device wire w ----------
+    def allocate_qubit(self):
+        self.L.rt__qubit_allocate.restype = C.c_void_p
+        self.q.append(C.c_void_p(self.L.rt__qubit_allocate()))
+        self.n += 1
+
+    def release_qubit(self, wire):
+        self.L.rt__qubit_release(self.q[wire])
+        del self.q[wire]
+        self.n -= 1
+
+    def allocate_register(self, k):
+        """qml.allocate(k) on a live device: a second QirArray; returns (handle, device wires)."""
+        reg = C.c_void_p(self.L.rt__qubit_allocate_array(C.c_int64(k)))
+        first = len(self.q)
+        self.q += [C.c_void_p(self.L.rt__array_get_element_ptr_1d(reg, C.c_int64(i))[0]) for i in range(k)]
+        self.n += k
+        return reg, list(range(first, first + k))
+
+    def release_register(self, reg, wires):
+        self.L.rt__qubit_release_array(reg)
+        for w in sorted(wires, reverse=True):
+            del self.q[w]
+        self.n -= len(wires)
+
     # -- gates --------------------------------------------------------------------------------
     def _mods(self, inverse, ctrl_wires, ctrl_values):
         if not inverse and not len(ctrl_wires):

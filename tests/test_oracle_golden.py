@@ -77,3 +77,36 @@ def test_seeded_sample_changelog_0_9_0(oracle_mod):
     dev = oracle_mod.OracleDevice(1, seed=g["seed"])
     rows = _seeded_program(dev, g["x"], lambda d: d.sample(g["shots"])[:, 0])
     assert np.array_equal(np.array(rows, dtype=int), np.array(g["samples"]))
+
+
+@pytest.mark.parametrize("case", G.DYNAMIC_CASES, ids=[c[0] for c in G.DYNAMIC_CASES])
+def test_dynamic_qubit_constants(oracle_mod, case):
+    """qml.allocate / deallocate programs of the reference's test_dynamic_qubit_allocation.py."""
+    from dsl import DynamicRegister
+    _, _, n, prog, wires, want = case
+    o = oracle_mod.OracleDevice(n, seed=37)
+    r = DynamicRegister(o, n)
+    prog(r)
+    assert o.n == n and r.ids == list(range(n))
+    assert np.allclose(r.probs(wires), want, atol=1e-12)
+
+
+def test_dynamic_qubit_release_keeps_the_rest(oracle_mod):
+    """Releasing a qubit in a basis state leaves the state of the other wires untouched, wherever the
+    wire sits, and later wires move down (QubitManager.hpp:124-126)."""
+    from dsl import apply_ops, random_circuit
+    n = 5
+    ops = random_circuit(9, n, 40)
+    want = oracle_mod.OracleDevice(n)
+    apply_ops(want, ops)
+    for at in range(n + 1):                       # the extra wire inserted at every position
+        for bit in (0, 1):
+            o = oracle_mod.OracleDevice(n + 1)
+            if bit:
+                o.named_op("PauliX", [], [at])
+            shifted = [(op[0], op[1], [w + (w >= at) for w in op[2]]) + tuple(op[3:]) for op in ops]
+            shifted = [s if len(s) < 4 else (s[0], s[1], s[2], {**s[3], "ctrl_wires": [w + (w >= at) for w in s[3].get("ctrl_wires", ())]}) for s in shifted]
+            apply_ops(o, shifted)
+            o.release_qubit(at)
+            assert o.n == n
+            assert np.max(np.abs(o.state() - want.state())) < 1e-12
