@@ -1,8 +1,9 @@
 """ReleaseQubit / ReleaseQubits of a sub-register on a live register (QuantumDevice.hpp:103,144; SURVEY.md
 8(f) N2): the programs of the reference's frontend/test/pytest/test_dynamic_qubit_allocation.py through the
 C ABI and through the reference's runtime C API + the plugin, and parity with the oracle on random states.
-(The file sorts after the other GPU suites on purpose: it was added after the round's GPU budget was spent
-and has only been compiled, not run on a GPU yet -- DESIGN.md section 8.)"""
+(Round 1: the C-ABI tests of this file ran green on a B200 -- 31 passed; the two `test_runtime_*` cases,
+which go through librt_capi + the plugin, were added after the round's GPU budget ended and have not run
+on a GPU yet -- DESIGN.md section 8.)"""
 import numpy as np
 import pytest
 

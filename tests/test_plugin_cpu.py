@@ -44,6 +44,18 @@ def test_driver_against_reference_null_qubit(built):
         p = d.probs()
         assert p[0] == 1.0 and p.shape == (8,)
         assert d.measure(0) in (False, True)
+        # dynamic qubits through __catalyst__rt__qubit_allocate / qubit_release and a second QirArray
+        # (RuntimeCAPI.cpp:305-372): the calls tests/test_gpu_zz_dynamic_release.py makes on our plugin
+        d.allocate_qubit()
+        assert d.num_qubits() == 4 and len(d.q) == 4
+        d.named_op("CNOT", [], [3, 0])
+        d.release_qubit(3)
+        assert d.num_qubits() == 3 and len(d.q) == 3
+        reg, w = d.allocate_register(2)
+        assert w == [3, 4] and d.num_qubits() == 5
+        d.named_op("CNOT", [], [w[1], 0])
+        d.release_register(reg, w)
+        assert d.num_qubits() == 3 and len(d.q) == 3
     finally:
         d.close()
 
