@@ -128,3 +128,11 @@ def test_runtime_sub_register(rt):
     dev.release_register(reg, w)
     assert dev.num_qubits() == 1
     assert np.allclose(dev.probs([0]), [0, 1], atol=TOL)
+
+
+# ---- mid-circuit measurement identities of the reference (test_mid_circuit_measurement.py:88-193) ------
+@pytest.mark.parametrize("seed", [None, 37, 1234])
+@pytest.mark.parametrize("case", G.MCM_CASES, ids=[c[0] for c in G.MCM_CASES])
+def test_mcm_identities(gpu, case, seed):
+    _, _, n, prog = case
+    assert prog(gpu.B200Device(n, seed=seed))

@@ -110,3 +110,10 @@ def test_dynamic_qubit_release_keeps_the_rest(oracle_mod):
             o.release_qubit(at)
             assert o.n == n
             assert np.max(np.abs(o.state() - want.state())) < 1e-12
+
+
+@pytest.mark.parametrize("seed", [None, 37, 1234])
+@pytest.mark.parametrize("case", G.MCM_CASES, ids=[c[0] for c in G.MCM_CASES])
+def test_mcm_identities(oracle_mod, case, seed):
+    _, _, n, prog = case
+    assert prog(oracle_mod.OracleDevice(n, seed=seed))
