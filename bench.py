@@ -138,7 +138,8 @@ def run_reference(args, rank, world):
     if cpu_n != n:  # the host cannot hold 2^34 amplitudes: same gate list restricted to cpu_n wires
         from catalyst_b200 import workloads
         ops = workloads.c5_random_depth(cpu_n, depth=args.depth)
-    sample = stride_sample(ops, args.cpu_sample_gates)
+    # per step: at most 16 gates (7 s at 30 qubits on 16 threads), so that any --steps K ends in minutes
+    sample = stride_sample(ops, min(16, args.cpu_sample_gates))
     cores = om.num_threads()
     o = om.OracleDevice(cpu_n)
     for _ in range(args.warmup):
