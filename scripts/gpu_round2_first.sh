@@ -13,3 +13,19 @@ python bench.py > gpurun_out/r2_bench.json 2> gpurun_out/r2_bench.err; echo "ben
 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/r2_reference_arm.json 2>> gpurun_out/r2_bench.err; echo "ref rc=$?"
 timeout 300 python scripts/jit30.py 30 4:11:1:3 3:11:1:3 4:11:0:3 3:11:0:3 3:10:1:3 > gpurun_out/r2_jit30_sweep.log 2>&1; echo "sweep rc=$?"
 grep "rep 3" gpurun_out/r2_jit30_sweep.log
+# adjoint gradient on registers smaller than the GPU suite covers (n = 1..3): closed form -cos(theta)
+python - <<'PY' > gpurun_out/r2_small_gradient.log 2>&1
+import sys, numpy as np
+sys.path[:0] = [".", "tests"]
+from catalyst_b200 import capi
+for n in (1, 2, 3):
+    for th in (1.0, 2.0):
+        try:
+            d = capi.B200Device(n)
+            d.start_tape(); d.named_op("RX", [th], [0]); d.expval(d.obs_named("PauliY", 0)); d.stop_tape()
+            g = d.gradient()
+            print(n, th, g, "ok" if abs(g[0, 0] + np.cos(th)) < 1e-12 else "MISMATCH")
+        except Exception as e:
+            print(n, th, "ERROR", e)
+PY
+cat gpurun_out/r2_small_gradient.log

@@ -136,3 +136,16 @@ def test_runtime_sub_register(rt):
 def test_mcm_identities(gpu, case, seed):
     _, _, n, prog = case
     assert prog(gpu.B200Device(n, seed=seed))
+
+
+# ---- adjoint gradients with a closed form (test_gradient.py:609-680) -------------------------------------
+@pytest.mark.parametrize("case", G.GRADIENT_CASES, ids=[c[0] for c in G.GRADIENT_CASES])
+def test_adjoint_gradient_closed_form(gpu, case):
+    from dsl import build_obs
+    _, _, n, ops, obs, want = case
+    d = gpu.B200Device(max(n, 4))       # the same one-wire program on the smallest register size the GPU
+    d.start_tape()                      # gradient tests cover (scripts/gpu_round2_first.sh probes n = 1..3)
+    apply_ops(d, ops)
+    d.expval(build_obs(d, obs))
+    d.stop_tape()
+    assert np.allclose(d.gradient(), [want], rtol=0, atol=1e-12)

@@ -117,3 +117,14 @@ def test_dynamic_qubit_release_keeps_the_rest(oracle_mod):
 def test_mcm_identities(oracle_mod, case, seed):
     _, _, n, prog = case
     assert prog(oracle_mod.OracleDevice(n, seed=seed))
+
+
+@pytest.mark.parametrize("case", G.GRADIENT_CASES, ids=[c[0] for c in G.GRADIENT_CASES])
+def test_adjoint_gradient_closed_form(oracle_mod, case):
+    _, _, n, ops, obs, want = case
+    o = oracle_mod.OracleDevice(n)
+    o.start_tape()
+    apply_ops(o, ops)
+    o.expval(build_obs(o, obs))
+    o.stop_tape()
+    assert np.allclose(o.gradient(), [want], rtol=0, atol=1e-12)
