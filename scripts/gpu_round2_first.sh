@@ -1,7 +1,7 @@
 #!/bin/bash
 # First GPU call of round 2 (about 6 GPU-minutes on one B200):
 #  1. the full GPU suite, which includes the two plugin-path tests of dynamic qubit release that were
-#     written after round 1's GPU budget ended (tests/test_gpu_zz_dynamic_release.py::test_runtime_*);
+#     written after round 1's GPU budget ended (tests/test_gpu_zz_reference_programs.py::test_runtime_*);
 #  2. bench, both arms;
 #  3. the register-blocking sweep on today's heavier passes (rows down to 2^3 amplitudes): 8 against 16
 #     amplitudes per thread, with and without the double-buffered tile prefetch -- round 1's ncu capture

@@ -1,9 +1,15 @@
-"""ReleaseQubit / ReleaseQubits of a sub-register on a live register (QuantumDevice.hpp:103,144; SURVEY.md
-8(f) N2): the programs of the reference's frontend/test/pytest/test_dynamic_qubit_allocation.py through the
-C ABI and through the reference's runtime C API + the plugin, and parity with the oracle on random states.
-(Round 1: the C-ABI tests of this file ran green on a B200 -- 31 passed; the two `test_runtime_*` cases,
-which go through librt_capi + the plugin, were added after the round's GPU budget ended and have not run
-on a GPU yet -- DESIGN.md section 8.)"""
+"""Programs transcribed from the reference's own tests, run on the device:
+
+* ReleaseQubit / ReleaseQubits of a sub-register on a live register (QuantumDevice.hpp:103,144): the programs
+  of frontend/test/pytest/test_dynamic_qubit_allocation.py through the C ABI and through the reference's
+  runtime C API + the plugin, and parity with the oracle on random states;
+* the mid-circuit measurement identities of test_mid_circuit_measurement.py:88-193;
+* adjoint gradients with a closed form (test_gradient.py:609-680).
+
+Round 1: the C-ABI release tests of this file ran green on a B200 (31 passed); the two `test_runtime_*`
+cases (librt_capi + plugin), the measurement identities and the gradient cases were added after the round's
+GPU budget ended and have not run on a GPU yet -- DESIGN.md section 8.  The file sorts after the other GPU
+suites so that a surprise here cannot hide them under `pytest -x`."""
 import numpy as np
 import pytest
 

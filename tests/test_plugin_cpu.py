@@ -45,7 +45,7 @@ def test_driver_against_reference_null_qubit(built):
         assert p[0] == 1.0 and p.shape == (8,)
         assert d.measure(0) in (False, True)
         # dynamic qubits through __catalyst__rt__qubit_allocate / qubit_release and a second QirArray
-        # (RuntimeCAPI.cpp:305-372): the calls tests/test_gpu_zz_dynamic_release.py makes on our plugin
+        # (RuntimeCAPI.cpp:305-372): the calls tests/test_gpu_zz_reference_programs.py makes on our plugin
         d.allocate_qubit()
         assert d.num_qubits() == 4 and len(d.q) == 4
         d.named_op("CNOT", [], [3, 0])
