@@ -12,6 +12,7 @@
 //   k_probs_* ............. Probs :462, PartialProbs :472, first half of Measure :234
 //   k_collapse ............ second half of Measure :234
 //   k_sampler_* ........... Sample :384 / Counts :433 (alias sampler of SURVEY.md Appendix A.4)
+#include <atomic>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string.h>
@@ -227,16 +228,16 @@ extern "C" int b200k_tile_program(double *psi, int n_local, const B200kTileProgr
         return (int)cudaErrorInvalidValue;
     // function attributes are per device: one bit per CUDA ordinal (ranks of one process may sit on
     // different GPUs)
-    static unsigned long long attr_mask = 0;
+    static std::atomic<unsigned long long> attr_mask{0}; // threads of one process may launch concurrently
     int cur_dev = 0;
     cudaGetDevice(&cur_dev);
-    const bool attr_set = (attr_mask >> (cur_dev & 63)) & 1ull;
+    const bool attr_set = (attr_mask.load(std::memory_order_acquire) >> (cur_dev & 63)) & 1ull;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(k_tile_program,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)(sizeof(cplx) << B200K_MAX_TILE_BITS));
         if (e != cudaSuccess) return (int)e;
-        attr_mask |= 1ull << (cur_dev & 63);
+        attr_mask.fetch_or(1ull << (cur_dev & 63), std::memory_order_release);
     }
     const uint64_t ntiles = 1ull << (n_local - prog->t);
     if (ntiles > 0x7fffffffull) return (int)cudaErrorInvalidValue;
@@ -1215,13 +1216,13 @@ extern "C" int b200k_bilinear_batch(const double *phi, const double *lam, int n_
     if (ngen < 1 || ngen > B200K_BATCH_GENS || hdr->t > 11 || hdr->t > n_local || hdr->c + hdr->nhigh != hdr->t ||
         hdr->ntiles != (1ull << (n_local - hdr->t)))
         return (int)cudaErrorInvalidValue;
-    static unsigned long long attr_mask = 0;
+    static std::atomic<unsigned long long> attr_mask{0}; // threads of one process may launch concurrently
     int cur_dev = 0;
     cudaGetDevice(&cur_dev);
-    if (!((attr_mask >> (cur_dev & 63)) & 1ull)) {
+    if (!((attr_mask.load(std::memory_order_acquire) >> (cur_dev & 63)) & 1ull)) {
         cudaError_t e = cudaFuncSetAttribute(k_bilinear_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 16 * 2048);
         if (e != cudaSuccess) return (int)e;
-        attr_mask |= 1ull << (cur_dev & 63);
+        attr_mask.fetch_or(1ull << (cur_dev & 63), std::memory_order_release);
     }
     BatchParams P;
     memset(&P, 0, sizeof(P));

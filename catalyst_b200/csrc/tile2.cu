@@ -10,6 +10,7 @@
 //   * XOR-swizzled shared memory: conflict-free for any choice of the three register bits;
 //   * persistent CTAs (grid = SMs x resident CTAs) striding over the tiles;
 //   * 2x2 matrices tagged real / swap so that CNOT, X, H, RY cost no or half the FP64 work.
+#include <atomic>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -222,10 +223,10 @@ static int launch2(double *psi, const B200k2Header *hdr, const B200k2Round *roun
     static int sm_count = 0;
     // function attributes are per device: one bit per CUDA ordinal (ranks of one process may sit on
     // different GPUs)
-    static unsigned long long attr_mask = 0;
+    static std::atomic<unsigned long long> attr_mask{0}; // threads of one process may launch concurrently
     int cur_dev = 0;
     cudaGetDevice(&cur_dev);
-    const bool attr_set = (attr_mask >> (cur_dev & 63)) & 1ull;
+    const bool attr_set = (attr_mask.load(std::memory_order_acquire) >> (cur_dev & 63)) & 1ull;
     auto kern = k_tile2<NOPS, NROUNDS>;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -239,7 +240,7 @@ static int launch2(double *psi, const B200k2Header *hdr, const B200k2Round *roun
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, TT, sizeof(cplx) << t);
             grid_per_sm[t] = nb > 0 ? nb : 1;
         }
-        attr_mask |= 1ull << (cur_dev & 63);
+        attr_mask.fetch_or(1ull << (cur_dev & 63), std::memory_order_release);
     }
     Prog2<NOPS, NROUNDS> P;
     P.h = *hdr;

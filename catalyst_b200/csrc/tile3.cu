@@ -14,6 +14,7 @@
 //    body cost ~45 instructions per op -> one dense dispatch code per op (jump table); 30 % of the
 //    stall samples sat on the tile's global loads -> the next tile is prefetched with cp.async into
 //    a second shared-memory buffer while the current one is processed.
+#include <atomic>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -342,10 +343,10 @@ static int launch3(double *psi, const B200k2Header *hdr, const B200k3Round *roun
     static int sm_count = 0;
     // function attributes are per device: one bit per CUDA ordinal (ranks of one process may sit on
     // different GPUs)
-    static unsigned long long attr_mask = 0;
+    static std::atomic<unsigned long long> attr_mask{0}; // threads of one process may launch concurrently
     int cur_dev = 0;
     cudaGetDevice(&cur_dev);
-    const bool attr_set = (attr_mask >> (cur_dev & 63)) & 1ull;
+    const bool attr_set = (attr_mask.load(std::memory_order_acquire) >> (cur_dev & 63)) & 1ull;
     auto kern = k_tile3<NOPS, NROUNDS>;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -360,7 +361,7 @@ static int launch3(double *psi, const B200k2Header *hdr, const B200k3Round *roun
                 cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, TT, (size_t)(d + 1) * (sizeof(cplx) << t));
                 grid_per_sm[d][t] = nb;
             }
-        attr_mask |= 1ull << (cur_dev & 63);
+        attr_mask.fetch_or(1ull << (cur_dev & 63), std::memory_order_release);
     }
     Prog3<NOPS, NROUNDS> P;
     P.h = *hdr;
