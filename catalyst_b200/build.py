@@ -1,6 +1,6 @@
 """In-tree build of the device libraries (nvcc cross-compiles sm_100a without a GPU).
 
-  libb200sv.so ........ kernels.cu + tile2.cu + shard.cu + simulator.cpp + comm.cpp: CUDA kernels, host
+  libb200sv.so ........ kernels.cu + tile3.cu + shard.cu + simulator.cpp + comm.cpp: CUDA kernels, host
                         layer, rank-to-rank plumbing (NCCL via dlopen), C ABI (include/b200sv.h)
   librtd_b200sv.so .... plugin.cpp: QuantumDevice vtable adapter for Catalyst's runtime.  Needs the
                         reference's interface headers (runtime/include, runtime/lib/backend/common),
@@ -41,8 +41,7 @@ def reference_runtime_dir() -> str | None:
 
 
 def build_sv(force: bool = False, verbose: bool = False) -> str:
-    srcs = [os.path.join(CSRC, "kernels.cu"), os.path.join(CSRC, "tile2.cu"),
-            os.path.join(CSRC, "tile3.cu"), os.path.join(CSRC, "shard.cu"), os.path.join(CSRC, "simulator.cpp"),
+    srcs = [os.path.join(CSRC, "kernels.cu"), os.path.join(CSRC, "tile3.cu"), os.path.join(CSRC, "shard.cu"), os.path.join(CSRC, "simulator.cpp"),
             os.path.join(CSRC, "simulator_jit.cpp"), os.path.join(CSRC, "jit.cpp"), os.path.join(CSRC, "comm.cpp")]
     deps = srcs + [os.path.join(CSRC, "simulator.hpp"), os.path.join(CSRC, "comm.hpp"), os.path.join(CSRC, "jit.hpp"),
                    os.path.join(INCLUDE, "b200sv.h"),

@@ -30,7 +30,7 @@ SYMBOLS = [
     "b200sv_sample", "b200sv_counts", "b200sv_measure", "b200sv_pauli_measure", "b200sv_start_tape_recording",
     "b200sv_stop_tape_recording", "b200sv_tape_num_params", "b200sv_tape_num_observables",
     "b200sv_gradient", "b200sv_get_stats", "b200sv_reset_stats", "b200sv_set_timing",
-    "b200sv_flush", "b200sv_synchronize", "b200sv_jit_wait", "b200sv_device_pointer",
+    "b200sv_flush", "b200sv_fp64_peak", "b200sv_stats_json", "b200sv_synchronize", "b200sv_jit_wait", "b200sv_device_pointer",
     "b200sv_nccl_unique_id", "b200sv_world_size", "b200sv_rank", "b200sv_layout",
 ]
 
@@ -42,7 +42,9 @@ class Stats(C.Structure):
                 ("rounds", C.c_int64), ("exchanges", C.c_int64), ("exchange_bytes", C.c_double),
                 ("jit_passes", C.c_int64), ("jit_compiled", C.c_int64), ("jit_pending", C.c_int64),
                 ("jit_compile_ms", C.c_double), ("p2p_exchanges", C.c_int64),
-                ("relabelled_swaps", C.c_int64)]
+                ("relabelled_swaps", C.c_int64), ("swap_device_ms", C.c_double), ("fp64_ops", C.c_double),
+                ("jit_disk_hits", C.c_int64), ("swap_push_exchanges", C.c_int64), ("d2h_bytes", C.c_double),
+                ("h2d_bytes", C.c_double)]
 
 
 _lib = None
@@ -364,6 +366,20 @@ class B200Device:
 
     def flush(self):
         self._chk(self.L.b200sv_flush(self.h))
+
+    def fp64_peak(self) -> float:
+        """Measured thread-level FP64 FMA instructions per second of this GPU (microbenchmark)."""
+        out = C.c_double()
+        self._chk(self.L.b200sv_fp64_peak(self.h, C.byref(out)))
+        return out.value
+
+    def stats_json(self) -> dict:
+        import json
+        buf = C.create_string_buffer(4096)
+        self.L.b200sv_stats_json.restype = C.c_int64
+        if self.L.b200sv_stats_json(self.h, buf, C.c_int64(4096)) < 0:
+            raise B200Error(self.L.b200sv_last_error().decode())
+        return json.loads(buf.value.decode())
 
     def synchronize(self):
         self._chk(self.L.b200sv_synchronize(self.h))

@@ -15,6 +15,11 @@
 #include <sstream>
 #include <thread>
 
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <sys/types.h>
+#include <unistd.h>
+
 namespace b200 {
 namespace jit {
 
@@ -46,8 +51,11 @@ struct Api {
     int (*nvrtcGetProgramLogSize)(nvrtcProgram_t, size_t *) = nullptr;
     int (*nvrtcGetProgramLog)(nvrtcProgram_t, char *) = nullptr;
     int (*nvrtcDestroyProgram)(nvrtcProgram_t *) = nullptr;
+    int (*nvrtcVersion)(int *, int *) = nullptr;
     std::string why;
-    bool ok = false;
+    bool ok = false;       // NVRTC + driver API: kernels can be compiled, loaded and launched
+    bool nvrtc_ok = false; // NVRTC alone: sources can be compiled to cubins (no driver needed)
+    int nvrtc_major = 0, nvrtc_minor = 0;
 };
 
 template <typename F> bool sym(void *h, const char *name, F &out, std::string &why)
@@ -59,13 +67,6 @@ template <typename F> bool sym(void *h, const char *name, F &out, std::string &w
 
 void load_api(Api &a)
 {
-    const char *cuda_names[] = {"libcuda.so.1", "libcuda.so"};
-    for (const char *n : cuda_names)
-        if ((a.h_cuda = dlopen(n, RTLD_NOW | RTLD_GLOBAL))) break;
-    if (!a.h_cuda) {
-        a.why = "libcuda.so.1 (driver API) not loadable";
-        return;
-    }
     const char *env = std::getenv("B200SV_NVRTC");
     const char *nvrtc_names[] = {env ? env : "libnvrtc.so.12", "libnvrtc.so.12", "/usr/local/cuda/lib64/libnvrtc.so.12",
                                  "/usr/local/cuda/lib64/libnvrtc.so", "libnvrtc.so"};
@@ -76,6 +77,24 @@ void load_api(Api &a)
         return;
     }
     bool ok = true;
+    ok &= sym(a.h_nvrtc, "nvrtcCreateProgram", a.nvrtcCreateProgram, a.why);
+    ok &= sym(a.h_nvrtc, "nvrtcCompileProgram", a.nvrtcCompileProgram, a.why);
+    ok &= sym(a.h_nvrtc, "nvrtcGetCUBINSize", a.nvrtcGetCUBINSize, a.why);
+    ok &= sym(a.h_nvrtc, "nvrtcGetCUBIN", a.nvrtcGetCUBIN, a.why);
+    ok &= sym(a.h_nvrtc, "nvrtcGetProgramLogSize", a.nvrtcGetProgramLogSize, a.why);
+    ok &= sym(a.h_nvrtc, "nvrtcGetProgramLog", a.nvrtcGetProgramLog, a.why);
+    ok &= sym(a.h_nvrtc, "nvrtcDestroyProgram", a.nvrtcDestroyProgram, a.why);
+    ok &= sym(a.h_nvrtc, "nvrtcVersion", a.nvrtcVersion, a.why);
+    if (!ok) return;
+    a.nvrtcVersion(&a.nvrtc_major, &a.nvrtc_minor);
+    a.nvrtc_ok = true;
+    const char *cuda_names[] = {"libcuda.so.1", "libcuda.so"};
+    for (const char *n : cuda_names)
+        if ((a.h_cuda = dlopen(n, RTLD_NOW | RTLD_GLOBAL))) break;
+    if (!a.h_cuda) {
+        a.why = "libcuda.so.1 (driver API) not loadable";
+        return;
+    }
     ok &= sym(a.h_cuda, "cuInit", a.cuInit, a.why);
     ok &= sym(a.h_cuda, "cuModuleLoadData", a.cuModuleLoadData, a.why);
     ok &= sym(a.h_cuda, "cuModuleGetFunction", a.cuModuleGetFunction, a.why);
@@ -84,13 +103,6 @@ void load_api(Api &a)
     ok &= sym(a.h_cuda, "cuOccupancyMaxActiveBlocksPerMultiprocessor", a.cuOccupancyMaxActiveBlocksPerMultiprocessor, a.why);
     ok &= sym(a.h_cuda, "cuLaunchKernel", a.cuLaunchKernel, a.why);
     ok &= sym(a.h_cuda, "cuGetErrorString", a.cuGetErrorString, a.why);
-    ok &= sym(a.h_nvrtc, "nvrtcCreateProgram", a.nvrtcCreateProgram, a.why);
-    ok &= sym(a.h_nvrtc, "nvrtcCompileProgram", a.nvrtcCompileProgram, a.why);
-    ok &= sym(a.h_nvrtc, "nvrtcGetCUBINSize", a.nvrtcGetCUBINSize, a.why);
-    ok &= sym(a.h_nvrtc, "nvrtcGetCUBIN", a.nvrtcGetCUBIN, a.why);
-    ok &= sym(a.h_nvrtc, "nvrtcGetProgramLogSize", a.nvrtcGetProgramLogSize, a.why);
-    ok &= sym(a.h_nvrtc, "nvrtcGetProgramLog", a.nvrtcGetProgramLog, a.why);
-    ok &= sym(a.h_nvrtc, "nvrtcDestroyProgram", a.nvrtcDestroyProgram, a.why);
     if (ok && a.cuInit(0) != 0) {
         a.why = "cuInit failed";
         ok = false;
@@ -98,12 +110,61 @@ void load_api(Api &a)
     a.ok = ok;
 }
 
+// ---- on-disk cubin cache ---------------------------------------------------------------------------
+uint64_t fnv1a(const std::string &s, uint64_t h)
+{
+    for (unsigned char c : s) {
+        h ^= c;
+        h *= 0x100000001b3ull;
+    }
+    return h;
+}
+
+std::string cache_dir()
+{
+    if (const char *e = std::getenv("B200SV_JIT_CACHE")) {
+        const std::string v(e);
+        return (v == "off" || v == "0" || v.empty()) ? std::string() : v;
+    }
+    if (const char *x = std::getenv("XDG_CACHE_HOME"))
+        if (*x) return std::string(x) + "/b200sv";
+    if (const char *h = std::getenv("HOME"))
+        if (*h) return std::string(h) + "/.cache/b200sv";
+    return std::string();
+}
+
+void mkdirs(const std::string &dir)
+{
+    for (size_t i = 1; i <= dir.size(); i++)
+        if (i == dir.size() || dir[i] == '/') ::mkdir(dir.substr(0, i).c_str(), 0755);
+}
+
+template <typename T> void wr(std::string &o, const T &v) { o.append(reinterpret_cast<const char *>(&v), sizeof(T)); }
+template <typename T> bool rd(const std::string &in, size_t &off, T &v)
+{
+    if (off + sizeof(T) > in.size()) return false;
+    std::memcpy(&v, in.data() + off, sizeof(T));
+    off += sizeof(T);
+    return true;
+}
+bool rd_bytes(const std::string &in, size_t &off, size_t n, std::string &out)
+{
+    if (off + n > in.size()) return false;
+    out.assign(in.data() + off, n);
+    off += n;
+    return true;
+}
+
+const uint32_t kCacheMagic = 0x42325356u; // "B2SV"
+const uint32_t kCacheVersion = 2;
 enum State { SEEN = 0, COMPILING = 1, COMPILED = 2, READY = 3, FAILED = 4 };
 
 struct Entry {
     int state = SEEN;
     int sightings = 0;
+    bool disk_checked = false;
     Kernel k;
+    std::string key; // structural key (without the device ordinal): names the cache file
     std::string source;
     std::vector<char> cubin;
 };
@@ -121,6 +182,42 @@ struct Engine::Impl {
     bool stop = false;
     Counters ctr;
     std::map<int, int> sms;
+
+    // Ranks of one job (one process per GPU) meet the same pass structures at the same moment: the first
+    // process to create <file>.lock compiles, the others wait for the cache file instead of running NVRTC
+    // on the same source (8 ranks x 69 kernels was 84 s of CPU per rank).  A stale lock only costs the wait.
+    void compile_shared(Entry &e)
+    {
+        const std::string path = cache_path(e.key);
+        if (path.empty()) return compile(e);
+        const std::string lock = path + ".lock";
+        mkdirs(cache_dir());
+        const int fd = ::open(lock.c_str(), O_CREAT | O_EXCL | O_WRONLY, 0644);
+        if (fd >= 0) {
+            ::close(fd);
+            compile(e);
+            unlink(lock.c_str());
+            return;
+        }
+        const auto t0 = std::chrono::steady_clock::now();
+        for (;;) {
+            if (disk_load(e)) {
+                e.k.error.clear();
+                e.k.compile_ms = 0.0;
+                return;
+            }
+            struct stat st;
+            const bool locked = ::stat(lock.c_str(), &st) == 0;
+            const double waited = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            if (!locked || waited > 90.0) break; // the compiling process gave up (or died): do it here
+            std::this_thread::sleep_for(std::chrono::milliseconds(25));
+        }
+        if (disk_load(e)) {
+            e.k.error.clear();
+            return;
+        }
+        compile(e);
+    }
 
     void compile(Entry &e) // runs without the lock; touches only e.source / e.cubin / e.k
     {
@@ -149,6 +246,97 @@ struct Engine::Impl {
         }
         e.k.error = err;
         e.k.compile_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        if (err.empty()) {
+            disk_store(e);
+            dump(e);
+        }
+    }
+
+    std::string cache_path(const std::string &key) const
+    {
+        const std::string dir = cache_dir();
+        if (dir.empty()) return std::string();
+        const std::string salted = "nvrtc" + std::to_string(api.nvrtc_major) + "." + std::to_string(api.nvrtc_minor) + "/sm_100a/" + key;
+        char name[64];
+        snprintf(name, sizeof name, "/%016llx%016llx.b2sv", (unsigned long long)fnv1a(salted, 0xcbf29ce484222325ull),
+                 (unsigned long long)fnv1a(salted, 0x84222325cbf29ce4ull));
+        return dir + name;
+    }
+
+    void disk_store(const Entry &e) const // no lock needed: touches only e and the file system
+    {
+        const std::string path = cache_path(e.key);
+        if (path.empty()) return;
+        mkdirs(cache_dir());
+        std::string blob;
+        wr(blob, kCacheMagic);
+        wr(blob, kCacheVersion);
+        wr(blob, (uint64_t)e.key.size());
+        blob += e.key;
+        wr(blob, (uint64_t)e.k.name.size());
+        blob += e.k.name;
+        wr(blob, (int32_t)e.k.threads);
+        wr(blob, (int32_t)e.k.smem_bytes);
+        wr(blob, (int32_t)e.k.param_doubles);
+        wr(blob, (double)e.k.fp64_per_thread);
+        wr(blob, (uint64_t)e.cubin.size());
+        blob.append(e.cubin.data(), e.cubin.size());
+        char tmp[64];
+        snprintf(tmp, sizeof tmp, ".tmp.%d.%p", (int)getpid(), (const void *)&e);
+        const std::string tpath = path + tmp;
+        FILE *f = fopen(tpath.c_str(), "wb");
+        if (!f) return;
+        const bool ok = fwrite(blob.data(), 1, blob.size(), f) == blob.size();
+        fclose(f);
+        if (!ok || rename(tpath.c_str(), path.c_str()) != 0) unlink(tpath.c_str());
+    }
+
+    bool disk_load(Entry &e) const
+    {
+        const std::string path = cache_path(e.key);
+        if (path.empty()) return false;
+        FILE *f = fopen(path.c_str(), "rb");
+        if (!f) return false;
+        std::string blob;
+        char buf[1 << 16];
+        size_t n;
+        while ((n = fread(buf, 1, sizeof buf, f)) > 0) blob.append(buf, n);
+        fclose(f);
+        size_t off = 0;
+        uint32_t magic = 0, ver = 0;
+        uint64_t klen = 0, nlen = 0, clen = 0;
+        int32_t threads = 0, smem = 0, pd = 0;
+        double fp64 = 0;
+        std::string key, name, cub;
+        if (!rd(blob, off, magic) || !rd(blob, off, ver) || magic != kCacheMagic || ver != kCacheVersion) return false;
+        if (!rd(blob, off, klen) || !rd_bytes(blob, off, (size_t)klen, key) || key != e.key) return false;
+        if (!rd(blob, off, nlen) || !rd_bytes(blob, off, (size_t)nlen, name)) return false;
+        if (!rd(blob, off, threads) || !rd(blob, off, smem) || !rd(blob, off, pd) || !rd(blob, off, fp64)) return false;
+        if (!rd(blob, off, clen) || !rd_bytes(blob, off, (size_t)clen, cub) || cub.empty()) return false;
+        e.k.name = name;
+        e.k.threads = threads;
+        e.k.smem_bytes = smem;
+        e.k.param_doubles = pd;
+        e.k.fp64_per_thread = fp64;
+        e.k.from_disk = true;
+        e.cubin.assign(cub.begin(), cub.end());
+        return true;
+    }
+
+    void dump(const Entry &e) const
+    {
+        const char *dir = std::getenv("B200SV_JIT_DUMP");
+        if (!dir || !*dir) return;
+        mkdirs(dir);
+        const std::string base = std::string(dir) + "/" + e.k.name;
+        if (FILE *f = fopen((base + ".cu").c_str(), "w")) {
+            fwrite(e.source.data(), 1, e.source.size(), f);
+            fclose(f);
+        }
+        if (FILE *f = fopen((base + ".cubin").c_str(), "wb")) {
+            fwrite(e.cubin.data(), 1, e.cubin.size(), f);
+            fclose(f);
+        }
     }
 
     void finish_compile(Entry &e) // with the lock
@@ -191,7 +379,8 @@ struct Engine::Impl {
         e.cubin.clear();
         e.cubin.shrink_to_fit();
         e.state = READY;
-        ctr.compiled++;
+        if (e.k.from_disk) ctr.disk_hits++;
+        else ctr.compiled++;
         if (std::getenv("B200SV_JIT_VERBOSE"))
             fprintf(stderr, "[b200sv jit] %s: %d regs, %d CTAs/SM x %d threads, %d B smem, %.0f ms\n",
                     e.k.name.c_str(), regs, e.k.ctas_per_sm, e.k.threads, e.k.smem_bytes, e.k.compile_ms);
@@ -206,7 +395,7 @@ struct Engine::Impl {
             std::shared_ptr<Entry> e = jobs.front();
             jobs.pop_front();
             lk.unlock();
-            compile(*e);
+            compile_shared(*e);
             lk.lock();
             finish_compile(*e);
             ctr.pending--;
@@ -272,6 +461,15 @@ const Kernel *Engine::lookup(int cuda_device, const std::string &key, int thresh
         if (e->state == COMPILED) p_->make_ready(*e, cuda_device);
         return e->state == READY ? &e->k : nullptr;
     }
+    if (!e->disk_checked) { // first sighting in this process: another process may have compiled this structure
+        e->disk_checked = true;
+        e->key = key;
+        if (p_->disk_load(*e)) {
+            e->state = COMPILED;
+            p_->make_ready(*e, cuda_device);
+            return e->state == READY ? &e->k : nullptr;
+        }
+    }
     if (++e->sightings < threshold) return nullptr;
     e->source = gen(e->k);
     e->state = COMPILING;
@@ -288,6 +486,26 @@ const Kernel *Engine::lookup(int cuda_device, const std::string &key, int thresh
     p_->jobs.push_back(e);
     p_->cv_jobs.notify_one();
     return nullptr;
+}
+
+bool Engine::nvrtc_available()
+{
+    std::call_once(p_->once, [&] { load_api(p_->api); });
+    return p_->api.nvrtc_ok;
+}
+
+// Offline path (development, no GPU needed): generate + compile + dump, never loaded or launched.
+bool Engine::compile_offline(const std::string &key, const std::function<std::string(Kernel &)> &gen, Kernel &out,
+                             std::string &source)
+{
+    if (!nvrtc_available()) return false;
+    Entry e;
+    e.key = key;
+    e.source = gen(e.k);
+    p_->compile(e);
+    out = e.k;
+    source = e.source;
+    return e.k.error.empty();
 }
 
 int Engine::launch(const Kernel &k, unsigned grid, double *psi, const double *m, void *stream)

@@ -15,6 +15,13 @@
 // library still loads on a box without a GPU driver).  Kernels are cached per process by their
 // structural key; compilation runs on a small thread pool, and until a kernel is ready the
 // interpreted k_tile3 path executes the pass (same results, lower speed).
+//
+// Compiled cubins also persist ACROSS processes: $B200SV_JIT_CACHE (default $XDG_CACHE_HOME/b200sv or
+// ~/.cache/b200sv; "off" disables) holds one file per structural key (two 64-bit FNV-1a hashes of
+// generator version + NVRTC version + key name the file; the full key is stored inside and compared),
+// written atomically (temp file + rename).  A second process that meets the same pass structure loads
+// the cubin at the FIRST sighting and never runs the interpreter or NVRTC for it.
+// $B200SV_JIT_DUMP=<dir> additionally writes every generated source (<kernel>.cu) and cubin there.
 #pragma once
 
 #include <cstdint>
@@ -32,6 +39,8 @@ struct Kernel {
     int ctas_per_sm = 0;       // resident CTAs per SM (occupancy query)
     int num_regs = 0;
     int param_doubles = 0;     // doubles in the parameter block after the state pointer
+    double fp64_per_thread = 0; // FP64 instructions one thread issues per tile (generator's count, upper bound)
+    bool from_disk = false;    // loaded from the on-disk cubin cache instead of compiled
     double compile_ms = 0.0;
     std::string name;
     std::string error;         // non-empty: compilation failed, the pass stays on the interpreter
@@ -40,7 +49,7 @@ struct Kernel {
 enum class Mode { Off = 0, Auto = 1, Sync = 2 };
 
 struct Counters {
-    int64_t compiled = 0, failed = 0, pending = 0;
+    int64_t compiled = 0, failed = 0, pending = 0, disk_hits = 0;
     double compile_ms = 0.0;
 };
 
@@ -50,6 +59,10 @@ class Engine {
     static Engine &get();
     // false + reason when NVRTC or the driver API cannot be loaded
     bool available(std::string *why = nullptr);
+    bool nvrtc_available(); // NVRTC alone (sources can be compiled to cubins without a driver)
+    // development path: generate, compile to a cubin ($B200SV_JIT_DUMP, disk cache), never load or launch
+    bool compile_offline(const std::string &key, const std::function<std::string(Kernel &)> &gen, Kernel &out,
+                         std::string &source);
     // Look the structural key up.  Returns the kernel when it is ready.  Otherwise counts the
     // sighting and, once the key has been seen `threshold` times, compiles it: synchronously when
     // `sync`, else on the pool (nullptr is returned until it is ready).  `gen` produces the CUDA

@@ -1241,3 +1241,52 @@ extern "C" int b200k_bilinear_batch(const double *phi, const double *lam, int n_
     k_bilinear_batch_final<<<ngen, 256, 0, (cudaStream_t)stream>>>(scratch, (int)grid, O);
     return (int)cudaGetLastError();
 }
+
+// =================================================================================================
+// FP64 pipe microbenchmark: the second roofline of a fused tile pass.  A pass that fuses ~50 gates issues
+// ~10^2 DFMA per amplitude, so it can be bound by the FP64 pipe rather than by HBM; bench.py reports each
+// pass time against max(HBM time, DFMA time) with this measured rate as the DFMA denominator.
+// 16 independent FMA chains per thread (latency fully hidden), 8 resident CTAs of 256 threads per SM.
+// =================================================================================================
+__global__ void __launch_bounds__(256)
+k_dfma_peak(double *__restrict__ out, int iters, double a, double b)
+{
+    double v[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) v[k] = (double)(threadIdx.x + k);
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) v[k] = fma(v[k], a, b);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < 16; k++) s += v[k];
+    if (s == 123.456) out[0] = s; // keeps the chains alive; never true for the arguments used
+}
+
+extern "C" int b200k_dfma_peak(double *scratch, double *dfma_per_second, void *stream)
+{
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaEvent_t e0, e1;
+    if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) return (int)cudaGetLastError();
+    const int iters = 1 << 14, grid = sms * 8;
+    k_dfma_peak<<<grid, 256, 0, st>>>(scratch, 256, 0.999999, 1e-9); // warm-up
+    double best = 0.0;
+    for (int rep = 0; rep < 3; rep++) {
+        cudaEventRecord(e0, st);
+        k_dfma_peak<<<grid, 256, 0, st>>>(scratch, iters, 0.999999, 1e-9);
+        cudaEventRecord(e1, st);
+        cudaEventSynchronize(e1);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double rate = (double)grid * 256.0 * 16.0 * (double)iters / (ms * 1e-3);
+        if (rate > best) best = rate;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *dfma_per_second = best;
+    return (int)cudaGetLastError();
+}

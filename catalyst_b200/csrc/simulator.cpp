@@ -14,6 +14,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <sstream>
+#include <thread>
 
 namespace b200 {
 
@@ -38,11 +39,17 @@ static const cplx I_(0.0, 1.0);
 
 class DeviceBuffer {
   public:
+    static bool dry; // B200SV_DRYRUN (development): plan + generate + compile only, no device memory
     explicit DeviceBuffer(size_t bytes) : bytes_(bytes)
     {
-        CUDA_CHECK(cudaMalloc(&p_, bytes ? bytes : 16));
+        if (dry) p_ = std::malloc(64);
+        else CUDA_CHECK(cudaMalloc(&p_, bytes ? bytes : 16));
     }
-    ~DeviceBuffer() { cudaFree(p_); }
+    ~DeviceBuffer()
+    {
+        if (dry) std::free(p_);
+        else cudaFree(p_);
+    }
     DeviceBuffer(const DeviceBuffer &) = delete;
     DeviceBuffer &operator=(const DeviceBuffer &) = delete;
     double *d() const { return static_cast<double *>(p_); }
@@ -53,6 +60,8 @@ class DeviceBuffer {
     void *p_ = nullptr;
     size_t bytes_;
 };
+
+bool DeviceBuffer::dry = false;
 
 // -------------------------------------------------------------------------------------------------
 Options parse_kwargs(const char *kwargs)
@@ -91,7 +100,6 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "rank") o.rank = (int)as_int(0);
         else if (k == "stage_mib") o.stage_mib = as_int(o.stage_mib);
         else if (k == "comm") o.comm = v;
-        else if (k == "kernel_gen") o.kernel_gen = (int)as_int(o.kernel_gen);
         else if (k == "jit") {
             if (v == "off") o.jit = 0;
             else if (v == "auto") o.jit = 1;
@@ -104,11 +112,16 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "jit_dbuf") o.jit_dbuf = (int)as_int(o.jit_dbuf);
         else if (k == "jit_fuse_diag") o.jit_fuse_diag = (int)as_int(o.jit_fuse_diag);
         else if (k == "jit_factor") o.jit_factor = (int)as_int(o.jit_factor);
+        else if (k == "jit_uniform") o.jit_uniform = (int)as_int(o.jit_uniform);
         else if (k == "lazy_adjoint") o.lazy_adjoint = as_int(1) != 0;
         else if (k == "p2p_swap") o.p2p_swap = (int)as_int(-1);
         else if (k == "adaptive_rows") o.adaptive_rows = as_int(1) != 0;
         else if (k == "virtual_swap") o.virtual_swap = as_int(1) != 0;
         else if (k == "batch_overlaps") o.batch_overlaps = as_int(1) != 0;
+        else if (k == "release_entangled") {
+            B200_FAIL_IF(v != "error" && v != "project", "release_entangled must be 'error' or 'project'");
+            o.release_project = v == "project";
+        }
     }
     B200_FAIL_IF(o.world < 1 || (o.world & (o.world - 1)) || o.world > 64, "world_size must be a power of two (<= 64)");
     B200_FAIL_IF(o.rank < 0 || o.rank >= o.world, "rank out of range");
@@ -126,6 +139,22 @@ Options parse_kwargs(const char *kwargs)
 // -------------------------------------------------------------------------------------------------
 Simulator::Simulator(const Options &opt) : opt_(opt)
 {
+    if (const char *e = std::getenv("B200SV_DRYRUN")) dry_ = std::atoi(e) != 0;
+    if (dry_) {
+        // Development mode, no GPU needed: gate calls are canonicalised, planned into passes and the
+        // specialised kernels are generated and compiled to cubins ($B200SV_JIT_DUMP), nothing is launched.
+        B200_FAIL_IF(opt_.world != 1, "B200SV_DRYRUN supports unsharded registers only");
+        DeviceBuffer::dry = true;
+        jit_mode_ = opt_.jit;
+        if (const char *e = std::getenv("B200SV_JIT")) {
+            const std::string v(e);
+            jit_mode_ = v == "off" || v == "0" ? 0 : (v == "always" || v == "2" ? 2 : 1);
+        }
+        if (const char *e = std::getenv("B200SV_JIT_UNIFORM")) opt_.jit_uniform = std::atoi(e);
+        if (const char *e = std::getenv("B200SV_JIT_REGBITS")) opt_.jit_regbits = std::max(1, std::min(5, std::atoi(e)));
+        if (const char *e = std::getenv("B200SV_MIN_ROW_BITS")) opt_.min_row_bits = std::max(0, std::min(opt_.tile_bits, std::atoi(e)));
+        return;
+    }
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
     if (e != cudaSuccess || count == 0) {
@@ -147,6 +176,7 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
     }
     if (const char *e = std::getenv("B200SV_JIT_DBUF")) opt_.jit_dbuf = std::atoi(e);
     if (const char *e = std::getenv("B200SV_JIT_FACTOR")) opt_.jit_factor = std::atoi(e);
+    if (const char *e = std::getenv("B200SV_JIT_UNIFORM")) opt_.jit_uniform = std::atoi(e);
     if (const char *e = std::getenv("B200SV_P2P_SWAP")) opt_.p2p_swap = std::atoi(e);
     if (const char *e = std::getenv("B200SV_MIN_ROW_BITS")) opt_.min_row_bits = std::max(0, std::min(opt_.tile_bits, std::atoi(e)));
     if (const char *e = std::getenv("B200SV_JIT_REGBITS")) opt_.jit_regbits = std::max(1, std::min(5, std::atoi(e)));
@@ -176,6 +206,7 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
 
 Simulator::~Simulator()
 {
+    if (dry_) return;
     cudaSetDevice(cuda_device_);
     if (stream_) cudaStreamSynchronize((cudaStream_t)stream_);
     drop_psi_peers();
@@ -192,10 +223,16 @@ Simulator::~Simulator()
     matrix_arena_.reset();
     if (pinned_) cudaFreeHost(pinned_);
     for (int h = 0; h < 2; h++) {
+        if (stage_host_[h]) cudaFreeHost(stage_host_[h]);
+        if (stage_ev_[h]) cudaEventDestroy((cudaEvent_t)stage_ev_[h]);
+    }
+    for (int h = 0; h < 2; h++) {
         if (ev_packed_[h]) cudaEventDestroy((cudaEvent_t)ev_packed_[h]);
         if (ev_moved_[h]) cudaEventDestroy((cudaEvent_t)ev_moved_[h]);
     }
     if (xfer_stream_) cudaStreamDestroy((cudaStream_t)xfer_stream_);
+    if (ev2_) cudaEventDestroy((cudaEvent_t)ev2_);
+    if (ev3_) cudaEventDestroy((cudaEvent_t)ev3_);
     if (ev0_) cudaEventDestroy((cudaEvent_t)ev0_);
     if (ev1_) cudaEventDestroy((cudaEvent_t)ev1_);
     if (stream_) cudaStreamDestroy((cudaStream_t)stream_);
@@ -211,7 +248,7 @@ void Simulator::ensure_buffer(std::unique_ptr<DeviceBuffer> &buf, size_t bytes)
 
 void Simulator::allocate(int64_t n)
 {
-    CUDA_CHECK(cudaSetDevice(cuda_device_));
+    if (!dry_) CUDA_CHECK(cudaSetDevice(cuda_device_));
     B200_FAIL_IF(n < 0 || n > 40, "Invalid number of qubits");
     if (n_ > 0 || psi_) release();
     B200_FAIL_IF(sharded() && n < 2 * g_,
@@ -240,7 +277,7 @@ void Simulator::allocate(int64_t n)
         throw Error(std::string("AllocateQubits: cannot allocate the state vector in HBM: ") +
                     e.what());
     }
-    CUDA_CHECK(b200k_set_basis(psi_->d(), (int)nl_, opt_.rank == 0 ? 0 : -1, stream_));
+    if (!dry_) CUDA_CHECK(b200k_set_basis(psi_->d(), (int)nl_, opt_.rank == 0 ? 0 : -1, stream_));
     note_launch();
 }
 
@@ -285,6 +322,13 @@ void Simulator::release_one(int64_t wire)
     double p[2];
     probs({wire}, p, 1); // flushes the queue
     const int keep = p[1] > 0.5 + 1e-9 ? 1 : 0;
+    // Deallocation presumes a qubit that is disentangled and in a basis state (what the reference's programs
+    // release: frontend/test/pytest/test_dynamic_qubit_allocation.py).  Anything else would be a silent
+    // projection of the remaining register, so it is an error unless release_entangled='project' asks for it.
+    B200_FAIL_IF(!opt_.release_project && p[keep] < 1.0 - 1e-9,
+                 "ReleaseQubit: wire " + std::to_string(wire) + " is not in a basis state (P(|" + std::to_string(keep) +
+                     ">) = " + std::to_string(p[keep]) +
+                     "); measure or reset it first, or create the device with release_entangled='project'");
     CUDA_CHECK(b200k_collapse(psi_->d(), (int)nl_, rank_base_, pos_[lbit(wire)], keep, 1.0 / std::sqrt(p[keep]), stream_));
     note_launch();
     std::vector<GateOp> ops;
@@ -315,7 +359,7 @@ void Simulator::release_one(int64_t wire)
 
 void Simulator::release()
 {
-    if (stream_) cudaStreamSynchronize((cudaStream_t)stream_);
+    if (stream_ && !dry_) cudaStreamSynchronize((cudaStream_t)stream_);
     queue_.clear();
     if (psi_peers_ok_ && psi_) psi_keep_ = std::move(psi_); // peers still map this allocation
     psi_.reset();
@@ -332,6 +376,43 @@ void Simulator::release()
 }
 
 void Simulator::reset_stats() { stats_ = b200sv_stats{}; }
+
+double Simulator::fp64_peak()
+{
+    B200_FAIL_IF(dry_, "no device in a dry run");
+    CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    double rate = 0.0;
+    CUDA_CHECK(b200k_dfma_peak(results_->d(), &rate, stream_));
+    return rate;
+}
+
+// Counters as JSON, in the spirit of the reference's ResourceTracker report
+// (runtime/lib/backend/null_qubit/NullQubit.hpp:104-112, ResourceTracker.hpp): what ran, not how fast.
+std::string Simulator::stats_json() const
+{
+    const b200sv_stats s = stats();
+    std::ostringstream o;
+    o << "{\"num_qubits\": " << n_ << ", \"local_qubits\": " << nl_ << ", \"world_size\": " << opt_.world
+      << ", \"rank\": " << opt_.rank << ", \"num_gates\": " << s.gates_enqueued << ", \"canonical_ops\": " << s.kernel_ops
+      << ", \"tile_passes\": " << s.tile_passes << ", \"specialised_passes\": " << s.jit_passes
+      << ", \"shared_memory_rounds\": " << s.rounds << ", \"relabelled_swaps\": " << s.relabelled_swaps
+      << ", \"other_launches\": " << s.other_launches << ", \"qubit_swaps\": " << s.exchanges
+      << ", \"peer_memory_swaps\": " << s.p2p_exchanges << ", \"push_swaps\": " << s.swap_push_exchanges
+      << ", \"nvlink_bytes_sent\": " << s.exchange_bytes << ", \"algorithmic_bytes\": " << s.algorithmic_bytes
+      << ", \"fp64_instructions\": " << s.fp64_ops << ", \"gate_device_ms\": " << s.gate_device_ms
+      << ", \"swap_device_ms\": " << s.swap_device_ms << ", \"kernels_compiled\": " << s.jit_compiled
+      << ", \"kernels_from_disk_cache\": " << s.jit_disk_hits << ", \"compilations_pending\": " << s.jit_pending
+      << ", \"nvrtc_cpu_ms\": " << s.jit_compile_ms << ", \"h2d_bytes\": " << s.h2d_bytes << ", \"d2h_bytes\": " << s.d2h_bytes
+      << "}";
+    return o.str();
+}
+
+void Simulator::make_current()
+{
+    if (dry_) return;
+    int cur = -1;
+    if (cudaGetDevice(&cur) != cudaSuccess || cur != cuda_device_) CUDA_CHECK(cudaSetDevice(cuda_device_));
+}
 
 void *Simulator::device_pointer() { return psi_ ? psi_->p() : nullptr; }
 
@@ -360,6 +441,26 @@ uint32_t Simulator::rng_next()
 {
     if (rng_fn_) return rng_fn_(rng_ctx_);
     return (uint32_t)own_gen_();
+}
+// One 32-bit seed for a sampling / measurement call: the next output of the runtime's generator when one is
+// set (reference stream), else entropy.  On a sharded register every rank must collapse onto the SAME
+// outcome, so without a generator rank 0's entropy is distributed to all ranks.
+uint32_t Simulator::fresh_seed()
+{
+    if (rng_fn_ || own_seeded_) return rng_next();
+    uint32_t s = (uint32_t)std::random_device{}();
+    if (sharded()) {
+        double mine = (double)s;
+        std::vector<double> all((size_t)opt_.world);
+        try {
+            comm_->allgather_host(&mine, all.data(), 1);
+        }
+        catch (const std::exception &e) {
+            B200_FAIL(std::string("distributing the measurement seed across ranks failed: ") + e.what());
+        }
+        s = (uint32_t)all[0];
+    }
+    return s;
 }
 namespace {
 struct BorrowedEngine { // same min/max as std::mt19937 => identical generate_canonical arithmetic
@@ -752,6 +853,12 @@ void Simulator::matrix_op(const CVec &matrix, const std::vector<int64_t> &wires,
 void Simulator::flush()
 {
     if (queue_.empty()) return;
+    if (dry_) {
+        std::vector<GateOp> ops;
+        ops.swap(queue_);
+        execute({psi_->d()}, pos_, ops);
+        return;
+    }
     CUDA_CHECK(cudaSetDevice(cuda_device_));
     std::vector<GateOp> ops;
     ops.swap(queue_);
@@ -769,6 +876,7 @@ void Simulator::flush()
 void Simulator::synchronize()
 {
     flush();
+    if (dry_) return;
     CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
 }
 
@@ -777,17 +885,15 @@ void Simulator::synchronize()
 // non-diagonal targets.  Ops are taken greedily in program order; an op that does not fit is
 // deferred and blocks later ops that do not commute with it (two ops commute when, on every
 // shared bit, both act diagonally — controls count as diagonal).
+static constexpr size_t kArenaBytes = size_t(64) << 20; // device arena of MatrixOperation matrices
+static inline size_t arena_aligned(size_t bytes) { return (bytes + 255) & ~size_t(255); }
+
 static int fit_rows(uint64_t req, int t)
 {
     if (__builtin_popcountll(req) > t) return -1;
     int c = t;
     while (c > 0 && __builtin_popcountll(req >> c) > t - c) c--;
     return c;
-}
-
-static inline bool is_pair1(const GateOp &g)
-{
-    return g.kind == GateOp::PAIR && g.a == 0 && g.b == g.xmask && __builtin_popcountll(g.xmask) == 1;
 }
 
 void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
@@ -815,6 +921,7 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
         uint64_t req = 0, blockedX = 0, blockedZ = 0;
         int c_cur = t;
         int64_t pass_params = 0;
+        size_t dense_bytes = 0; // matrices of a dense pass live in the device arena until the pass has run
         out.idx.clear();
         const size_t cap = dense_pass ? (size_t)B200K_MAX_OPS : (size_t)pass_op_cap_;
         for (size_t i = first; i < ops.size() && out.idx.size() < cap && i - first < LOOKAHEAD; i++) {
@@ -824,7 +931,9 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
             const bool commutes = !(xs & (blockedX | blockedZ)) && !(zs & blockedX);
             // a specialised pass carries its matrices in the kernel parameter block (<= 32 KB)
             const int64_t pcost = op.kind == GateOp::DENSE ? 2 * (int64_t)op.matrix->size() : 8;
-            const bool room = dense_pass || !jit_on || out.idx.empty() || pass_params + pcost <= 3800;
+            const size_t dbytes = op.kind == GateOp::DENSE ? arena_aligned(op.matrix->size() * sizeof(cplx)) : 0;
+            const bool room = dense_pass ? (out.idx.empty() || dense_bytes + dbytes <= kArenaBytes)
+                                         : (!jit_on || out.idx.empty() || pass_params + pcost <= 3800);
             if (commutes && room && (dense_pass || op.kind != GateOp::DENSE || jit_dense(op))) {
                 const uint64_t nreq = req | xs;
                 const int c = fit_rows(nreq, t);
@@ -835,6 +944,7 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
                     c_cur = c;
                     out.idx.push_back(i);
                     pass_params += pcost;
+                    dense_bytes += dbytes;
                     if (!opt_.fuse) break;
                     continue;
                 }
@@ -901,7 +1011,6 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
             }
             if (!run.empty()) launch_pass3(vec, run, high, c_cur);
         }
-        else if (opt_.kernel_gen == 2) launch_pass2(vec, pass, high, c_cur);
         else launch_pass3(vec, pass, high, c_cur);
     }
 }
@@ -1036,6 +1145,31 @@ void Simulator::make_local(const std::vector<double *> &vecs, std::vector<int> &
 // bounded staging buffer (pack -> exchange -> unpack on one stream).
 void Simulator::swap_bits(const std::vector<double *> &vecs, std::vector<int> &pos,
                           std::vector<std::pair<int, int>> pairs)
+{
+    if (pairs.empty()) return;
+    if (!timing_) {
+        swap_bits_impl(vecs, pos, std::move(pairs));
+        return;
+    }
+    // timing on (benchmarks): the swap's share of the step, by CUDA events on the compute stream
+    if (!ev2_) {
+        cudaEvent_t a, b;
+        CUDA_CHECK(cudaEventCreate(&a));
+        CUDA_CHECK(cudaEventCreate(&b));
+        ev2_ = a;
+        ev3_ = b;
+    }
+    CUDA_CHECK(cudaEventRecord((cudaEvent_t)ev2_, (cudaStream_t)stream_));
+    swap_bits_impl(vecs, pos, std::move(pairs));
+    CUDA_CHECK(cudaEventRecord((cudaEvent_t)ev3_, (cudaStream_t)stream_));
+    CUDA_CHECK(cudaEventSynchronize((cudaEvent_t)ev3_));
+    float ms = 0;
+    CUDA_CHECK(cudaEventElapsedTime(&ms, (cudaEvent_t)ev2_, (cudaEvent_t)ev3_));
+    stats_.swap_device_ms += ms;
+}
+
+void Simulator::swap_bits_impl(const std::vector<double *> &vecs, std::vector<int> &pos,
+                               std::vector<std::pair<int, int>> pairs)
 {
     const int m = (int)pairs.size();
     if (m == 0) return;
@@ -1220,221 +1354,11 @@ void Simulator::reduce_results(std::vector<double> &host)
     }
 }
 
-// ---- second-generation pass: group the pass's ops into rounds ------------------------------------------
-// A register round holds three tile bits in each thread's registers; it takes every op that is
-// diagonal or a one-target PAIR on one of those bits.  Ops are taken greedily in order; an op that
-// does not fit is deferred to a later round and blocks the ops that do not commute with it.
-void Simulator::launch_pass2(double *vec, const std::vector<const GateOp *> &ops,
-                             const std::vector<int> &high, int c)
-{
-    const int t = c + (int)high.size();
-    B200_FAIL_IF((int)high.size() > B200K_MAX_HIGH, "too many scattered tile bits");
-    int loc[64];
-    for (int p = 0; p < 64; p++) loc[p] = p < c ? p : -1;
-    for (size_t h = 0; h < high.size(); h++) loc[high[h]] = c + (int)h;
-    auto split = [&](uint64_t mask, uint32_t &inside, uint64_t &outside) {
-        inside = 0;
-        outside = 0;
-        while (mask) {
-            const int p = __builtin_ctzll(mask);
-            mask &= mask - 1;
-            if (loc[p] >= 0) inside |= 1u << loc[p];
-            else outside |= 1ull << p;
-        }
-    };
-    auto inside_only = [&](uint64_t mask) -> uint32_t {
-        uint32_t in;
-        uint64_t outm;
-        split(mask, in, outm);
-        B200_FAIL_IF(outm != 0, "internal: target bit outside the tile");
-        return in;
-    };
-
-    std::vector<B200k2Round> rounds;
-    std::vector<B200k2Op> dops;
-    auto emit = [&]() {
-        if (rounds.empty()) return;
-        B200k2Header H;
-        std::memset(&H, 0, sizeof(H));
-        H.n_rounds = (int)rounds.size();
-        H.n_ops = (int)dops.size();
-        H.t = t;
-        H.c = c;
-        H.nhigh = (int)high.size();
-        for (size_t h = 0; h < high.size(); h++) H.high_pos[h] = (uint8_t)high[h];
-        H.rank_base = rank_base_;
-        H.ntiles = 1ull << (nl_ - t);
-        CUDA_CHECK(b200k_tile_program2(vec, (int)nl_, &H, rounds.data(), dops.data(), stream_));
-        stats_.tile_passes++;
-        stats_.kernel_ops += (int64_t)dops.size();
-        stats_.rounds += (int64_t)rounds.size();
-        rounds.clear();
-        dops.clear();
-    };
-    auto base_op = [&](const GateOp &g, B200k2Op &o, uint32_t &ic, uint32_t &iv) {
-        std::memset(&o, 0, sizeof(o));
-        split(g.cmask, ic, o.co_mask);
-        split(g.cval, iv, o.co_val);
-    };
-
-    std::vector<const GateOp *> rem(ops.begin(), ops.end()), deferred, taken;
-    while (!rem.empty()) {
-        uint64_t blockedX = 0, blockedZ = 0;
-        uint32_t S = 0; // tile-local register bits of this round
-        bool smem_round = false;
-        deferred.clear();
-        taken.clear();
-        for (size_t i = 0; i < rem.size(); i++) {
-            const GateOp *g = rem[i];
-            const uint64_t xs = g->xmask, zs = g->zsupport();
-            bool fits = false;
-            if (!smem_round && !(xs & (blockedX | blockedZ)) && !(zs & blockedX)) {
-                const bool diag = g->kind == GateOp::PHASE || g->kind == GateOp::PARITY;
-                if (t >= 3 && diag) fits = true;
-                else if (t >= 3 && is_pair1(*g)) {
-                    const uint32_t b = inside_only(g->xmask);
-                    if ((S & b) || __builtin_popcount(S) < 3) {
-                        S |= b;
-                        fits = true;
-                    }
-                }
-                else if (taken.empty()) { // anything else: a shared-memory round of its own
-                    fits = true;
-                    smem_round = true;
-                }
-            }
-            if (fits) taken.push_back(g);
-            else {
-                deferred.push_back(g);
-                blockedX |= xs;
-                blockedZ |= zs;
-            }
-        }
-        if (dops.size() + taken.size() > (size_t)B200K2_LARGE_OPS || rounds.size() + 1 > (size_t)B200K2_LARGE_ROUNDS)
-            emit();
-        B200k2Round R;
-        std::memset(&R, 0, sizeof(R));
-        R.first = (uint16_t)dops.size();
-        R.count = (uint16_t)taken.size();
-        if (smem_round) {
-            R.kind = B200K2_ROUND_SMEM;
-            const GateOp &g = *taken[0];
-            B200k2Op o;
-            uint32_t ic, iv;
-            base_op(g, o, ic, iv);
-            o.tc_mask = ic;
-            o.tc_val = iv;
-            switch (g.kind) {
-            case GateOp::PAIR: {
-                o.kind = B200K2_PAIRG;
-                o.tmask = inside_only(g.xmask);
-                o.a = inside_only(g.a);
-                o.b = inside_only(g.b);
-                uint32_t m = o.tmask;
-                while (m) {
-                    B200_FAIL_IF(o.npos >= 4, "internal: PAIR on more than 4 bits");
-                    o.pos[o.npos++] = (uint32_t)__builtin_ctz(m);
-                    m &= m - 1;
-                }
-                for (int q = 0; q < 4; q++) {
-                    o.m[2 * q] = g.m[q].real();
-                    o.m[2 * q + 1] = g.m[q].imag();
-                }
-                break;
-            }
-            case GateOp::PAULIROT:
-                o.kind = B200K2_PAULIROT;
-                o.tmask = inside_only(g.xmask);
-                o.pos[0] = 31u - (uint32_t)__builtin_clz(o.tmask);
-                o.npos = 1;
-                split(g.zmask, o.tz_mask, o.zo_mask);
-                o.ny = (uint8_t)(g.ny & 3);
-                o.m[0] = g.m[0].real();
-                o.m[1] = g.m[0].imag();
-                break;
-            case GateOp::PHASE:
-                o.kind = B200K2_PHASE;
-                o.m[0] = g.m[0].real();
-                o.m[1] = g.m[0].imag();
-                break;
-            case GateOp::PARITY:
-                o.kind = B200K2_PARITY;
-                split(g.zmask, o.tz_mask, o.zo_mask);
-                o.m[0] = g.m[0].real(); o.m[1] = g.m[0].imag();
-                o.m[2] = g.m[1].real(); o.m[3] = g.m[1].imag();
-                break;
-            default: B200_FAIL("internal: DENSE op in a second-generation pass");
-            }
-            dops.push_back(o);
-        }
-        else {
-            R.kind = B200K2_ROUND_REG;
-            // pad the register bits to three with the highest free tile bits
-            for (int b = t - 1; b >= 0 && __builtin_popcount(S) < 3; b--)
-                if (!(S & (1u << b))) S |= 1u << b;
-            int rb[3], nrb = 0, ridx[32];
-            for (int b = 0; b < t; b++)
-                if (S & (1u << b)) {
-                    ridx[b] = nrb;
-                    rb[nrb++] = b;
-                }
-            R.rb0 = (uint8_t)rb[0];
-            R.rb1 = (uint8_t)rb[1];
-            R.rb2 = (uint8_t)rb[2];
-            auto regpart = [&](uint32_t m) -> uint8_t {
-                uint8_t r = 0;
-                for (int q = 0; q < 3; q++)
-                    if (m & (1u << rb[q])) r |= (uint8_t)(1u << q);
-                return r;
-            };
-            for (const GateOp *gp : taken) {
-                const GateOp &g = *gp;
-                B200k2Op o;
-                uint32_t ic, iv;
-                base_op(g, o, ic, iv);
-                o.rc_mask = regpart(ic);
-                o.rc_val = regpart(iv);
-                o.tc_mask = ic & ~S;
-                o.tc_val = iv & ~S;
-                if (g.kind == GateOp::PAIR) {
-                    o.kind = B200K2_PAIR1;
-                    o.j = (uint8_t)ridx[__builtin_ctz(inside_only(g.xmask))];
-                    bool real = true;
-                    for (int q = 0; q < 4; q++) {
-                        o.m[2 * q] = g.m[q].real();
-                        o.m[2 * q + 1] = g.m[q].imag();
-                        real = real && g.m[q].imag() == 0.0;
-                    }
-                    const bool swp = real && g.m[0].real() == 0.0 && g.m[3].real() == 0.0 &&
-                                     g.m[1].real() == 1.0 && g.m[2].real() == 1.0;
-                    o.mflag = swp ? B200K2_M_SWAP : (real ? B200K2_M_REAL : B200K2_M_GENERAL);
-                }
-                else if (g.kind == GateOp::PHASE) {
-                    o.kind = B200K2_PHASE;
-                    o.m[0] = g.m[0].real();
-                    o.m[1] = g.m[0].imag();
-                }
-                else {
-                    o.kind = B200K2_PARITY;
-                    uint32_t zi;
-                    split(g.zmask, zi, o.zo_mask);
-                    o.rz_mask = regpart(zi);
-                    o.tz_mask = zi & ~S;
-                    o.m[0] = g.m[0].real(); o.m[1] = g.m[0].imag();
-                    o.m[2] = g.m[1].real(); o.m[3] = g.m[1].imag();
-                }
-                dops.push_back(o);
-            }
-        }
-        rounds.push_back(R);
-        rem.swap(deferred);
-    }
-    emit();
-}
-
-// ---- third-generation pass (tile3.cu): rounds with host-precomputed slot masks -------------------------
-// Same round formation as launch_pass2, plus: two-target PAIRs (01<->10, 00<->11) whose two bits are both
-// register bits run in registers; every op carries masks over the thread's 8 register slots.
+// ---- interpreted pass: group the pass's ops into rounds --------------------------------------------------
+// A register round holds three tile bits in each thread's registers; it takes every op that is diagonal, a
+// one-target PAIR on one of those bits, or a two-target PAIR (01<->10, 00<->11) whose two bits are both
+// register bits.  Ops are taken greedily in order; an op that does not fit is deferred to a later round and
+// blocks the ops that do not commute with it.  Every op carries masks over the thread's 8 register slots.
 namespace {
 // kind of a PAIR op for the register rounds: 1 = one target (a = 0, b = bit), 2 = two targets
 // exchanging 01 <-> 10, 3 = two targets exchanging 00 <-> 11, 0 = none of these
@@ -1455,6 +1379,10 @@ void Simulator::launch_pass3(double *vec, const std::vector<const GateOp *> &ops
                              const std::vector<int> &high, int c)
 {
     const int t = c + (int)high.size();
+    if (dry_) {
+        stats_.tile_passes++;
+        return;
+    }
     B200_FAIL_IF((int)high.size() > B200K_MAX_HIGH, "too many scattered tile bits");
     int loc[64];
     for (int p = 0; p < 64; p++) loc[p] = p < c ? p : -1;
@@ -1492,6 +1420,7 @@ void Simulator::launch_pass3(double *vec, const std::vector<const GateOp *> &ops
         H.rank_base = rank_base_;
         H.ntiles = 1ull << (nl_ - t);
         CUDA_CHECK(b200k_tile_program3(vec, (int)nl_, &H, rounds.data(), dops.data(), stream_));
+        stats_.h2d_bytes += (double)(sizeof(H) + rounds.size() * sizeof(B200k3Round) + dops.size() * sizeof(B200k3Op));
         stats_.tile_passes++;
         stats_.kernel_ops += (int64_t)dops.size();
         stats_.rounds += (int64_t)rounds.size();
@@ -1736,16 +1665,15 @@ void Simulator::launch_pass3(double *vec, const std::vector<const GateOp *> &ops
 const double *Simulator::upload_matrix(const CVec &m)
 {
     const size_t bytes = m.size() * sizeof(cplx);
-    const size_t cap = size_t(64) << 20;
+    const size_t cap = kArenaBytes;
     if (!matrix_arena_) matrix_arena_ = std::make_unique<DeviceBuffer>(cap);
-    const size_t aligned = (bytes + 255) & ~size_t(255);
-    B200_FAIL_IF(aligned > cap, "matrix too large for the device matrix arena");
-    if (arena_used_ + aligned > cap) {
-        CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
-        arena_used_ = 0;
-    }
+    const size_t aligned = arena_aligned(bytes);
+    // launch_pass reserved room for ALL matrices of its pass before the first upload, so the arena never
+    // wraps while earlier ops of the same, not yet launched, pass still point into it
+    B200_FAIL_IF(arena_used_ + aligned > cap, "internal: device matrix arena overflow inside one pass");
     char *dst = static_cast<char *>(matrix_arena_->p()) + arena_used_;
     CUDA_CHECK(cudaMemcpyAsync(dst, m.data(), bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+    stats_.h2d_bytes += (double)bytes;
     arena_used_ += aligned;
     return reinterpret_cast<const double *>(dst);
 }
@@ -1753,6 +1681,10 @@ const double *Simulator::upload_matrix(const CVec &m)
 void Simulator::launch_pass(double *vec, const std::vector<const GateOp *> &ops,
                             const std::vector<int> &high, int c)
 {
+    if (dry_) {
+        stats_.tile_passes++;
+        return;
+    }
     B200kTileProgram P;
     std::memset(&P, 0, sizeof(P));
     const int t = c + (int)high.size();
@@ -1783,6 +1715,16 @@ void Simulator::launch_pass(double *vec, const std::vector<const GateOp *> &ops,
         return in;
     };
     P.n_ops = (int)ops.size();
+    {
+        size_t need = 0;
+        for (const GateOp *g : ops)
+            if (g->kind == GateOp::DENSE) need += arena_aligned(g->matrix->size() * sizeof(cplx));
+        B200_FAIL_IF(need > kArenaBytes, "matrix too large for the device matrix arena");
+        if (arena_used_ + need > kArenaBytes) { // wrap BEFORE the pass: kernels that read the old contents must be done
+            CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+            arena_used_ = 0;
+        }
+    }
     for (size_t i = 0; i < ops.size(); i++) {
         const GateOp &g = *ops[i];
         B200kTileOp &o = P.ops[i];
@@ -1850,6 +1792,7 @@ void Simulator::set_basis_state(const std::vector<int8_t> &bits, const std::vect
     }
     for (int q = 0; q < (int)n_; q++) pos_[q] = q; // fresh register: identity layout
     const int64_t local = (idx >> nl_) == (uint64_t)opt_.rank ? (int64_t)(idx & ((1ull << nl_) - 1ull)) : -1;
+    if (dry_) return;
     CUDA_CHECK(b200k_set_basis(psi_->d(), (int)nl_, local, stream_));
     note_launch();
 }
@@ -1868,6 +1811,7 @@ void Simulator::set_state(const CVec &st, const std::vector<int64_t> &wires)
     if (natural) { // each rank takes its contiguous slice
         CUDA_CHECK(cudaMemcpyAsync(psi_->p(), st.data() + ((size_t)opt_.rank << nl_), sizeof(cplx) << nl_,
                                    cudaMemcpyHostToDevice, (cudaStream_t)stream_));
+        stats_.h2d_bytes += (double)(sizeof(cplx) << nl_);
         CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
         return;
     }
@@ -2053,6 +1997,7 @@ void Simulator::read_results(int nslots, std::vector<double> &host)
     if (nslots == 0) return;
     CUDA_CHECK(cudaMemcpyAsync(host.data(), results_->p(), host.size() * sizeof(double),
                                cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+    stats_.d2h_bytes += (double)(host.size() * sizeof(double));
     CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
     reduce_results(host);
 }
@@ -2274,27 +2219,65 @@ double Simulator::var(int64_t key)
 }
 
 // ---- State / Probs ----------------------------------------------------------------------------------
-static void d2h_strided(void *stream, const void *dsrc, size_t elem_bytes, size_t count, void *hdst,
-                        int64_t stride)
+// Device -> caller's host buffer (pageable memory, DataView strides: runtime/include/DataView.hpp:124-134).
+// Large results (Probs of 30 wires = 8 GiB, State) go through two pinned staging buffers: the DMA of chunk k+1
+// runs while host threads copy (or scatter, for a strided view) chunk k out of the other buffer.
+void Simulator::d2h_strided(const void *dsrc, size_t elem_bytes, size_t count, void *hdst, int64_t stride)
 {
-    cudaStream_t st = (cudaStream_t)stream;
-    if (stride == 1) {
-        CUDA_CHECK(cudaMemcpyAsync(hdst, dsrc, elem_bytes * count, cudaMemcpyDeviceToHost, st));
+    cudaStream_t st = (cudaStream_t)stream_;
+    const size_t total = elem_bytes * count;
+    if (stride == 1 && total <= (size_t(1) << 20)) {
+        CUDA_CHECK(cudaMemcpyAsync(hdst, dsrc, total, cudaMemcpyDeviceToHost, st));
         CUDA_CHECK(cudaStreamSynchronize(st));
+        stats_.d2h_bytes += (double)total;
         return;
     }
-    // honour DataView strides (reference: runtime/include/DataView.hpp:124-134)
-    const size_t chunk = size_t(1) << 20;
-    std::vector<char> stage(std::min(chunk, count) * elem_bytes);
-    for (size_t o = 0; o < count; o += chunk) {
-        const size_t cnt = std::min(chunk, count - o);
-        CUDA_CHECK(cudaMemcpyAsync(stage.data(), static_cast<const char *>(dsrc) + o * elem_bytes,
-                                   cnt * elem_bytes, cudaMemcpyDeviceToHost, st));
-        CUDA_CHECK(cudaStreamSynchronize(st));
-        for (size_t i = 0; i < cnt; i++)
-            std::memcpy(static_cast<char *>(hdst) + (int64_t)(o + i) * stride * (int64_t)elem_bytes,
-                        stage.data() + i * elem_bytes, elem_bytes);
+    const size_t CH = size_t(32) << 20; // bytes per staging buffer
+    for (int h = 0; h < 2; h++)
+        if (!stage_host_[h]) {
+            CUDA_CHECK(cudaMallocHost(&stage_host_[h], CH));
+            cudaEvent_t e;
+            CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            stage_ev_[h] = e;
+        }
+    const size_t per = CH / elem_bytes; // elements per chunk
+    const size_t nchunks = (count + per - 1) / per;
+    unsigned nthreads = std::min(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
+    auto drain = [&](size_t k) { // chunk k: staging buffer -> caller's memory
+        const int h = (int)(k & 1);
+        CUDA_CHECK(cudaEventSynchronize((cudaEvent_t)stage_ev_[h]));
+        const size_t o = k * per, cnt = std::min(per, count - o);
+        const char *src = static_cast<const char *>(stage_host_[h]);
+        auto part = [&](size_t i0, size_t i1) {
+            if (stride == 1) {
+                std::memcpy(static_cast<char *>(hdst) + (o + i0) * elem_bytes, src + i0 * elem_bytes, (i1 - i0) * elem_bytes);
+                return;
+            }
+            for (size_t i = i0; i < i1; i++)
+                std::memcpy(static_cast<char *>(hdst) + (int64_t)(o + i) * stride * (int64_t)elem_bytes, src + i * elem_bytes,
+                            elem_bytes);
+        };
+        if (cnt * elem_bytes < (size_t(4) << 20) || nthreads == 1) {
+            part(0, cnt);
+            return;
+        }
+        std::vector<std::thread> th;
+        const size_t step = (cnt + nthreads - 1) / nthreads;
+        for (unsigned t = 1; t < nthreads; t++)
+            if (t * step < cnt) th.emplace_back(part, t * step, std::min(cnt, (t + 1) * step));
+        part(0, std::min(cnt, step));
+        for (auto &x : th) x.join();
+    };
+    for (size_t k = 0; k < nchunks; k++) {
+        const int h = (int)(k & 1);
+        const size_t o = k * per, cnt = std::min(per, count - o);
+        CUDA_CHECK(cudaMemcpyAsync(stage_host_[h], static_cast<const char *>(dsrc) + o * elem_bytes, cnt * elem_bytes,
+                                   cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaEventRecord((cudaEvent_t)stage_ev_[h], st));
+        if (k >= 1) drain(k - 1); // overlaps the DMA of chunk k; buffer (k-1)&1 is free again before chunk k+1 is issued
     }
+    drain(nchunks - 1);
+    stats_.d2h_bytes += (double)total;
 }
 
 void Simulator::state(double *out_ri, int64_t stride)
@@ -2303,7 +2286,7 @@ void Simulator::state(double *out_ri, int64_t stride)
     if (!wire_identity()) restore_wire_order();
     flush();
     if (!sharded()) {
-        d2h_strided(stream_, psi_->p(), sizeof(cplx), size_t(1) << n_, out_ri, stride);
+        d2h_strided(psi_->p(), sizeof(cplx), size_t(1) << n_, out_ri, stride);
         return;
     }
     // SPMD contract: every rank returns the whole vector.  Shards are gathered through the host and
@@ -2413,7 +2396,7 @@ void Simulator::probs(const std::vector<int64_t> &wires_in, double *out, int64_t
                                            probs_buf_->d(), stream_));
         }
         note_launch();
-        if (out) d2h_strided(stream_, probs_buf_->p(), sizeof(double), size_t(1) << k, out, stride);
+        if (out) d2h_strided(probs_buf_->p(), sizeof(double), size_t(1) << k, out, stride);
         return;
     }
     // sharded: marginal over the wires that sit on local bits (kernel), wires on rank bits select the
@@ -2486,9 +2469,7 @@ std::vector<int64_t> Simulator::sample_indices(const std::vector<int64_t> &wires
     probs(wires, nullptr, 1); // leaves the distribution in probs_buf_ on the device
     const size_t k = wires.empty() ? (size_t)n_ : wires.size();
     const int64_t nbins = int64_t(1) << k;
-    std::mt19937 rng;
-    if (rng_fn_ || own_seeded_) rng = std::mt19937(rng_next());
-    else rng = std::mt19937(std::random_device{}());
+    std::mt19937 rng(fresh_seed());
     std::vector<int64_t> idx((size_t)shots);
     if (shots == 0) return idx;
     std::vector<double> u(2 * (size_t)shots);
@@ -2504,6 +2485,8 @@ std::vector<int64_t> Simulator::sample_indices(const std::vector<int64_t> &wires
     int64_t *di = reinterpret_cast<int64_t *>(reinterpret_cast<char *>(du) + ubytes);
     cudaStream_t st = (cudaStream_t)stream_;
     CUDA_CHECK(cudaMemcpyAsync(du, u.data(), ubytes, cudaMemcpyHostToDevice, st));
+    stats_.h2d_bytes += (double)ubytes;
+    stats_.d2h_bytes += (double)ibytes;
     CUDA_CHECK(b200k_sampler_prepare(probs_buf_->d(), nbins, dscr, stream_));
     CUDA_CHECK(b200k_sampler_draw(probs_buf_->d(), nbins, dscr, du, shots, di, stream_));
     note_launch();
@@ -2533,8 +2516,7 @@ bool Simulator::draw_outcome(const double p[2], int postselect)
         (void)rng_next();
     }
     else {
-        std::random_device rd;
-        std::mt19937 g(rd());
+        std::mt19937 g(fresh_seed());
         draw = (float)dis(g);
     }
     return draw > p[0];
@@ -2940,6 +2922,7 @@ static thread_local std::string g_err;
 
 #define B200_TRY(...)                                                                              \
     try {                                                                                          \
+        d->sim->make_current(); /* the caller's thread may have another CUDA device current */     \
         __VA_ARGS__;                                                                               \
         return 0;                                                                                  \
     }                                                                                              \
@@ -2979,7 +2962,25 @@ b200sv_device *b200sv_create(const char *kwargs)
         return nullptr;
     }
 }
-void b200sv_destroy(b200sv_device *d) { delete d; }
+void b200sv_destroy(b200sv_device *d)
+{
+    if (!d) return;
+    // $B200SV_STATS_FILE: one JSON line of counters per device activation, appended when the device goes away
+    // (the hook the reference's ResourceTracker plays for null.qubit: NullQubit.hpp:104-112) -- how a host that
+    // only sees the plugin (librt_capi -> librtd_b200sv.so) gets at the counters
+    if (const char *path = std::getenv("B200SV_STATS_FILE")) {
+        try {
+            const std::string js = d->sim->stats_json();
+            if (FILE *f = fopen(path, "a")) {
+                fprintf(f, "%s\n", js.c_str());
+                fclose(f);
+            }
+        }
+        catch (...) {
+        }
+    }
+    delete d;
+}
 
 int b200sv_allocate_qubits(b200sv_device *d, int64_t n) { B200_TRY(d->sim->allocate(n)) }
 int b200sv_allocate_qubit(b200sv_device *d) { B200_TRY(d->sim->allocate_one()) }
@@ -3031,6 +3032,7 @@ int64_t b200sv_observable(b200sv_device *d, int obs_id, const double *matrix_ri,
                           const int64_t *wires, int64_t nwires)
 {
     try {
+        d->sim->make_current();
         return d->sim->obs_named(obs_id, cvv(matrix_ri, (size_t)(nmatrix > 0 ? nmatrix : 0)), wv(wires, nwires));
     }
     catch (const std::exception &e) {
@@ -3041,6 +3043,7 @@ int64_t b200sv_observable(b200sv_device *d, int obs_id, const double *matrix_ri,
 int64_t b200sv_tensor_observable(b200sv_device *d, const int64_t *keys, int64_t nkeys)
 {
     try {
+        d->sim->make_current();
         return d->sim->obs_tensor(wv(keys, nkeys));
     }
     catch (const std::exception &e) {
@@ -3052,6 +3055,7 @@ int64_t b200sv_hamiltonian_observable(b200sv_device *d, const double *coeffs, co
                                       int64_t nkeys)
 {
     try {
+        d->sim->make_current();
         return d->sim->obs_hamiltonian(std::vector<double>(coeffs, coeffs + (nkeys > 0 ? nkeys : 0)),
                                        wv(keys, nkeys));
     }
@@ -3126,6 +3130,20 @@ int b200sv_get_stats(b200sv_device *d, b200sv_stats *out) { B200_TRY(*out = d->s
 int b200sv_reset_stats(b200sv_device *d) { B200_TRY(d->sim->reset_stats()) }
 int b200sv_set_timing(b200sv_device *d, int on) { B200_TRY(d->sim->set_timing(on != 0)) }
 int b200sv_flush(b200sv_device *d) { B200_TRY(d->sim->flush()) }
+int b200sv_fp64_peak(b200sv_device *d, double *dfma_per_second) { B200_TRY(*dfma_per_second = d->sim->fp64_peak()) }
+int64_t b200sv_stats_json(b200sv_device *d, char *buf, int64_t cap)
+{
+    try {
+        const std::string js = d->sim->stats_json();
+        if ((int64_t)js.size() + 1 > cap) return -1;
+        std::memcpy(buf, js.c_str(), js.size() + 1);
+        return (int64_t)js.size();
+    }
+    catch (const std::exception &e) {
+        g_err = e.what();
+        return -1;
+    }
+}
 int b200sv_synchronize(b200sv_device *d) { B200_TRY(d->sim->synchronize()) }
 int b200sv_jit_wait(b200sv_device *d) { B200_TRY(d->sim->jit_wait()) }
 void *b200sv_device_pointer(b200sv_device *d) { return d->sim->device_pointer(); }

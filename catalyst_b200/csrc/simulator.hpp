@@ -94,7 +94,6 @@ struct Options {
     int world = 1, rank = 0;
     std::string comm;
     int64_t stage_mib = 4096; // staging memory of the global<->local qubit swap (two pipelined halves)
-    int kernel_gen = 3;       // tile kernel generation (2 = k_tile2, 3 = k_tile3)
     // run-time specialised tile passes (jit.hpp): 0 = off, 1 = auto (a pass structure seen
     // `jit_threshold` times is compiled in the background, the interpreter runs it until the
     // kernel is ready), 2 = always (compile synchronously at first sight; tests)
@@ -104,10 +103,13 @@ struct Options {
     int jit_min_qubits = 22;  // smaller local states stay on the interpreter
     int jit_dbuf = 1;         // cp.async double-buffered tiles in specialised passes
     int jit_fuse_diag = 1;    // fuse runs of diagonal ops inside a register round
+    int jit_uniform = 1;      // evaluate tile-uniform diagonal factors once per tile (warp-collective), not per thread
     int jit_factor = 1;       // factor u00 out of uncontrolled one-qubit gates, fold the product into one op
     bool virtual_swap = true; // uncontrolled SWAP gates relabel wires instead of moving amplitudes
     int p2p_swap = -1;        // qubit swap over mapped peer memory: 1 on, 0 off, -1 auto (on for 'local:' rank groups)
     bool batch_overlaps = true; // adjoint gradient: evaluate commuting generators' overlaps in batched read passes
+    bool release_project = false; // ReleaseQubit of a wire that is not in a basis state: error (default) or keep
+                                  // the more probable branch (release_entangled='project')
     bool lazy_adjoint = true; // adjoint gradient: apply U^dagger only when the next generator does not commute with it
 };
 
@@ -168,6 +170,9 @@ class Simulator {
     // instrumentation
     b200sv_stats stats() const; // simulator_jit.cpp (adds the process-wide JIT counters)
     void reset_stats();
+    double fp64_peak();            // measured thread-level DFMA instructions per second (microbenchmark)
+    std::string stats_json() const; // counters as one JSON object
+    void make_current(); // every public entry point runs on this object's CUDA device
     void set_timing(bool on) { timing_ = on; }
     void flush();
     void synchronize();
@@ -201,6 +206,7 @@ class Simulator {
     void make_local(const std::vector<double *> &vecs, std::vector<int> &pos, uint64_t logical_mask);
     void swap_bits(const std::vector<double *> &vecs, std::vector<int> &pos,
                    std::vector<std::pair<int, int>> pairs); // (global position, local position)
+    void swap_bits_impl(const std::vector<double *> &vecs, std::vector<int> &pos, std::vector<std::pair<int, int>> pairs);
     uint64_t to_phys(const std::vector<int> &pos, uint64_t logical_mask) const;
     GateOp phys_op(const std::vector<int> &pos, const GateOp &g) const;
     bool sharded() const { return opt_.world > 1; }
@@ -216,13 +222,12 @@ class Simulator {
     void run_ops(double *vec, std::vector<GateOp> &ops);
     void launch_pass(double *vec, const std::vector<const GateOp *> &ops,
                      const std::vector<int> &req_high, int c);
-    void launch_pass2(double *vec, const std::vector<const GateOp *> &ops,
-                      const std::vector<int> &req_high, int c);
     void launch_pass3(double *vec, const std::vector<const GateOp *> &ops,
                       const std::vector<int> &req_high, int c);
     bool launch_pass_jit(double *vec, const std::vector<const GateOp *> &ops,
                          const std::vector<int> &req_high, int c);
     int jit_mode_ = 0;
+    bool dry_ = false; // B200SV_DRYRUN: plan, generate and compile only (development, no GPU)
     int pass_op_cap_ = 160;
     const double *upload_matrix(const CVec &m);
 
@@ -248,8 +253,12 @@ class Simulator {
     double sampled_term_mean(const ObsTerm &t);
     double uniform01();
     uint32_t rng_next();
+    uint32_t fresh_seed();
 
     void ensure_buffer(std::unique_ptr<DeviceBuffer> &buf, size_t bytes);
+    void d2h_strided(const void *dsrc, size_t elem_bytes, size_t count, void *hdst, int64_t stride);
+    void *stage_host_[2] = {nullptr, nullptr}; // pinned staging of large device -> host results
+    void *stage_ev_[2] = {nullptr, nullptr};
     void note_launch() { stats_.other_launches++; }
 
     Options opt_;
@@ -283,7 +292,7 @@ class Simulator {
 
     b200sv_stats stats_{};
     bool timing_ = false;
-    void *ev0_ = nullptr, *ev1_ = nullptr;
+    void *ev0_ = nullptr, *ev1_ = nullptr, *ev2_ = nullptr, *ev3_ = nullptr;
 };
 
 Options parse_kwargs(const char *kwargs);

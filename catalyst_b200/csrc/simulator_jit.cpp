@@ -8,6 +8,7 @@
 
 #include <algorithm>
 #include <cstring>
+#include <map>
 #include <sstream>
 
 #include "jit.hpp"
@@ -38,6 +39,17 @@ struct JOp {
     double vals[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     std::vector<int> tg;           // DENSE: tile-local target positions, most significant first
     std::vector<double> dvals;     // DENSE: 2 * 4^k doubles, row-major (re, im)
+    int uacc = -1;                 // >= 0: tile-uniform diagonal op, folded into uniform accumulator `uacc`
+};
+
+// A tile-uniform accumulator: the product of the diagonal ops of one fused run (one register-bit signature)
+// whose predicate / parity depends on bits OUTSIDE the tile only.  Its value is the same for every thread of
+// the CTA, so ONE warp evaluates it per tile (one op per lane, warp-shuffle product tree) instead of every
+// thread multiplying through the whole fan (a QFT fan: 19 of its 29 controlled phases).
+struct UAcc {
+    int type = 0;   // 0 PHASE (one complex), 1 PARITY (even / odd pair)
+    int n = 0;      // ops
+    int first = 0;  // first table entry (entries of one accumulator are contiguous)
 };
 
 struct JRound {
@@ -51,6 +63,9 @@ struct JPlan {
     uint64_t rank_base = 0;
     std::vector<JRound> rounds;
     int nm = 0;
+    std::vector<UAcc> uaccs;
+    int nu = 0, uoff = 0; // uniform-table entries (8 doubles each) and their offset in the parameter doubles
+    int uniform = 1;      // option: evaluate tile-uniform diagonal factors once per tile
 };
 
 inline int cls_of(double v) { return v == 0.0 ? CLS_ZERO : (v == 1.0 ? CLS_ONE : (v == -1.0 ? CLS_MONE : CLS_GEN)); }
@@ -129,6 +144,9 @@ struct Term {
     bool neg;
 };
 
+// FP64-pipe instructions emitted so far by the current generate() call (DFMA / DMUL / DADD each count one)
+thread_local double g_fp64_emitted = 0.0;
+
 std::string lin(const std::vector<Term> &terms)
 {
     std::string acc;
@@ -141,6 +159,7 @@ std::string lin(const std::vector<Term> &terms)
     for (const Term *t : ord) {
         bool neg = t->neg;
         if (t->cls == CLS_MONE) neg = !neg;
+        g_fp64_emitted += (t->cls != CLS_GEN && acc.empty()) ? 0.0 : 1.0;
         if (t->cls != CLS_GEN) {
             if (acc.empty()) acc = neg ? "(-" + t->opnd + ")" : t->opnd;
             else acc = "(" + acc + (neg ? " - " : " + ") + t->opnd + ")";
@@ -167,6 +186,64 @@ void cmul_terms(std::vector<Term> &re, std::vector<Term> &im, const Coef &k, con
     im.push_back({k.ci, k.ei, xr, false});
 }
 
+// Marks the diagonal ops that fold into tile-uniform accumulators (see UAcc).  Mirrors the run / accumulator
+// formation of emit_diag_run in generate(): a run is a maximal sequence of consecutive PHASE / PARITY ops of
+// a round (length >= 2); inside a run an accumulator is identified by its register-bit signature.
+inline bool diag_kind(int k) { return k == (int)GateOp::PHASE || k == (int)GateOp::PARITY; }
+
+void analyze_uniform(JPlan &P)
+{
+    P.uaccs.clear();
+    P.nu = 0;
+    const int threads = 1 << (P.t - P.nr);
+    if (!P.uniform || !P.fuse_diag || threads < 32) return;
+    for (JRound &R : P.rounds) {
+        for (size_t i0 = 0; i0 < R.ops.size();) {
+            if (!diag_kind(R.ops[i0].kind)) {
+                i0++;
+                continue;
+            }
+            size_t i1 = i0;
+            while (i1 < R.ops.size() && diag_kind(R.ops[i1].kind)) i1++;
+            if (i1 - i0 >= 2) {
+                struct Sig {
+                    int type;
+                    uint32_t rcm, rcv, rz;
+                    std::vector<size_t> idx;
+                };
+                std::vector<Sig> sigs;
+                for (size_t i = i0; i < i1; i++) {
+                    const JOp &g = R.ops[i];
+                    const bool parity = g.kind == (int)GateOp::PARITY;
+                    if (g.cin_m & ~R.S) continue;                       // thread-bit predicate: per thread
+                    if (parity && (g.zin & ~R.S)) continue;             // thread-bit parity: per thread
+                    if (!g.co_m && !(parity && g.zo)) continue;         // nothing outside: a plain constant
+                    const uint32_t rcm = g.cin_m & R.S, rcv = g.cin_v & R.S, rz = parity ? (g.zin & R.S) : 0u;
+                    Sig *hit = nullptr;
+                    for (auto &sg : sigs)
+                        if (sg.type == (parity ? 1 : 0) && sg.rcm == rcm && sg.rcv == rcv && sg.rz == rz) hit = &sg;
+                    if (!hit) {
+                        sigs.push_back(Sig{parity ? 1 : 0, rcm, rcv, rz, {}});
+                        hit = &sigs.back();
+                    }
+                    hit->idx.push_back(i);
+                }
+                for (auto &sg : sigs) {
+                    if (sg.idx.size() < 3) continue; // a warp-collective per tile must replace enough per-thread work
+                    UAcc u;
+                    u.type = sg.type;
+                    u.n = (int)sg.idx.size();
+                    u.first = P.nu;
+                    for (size_t i : sg.idx) R.ops[i].uacc = (int)P.uaccs.size();
+                    P.nu += u.n;
+                    P.uaccs.push_back(u);
+                }
+            }
+            i0 = i1;
+        }
+    }
+}
+
 // ---- CUDA source of one pass ---------------------------------------------------------------------
 std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
 {
@@ -178,6 +255,7 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
     const uint32_t nslots = 1u << nr;
     const uint64_t ntiles = 1ull << (P.nl - t);
     std::ostringstream o;
+    g_fp64_emitted = 0.0;
     auto mref = [&](int k) { return "P.m[" + std::to_string(k) + "]"; };
     // global offset of tile-local index e (an OR over disjoint bit sets)
     auto off_of = [&](uint32_t e) -> uint64_t {
@@ -190,7 +268,8 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
     o << "// generated by catalyst_b200/csrc/simulator_jit.cpp: t=" << t << " c=" << c << " nr=" << nr
       << " rounds=" << P.rounds.size() << "\n";
     o << "typedef double2 cplx;\n";
-    o << "struct Params { double m[" << std::max(1, P.nm) << "]; };\n";
+    // rank_base (rank << local bits) is a run-time argument: every rank of a sharded job runs the same cubin
+    o << "struct Params { unsigned long long rank_base; double m[" << std::max(1, P.nm) << "]; };\n";
     o << "__device__ __forceinline__ void cpa16(void *d, const void *s) {\n"
          "  const unsigned a = (unsigned)__cvta_generic_to_shared(d);\n"
          "  asm volatile(\"cp.async.cg.shared.global [%0], [%1], 16;\\n\" :: \"r\"(a), \"l\"(s) : \"memory\");\n}\n";
@@ -204,17 +283,33 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
         o << "  b = ((b >> " << p << ") << " << (p + 1) << ") | (b & " << hex64((1ull << p) - 1ull) << ");\n";
     }
     o << "  return b;\n}\n";
-    const int minb = P.dbuf ? std::max(1, std::min(8, (227 * 1024) / (int)(2 * 16 * nelem + 1024)))
-                            : std::max(1, std::min(8, (227 * 1024) / (int)(16 * nelem + 1024)));
+    const int usmem = P.uaccs.empty() ? 0 : 8 * (8 * P.nu + 4 * (int)P.uaccs.size());
+    const int minb = P.dbuf ? std::max(1, std::min(8, (227 * 1024) / (int)(2 * 16 * nelem + 1024 + usmem)))
+                            : std::max(1, std::min(8, (227 * 1024) / (int)(16 * nelem + 1024 + usmem)));
     // register budget: leave the compiler room for 2^nr amplitudes (4 registers each) + temporaries
     int minb_regs = (int)(65536 / (TT * (uint32_t)(4 * nslots + 56)));
     // (measured at 30 qubits, 16 amplitudes per thread: 3 CTAs x 128 threads with the cp.async double
     // buffer 137 ms per circuit; 4 CTAs without it 150 ms; 5 CTAs, 102 registers, spilling: 190 ms)
     const int launch_minb = std::max(1, std::min(minb, std::max(1, minb_regs)));
+    if (!P.uaccs.empty()) {
+        o << "__constant__ unsigned UMETA[" << P.uaccs.size() << "] = {";
+        for (size_t u = 0; u < P.uaccs.size(); u++)
+            o << (u ? ", " : "") << (((uint32_t)P.uaccs[u].n << 16) | (uint32_t)P.uaccs[u].first) << "u";
+        o << "};\n";
+    }
     o << "extern \"C\" __global__ void __launch_bounds__(" << TT << ", " << launch_minb << ") " << name
       << "(cplx *__restrict__ psi, const __grid_constant__ Params P)\n{\n";
     o << "  extern __shared__ __align__(16) cplx smem[];\n";
     o << "  const unsigned tid = threadIdx.x;\n";
+    const uint32_t tile_bufs = P.dbuf ? 2u : 1u;
+    if (!P.uaccs.empty()) {
+        // tile-uniform diagonal factors: op table (8 doubles per op: predicate mask / value, z mask, e0, e1) copied
+        // once from the parameter block, and one (even, odd) result pair per accumulator, rewritten every tile
+        o << "  double *const utab = reinterpret_cast<double *>(smem + " << tile_bufs * nelem << "u);\n";
+        o << "  double *const su = utab + " << 8 * P.nu << "u;\n";
+        o << "  for (unsigned i = tid; i < " << 8 * P.nu << "u; i += " << TT << "u) utab[i] = P.m[" << P.uoff << "u + i];\n";
+        o << "  __syncthreads();\n";
+    }
     // off_tid: tid covers tile-local bits 0..tbits-1
     {
         o << "  const unsigned long long off_tid = (unsigned long long)(tid & " << hex32((1u << std::min(c, tbits)) - 1u) << ")";
@@ -240,21 +335,67 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
     }
     o << "  for (unsigned long long tile = blockIdx.x; tile < " << hex64(ntiles) << "; tile += gridDim.x) {\n";
     o << "    const unsigned long long base = base_of(tile);\n";
-    o << "    const unsigned long long obase = base | " << hex64(P.rank_base) << ";\n";
+    o << "    const unsigned long long obase = base | P.rank_base;\n";
     o << "    cplx *__restrict__ tp = psi + (base | off_tid);\n";
     if (P.dbuf) {
         o << "    cplx *__restrict__ s = smem + cur * " << nelem << "u;\n";
-        o << "    { const unsigned long long next = tile + gridDim.x;\n"
-             "      if (next < "
-          << hex64(ntiles) << ") { prefetch(next, smem + (cur ^ 1u) * " << nelem
-          << "u); asm volatile(\"cp.async.wait_group 1;\\n\" ::: \"memory\"); }\n"
-             "      else asm volatile(\"cp.async.wait_group 0;\\n\" ::: \"memory\"); }\n";
+        o << "    const bool has_next = tile + gridDim.x < " << hex64(ntiles) << ";\n";
+        o << "    if (has_next) prefetch(tile + gridDim.x, smem + (cur ^ 1u) * " << nelem << "u);\n";
     }
     else {
         o << "    cplx *__restrict__ s = smem;\n";
         for (uint32_t k = 0; k < niter; k++)
             o << "    s[" << slot_expr("swtid", k * TT) << "] = tp[" << hex64(off_of(k * TT)) << "];\n";
     }
+    if (!P.uaccs.empty()) {
+        // Tile-uniform factors.  Accumulator g is evaluated by a group of four lanes: each lane multiplies through
+        // every fourth op of the accumulator (table in shared memory), two shuffle steps combine the group, its
+        // first lane publishes the (even, odd) pair.  Every warp runs the same straight code (idle groups see
+        // n = 0), so the shuffles sit in convergent code.
+        const uint32_t nwarps = TT / 32u, per_iter = 8u * nwarps, nacc = (uint32_t)P.uaccs.size();
+        bool any_par = false;
+        for (const UAcc &A : P.uaccs) any_par = any_par || A.type == 1;
+        o << "    { // tile-uniform diagonal factors: " << nacc << " accumulators, " << P.nu << " ops\n";
+        o << "      const unsigned lane = tid & 31u, grp = (tid >> 5) * 8u + (lane >> 2);\n";
+        for (uint32_t base = 0; base < nacc; base += per_iter) {
+            o << "      {\n";
+            o << "        const unsigned acc = " << base << "u + grp;\n";
+            o << "        const unsigned meta = acc < " << nacc << "u ? UMETA[acc] : 0u;\n";
+            o << "        const unsigned first = meta & 0xffffu, n = meta >> 16;\n";
+            o << "        double ar = 1.0, ai = 0.0" << (any_par ? ", br = 1.0, bi = 0.0" : "") << ";\n";
+            o << "        for (unsigned k = lane & 3u; k < n; k += 4u) {\n";
+            o << "          const double2 *e = reinterpret_cast<const double2 *>(utab) + 4u * (first + k);\n";
+            o << "          const double2 mk = e[0];\n";
+            o << "          if ((obase & (unsigned long long)__double_as_longlong(mk.x)) == (unsigned long long)__double_as_longlong(mk.y)) {\n";
+            if (any_par) {
+                o << "            const double2 zz = e[1], e0 = e[2], e1 = e[3];\n";
+                o << "            const bool p = (__popcll(obase & (unsigned long long)__double_as_longlong(zz.x)) & 1) != 0;\n";
+                o << "            const double xr = p ? e1.x : e0.x, xi = p ? e1.y : e0.y, yr = p ? e0.x : e1.x, yi = p ? e0.y : e1.y;\n";
+                o << "            { const double tr = ar; ar = fma(-ai, xi, tr * xr); ai = fma(ai, xr, tr * xi); }\n";
+                o << "            { const double tr = br; br = fma(-bi, yi, tr * yr); bi = fma(bi, yr, tr * yi); }\n";
+            }
+            else {
+                o << "            const double2 e0 = e[2];\n";
+                o << "            { const double tr = ar; ar = fma(-ai, e0.y, tr * e0.x); ai = fma(ai, e0.x, tr * e0.y); }\n";
+            }
+            o << "          }\n        }\n";
+            for (int d = 1; d <= 2; d <<= 1) {
+                o << "        { const double xr = __shfl_xor_sync(0xffffffffu, ar, " << d << "), xi = __shfl_xor_sync(0xffffffffu, ai, " << d << ");\n"
+                     "          const double tr = ar; ar = fma(-ai, xi, tr * xr); ai = fma(ai, xr, tr * xi); }\n";
+                if (any_par)
+                    o << "        { const double xr = __shfl_xor_sync(0xffffffffu, br, " << d << "), xi = __shfl_xor_sync(0xffffffffu, bi, " << d << ");\n"
+                         "          const double tr = br; br = fma(-bi, xi, tr * xr); bi = fma(bi, xr, tr * xi); }\n";
+            }
+            o << "        if ((lane & 3u) == 0u && acc < " << nacc << "u) {\n";
+            o << "          reinterpret_cast<double2 *>(su)[2u * acc] = make_double2(ar, ai);\n";
+            if (any_par) o << "          reinterpret_cast<double2 *>(su)[2u * acc + 1u] = make_double2(br, bi);\n";
+            o << "        }\n      }\n";
+        }
+        o << "    }\n";
+    }
+    if (P.dbuf)
+        o << "    if (has_next) asm volatile(\"cp.async.wait_group 1;\\n\" ::: \"memory\");\n"
+             "    else asm volatile(\"cp.async.wait_group 0;\\n\" ::: \"memory\");\n";
     o << "    __syncthreads();\n";
 
 
@@ -341,23 +482,47 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
                 o << "        const double " << name << "r = " << lin(re) << ", " << name << "i = " << lin(im) << ";\n";
                 acc = Coef{CLS_GEN, CLS_GEN, name + "r", name + "i"};
             };
+            // acc = acc * f only where `cond` holds: predicated FP64 instructions with the constants as direct
+            // operands (a select-then-multiply costs 4 FSEL + 2..4 LDC more per op)
+            auto mul_into_if = [&](Coef &acc, const Coef &f, const std::string &cond, const std::string &name) {
+                std::vector<Term> re, im;
+                cmul_terms(re, im, f, acc.er, acc.ei);
+                o << "        double " << name << "r = " << acc.er << ", " << name << "i = " << acc.ei << ";\n";
+                o << "        if (" << cond << ") { " << name << "r = " << lin(re) << "; " << name << "i = " << lin(im) << "; }\n";
+                acc = Coef{CLS_GEN, CLS_GEN, name + "r", name + "i"};
+            };
+            std::vector<char> useen(P.uaccs.size(), 0);
             for (size_t i = i0; i < i1; i++) {
                 const JOp &g = R.ops[i];
-                const std::string cond = cond_of(g);
+                std::string cond = cond_of(g);
                 const uint32_t rcm = g.cin_m & R.S, rcv = g.cin_v & R.S;
                 const int u = uid++;
                 const std::string un = "f" + std::to_string(u);
+                const bool uni = g.uacc >= 0;
+                if (uni) { // tile-uniform op: its whole accumulator was evaluated once per tile (su[])
+                    if (useen[(size_t)g.uacc]) continue;
+                    useen[(size_t)g.uacc] = 1;
+                    cond.clear();
+                }
                 if (g.kind == GateOp::PHASE) {
                     Coef f{(int)(g.cls & 3u), (int)((g.cls >> 2) & 3u), mref(g.moff), mref(g.moff + 1)};
+                    if (uni) {
+                        o << "        const double " << un << "r = su[" << 4 * g.uacc << "], " << un << "i = su[" << 4 * g.uacc + 1 << "];\n";
+                        f = Coef{CLS_GEN, CLS_GEN, un + "r", un + "i"};
+                    }
+                    Acc *A = nullptr;
+                    for (auto &a : accs)
+                        if (a.type == 0 && a.rcm == rcm && a.rcv == rcv) A = &a;
+                    if (A && !cond.empty()) {
+                        mul_into_if(A->a, f, cond, "g" + std::to_string(A->id) + "_" + std::to_string(u));
+                        continue;
+                    }
                     if (!cond.empty()) {
                         o << "        const bool " << un << "c = " << cond << ";\n";
                         o << "        const double " << un << "r = " << un << "c ? " << mref(g.moff) << " : 1.0, " << un << "i = " << un
                           << "c ? " << mref(g.moff + 1) << " : 0.0;\n";
                         f = Coef{CLS_GEN, CLS_GEN, un + "r", un + "i"};
                     }
-                    Acc *A = nullptr;
-                    for (auto &a : accs)
-                        if (a.type == 0 && a.rcm == rcm && a.rcv == rcv) A = &a;
                     if (!A) {
                         accs.push_back(Acc{0, rcm, rcv, 0, f, f, (int)accs.size()});
                         continue;
@@ -369,7 +534,13 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
                     const uint32_t tz = g.zin & ~R.S, rz = g.zin & R.S;
                     Coef fa{(int)(g.cls & 3u), (int)((g.cls >> 2) & 3u), mref(g.moff), mref(g.moff + 1)};
                     Coef fb{(int)((g.cls >> 4) & 3u), (int)((g.cls >> 6) & 3u), mref(g.moff + 2), mref(g.moff + 3)};
-                    if (tz || g.zo || !cond.empty()) {
+                    if (uni) {
+                        o << "        const double " << un << "ar = su[" << 4 * g.uacc << "], " << un << "ai = su[" << 4 * g.uacc + 1
+                          << "], " << un << "br = su[" << 4 * g.uacc + 2 << "], " << un << "bi = su[" << 4 * g.uacc + 3 << "];\n";
+                        fa = Coef{CLS_GEN, CLS_GEN, un + "ar", un + "ai"};
+                        fb = Coef{CLS_GEN, CLS_GEN, un + "br", un + "bi"};
+                    }
+                    else if (tz || g.zo || !cond.empty()) {
                         std::string pz = "false";
                         if (tz || g.zo) {
                             pz = "(((";
@@ -568,6 +739,7 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
                     bool nr_, ni_;
                     b << "        { const double ar = " << V(A, 'r') << ", ai = " << V(A, 'i') << ", br = " << V(B, 'r')
                       << ", bi = " << V(B, 'i') << ";\n";
+                    g_fp64_emitted += 8.0;
                     W("br", "bi", eB, wr, nr_, wi, ni_); // new_A = cs * A + sn * W(B, eB)
                     b << "          " << V(A, 'r') << " = fma(" << (nr_ ? "-" : "") << sn << ", " << wr << ", " << cs << " * ar); "
                       << V(A, 'i') << " = fma(" << (ni_ ? "-" : "") << sn << ", " << wi << ", " << cs << " * ai);\n";
@@ -594,8 +766,9 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
 
     K.name = name;
     K.threads = (int)TT;
-    K.smem_bytes = (int)((P.dbuf ? 2 : 1) * 16 * nelem);
-    K.param_doubles = std::max(1, P.nm);
+    K.smem_bytes = (int)((P.dbuf ? 2 : 1) * 16 * nelem) + (P.uaccs.empty() ? 0 : 8 * (8 * P.nu + 4 * (int)P.uaccs.size()));
+    K.param_doubles = 1 + std::max(1, P.nm);
+    K.fp64_per_thread = g_fp64_emitted;
     return o.str();
 }
 
@@ -612,7 +785,8 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
     const int nr = std::min(opt_.jit_regbits, always ? t - 1 : t - 5);
     if (nr < (always ? 1 : 3) || t > 13 || (!always && nl_ < opt_.jit_min_qubits)) return false;
     jit::Engine &E = jit::Engine::get();
-    if (!E.available()) {
+    if (dry_) B200_FAIL_IF(!E.nvrtc_available(), "dry run needs NVRTC");
+    else if (!E.available()) {
         B200_FAIL_IF(jit_mode_ == 2, "jit='always' but NVRTC / the driver API could not be loaded");
         return false;
     }
@@ -752,9 +926,12 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
         rem.swap(deferred);
     }
     if (opt_.jit_factor) factor_scales(P);
+    P.uniform = opt_.jit_uniform;
+    analyze_uniform(P);
     for (JRound &R : P.rounds)
         for (JOp &o : R.ops) {
             o.cls = 0;
+            if (o.uacc >= 0) continue; // its values travel in the uniform table, below
             o.moff = (int)mvals.size();
             if (o.kind == (int)GateOp::DENSE) mvals.insert(mvals.end(), o.dvals.begin(), o.dvals.end());
             else {
@@ -762,15 +939,38 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
                 for (int q = 0; q < o.nm; q++) mvals.push_back(o.vals[q]);
             }
         }
+    // uniform table: entries of one accumulator are contiguous; 8 doubles per op =
+    // { predicate mask, predicate value, z mask (bit patterns), 0, e0.re, e0.im, e1.re, e1.im }
+    P.uoff = (int)mvals.size();
+    if (!P.uaccs.empty()) {
+        mvals.resize((size_t)P.uoff + 8 * (size_t)P.nu, 0.0);
+        std::vector<int> fill(P.uaccs.size(), 0);
+        for (JRound &R : P.rounds)
+            for (JOp &o : R.ops) {
+                if (o.uacc < 0) continue;
+                const int e = P.uaccs[(size_t)o.uacc].first + fill[(size_t)o.uacc]++;
+                double *dst = &mvals[(size_t)P.uoff + 8 * (size_t)e];
+                const uint64_t zm = o.kind == (int)GateOp::PARITY ? o.zo : 0ull;
+                std::memcpy(dst + 0, &o.co_m, 8);
+                std::memcpy(dst + 1, &o.co_v, 8);
+                std::memcpy(dst + 2, &zm, 8);
+                dst[4] = o.vals[0];
+                dst[5] = o.vals[1];
+                dst[6] = o.kind == (int)GateOp::PARITY ? o.vals[2] : o.vals[0];
+                dst[7] = o.kind == (int)GateOp::PARITY ? o.vals[3] : o.vals[1];
+                o.moff = P.uoff + 8 * e;
+            }
+    }
     P.nm = (int)mvals.size();
-    if (P.nm * 8 + 16 > 32000) return false; // kernel parameter block limit
+    if (P.nm * 8 + 24 > 32000) return false; // kernel parameter block limit
 
     // structural key
     std::string key;
     key.reserve(64 + 64 * ops.size());
-    put(key, (int)7); // generator version
+    put(key, (int)9); // generator version
     put(key, P.fuse_diag);
-    put(key, P.t); put(key, P.c); put(key, P.nr); put(key, P.nl); put(key, P.dbuf); put(key, P.rank_base);
+    put(key, P.uniform);
+    put(key, P.t); put(key, P.c); put(key, P.nr); put(key, P.nl); put(key, P.dbuf);
     for (int h : P.high) put(key, (uint8_t)h);
     for (const JRound &R : P.rounds) {
         put(key, (uint32_t)0xffffffffu);
@@ -779,16 +979,38 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
             put(key, (uint8_t)o.kind); put(key, (uint8_t)o.ny);
             put(key, o.x); put(key, o.a); put(key, o.b); put(key, o.cin_m); put(key, o.cin_v);
             put(key, o.co_m); put(key, o.co_v); put(key, o.zin); put(key, o.zo); put(key, o.cls);
+            put(key, (int16_t)o.uacc);
             for (int tb : o.tg) put(key, (uint8_t)tb);
         }
     }
-    const jit::Kernel *K = E.lookup(cuda_device_, key, jit_mode_ == 2 ? 1 : opt_.jit_threshold, jit_mode_ == 2,
-                                    [&](jit::Kernel &k) {
-                                        const uint64_t h = std::hash<std::string>{}(key);
-                                        char name[64];
-                                        snprintf(name, sizeof name, "k_pass_%016llx", (unsigned long long)h);
-                                        return generate(P, k, name);
-                                    });
+    auto gen = [&](jit::Kernel &k) {
+        const uint64_t h = std::hash<std::string>{}(key);
+        char name[64];
+        snprintf(name, sizeof name, "k_pass_%016llx", (unsigned long long)h);
+        return generate(P, k, name);
+    };
+    if (dry_) { // development: compile to a cubin once per structure, launch nothing
+        static std::map<std::string, double> seen;
+        auto it = seen.find(key);
+        if (it == seen.end()) {
+            jit::Kernel k;
+            std::string src;
+            B200_FAIL_IF(!E.compile_offline(key, gen, k, src), "dry run: NVRTC failed: " + k.error);
+            it = seen.emplace(key, k.fp64_per_thread * (double)k.threads).first;
+            if (std::getenv("B200SV_JIT_VERBOSE"))
+                fprintf(stderr, "[b200sv dry] %s: t=%d c=%d rounds=%zu ops=%zu fp64/thread=%.0f %.0f ms\n", k.name.c_str(), t, c,
+                        P.rounds.size(), ops.size(), k.fp64_per_thread, k.compile_ms);
+        }
+        stats_.tile_passes++;
+        stats_.jit_passes++;
+        stats_.kernel_ops += (int64_t)ops.size();
+        stats_.rounds += (int64_t)P.rounds.size();
+        stats_.fp64_ops += it->second * (double)(1ull << (nl_ - t));
+        return true;
+    }
+    // a state of >= 1 GiB pays ~20 ms per interpreted pass: compile at the first sighting (in the background)
+    const int threshold = jit_mode_ == 2 ? 1 : (nl_ >= 26 ? 1 : opt_.jit_threshold);
+    const jit::Kernel *K = E.lookup(cuda_device_, key, threshold, jit_mode_ == 2, gen);
     if (!K) {
         B200_FAIL_IF(jit_mode_ == 2, "jit='always': specialised pass failed to compile (set B200SV_JIT_VERBOSE=1)");
         return false;
@@ -797,12 +1019,17 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
     uint64_t grid = (uint64_t)E.sm_count(cuda_device_) * (uint64_t)K->ctas_per_sm;
     if (grid > ntiles) grid = ntiles;
     if (mvals.empty()) mvals.push_back(0.0);
-    const int rc = E.launch(*K, (unsigned)grid, vec, mvals.data(), stream_);
+    std::vector<double> blk(1 + mvals.size());
+    std::memcpy(&blk[0], &rank_base_, sizeof(double)); // Params::rank_base
+    std::memcpy(&blk[1], mvals.data(), mvals.size() * sizeof(double));
+    const int rc = E.launch(*K, (unsigned)grid, vec, blk.data(), stream_);
     B200_FAIL_IF(rc != 0, "cuLaunchKernel of a specialised pass failed with driver error " + std::to_string(rc));
     stats_.tile_passes++;
     stats_.jit_passes++;
     stats_.kernel_ops += (int64_t)ops.size();
     stats_.rounds += (int64_t)P.rounds.size();
+    stats_.fp64_ops += K->fp64_per_thread * (double)K->threads * (double)ntiles;
+    stats_.h2d_bytes += (double)(8 + blk.size() * sizeof(double)); // the kernel parameter block
     return true;
 }
 
@@ -814,6 +1041,7 @@ b200sv_stats Simulator::stats() const
         s.jit_compiled = c.compiled;
         s.jit_pending = c.pending;
         s.jit_compile_ms = c.compile_ms;
+        s.jit_disk_hits = c.disk_hits;
     }
     return s;
 }

@@ -15,6 +15,7 @@
 //    stall samples sat on the tile's global loads -> the next tile is prefetched with cp.async into
 //    a second shared-memory buffer while the current one is processed.
 #include <atomic>
+#include <mutex>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -338,31 +339,38 @@ template <int NOPS, int NROUNDS>
 static int launch3(double *psi, const B200k2Header *hdr, const B200k3Round *rounds, const B200k3Op *ops,
                    cudaStream_t st)
 {
-    // resident CTAs per SM for [double-buffered?][tile bits]
-    static int grid_per_sm[2][B200K_MAX_TILE_BITS + 1];
-    static int sm_count = 0;
-    // function attributes are per device: one bit per CUDA ordinal (ranks of one process may sit on
-    // different GPUs)
-    static std::atomic<unsigned long long> attr_mask{0}; // threads of one process may launch concurrently
+    // Per CUDA device (ranks of one process may sit on different GPUs and launch concurrently): function
+    // attributes, SM count and resident CTAs per SM for [double-buffered?][tile bits].  A slot is filled under
+    // the mutex and published with a release store; later launches only read it after the acquire load.
+    struct PerDevice {
+        std::atomic<int> ready{0};
+        int sm_count = 0;
+        int grid_per_sm[2][B200K_MAX_TILE_BITS + 1];
+    };
+    static PerDevice per_device[64];
+    static std::mutex init_mu;
     int cur_dev = 0;
     cudaGetDevice(&cur_dev);
-    const bool attr_set = (attr_mask.load(std::memory_order_acquire) >> (cur_dev & 63)) & 1ull;
+    PerDevice &D = per_device[cur_dev & 63];
     auto kern = k_tile3<NOPS, NROUNDS>;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)(2 * sizeof(cplx) << B200K_MAX_TILE_BITS));
-        if (e != cudaSuccess) return (int)e;
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
-        for (int d = 0; d < 2; d++)
-            for (int t = 0; t <= B200K_MAX_TILE_BITS; t++) {
-                int nb = 0;
-                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, TT, (size_t)(d + 1) * (sizeof(cplx) << t));
-                grid_per_sm[d][t] = nb;
-            }
-        attr_mask.fetch_or(1ull << (cur_dev & 63), std::memory_order_release);
+    if (!D.ready.load(std::memory_order_acquire)) {
+        std::lock_guard<std::mutex> lk(init_mu);
+        if (!D.ready.load(std::memory_order_relaxed)) {
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (int)(2 * sizeof(cplx) << B200K_MAX_TILE_BITS));
+            if (e != cudaSuccess) return (int)e;
+            cudaDeviceGetAttribute(&D.sm_count, cudaDevAttrMultiProcessorCount, cur_dev);
+            for (int d = 0; d < 2; d++)
+                for (int t = 0; t <= B200K_MAX_TILE_BITS; t++) {
+                    int nb = 0;
+                    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, TT, (size_t)(d + 1) * (sizeof(cplx) << t));
+                    D.grid_per_sm[d][t] = nb;
+                }
+            D.ready.store(1, std::memory_order_release);
+        }
     }
+    const int sm_count = D.sm_count;
+    const auto &grid_per_sm = D.grid_per_sm;
     Prog3<NOPS, NROUNDS> P;
     P.h = *hdr;
     for (int i = 0; i < hdr->n_rounds; i++) P.rounds[i] = rounds[i];

@@ -136,11 +136,25 @@ typedef struct b200sv_stats {
     double jit_compile_ms;    /* process-wide: NVRTC time spent so far (sum over pool threads) */
     int64_t p2p_exchanges;    /* qubit swaps that ran as in-place kernels over mapped peer memory */
     int64_t relabelled_swaps; /* uncontrolled SWAP gates executed as wire relabelling (no data movement) */
+    double swap_device_ms;    /* CUDA-event time of the global<->local qubit swaps (timing on), part of gate_device_ms */
+    double fp64_ops;          /* thread-level FP64 instructions the specialised passes issued (upper bound:
+                                 run-time-conditional op bodies are counted as taken) */
+    int64_t jit_disk_hits;    /* process-wide: specialised kernels loaded from the on-disk cubin cache */
+    int64_t swap_push_exchanges; /* qubit swaps that ran as ONE push kernel writing into every peer's shard */
+    double d2h_bytes;         /* result bytes copied device -> host (State, Probs, Sample indices, scalars excluded) */
+    double h2d_bytes;         /* bytes copied host -> device (kernel parameter blocks, matrices, sampler uniforms, SetState) */
 } b200sv_stats;
 int b200sv_get_stats(b200sv_device *d, b200sv_stats *out);
 int b200sv_reset_stats(b200sv_device *d);
 int b200sv_set_timing(b200sv_device *d, int on); /* record CUDA events around each flush */
 int b200sv_flush(b200sv_device *d);              /* launch everything queued (no host sync) */
+/* Thread-level FP64 FMA instructions per second this GPU sustains (microbenchmark, ~20 ms): the second
+ * roofline of a fused tile pass next to the HBM bandwidth. */
+int b200sv_fp64_peak(b200sv_device *d, double *dfma_per_second);
+/* Counters as one JSON object (the role of the reference's ResourceTracker output,
+ * runtime/lib/backend/null_qubit/NullQubit.hpp:104-112): gates, passes, swaps, launches, JIT.
+ * Returns the length written (excluding the terminating 0), or -1 if `cap` is too small. */
+int64_t b200sv_stats_json(b200sv_device *d, char *buf, int64_t cap);
 int b200sv_synchronize(b200sv_device *d);        /* flush + wait */
 /* Tile passes whose structure recurs are compiled at run time into specialised kernels (kwarg
  * 'jit': 'off' | 'auto' (default) | 'always'; catalyst_b200/csrc/jit.hpp).  In 'auto' mode the

@@ -70,48 +70,13 @@ typedef struct B200kTileProgram {
 
 int b200k_tile_program(double *psi, int n_local, const B200kTileProgram *prog, void *stream);
 
-/* ---- fused tile pass, second generation (tile2.cu) ---------------------------------------------
- * Same tile geometry, but the CTAs are persistent (grid = a multiple of the SM count, striding over
- * the tiles) and the op list is grouped by the host into ROUNDS.  In a register round every thread
- * owns the 8 amplitudes spanned by three tile bits (rb[0..2]) and applies all of the round's ops
- * to them in registers: one shared-memory read+write per round instead of per op, no index
- * arithmetic per amplitude (all bit positions are precomputed on the host).  Shared memory is
- * XOR-swizzled so that any choice of the three bits is bank-conflict free.  Ops a register round
- * cannot express (two-pattern PAIR, PAULIROT) run as single-op shared-memory rounds. */
-enum {
-    B200K2_PAIR1 = 0,    /* 2x2 matrix on register bit j (controls anywhere)        */
-    B200K2_PHASE = 1,
-    B200K2_PARITY = 2,
-    B200K2_PAIRG = 3,    /* shared-memory round: general PAIR (patterns a, b)       */
-    B200K2_PAULIROT = 4  /* shared-memory round                                      */
-};
-enum { B200K2_M_GENERAL = 0, B200K2_M_REAL = 1, B200K2_M_SWAP = 2 };
+/* ---- shared by the register-blocked tile kernels --------------------------------------------------
+ * The CTAs are persistent (grid = a multiple of the SM count, striding over the tiles) and the op list is
+ * grouped by the host into ROUNDS.  In a register round every thread owns the 8 amplitudes spanned by
+ * three tile bits and applies all of the round's ops to them in registers: one shared-memory read+write
+ * per round instead of per op.  Shared memory is XOR-swizzled so that any choice of the three bits is
+ * bank-conflict free.  Ops a register round cannot express run as single-op shared-memory rounds. */
 enum { B200K2_ROUND_REG = 0, B200K2_ROUND_SMEM = 1 };
-
-typedef struct B200k2Op {  /* 128 bytes */
-    uint8_t kind, j, mflag, ny;
-    uint8_t rc_mask, rc_val; /* control predicate over the 3 register bits            */
-    uint8_t rz_mask, pad0;   /* PARITY: z mask over the 3 register bits               */
-    uint32_t tc_mask, tc_val; /* control predicate over the other tile-local bits (for shared-memory
-                                 rounds: over all tile-local bits)                    */
-    uint32_t tz_mask;         /* PARITY/PAULIROT: z mask, same convention             */
-    uint32_t tmask, a, b;     /* shared-memory rounds: tile-local target mask / patterns */
-    uint32_t pos[4];          /* shared-memory rounds: ascending positions of tmask bits (PAULIROT: top x bit) */
-    uint32_t npos;
-    uint64_t co_mask, co_val; /* control predicate on the bits outside the tile       */
-    uint64_t zo_mask;         /* z mask outside the tile                              */
-    double m[8];
-} B200k2Op;
-
-typedef struct B200k2Round {
-    uint8_t kind, rb0, rb1, rb2;
-    uint16_t first, count;
-} B200k2Round;
-
-#define B200K2_SMALL_OPS 24
-#define B200K2_SMALL_ROUNDS 16
-#define B200K2_LARGE_OPS 216
-#define B200K2_LARGE_ROUNDS 128
 
 typedef struct B200k2Header {
     int32_t n_rounds, n_ops;
@@ -121,13 +86,9 @@ typedef struct B200k2Header {
     uint64_t ntiles;
 } B200k2Header;
 
-/* rounds[n_rounds], ops[n_ops] are copied into the kernel's parameter block (<= 32 KB). */
-int b200k_tile_program2(double *psi, int n_local, const B200k2Header *hdr, const B200k2Round *rounds,
-                        const B200k2Op *ops, void *stream);
-
 /* ---- fused tile pass, third generation (tile3.cu) ------------------------------------------------
- * Same tile geometry and round structure as the second generation; what changed follows the ncu
- * reading of k_tile2 (profiles/README.md: issue-bound on per-op decode, not on HBM or FP64):
+ * What it does follows the ncu reading of its predecessor (profiles/README.md r1_v2: issue-bound on
+ * per-op decode, not on HBM or FP64):
  *   - tile load/store offsets are precomputed once per thread (persistent CTAs), not per amplitude;
  *   - a round's eight shared-memory slots are SW(thread base) ^ swz[a] (the XOR swizzle is linear),
  *   - every op carries host-precomputed SLOT MASKS over the thread's 8 registers instead of
@@ -182,7 +143,6 @@ typedef struct B200k3Round { /* 24 bytes */
 #define B200K3_LARGE_OPS 215 /* + 1 readable pad entry for the control-word prefetch */
 #define B200K3_LARGE_ROUNDS 128
 
-/* header is shared with the second generation (B200k2Header) */
 int b200k_tile_program3(double *psi, int n_local, const struct B200k2Header *hdr, const B200k3Round *rounds,
                         const B200k3Op *ops, void *stream);
 
@@ -275,6 +235,10 @@ int b200k_swap_p2p(double *mine, double *peer, const uint8_t *lpos, int m, uint3
 
 /* ---- alias-method sampler on device (reference algorithm: Walker alias table with LIFO pairing,
  * SURVEY.md Appendix A.4; restated as prefix sums so that no sequential pass over 2^n is needed) */
+/* FP64 pipe microbenchmark: thread-level DFMA instructions per second this GPU sustains (16 independent
+ * chains per thread, full occupancy); `scratch` = any device buffer of >= 8 bytes.  Synchronises. */
+int b200k_dfma_peak(double *scratch, double *dfma_per_second, void *stream);
+
 int64_t b200k_sampler_scratch_doubles(int64_t nbins);
 int b200k_sampler_prepare(const double *probs, int64_t nbins, double *scratch, void *stream);
 /* u: 2*nshots uniforms (u1,u2 per shot) on device; out_idx: nshots int64 on device */

@@ -203,3 +203,68 @@ def test_jit_sharded_virtual_ranks(gpu, oracle_mod):
     for st, jp in res:
         assert np.max(np.abs(st - ref)) < TOL
         assert jp > 0
+
+
+# ---- tile-uniform diagonal factors (UAcc in simulator_jit.cpp) -----------------------------------------------
+DIAG_MIX = ["ControlledPhaseShift", "CZ", "RZ", "IsingZZ", "MultiRZ", "PhaseShift", "T", "S", "CRZ", "PCPhase",
+            "GlobalPhase", "Hadamard", "RX", "CNOT"]
+
+
+@pytest.mark.parametrize("uniform", [0, 1])
+@pytest.mark.parametrize("n,tile_bits,seed", [(14, 8, 1), (17, 9, 2), (20, 11, 3)])
+def test_jit_uniform_diagonal_factors(gpu, oracle_mod, n, tile_bits, seed, uniform):
+    """Long fans of diagonal ops whose predicates / parities sit on bits OUTSIDE the tile (incl. negative control
+    values, parity over several outside bits, controlled parities): evaluated once per tile by a lane group
+    (jit_uniform=1) they must equal the per-thread evaluation (jit_uniform=0) and the oracle."""
+    rng = np.random.default_rng(seed)
+    ops = []
+    for j in range(0, n, 3):                                   # QFT-like fans: H(j) then phases controlled on every other wire
+        ops.append(("Hadamard", [], [j]))
+        for k in range(n):
+            if k != j:
+                ops.append(("ControlledPhaseShift", [float(rng.uniform(0, 6))], [k, j]))
+        for k in range(0, n, 2):
+            if k != j:
+                ops.append(("PhaseShift", [float(rng.uniform(0, 6))], [j],
+                            {"ctrl_wires": [k], "ctrl_values": [bool(rng.integers(2))]}))
+        ws = [int(w) for w in rng.permutation(n)[:4]]
+        ops.append(("MultiRZ", [float(rng.uniform(0, 6))], ws))
+        ops.append(("IsingZZ", [float(rng.uniform(0, 6))], ws[:2]))
+        ops.append(("RZ", [float(rng.uniform(0, 6))], [ws[2]], {"ctrl_wires": [ws[3]], "ctrl_values": [True]}))
+    ops += random_circuit(seed, n, 150, names=DIAG_MIX)
+    d, err = _run(gpu, oracle_mod, n, ops, init=random_state(seed, n), jit_uniform=uniform, tile_bits=tile_bits,
+                  jit_regbits=3 if tile_bits == 8 else 4)
+    s = d.stats()
+    assert s.jit_passes == s.tile_passes > 0
+    assert err < TOL, err
+
+
+def test_jit_disk_cache_across_processes(tmp_path):
+    """A second PROCESS that meets the same pass structures loads the cubins from $B200SV_JIT_CACHE at the first
+    sighting: nothing is compiled and every pass runs specialised."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    prog = (
+        "import sys, json; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "from catalyst_b200 import capi, workloads\nfrom dsl import apply_ops\n"
+        "d = capi.B200Device(16, jit_min_qubits=10, jit_threshold=1)\n"
+        "apply_ops(d, workloads.c3_qft_random(16, layers=3)); d.synchronize(); d.jit_wait()\n"
+        "d.set_basis_state([0]*16, list(range(16))); apply_ops(d, workloads.c3_qft_random(16, layers=3)); st = d.state()\n"
+        "s = d.stats()\n"
+        "print(json.dumps({'compiled': s.jit_compiled, 'disk': s.jit_disk_hits, 'jit_passes': s.jit_passes,\n"
+        "                  'tile_passes': s.tile_passes, 'norm': float(abs((st.conj()*st).sum())), 'a0': [st[5].real, st[5].imag]}))\n"
+    ) % (root, os.path.join(root, "tests"))
+    env = dict(os.environ, B200SV_JIT_CACHE=str(tmp_path / "cache"), B200SV_JIT="auto")
+    runs = []
+    for _ in range(2):
+        out = subprocess.run([sys.executable, "-c", prog], env=env, capture_output=True, text=True, timeout=600)
+        assert out.returncode == 0, out.stderr[-2000:]
+        runs.append(json.loads(out.stdout.strip().splitlines()[-1]))
+    first, second = runs
+    assert first["compiled"] > 0 and first["disk"] == 0
+    assert second["compiled"] == 0 and second["disk"] == first["compiled"]
+    assert second["jit_passes"] == second["tile_passes"], "the second process must run specialised from its first pass"
+    assert abs(second["norm"] - 1.0) < 1e-12 and second["a0"] == first["a0"]

@@ -515,3 +515,31 @@ def test_swap_relabelling_with_tape_and_dynamic_qubits(gpu, oracle_mod):
     o2 = oracle_mod.OracleDevice(4)
     apply_ops(o2, [("Hadamard", [], [0]), ("SWAP", [], [0, 2]), ("CNOT", [], [2, 1]), ("CNOT", [], [1, 3])])
     assert np.max(np.abs(o2.state() - d2.state())) < TOL
+
+
+def test_many_large_matrix_operations_do_not_wrap_the_arena(gpu, oracle_mod):
+    """Five back-to-back 10-wire QubitUnitary ops (16 MiB each) exceed the 64 MiB device matrix arena: the pass
+    must be closed before the arena wraps, not overwrite the first matrix."""
+    from dsl import random_unitary
+    n = 11
+    rng = np.random.default_rng(5)
+    mats = [random_unitary(rng, 10) for _ in range(5)]
+    o, d = oracle_mod.OracleDevice(n), gpu.B200Device(n)
+    for dev in (o, d):
+        dev.named_op("Hadamard", [], [0])
+        for i, m in enumerate(mats):
+            wires = [int(w) for w in np.roll(np.arange(n), i)[:10]]
+            dev.matrix_op(m, wires)
+    assert np.max(np.abs(o.state() - d.state())) < 1e-12
+
+
+def test_stats_json_and_fp64_peak(gpu):
+    d = gpu.B200Device(12, jit="always")
+    for w in range(12):
+        d.named_op("RX", [0.1 * w], [w])
+    d.synchronize()
+    js = d.stats_json()
+    assert js["num_qubits"] == 12 and js["num_gates"] == 12 and js["tile_passes"] >= 1
+    assert js["specialised_passes"] == js["tile_passes"] and js["fp64_instructions"] > 0
+    rate = d.fp64_peak()
+    assert 1e12 < rate < 1e14, rate       # B200: 148 SMs x 64 FP64 lanes x ~1.9 GHz = 1.8e13 DFMA/s

@@ -152,3 +152,128 @@ def test_runtime_adjoint_gradient(rt, oracle_mod, n, seed):
     if jo.shape[1] >= 2:
         sub = [0, jo.shape[1] - 1]
         assert np.max(np.abs(d.gradient(len(obs_list), jo.shape[1], train=sub) - jo[:, sub])) < TOL * 10
+
+
+# ---- DataView strides and offsets (runtime/include/DataView.hpp:124-134, row t1 of SURVEY.md 8(a)) --------
+def _strided_memref(M, ctype, base, offset, sizes, strides):
+    """A memref descriptor over `base` (1-D numpy array of the element type) with an explicit element
+    offset and element strides, as MLIR hands non-contiguous views to the runtime (Types.h:84-150)."""
+    m = M()
+    p = base.ctypes.data_as(rt_driver.C.POINTER(ctype))
+    m.allocated, m.aligned, m.offset = p, p, offset
+    for i, (sz, st) in enumerate(zip(sizes, strides)):
+        m.sizes[i] = sz
+        m.strides[i] = st
+    return m
+
+
+def test_runtime_strided_and_offset_memrefs(rt, oracle_mod):
+    """State, Probs, PartialProbs, Sample, Gradient and SetState through views with offset != 0 and
+    stride != 1: every element must land where the DataView says, and nothing else may be written."""
+    C = rt_driver.C
+    n, shots = 6, 200
+    ops = random_circuit(21, n, 40)
+    init = random_state(5, n)
+    o = oracle_mod.OracleDevice(n, seed=11)
+    d = rt(n, seed=11, shots=shots)
+    L = d.L
+    # SetState from a strided complex view: element i at base[3 + 2 i]
+    src = np.full(3 + 2 * (1 << n), 7.0 + 7.0j, dtype=np.complex128)
+    src[3::2][:1 << n] = init
+    cplx_t = C.c_double * 2
+    mr = _strided_memref(rt_driver._memref(cplx_t, 1), cplx_t, src.view(np.float64).reshape(-1, 2), 3, [1 << n], [2])
+    L.qis__SetState(C.byref(mr), C.c_uint64(n), *[d.q[w] for w in range(n)])
+    o.set_state(init, list(range(n)))
+    apply_ops(o, ops)
+    apply_ops(d, ops)
+    # State into base[5 + 3 i]
+    SENT = -123.0 - 456.0j
+    dst = np.full(5 + 3 * (1 << n), SENT, dtype=np.complex128)
+    mr = _strided_memref(rt_driver._memref(cplx_t, 1), cplx_t, dst.view(np.float64).reshape(-1, 2), 5, [1 << n], [3])
+    L.qis__State(C.byref(mr), C.c_int64(0))
+    want = o.state()
+    assert np.max(np.abs(dst[5::3][:1 << n] - want)) < TOL
+    mask = np.ones(dst.size, dtype=bool)
+    mask[5 + 3 * np.arange(1 << n)] = False
+    assert np.all(dst[mask] == SENT), "State wrote outside the view"
+    # Probs (all wires) into base[1 + 4 i]; PartialProbs on 3 wires into base[2 + 5 i]
+    pd = np.full(1 + 4 * (1 << n), -1.0)
+    mr = _strided_memref(rt_driver.MR_d1, C.c_double, pd, 1, [1 << n], [4])
+    L.qis__Probs(C.byref(mr), C.c_int64(0))
+    assert np.max(np.abs(pd[1::4][:1 << n] - o.probs())) < TOL
+    assert np.count_nonzero(pd == -1.0) == pd.size - (1 << n)
+    w = [4, 0, 2]
+    pp = np.full(2 + 5 * 8, -1.0)
+    mr = _strided_memref(rt_driver.MR_d1, C.c_double, pp, 2, [8], [5])
+    L.qis__Probs(C.byref(mr), C.c_int64(3), *[d.q[x] for x in w])
+    assert np.max(np.abs(pp[2::5][:8] - o.probs(w))) < TOL
+    # Sample into a column-major-like 2-D view: element (s, k) at base[7 + s * 2 + k * (2 * shots + 3)]
+    st1 = 2 * shots + 3
+    sd = np.full(7 + 2 * shots + n * st1, -1.0)
+    mr = _strided_memref(rt_driver.MR_d2, C.c_double, sd, 7, [shots, n], [2, st1])
+    L.qis__Sample(C.byref(mr), C.c_int64(0))
+    got = np.array([[sd[7 + s * 2 + k * st1] for k in range(n)] for s in range(shots)])
+    assert np.array_equal(got, o.sample(shots))
+    assert np.count_nonzero(sd == -1.0) == sd.size - shots * n
+
+
+def test_runtime_strided_gradient(rt, oracle_mod):
+    C = rt_driver.C
+    n = 5
+    ops = [("RX", [0.3], [0]), ("RY", [1.1], [1]), ("CNOT", [], [0, 2]), ("IsingZZ", [0.7], [1, 3]), ("CRX", [-0.4], [2, 4]),
+           ("RZ", [2.2], [4])]
+    obs_list = [("N", "PauliZ", 2), ("T", [("N", "PauliX", 1), ("N", "PauliY", 4)])]
+    o = oracle_mod.OracleDevice(n)
+    o.start_tape()
+    apply_ops(o, ops)
+    for ob in obs_list:
+        o.expval(build_obs(o, ob))
+    o.stop_tape()
+    jo = o.gradient()
+    d = rt(n)
+    d.start_tape()
+    apply_ops(d, ops)
+    for ob in obs_list:
+        d.expval(build_obs(d, ob))
+    d.stop_tape()
+    P = jo.shape[1]
+    rows = [np.full(4 + 3 * P, -9.0) for _ in obs_list]
+    mrs = [_strided_memref(rt_driver.MR_d1, C.c_double, r, 4, [P], [3]) for r in rows]
+    d.L.qis__Gradient(C.c_int64(len(obs_list)), *[C.byref(m) for m in mrs])
+    for k, r in enumerate(rows):
+        assert np.max(np.abs(r[4::3][:P] - jo[k])) < TOL * 10
+        assert np.count_nonzero(r == -9.0) == r.size - P
+
+
+# ---- runtime-side wrappers that need nothing new from the device (SURVEY.md 8(f) N4) ------------------
+def test_runtime_mbqc_measure_in_basis(rt, oracle_mod):
+    """__catalyst__mbqc__measure_in_basis (RuntimeCAPI.cpp:1173-1184) is Measure() on the device: same seeded
+    outcomes and the same collapsed state as the oracle's Measure."""
+    C = rt_driver.C
+    n = 5
+    ops = random_circuit(3, n, 25)
+    o = oracle_mod.OracleDevice(n, seed=37)
+    d = rt(n, seed=37)
+    apply_ops(o, ops)
+    apply_ops(d, ops)
+    d.L.mbqc__measure_in_basis.restype = C.POINTER(C.c_bool)
+    for wire, post in [(0, -1), (3, -1), (1, 1), (4, -1)]:
+        r = d.L.mbqc__measure_in_basis(d.q[wire], C.c_uint32(0), C.c_double(0.25), C.c_int32(post))
+        assert bool(r[0]) == o.measure(wire, None if post < 0 else post)
+    assert np.max(np.abs(o.state() - d.state())) < 1e-11
+
+
+def test_runtime_print_state(rt, capfd):
+    """__catalyst__rt__print_state (RuntimeCAPI.cpp:278-290) = State() of the plugin written to stdout."""
+    d = rt(2)
+    d.named_op("Hadamard", [], [0])
+    d.named_op("CNOT", [], [0, 1])
+    d.L.rt__print_state()
+    import ctypes
+    ctypes.CDLL(None).fflush(None)
+    out = capfd.readouterr().out
+    assert "State = [" in out
+    vals = [ln.strip().rstrip(",") for ln in out.splitlines() if ln.strip().startswith("(")]
+    assert len(vals) == 4
+    amps = [complex(*map(float, v.strip("()").split(","))) for v in vals]
+    assert np.allclose(amps, [2 ** -0.5, 0, 0, 2 ** -0.5])

@@ -297,3 +297,31 @@ def test_swap_relabelling_sharded(gpu, oracle_mod, world):
         assert np.max(np.abs(p - want_p)) < TOL and np.max(np.abs(pp - want_pp)) < TOL
         assert np.array_equal(s, want_s)
         assert np.max(np.abs(st - want)) < TOL
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_unseeded_measurement_agrees_across_ranks(gpu, world):
+    """No PRNG set (the reference default, SetDevicePRNG(nullptr)): every rank must still collapse onto the
+    SAME outcome and return the same samples — rank 0's entropy is distributed."""
+    n = 8
+
+    def prog(d, r):
+        d.allocate_qubits(n)                      # note: no seed
+        for w in range(n):
+            d.named_op("Hadamard", [], [w])
+        outs = [d.measure(w) for w in (0, n - 1, 3)]            # wire 0 sits on a rank bit
+        pm = d.pauli_measure("XZ", [1, 2])
+        smp = d.sample(64)
+        st = d.state()
+        return outs, pm, smp, st
+
+    res = gpu.run_spmd(world, prog)
+    for outs, pm, smp, st in res[1:]:
+        assert outs == res[0][0] and pm == res[0][1]
+        assert np.array_equal(smp, res[0][2])
+        assert np.array_equal(st, res[0][3])
+    st = res[0][3]
+    assert abs(np.vdot(st, st).real - 1.0) < 1e-12
+    # the measured wires are frozen at their outcomes
+    for w, m in zip((0, n - 1, 3), res[0][0]):
+        assert np.all(res[0][2][:, w] == float(m))

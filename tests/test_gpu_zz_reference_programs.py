@@ -43,7 +43,8 @@ def test_release_matches_oracle(gpu, oracle_mod, n, seed, cfg):
     """Wires released at every kind of position, in |0> and |1>, on a register whose wires were also
     relabelled by SWAPs; gates, probabilities, samples and further allocations afterwards."""
     rng = np.random.default_rng(seed)
-    o, d = oracle_mod.OracleDevice(n, seed=37), gpu.B200Device(n, seed=37, **cfg)
+    # release_entangled='project': the last leg releases a wire that is NOT in a basis state
+    o, d = oracle_mod.OracleDevice(n, seed=37), gpu.B200Device(n, seed=37, release_entangled="project", **cfg)
     for rnd in range(3):
         ops = random_circuit(100 * seed + rnd, o.n, 30)
         a, b = (int(x) for x in rng.permutation(o.n)[:2])
@@ -70,6 +71,25 @@ def test_release_matches_oracle(gpu, oracle_mod, n, seed, cfg):
         o.named_op("CNOT", [], [0, n - 1]); d.named_op("CNOT", [], [0, n - 1])
         o.release_qubit(n - 1); d.release_qubit(n - 1)
         assert np.max(np.abs(o.state() - d.state())) < 1e-11
+
+
+def test_release_of_entangled_wire_is_an_error_by_default(gpu):
+    """ReleaseQubit presumes a disentangled basis-state qubit; anything else would silently project the rest
+    of the register, so it fails unless the device was created with release_entangled='project'."""
+    d = gpu.B200Device(3)
+    d.named_op("RY", [0.7], [0])
+    d.named_op("CNOT", [], [0, 2])
+    with pytest.raises(RuntimeError, match="not in a basis state"):
+        d.release_qubit(2)
+    assert d.num_qubits() == 3                              # nothing happened
+    d.named_op("CNOT", [], [0, 2])                          # disentangle again: wire 2 back in |0>
+    d.release_qubit(2)
+    assert d.num_qubits() == 2
+    want = np.zeros(4, dtype=complex)
+    want[0], want[2] = np.cos(0.35), np.sin(0.35)
+    assert np.max(np.abs(d.state() - want)) < TOL
+    with pytest.raises(RuntimeError, match="release_entangled"):
+        gpu.B200Device(2, release_entangled="maybe")
 
 
 def test_release_errors(gpu):
