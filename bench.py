@@ -277,7 +277,7 @@ def e2e_plugin_single(args, n, ops, ngates):
         d.probs(out=probs_out)
     ta = (time.perf_counter() - t0) / args.steps
     d.close()
-    lines_a = read_stats_lines(stats_path)[n_before + 1:]
+    lines_a = read_stats_lines(stats_path)[n_before:]
     res["probs_mass"] = float(probs_out.sum())
     # run B: shots = 1e5, Sample of all wires
     d = rt_driver.RuntimeDevice(n, seed=37, shots=SHOTS)
@@ -291,7 +291,7 @@ def e2e_plugin_single(args, n, ops, ngates):
         d.sample(SHOTS, out=sample_out)
     tb = (time.perf_counter() - t0) / args.steps
     d.close()
-    lines_b = read_stats_lines(stats_path)[n_before + 1:]
+    lines_b = read_stats_lines(stats_path)[n_before:]
     os.environ.pop("B200SV_STATS_FILE", None)
     try:
         os.unlink(stats_path)
@@ -299,7 +299,9 @@ def e2e_plugin_single(args, n, ops, ngates):
         pass
 
     def per_step(lines, key):
-        return int(sum(x.get(key, 0.0) for x in lines) / max(1, len(lines)))
+        # the runtime pools device objects: one line per context, written when it is finalized, with the totals
+        # of its (1 untimed + steps timed) programs
+        return int(sum(x.get(key, 0.0) for x in lines) / (args.steps + 1))
     h2d = per_step(lines_a, "h2d_bytes") + per_step(lines_b, "h2d_bytes")
     d2h = per_step(lines_a, "d2h_bytes") + per_step(lines_b, "d2h_bytes")
     res.update({

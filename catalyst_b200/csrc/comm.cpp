@@ -186,6 +186,7 @@ struct NcclApi {
     int (*Send)(const void *, size_t, int, int, nccl_comm, cudaStream_t) = nullptr;
     int (*Recv)(void *, size_t, int, int, nccl_comm, cudaStream_t) = nullptr;
     int (*AllGather)(const void *, void *, size_t, int, nccl_comm, cudaStream_t) = nullptr;
+    int (*CommGetAsyncError)(nccl_comm, int *) = nullptr; // optional (NCCL >= 2.4)
     std::string error;
 };
 
@@ -216,6 +217,7 @@ NcclApi &nccl_api()
         B200_SYM(Recv, "ncclRecv")
         B200_SYM(AllGather, "ncclAllGather")
 #undef B200_SYM
+        api.CommGetAsyncError = reinterpret_cast<decltype(api.CommGetAsyncError)>(dlsym(api.handle, "ncclCommGetAsyncError"));
     });
     return api;
 }
@@ -248,6 +250,7 @@ class NcclComm final : public Comm {
         for (const Xfer &r : recvs) ok(a.Recv(r.ptr, r.bytes, NCCL_INT8, r.peer, comm_, (cudaStream_t)stream), "ncclRecv");
         for (const Xfer &s : sends) ok(a.Send(s.ptr, s.bytes, NCCL_INT8, s.peer, comm_, (cudaStream_t)stream), "ncclSend");
         ok(a.GroupEnd(), "ncclGroupEnd");
+        poll_async("qubit-swap exchange");
     }
     void allgather(const double *send, double *recv, size_t count, void *stream) override
     {
@@ -342,11 +345,26 @@ class NcclComm final : public Comm {
         if (!sync_buf_) cuda_ok(cudaMalloc(&sync_buf_, (size_t)(world_ + 1) * sizeof(double)), "NcclComm sync buffer");
         double *d = static_cast<double *>(sync_buf_);
         ok(nccl_api().AllGather(d, d + 1, 1, NCCL_FLOAT64, comm_, (cudaStream_t)stream), "ncclAllGather (barrier)");
+        poll_async("stream barrier");
     }
 
   private:
     std::map<void *, std::vector<void *>> maps_;
     void *sync_buf_ = nullptr;
+    // Errors of work already enqueued (a peer died, a link went down) surface asynchronously on the
+    // communicator: poll after every data-path call so that the NEXT device call fails with RT_FAIL instead of
+    // the job hanging in a later collective (ncclInProgress = 7 is not an error).
+    void poll_async(const char *where)
+    {
+        NcclApi &a = nccl_api();
+        if (!a.CommGetAsyncError) return;
+        int st = 0;
+        if (a.CommGetAsyncError(comm_, &st) != 0) return;
+        if (st != 0 && st != 7) {
+            const char *m = a.GetErrorString ? a.GetErrorString(st) : "?";
+            throw CommError(std::string("NCCL asynchronous error after ") + where + ": " + m);
+        }
+    }
     void ok(int rc, const char *what)
     {
         if (rc != 0) {

@@ -403,9 +403,28 @@ struct Engine::Impl {
         }
     }
 
+    // The engine is never destroyed (the library may be loaded RTLD_NODELETE), but a process must not run static
+    // destructors (NVRTC's among them) while a pool thread is still inside nvrtcCompileProgram: at exit the pool is
+    // told to stop, queued jobs are dropped and the threads are joined after their current compilation.
+    static void stop_pool_at_exit()
+    {
+        Engine &E = Engine::get();
+        {
+            std::lock_guard<std::mutex> lk(E.p_->mu);
+            E.p_->stop = true;
+            E.p_->jobs.clear();
+        }
+        E.p_->cv_jobs.notify_all();
+        for (auto &t : E.p_->pool)
+            if (t.joinable()) t.join();
+        E.p_->pool.clear();
+    }
+
     void ensure_pool()
     {
         if (!pool.empty()) return;
+        static std::once_flag reg;
+        std::call_once(reg, [] { std::atexit(&Impl::stop_pool_at_exit); });
         unsigned n = std::thread::hardware_concurrency();
         if (const char *s = std::getenv("B200SV_JIT_THREADS")) n = (unsigned)std::atoi(s);
         n = n < 1 ? 1 : (n > 16 ? 16 : n);

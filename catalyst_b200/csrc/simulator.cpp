@@ -8,6 +8,7 @@
 #include "comm.hpp"
 
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h> // header-only; a no-op unless a profiler injects its library
 
 #include <algorithm>
 #include <cmath>
@@ -36,6 +37,11 @@ namespace b200 {
     } while (0)
 
 static const cplx I_(0.0, 1.0);
+
+struct NvtxRange { // ranges per flush / qubit swap / gradient: what nsys or ncu --nvtx groups the launches by
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
 
 class DeviceBuffer {
   public:
@@ -115,6 +121,7 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "jit_uniform") o.jit_uniform = (int)as_int(o.jit_uniform);
         else if (k == "lazy_adjoint") o.lazy_adjoint = as_int(1) != 0;
         else if (k == "p2p_swap") o.p2p_swap = (int)as_int(-1);
+        else if (k == "swap_push") o.swap_push = (int)as_int(-1);
         else if (k == "adaptive_rows") o.adaptive_rows = as_int(1) != 0;
         else if (k == "virtual_swap") o.virtual_swap = as_int(1) != 0;
         else if (k == "batch_overlaps") o.batch_overlaps = as_int(1) != 0;
@@ -178,6 +185,7 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
     if (const char *e = std::getenv("B200SV_JIT_FACTOR")) opt_.jit_factor = std::atoi(e);
     if (const char *e = std::getenv("B200SV_JIT_UNIFORM")) opt_.jit_uniform = std::atoi(e);
     if (const char *e = std::getenv("B200SV_P2P_SWAP")) opt_.p2p_swap = std::atoi(e);
+    if (const char *e = std::getenv("B200SV_SWAP_PUSH")) opt_.swap_push = std::atoi(e);
     if (const char *e = std::getenv("B200SV_MIN_ROW_BITS")) opt_.min_row_bits = std::max(0, std::min(opt_.tile_bits, std::atoi(e)));
     if (const char *e = std::getenv("B200SV_JIT_REGBITS")) opt_.jit_regbits = std::max(1, std::min(5, std::atoi(e)));
     CUDA_CHECK(cudaSetDevice(dev));
@@ -210,6 +218,7 @@ Simulator::~Simulator()
     cudaSetDevice(cuda_device_);
     if (stream_) cudaStreamSynchronize((cudaStream_t)stream_);
     drop_psi_peers();
+    if (stage_peers_ok_ && comm_) comm_->unmap_peers(stage_peers_ptr_); // no rendezvous in a destructor
     psi_.reset();
     psi_keep_.reset();
     tmp_.reset();
@@ -284,40 +293,48 @@ void Simulator::allocate(int64_t n)
 void Simulator::allocate_one()
 {
     if (!psi_) {
+        B200_FAIL_IF(sharded(), "AllocateQubit: the first allocation on a device sharded over " + std::to_string(opt_.world) +
+                                    " ranks must be an array of at least " + std::to_string(2 * g_) + " qubits");
         allocate(1);
         return;
     }
-    B200_FAIL_IF(sharded(), "AllocateQubit: dynamic allocation is not supported on a sharded register");
     flush();
-    auto nb = std::make_unique<DeviceBuffer>(sizeof(cplx) << (n_ + 1));
-    CUDA_CHECK(b200k_append_qubit(nb->d(), psi_->d(), (int)n_, stream_));
+    // The new wire becomes the new LEAST significant logical bit, physically position 0 of every shard: each
+    // rank doubles its own shard (out[2i] = in[i], out[2i+1] = 0), rank bits stay where they are.
+    auto nb = std::make_unique<DeviceBuffer>(sizeof(cplx) << (nl_ + 1));
+    CUDA_CHECK(b200k_append_qubit(nb->d(), psi_->d(), (int)nl_, stream_));
     note_launch();
     CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    drop_psi_peers(); // peers mapped the old allocation (collective: every rank is in this call)
+    psi_keep_.reset();
     psi_ = std::move(nb);
     tmp_.reset();
     acc_.reset();
     n_ += 1;
-    nl_ = n_;
-    pos_.push_back((int)n_ - 1);
-    for (auto &b : wire_bit_) b += 1; // every existing index bit moved up by one
-    wire_bit_.push_back(0);           // the new wire is the new least significant bit
+    nl_ += 1;
+    rank_base_ = (uint64_t)opt_.rank << nl_;
+    for (auto &p : pos_) p += 1;      // every existing logical bit moved up by one physical position ...
+    pos_.insert(pos_.begin(), 0);     // ... and one logical index: the new bit is logical 0 at position 0
+    for (auto &b : wire_bit_) b += 1;
+    wire_bit_.push_back(0);
 }
 
 // ReleaseQubit (reference: runtime/include/QuantumDevice.hpp:144; id bookkeeping of the caller:
 // runtime/lib/backend/common/QubitManager.hpp:124-126 -- the wire leaves, later device indices move down).
 // Composed from the paths the rest of the device already uses: marginal of the wire (read pass), collapse
-// onto its more probable branch with renormalisation (exact for a qubit in a basis state, which is what
-// deallocation requires; a tie keeps |0>), X if that branch was |1>, a SWAP that brings the wire's index
-// bit to the top, and the lower half of the vector is the (n-1)-qubit state.
+// onto its branch with renormalisation, X if that branch was |1>, a SWAP with the qubit that sits on the top
+// LOCAL index position (on a sharded register the executor brings a rank-bit qubit in with one global<->local
+// swap), and the lower half of every shard is the (n-1)-qubit state.
 void Simulator::release_one(int64_t wire)
 {
     B200_FAIL_IF(!psi_, "No qubits allocated");
     B200_FAIL_IF(wire < 0 || wire >= n_, "Invalid wire index " + std::to_string(wire));
-    if (n_ == 1) {
+    if (n_ == 1 && !sharded()) {
         release();
         return;
     }
-    B200_FAIL_IF(sharded(), "ReleaseQubit: dynamic release is not supported on a sharded register");
+    B200_FAIL_IF(sharded() && n_ - 1 < 2 * g_, "ReleaseQubit: a register sharded over " + std::to_string(opt_.world) +
+                                                   " ranks keeps at least " + std::to_string(2 * g_) + " qubits");
     B200_FAIL_IF(recording_, "ReleaseQubit: not supported while the tape is recording");
     double p[2];
     probs({wire}, p, 1); // flushes the queue
@@ -333,28 +350,61 @@ void Simulator::release_one(int64_t wire)
     note_launch();
     std::vector<GateOp> ops;
     if (keep) canonicalize(ops, "PauliX", {}, {wire}, false, {}, {}, "");
-    const int top = (int)n_ - 1;
-    if (wire_bit_[(size_t)wire] != top) {
+    const int top_pos = (int)nl_ - 1; // top LOCAL physical position
+    auto holder_of_top = [&]() {
+        int q_top = -1;
+        for (int q = 0; q < (int)n_; q++)
+            if (pos_[q] == top_pos) q_top = q;
+        return q_top;
+    };
+    int q_top = holder_of_top();
+    if (wire_bit_[(size_t)wire] != q_top) {
         int64_t v = -1;
         for (int64_t u = 0; u < n_; u++)
-            if (wire_bit_[(size_t)u] == top) v = u;
-        canonicalize(ops, "SWAP", {}, {wire, v}, false, {}, {}, ""); // exchanges the contents of the two bits
+            if (wire_bit_[(size_t)u] == q_top) v = u;
+        canonicalize(ops, "SWAP", {}, {wire, v}, false, {}, {}, ""); // exchanges the contents of the two logical bits
         std::swap(wire_bit_[(size_t)wire], wire_bit_[(size_t)v]);    // ... and the labels
     }
     if (!ops.empty()) enqueue(std::move(ops));
     flush();
-    const size_t bytes = sizeof(cplx) << (n_ - 1);
+    // a global<->local swap during the flush may have moved another logical bit onto the top local position
+    q_top = holder_of_top();
+    if (wire_bit_[(size_t)wire] != q_top) {
+        // (only reachable on a sharded register) the SWAP gate left the wire's logical bit elsewhere: bring it to
+        // the top local position physically
+        const int lw = wire_bit_[(size_t)wire];
+        std::vector<GateOp> more;
+        int64_t v = -1;
+        for (int64_t u = 0; u < n_; u++)
+            if (wire_bit_[(size_t)u] == q_top) v = u;
+        make_local({psi_->d()}, pos_, (1ull << lw) | (1ull << q_top));
+        canonicalize(more, "SWAP", {}, {wire, v}, false, {}, {}, "");
+        std::swap(wire_bit_[(size_t)wire], wire_bit_[(size_t)v]);
+        enqueue(std::move(more));
+        flush();
+        q_top = holder_of_top();
+        B200_FAIL_IF(wire_bit_[(size_t)wire] != q_top, "internal: ReleaseQubit could not bring the wire to the top local bit");
+    }
+    const size_t bytes = sizeof(cplx) << (nl_ - 1);
     auto nb = std::make_unique<DeviceBuffer>(bytes);
     CUDA_CHECK(cudaMemcpyAsync(nb->p(), psi_->p(), bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
     CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
+    drop_psi_peers();
+    psi_keep_.reset();
     psi_ = std::move(nb);
     tmp_.reset();
     acc_.reset();
     probs_buf_.reset();
+    // logical bit q_top (physical position top_pos) leaves: higher logical bits and higher positions move down
+    pos_.erase(pos_.begin() + q_top);
+    for (auto &pp : pos_)
+        if (pp > top_pos) pp -= 1;
+    wire_bit_.erase(wire_bit_.begin() + wire);
+    for (auto &bq : wire_bit_)
+        if (bq > q_top) bq -= 1;
     n_ -= 1;
-    nl_ = n_;
-    pos_.pop_back();
-    wire_bit_.erase(wire_bit_.begin() + wire); // held the top bit: the rest is a permutation of 0..n-2
+    nl_ -= 1;
+    rank_base_ = (uint64_t)opt_.rank << nl_;
 }
 
 void Simulator::release()
@@ -860,6 +910,7 @@ void Simulator::flush()
         return;
     }
     CUDA_CHECK(cudaSetDevice(cuda_device_));
+    NvtxRange nvtx("b200sv::flush");
     std::vector<GateOp> ops;
     ops.swap(queue_);
     if (timing_) CUDA_CHECK(cudaEventRecord((cudaEvent_t)ev0_, (cudaStream_t)stream_));
@@ -1173,6 +1224,7 @@ void Simulator::swap_bits_impl(const std::vector<double *> &vecs, std::vector<in
 {
     const int m = (int)pairs.size();
     if (m == 0) return;
+    NvtxRange nvtx("b200sv::qubit_swap");
     B200_FAIL_IF(m > 8 || m > g_, "internal: too many bits in one swap");
     std::sort(pairs.begin(), pairs.end(), [](auto &x, auto &y) { return x.second < y.second; });
     uint8_t lpos[8];
@@ -1225,6 +1277,70 @@ void Simulator::swap_bits_impl(const std::vector<double *> &vecs, std::vector<in
         }
         return;
     }
+    // Push path (default over NCCL process groups): every rank maps its peers' receive staging once; per chunk
+    // ONE kernel reads this rank's sub-blocks and writes them straight into all peers' staging over NVLink while
+    // it scatters the previously received chunk into the slots that chunk vacated; a stream-ordered rendezvous
+    // separates the rounds.  Against the staged path below: no pack pass, no send-side staging, no NCCL transfer.
+    const bool want_push = opt_.swap_push == 1 || (opt_.swap_push < 0 && std::string(comm_->kind()) == "nccl");
+    if (want_push && npat - 1 <= (uint32_t)B200K_PUSH_MAX_PEERS) {
+        const uint64_t budget = ((uint64_t)opt_.stage_mib << 20) / sizeof(cplx);
+        uint64_t chunk = budget / (2ull * (npat - 1));
+        if (chunk > sub) chunk = sub;
+        B200_FAIL_IF(chunk == 0, "stage_mib too small for the qubit swap");
+        const uint64_t half_amps = (uint64_t)(npat - 1) * chunk;
+        if (ensure_stage_peers(2ull * half_amps * sizeof(cplx))) {
+            cplx *stage = static_cast<cplx *>(stage_->p());
+            struct Job {
+                double *vec;
+                uint64_t j0, cnt;
+            };
+            std::vector<Job> jobs;
+            for (double *vec : vecs)
+                for (uint64_t j0 = 0; j0 < sub; j0 += chunk) jobs.push_back({vec, j0, std::min(chunk, sub - j0)});
+            std::vector<uint32_t> pats;
+            std::vector<uint64_t> my_slot_there, their_slot_here;
+            std::vector<cplx *> peer_stage;
+            for (uint32_t b = 0; b < npat; b++) {
+                if (b == mine) continue;
+                pats.push_back(b);
+                my_slot_there.push_back(mine < b ? mine : mine - 1);
+                their_slot_here.push_back(b < mine ? b : b - 1);
+                peer_stage.push_back(static_cast<cplx *>(stage_peers_[(size_t)peer_of(b)]));
+            }
+            const int np = (int)pats.size();
+            try {
+                for (size_t k = 0; k <= jobs.size(); k++) {
+                    const bool do_push = k < jobs.size(), do_unpack = k >= 1;
+                    std::vector<double *> dst((size_t)np);
+                    std::vector<const double *> src((size_t)np);
+                    for (int p = 0; p < np; p++) {
+                        dst[(size_t)p] = reinterpret_cast<double *>(peer_stage[(size_t)p] + (k & 1) * half_amps + my_slot_there[(size_t)p] * chunk);
+                        src[(size_t)p] = reinterpret_cast<const double *>(stage + ((k + 1) & 1) * half_amps + their_slot_here[(size_t)p] * chunk);
+                    }
+                    const Job *jp = do_push ? &jobs[k] : nullptr, *ju = do_unpack ? &jobs[k - 1] : nullptr;
+                    CUDA_CHECK(b200k_swap_push(jp ? jp->vec : vecs[0], ju ? ju->vec : vecs[0], dst.data(), src.data(), pats.data(), np,
+                                               lpos, m, jp ? jp->j0 : 0, jp ? jp->cnt : 0, ju ? ju->j0 : 0, ju ? ju->cnt : 0, stream_));
+                    note_launch();
+                    if (jp) stats_.exchange_bytes += (double)(npat - 1) * (double)jp->cnt * sizeof(cplx);
+                    comm_->stream_barrier(stream_); // round k landed everywhere; staging half (k+1)&1 is free again
+                }
+            }
+            catch (const std::exception &e) {
+                B200_FAIL(std::string("push-mode qubit swap failed: ") + e.what());
+            }
+            stats_.exchanges++;
+            stats_.swap_push_exchanges++;
+            for (int i = 0; i < m; i++) {
+                int qg = -1, ql = -1;
+                for (int q = 0; q < (int)n_; q++) {
+                    if (pos[q] == pairs[i].first) qg = q;
+                    if (pos[q] == pairs[i].second) ql = q;
+                }
+                std::swap(pos[qg], pos[ql]);
+            }
+            return;
+        }
+    }
     // Staged path, software-pipelined over two halves of the staging buffer: the transfers run on their own
     // stream, so that packing chunk k+1 and unpacking chunk k-1 (HBM passes on the compute stream) overlap
     // the NVLink transfer of chunk k.  Order on the compute stream: pack 0, pack 1, unpack 0, pack 2,
@@ -1234,6 +1350,7 @@ void Simulator::swap_bits_impl(const std::vector<double *> &vecs, std::vector<in
     uint64_t chunk = stage_amps / (4ull * (npat - 1));
     if (chunk > sub) chunk = sub;
     B200_FAIL_IF(chunk == 0, "stage_mib too small for the qubit swap");
+    if (stage_peers_ok_ && (!stage_ || stage_->bytes() < 4ull * (npat - 1) * chunk * sizeof(cplx))) drop_stage_peers();
     ensure_buffer(stage_, 4ull * (npat - 1) * chunk * sizeof(cplx));
     cplx *stage = static_cast<cplx *>(stage_->p());
     if (!xfer_stream_) {
@@ -1312,6 +1429,44 @@ void Simulator::swap_bits_impl(const std::vector<double *> &vecs, std::vector<in
         }
         std::swap(pos[qg], pos[ql]);
     }
+}
+
+// Collective: (re)allocate the swap staging to at least `bytes` and map every rank's staging into this GPU's
+// address space.  Ranks run the same program, so they all come here with the same size at the same point.
+bool Simulator::ensure_stage_peers(size_t bytes)
+{
+    if (stage_ && stage_->bytes() >= bytes && stage_peers_ok_ && stage_peers_ptr_ == stage_->p()) return true;
+    if (stage_peers_failed_) return false;
+    drop_stage_peers();
+    if (!stage_ || stage_->bytes() < bytes) {
+        stage_.reset();
+        stage_ = std::make_unique<DeviceBuffer>(bytes);
+    }
+    stage_peers_ptr_ = stage_->p();
+    try {
+        stage_peers_ok_ = comm_->map_peers(stage_peers_ptr_, stage_peers_);
+    }
+    catch (const std::exception &) {
+        stage_peers_ok_ = false;
+    }
+    if (!stage_peers_ok_) stage_peers_failed_ = true; // no peer path between these GPUs: the staged exchange serves
+    return stage_peers_ok_;
+}
+
+// Collective as well: nobody may still be writing into, or keep a mapping of, a staging buffer about to be freed.
+void Simulator::drop_stage_peers()
+{
+    if (!stage_peers_ok_ || !comm_) return;
+    cudaStreamSynchronize((cudaStream_t)stream_);
+    comm_->unmap_peers(stage_peers_ptr_);
+    try {
+        comm_->barrier();
+    }
+    catch (const std::exception &) {
+    }
+    stage_peers_ok_ = false;
+    stage_peers_ptr_ = nullptr;
+    stage_peers_.clear();
 }
 
 bool Simulator::ensure_psi_peers()
@@ -2200,8 +2355,9 @@ double Simulator::var(int64_t key)
         std::vector<ObsTerm> terms;
         flatten(key, terms);
         B200_FAIL_IF(terms.size() != 1, "Var of a sum of observables does not support finite shots");
-        const double m = sampled_term_mean(terms[0]); // eigenvalues are +-1: <O^2> = coef^2
-        return terms[0].coef * terms[0].coef * (1.0 - m * m);
+        double m1, m2; // sampled <O> and <O^2> of the single term (Pauli products: <O^2> = 1)
+        sampled_term_moments(terms[0], m1, m2);
+        return terms[0].coef * terms[0].coef * (m2 - m1 * m1);
     }
     const size_t bytes = sizeof(cplx) << nl_;
     make_local({psi_->d()}, pos_, observable_xmask(key));
@@ -2317,13 +2473,74 @@ void Simulator::state(double *out_ri, int64_t stride)
 // the reference rotates a copy, which at 30 qubits would cost a second 16 GiB vector), the term's wires
 // are sampled with the alias sampler on the runtime's RNG stream (one seed draw per term), and the
 // rotation is undone; rotation and un-rotation of consecutive terms fuse into the same tile passes.
-double Simulator::sampled_term_mean(const ObsTerm &t)
+// Eigen-decomposition of a small Hermitian matrix (cyclic complex Jacobi rotations), eigenvalues ascending:
+// M = V diag(lam) V^dagger.  Host side of finite-shot Hermitian observables (2^k x 2^k, k <= ~5).
+static void hermitian_eig(const CVec &m, size_t dim, std::vector<double> &lam, CVec &V)
+{
+    CVec A = m;
+    V.assign(dim * dim, cplx(0.0));
+    for (size_t i = 0; i < dim; i++) V[i * dim + i] = 1.0;
+    for (int sweep = 0; sweep < 100; sweep++) {
+        double off = 0.0;
+        for (size_t p = 0; p < dim; p++)
+            for (size_t q = p + 1; q < dim; q++) off += std::norm(A[p * dim + q]);
+        if (off < 1e-290) break;
+        for (size_t p = 0; p < dim; p++)
+            for (size_t q = p + 1; q < dim; q++) {
+                const double g = std::abs(A[p * dim + q]);
+                if (g == 0.0) continue;
+                const cplx e = A[p * dim + q] / g; // phase of the pivot
+                const double th = 0.5 * std::atan2(2.0 * g, (A[p * dim + p] - A[q * dim + q]).real());
+                const double c = std::cos(th), sn = std::sin(th);
+                for (size_t k = 0; k < dim; k++) { // A <- A R
+                    const cplx x = A[k * dim + p], y = A[k * dim + q];
+                    A[k * dim + p] = c * x + sn * std::conj(e) * y;
+                    A[k * dim + q] = -sn * e * x + c * y;
+                }
+                for (size_t k = 0; k < dim; k++) { // A <- R^dagger A
+                    const cplx x = A[p * dim + k], y = A[q * dim + k];
+                    A[p * dim + k] = c * x + sn * e * y;
+                    A[q * dim + k] = -sn * std::conj(e) * x + c * y;
+                }
+                for (size_t k = 0; k < dim; k++) {
+                    const cplx x = V[k * dim + p], y = V[k * dim + q];
+                    V[k * dim + p] = c * x + sn * std::conj(e) * y;
+                    V[k * dim + q] = -sn * e * x + c * y;
+                }
+            }
+    }
+    std::vector<size_t> order(dim);
+    for (size_t i = 0; i < dim; i++) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](size_t x, size_t y) { return A[x * dim + x].real() < A[y * dim + y].real(); });
+    lam.resize(dim);
+    CVec Vs(dim * dim);
+    for (size_t j = 0; j < dim; j++) {
+        lam[j] = A[order[j] * dim + order[j]].real();
+        for (size_t k = 0; k < dim; k++) Vs[k * dim + j] = V[k * dim + order[j]];
+    }
+    V.swap(Vs);
+}
+
+// First and second moment of one flattened term (a product of named Paulis / Hadamards / Hermitian matrices on
+// distinct wires) over `shots` samples.  Hermitian factors are diagonalised on the host (eigenvalues ascending)
+// and rotated with V^dagger; a shot's value is the product of its factors' eigenvalues.
+void Simulator::sampled_term_moments(const ObsTerm &t, double &m1, double &m2)
 {
     std::vector<GateOp> pre, post;
     std::vector<int64_t> wires;
+    struct HermPart {
+        size_t first, k; // position of its first wire in `wires`, number of wires
+        std::vector<double> lam;
+    };
+    std::vector<HermPart> herm;
+    size_t npauli_first = 0; // Pauli-type wires are listed first: their eigenvalue is (-1)^popcount of those bits
+    std::vector<const ObsFactor *> hfac;
     for (auto &f : t.factors) {
-        B200_FAIL_IF(f.named_id == 5, "Hermitian observables do not support finite shots");
         if (f.named_id == 0) continue;
+        if (f.named_id == 5) {
+            hfac.push_back(&f);
+            continue;
+        }
         B200_FAIL_IF(f.wires.size() != 1, "Named observable acts on one wire");
         for (auto w : wires) B200_FAIL_IF(w == f.wires[0], "Repeated wire in a tensor observable with finite shots");
         wires.push_back(f.wires[0]);
@@ -2343,13 +2560,53 @@ double Simulator::sampled_term_mean(const ObsTerm &t)
             canonicalize(post, "RY", {M_PI / 4}, w, false, {}, {}, "");
         }
     }
-    if (wires.empty()) return 1.0;
+    npauli_first = wires.size();
+    for (const ObsFactor *f : hfac) {
+        const size_t k = f->wires.size(), dim = size_t(1) << k;
+        B200_FAIL_IF(k > 6, "Hermitian observables on more than 6 wires do not support finite shots");
+        for (auto w : f->wires) {
+            for (auto x : wires) B200_FAIL_IF(x == w, "Repeated wire in a tensor observable with finite shots");
+            wires.push_back(w);
+        }
+        HermPart hp;
+        hp.first = wires.size() - k;
+        hp.k = k;
+        CVec V, Vd(dim * dim);
+        hermitian_eig(*f->matrix, dim, hp.lam, V);
+        for (size_t i = 0; i < dim; i++)
+            for (size_t j = 0; j < dim; j++) Vd[i * dim + j] = std::conj(V[j * dim + i]);
+        canonicalize_matrix(pre, Vd, f->wires, false, {}, {});
+        canonicalize_matrix(post, V, f->wires, false, {}, {});
+        herm.push_back(std::move(hp));
+    }
+    if (wires.empty()) {
+        m1 = m2 = 1.0;
+        return;
+    }
     enqueue(std::move(pre));
     const auto idx = sample_indices(wires, opt_.shots); // flushes
     enqueue(std::move(post));
-    double acc = 0.0;
-    for (auto i : idx) acc += (__builtin_popcountll((uint64_t)i) & 1) ? -1.0 : 1.0;
-    return acc / (double)opt_.shots;
+    const size_t K = wires.size();
+    double a1 = 0.0, a2 = 0.0;
+    for (auto i : idx) {
+        const uint64_t u = (uint64_t)i;
+        double v = (__builtin_popcountll(u >> (K - npauli_first)) & 1) ? -1.0 : 1.0;
+        for (auto &hp : herm) {
+            const uint64_t sub = (u >> (K - hp.first - hp.k)) & ((1ull << hp.k) - 1ull);
+            v *= hp.lam[(size_t)sub];
+        }
+        a1 += v;
+        a2 += v * v;
+    }
+    m1 = a1 / (double)opt_.shots;
+    m2 = a2 / (double)opt_.shots;
+}
+
+double Simulator::sampled_term_mean(const ObsTerm &t)
+{
+    double m1, m2;
+    sampled_term_moments(t, m1, m2);
+    return m1;
 }
 
 // Probs / PartialProbs as the interface sees them: sampled frequencies when shots > 0
@@ -2742,6 +2999,7 @@ std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
             train.push_back((size_t)t);
         }
     const size_t T = train.size(), K = tape_obs_.size();
+    NvtxRange nvtx("b200sv::adjoint_gradient");
     std::vector<double> jac(K * T, 0.0);
     if (K * T == 0) return jac;
     for (auto &o : tape_obs_)

@@ -107,6 +107,7 @@ struct Options {
     int jit_factor = 1;       // factor u00 out of uncontrolled one-qubit gates, fold the product into one op
     bool virtual_swap = true; // uncontrolled SWAP gates relabel wires instead of moving amplitudes
     int p2p_swap = -1;        // qubit swap over mapped peer memory: 1 on, 0 off, -1 auto (on for 'local:' rank groups)
+    int swap_push = -1;       // qubit swap as one push kernel into all peers' staging: 1 on, 0 off, -1 auto (on over NCCL)
     bool batch_overlaps = true; // adjoint gradient: evaluate commuting generators' overlaps in batched read passes
     bool release_project = false; // ReleaseQubit of a wire that is not in a basis state: error (default) or keep
                                   // the more probable branch (release_entangled='project')
@@ -212,6 +213,11 @@ class Simulator {
     bool sharded() const { return opt_.world > 1; }
     bool ensure_psi_peers(); // collective: map every rank's state shard into this GPU's address space
     void drop_psi_peers();
+    bool ensure_stage_peers(size_t bytes); // collective: swap staging of >= bytes, mapped on every rank
+    void drop_stage_peers();
+    std::vector<void *> stage_peers_;
+    void *stage_peers_ptr_ = nullptr;
+    bool stage_peers_ok_ = false, stage_peers_failed_ = false;
     std::vector<void *> psi_peers_;
     void *psi_peers_ptr_ = nullptr;
     bool psi_peers_tried_ = false, psi_peers_ok_ = false;
@@ -251,6 +257,7 @@ class Simulator {
                           std::vector<int> &lay, const std::vector<OvTerm> &terms);
     bool draw_outcome(const double p[2], int postselect);
     double sampled_term_mean(const ObsTerm &t);
+    void sampled_term_moments(const ObsTerm &t, double &m1, double &m2);
     double uniform01();
     uint32_t rng_next();
     uint32_t fresh_seed();

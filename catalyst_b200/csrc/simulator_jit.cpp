@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 #include <map>
 #include <sstream>
@@ -1022,8 +1023,32 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
     std::vector<double> blk(1 + mvals.size());
     std::memcpy(&blk[0], &rank_base_, sizeof(double)); // Params::rank_base
     std::memcpy(&blk[1], mvals.data(), mvals.size() * sizeof(double));
+    // $B200SV_PASS_LOG=1 (analysis): one stderr line per specialised pass with its CUDA-event time
+    static const bool pass_log = std::getenv("B200SV_PASS_LOG") != nullptr;
+    if (pass_log) {
+        if (!ev2_) {
+            cudaEvent_t a, b;
+            cudaEventCreate(&a);
+            cudaEventCreate(&b);
+            ev2_ = a;
+            ev3_ = b;
+        }
+        cudaEventRecord((cudaEvent_t)ev2_, (cudaStream_t)stream_);
+    }
     const int rc = E.launch(*K, (unsigned)grid, vec, blk.data(), stream_);
     B200_FAIL_IF(rc != 0, "cuLaunchKernel of a specialised pass failed with driver error " + std::to_string(rc));
+    if (pass_log) {
+        cudaEventRecord((cudaEvent_t)ev3_, (cudaStream_t)stream_);
+        cudaEventSynchronize((cudaEvent_t)ev3_);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, (cudaEvent_t)ev2_, (cudaEvent_t)ev3_);
+        int nuni = 0;
+        for (const JRound &R : P.rounds)
+            for (const JOp &o : R.ops) nuni += o.uacc >= 0;
+        fprintf(stderr, "[b200sv pass] %s t=%d c=%d rounds=%zu ops=%zu uniform_ops=%d uaccs=%zu fp64/thread=%.0f regs=%d ctas/sm=%d %.3f ms %.0f GB/s\n",
+                K->name.c_str(), t, c, P.rounds.size(), ops.size(), nuni, P.uaccs.size(), K->fp64_per_thread, K->num_regs,
+                K->ctas_per_sm, ms, 32.0 * std::ldexp(1.0, (int)nl_) / (ms * 1e-3) / 1e9);
+    }
     stats_.tile_passes++;
     stats_.jit_passes++;
     stats_.kernel_ops += (int64_t)ops.size();

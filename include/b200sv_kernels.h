@@ -235,6 +235,15 @@ int b200k_swap_p2p(double *mine, double *peer, const uint8_t *lpos, int m, uint3
 
 /* ---- alias-method sampler on device (reference algorithm: Walker alias table with LIFO pairing,
  * SURVEY.md Appendix A.4; restated as prefix sums so that no sequential pass over 2^n is needed) */
+/* Push-mode qubit swap (shard.cu): one launch writes chunk [push_j0, push_j0 + push_cnt) of this rank's
+ * sub-block (of the vector push_state) for every peer p (lpos bits spell peer_pat[p]) into peer_dst[p] (the peer's receive staging, mapped
+ * peer memory) and, in the same launch, scatters the previous chunk received from every peer (my_src[p]) into
+ * the slots (of the vector unpack_state) that chunk vacated.  Either count may be 0. */
+#define B200K_PUSH_MAX_PEERS 15
+int b200k_swap_push(double *push_state, double *unpack_state, double *const *peer_dst, const double *const *my_src, const uint32_t *peer_pat,
+                    int npeer, const uint8_t *lpos, int m, uint64_t push_j0, uint64_t push_cnt, uint64_t unpack_j0,
+                    uint64_t unpack_cnt, void *stream);
+
 /* FP64 pipe microbenchmark: thread-level DFMA instructions per second this GPU sustains (16 independent
  * chains per thread, full occupancy); `scratch` = any device buffer of >= 8 bytes.  Synchronises. */
 int b200k_dfma_peak(double *scratch, double *dfma_per_second, void *stream);

@@ -558,10 +558,61 @@ class Oracle {
     //      (-1)^popcount are averaged.  Hermitian observables are analytic-only here.  The RNG stream of
     //      the reference for this path is not pinned by any in-tree vector (SURVEY 8(c) iii): what the
     //      tests pin is determinism, convergence to the analytic value, and device == oracle.
+    struct ShotHerm {
+        std::vector<size_t> wires;
+        CVec matrix;
+    };
     struct ShotTerm {
         double coef = 1.0;
         std::vector<std::pair<int, size_t>> f; // (named id, wire), identities dropped
+        std::vector<ShotHerm> h;               // Hermitian factors (sampled in their eigenbasis)
     };
+    // Hermitian eigenproblem by cyclic Jacobi sweeps (eigenvalues ascending, columns of U the eigenvectors):
+    // what the reference gets from LAPACK's zheev for the diagonalizing gates of a Hermitian observable.
+    static void eig_hermitian(CVec a, size_t d, std::vector<double> &w, CVec &U)
+    {
+        U.assign(d * d, cplx(0));
+        for (size_t i = 0; i < d; i++) U[i * d + i] = cplx(1);
+        auto rot_cols = [&](CVec &M, size_t p, size_t q, double c, cplx se) { // columns p, q of M times the rotation
+            for (size_t k = 0; k < d; k++) {
+                const cplx x = M[k * d + p], y = M[k * d + q];
+                M[k * d + p] = c * x + std::conj(se) * y;
+                M[k * d + q] = c * y - se * x;
+            }
+        };
+        for (int it = 0; it < 100; it++) {
+            double rest = 0;
+            for (size_t p = 0; p < d; p++)
+                for (size_t q = 0; q < d; q++)
+                    if (p != q) rest += std::norm(a[p * d + q]);
+            if (rest < 1e-290) break;
+            for (size_t p = 0; p + 1 < d; p++)
+                for (size_t q = p + 1; q < d; q++) {
+                    const double mag = std::abs(a[p * d + q]);
+                    if (mag == 0) continue;
+                    const double ang = 0.5 * std::atan2(2 * mag, (a[p * d + p] - a[q * d + q]).real());
+                    const double c = std::cos(ang);
+                    const cplx se = std::sin(ang) * (a[p * d + q] / mag);
+                    rot_cols(a, p, q, c, se);
+                    for (size_t k = 0; k < d; k++) { // rows p, q: the adjoint rotation from the left
+                        const cplx x = a[p * d + k], y = a[q * d + k];
+                        a[p * d + k] = c * x + se * y;
+                        a[q * d + k] = c * y - std::conj(se) * x;
+                    }
+                    rot_cols(U, p, q, c, se);
+                }
+        }
+        std::vector<size_t> ord(d);
+        for (size_t i = 0; i < d; i++) ord[i] = i;
+        std::stable_sort(ord.begin(), ord.end(), [&](size_t x, size_t y) { return a[x * d + x].real() < a[y * d + y].real(); });
+        w.resize(d);
+        CVec Us(d * d);
+        for (size_t j = 0; j < d; j++) {
+            w[j] = a[ord[j] * d + ord[j]].real();
+            for (size_t k = 0; k < d; k++) Us[k * d + j] = U[k * d + ord[j]];
+        }
+        U.swap(Us);
+    }
     void flatten_shots(int64_t key, std::vector<ShotTerm> &out) const
     {
         ORC_FAIL_IF(key < 0 || size_t(key) >= obs.size(), "Invalid key for cached observables");
@@ -576,7 +627,12 @@ class Oracle {
             out.push_back(t);
             return;
         }
-        case OBS_HERMITIAN: ORC_FAIL_IF(true, "Hermitian observables do not support finite shots"); return;
+        case OBS_HERMITIAN: {
+            ShotTerm t;
+            t.h.push_back({o.wires, o.matrix});
+            out.push_back(t);
+            return;
+        }
         case OBS_TENSOR: {
             std::vector<ShotTerm> acc(1);
             for (auto c : o.children) {
@@ -587,6 +643,7 @@ class Oracle {
                         ShotTerm t = a;
                         t.coef *= b.coef;
                         t.f.insert(t.f.end(), b.f.begin(), b.f.end());
+                        t.h.insert(t.h.end(), b.h.begin(), b.h.end());
                         next.push_back(t);
                     }
                 acc.swap(next);
@@ -606,10 +663,14 @@ class Oracle {
             return;
         }
     }
-    // mean eigenvalue of one Pauli/Hadamard product over `shots` samples
-    double sampled_term_mean(const ShotTerm &t)
+    // first and second moment of one term's eigenvalue over `shots` samples: Pauli / Hadamard wires first
+    // (eigenvalue (-1)^popcount), then each Hermitian factor's wires (eigenvalue lambda[bits], ascending order)
+    void sampled_term_moments(const ShotTerm &t, double &m1, double &m2)
     {
-        if (t.f.empty()) return 1.0;
+        if (t.f.empty() && t.h.empty()) {
+            m1 = m2 = 1.0;
+            return;
+        }
         CVec keep = psi; // the reference rotates a copy; psi is restored below
         std::vector<size_t> wires;
         for (auto &fw : t.f) {
@@ -623,11 +684,46 @@ class Oracle {
             }
             else if (fw.first == ID_Hadamard) apply_named(psi, "RY", {-M_PI / 4}, w, false, {}, {}, "");
         }
+        const size_t npauli = wires.size();
+        std::vector<std::vector<double>> lams;
+        for (auto &hf : t.h) {
+            const size_t d = size_t(1) << hf.wires.size();
+            for (auto w : hf.wires) {
+                for (auto x : wires) ORC_FAIL_IF(x == w, "Repeated wire in a tensor observable with finite shots");
+                wires.push_back(w);
+            }
+            std::vector<double> lam;
+            CVec U;
+            eig_hermitian(hf.matrix, d, lam, U);
+            CVec Ud(d * d);
+            for (size_t r = 0; r < d; r++)
+                for (size_t c = 0; c < d; c++) Ud[r * d + c] = std::conj(U[c * d + r]);
+            apply_matrix(psi, Ud, hf.wires); // U^dagger: to the eigenbasis
+            lams.push_back(lam);
+        }
         const auto idx = sample_indices(wires, shots);
         psi.swap(keep);
-        double acc = 0.0;
-        for (auto i : idx) acc += (__builtin_popcountll(i) & 1) ? -1.0 : 1.0;
-        return acc / double(shots);
+        const size_t K = wires.size();
+        double a1 = 0.0, a2 = 0.0;
+        for (auto i : idx) {
+            double v = (__builtin_popcountll(i >> (K - npauli)) & 1) ? -1.0 : 1.0;
+            size_t first = npauli;
+            for (size_t q = 0; q < t.h.size(); q++) {
+                const size_t k = t.h[q].wires.size();
+                v *= lams[q][(i >> (K - first - k)) & ((uint64_t(1) << k) - 1)];
+                first += k;
+            }
+            a1 += v;
+            a2 += v * v;
+        }
+        m1 = a1 / double(shots);
+        m2 = a2 / double(shots);
+    }
+    double sampled_term_mean(const ShotTerm &t)
+    {
+        double m1, m2;
+        sampled_term_moments(t, m1, m2);
+        return m1;
     }
 
     // Expval / Var (QuantumDevice.hpp:488,503)
@@ -656,8 +752,9 @@ class Oracle {
             std::vector<ShotTerm> terms;
             flatten_shots(key, terms);
             ORC_FAIL_IF(terms.size() != 1, "Var of a sum of observables does not support finite shots");
-            const double m = sampled_term_mean(terms[0]); // eigenvalues are +-1: <O^2> = coef^2
-            return terms[0].coef * terms[0].coef * (1.0 - m * m);
+            double m1, m2; // sampled <O> and <O^2> (Pauli products: <O^2> = 1)
+            sampled_term_moments(terms[0], m1, m2);
+            return terms[0].coef * terms[0].coef * (m2 - m1 * m1);
         }
         CVec ov = psi;
         apply_obs(key, ov);

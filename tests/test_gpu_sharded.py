@@ -325,3 +325,41 @@ def test_unseeded_measurement_agrees_across_ranks(gpu, world):
     # the measured wires are frozen at their outcomes
     for w, m in zip((0, n - 1, 3), res[0][0]):
         assert np.all(res[0][2][:, w] == float(m))
+
+
+@pytest.mark.parametrize("stage_mib", [1, 4096])
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_swap_push_mode(gpu, oracle_mod, world, stage_mib):
+    """Third transport of the qubit swap (default over NCCL process groups): one kernel per chunk pushes this
+    rank's sub-blocks into every peer's mapped receive staging and scatters the previous chunk.  stage_mib=1 at
+    17 qubits forces several chunks per swap (both staging halves, the trailing unpack-only round); a release /
+    allocate at another size re-creates and re-maps the staging; the adjoint gradient swaps several vectors."""
+    n = 17 if stage_mib == 1 else 11
+    ops = random_circuit(900 + world, n, 80, names=["RX", "RY", "RZ", "Hadamard", "CNOT", "CZ", "IsingXX", "CRY", "T"])
+    want = _oracle(oracle_mod, n, ops).state()
+    gops = [("RX", [0.3], [0]), ("RY", [0.7], [n - 1]), ("CNOT", [], [0, n - 1]), ("IsingXX", [0.4], [1, n - 2]),
+            ("RZ", [1.2], [0]), ("CRX", [0.9], [n - 1, 0])]
+    og = oracle_mod.OracleDevice(9)
+    og.start_tape()
+    apply_ops(og, [(g[0], g[1], [w if w < 4 else 9 - (n - w) for w in g[2]]) for g in gops])
+    og.expval(og.obs_tensor([og.obs_named("PauliX", 0), og.obs_named("PauliZ", 8)]))
+    og.stop_tape()
+    jo = og.gradient()
+
+    def prog(d, r):
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        st = d.state()
+        s = d.stats()
+        d.release_qubits()
+        d.allocate_qubits(9)                      # another shard size: staging is re-created and re-mapped
+        d.start_tape()
+        apply_ops(d, [(g[0], g[1], [w if w < 4 else 9 - (n - w) for w in g[2]]) for g in gops])
+        d.expval(d.obs_tensor([d.obs_named("PauliX", 0), d.obs_named("PauliZ", 8)]))
+        d.stop_tape()
+        return st, int(s.exchanges), int(s.swap_push_exchanges), d.gradient()
+
+    for st, ex, pushed, jd in gpu.run_spmd(world, prog, swap_push=1, p2p_swap=0, stage_mib=stage_mib, tile_bits=6, min_row_bits=2):
+        assert np.max(np.abs(st - want)) < TOL
+        assert ex > 0 and pushed == ex
+        assert np.max(np.abs(jd - jo)) < 1e-12

@@ -107,13 +107,56 @@ def test_release_errors(gpu):
     assert np.array_equal(d.state(), [1, 0, 0, 0])
 
 
-def test_release_refused_on_sharded_register(gpu):
+@pytest.mark.parametrize("world", [2, 4])
+def test_dynamic_qubits_on_a_sharded_register(gpu, oracle_mod, world):
+    """AllocateQubit / ReleaseQubit on a register sharded over `world` ranks: the new wire is a new local index
+    bit of every shard; a released wire (also one that sits on a RANK bit, like wire 0) is swapped onto the top
+    local position and every shard keeps its lower half.  Results equal the oracle on every rank."""
+    n = 8
+    rng = np.random.default_rng(world)
+    prog_ops = []
+    for rnd in range(4):
+        k = [0, n - 1, 3, 1][rnd]                       # wire 0 is a rank bit under the initial layout
+        prog_ops.append((random_circuit(50 * world + rnd, n, 25), k, rnd % 2 == 1))
+
+    def run(dev):
+        out = []
+        for ops, k, one in prog_ops:
+            apply_ops(dev, ops)
+            dev.allocate_qubit()
+            new = dev.n - 1 if hasattr(dev, "n") else n
+            more = [("Hadamard", [], [new]), ("CNOT", [], [new, 2]), ("CNOT", [], [new, 2]), ("Hadamard", [], [new])]
+            if one:
+                more.append(("PauliX", [], [new]))
+            more.append(("SWAP", [], [new, k]))          # the ancilla's state moves to wire k
+            apply_ops(dev, more)
+            dev.release_qubit(k)
+            out.append(dev.probs())
+        out.append(dev.state())
+        return out
+
+    want = run(oracle_mod.OracleDevice(n, seed=37))
+
     def prog(d, r):
-        d.allocate_qubits(6)
-        with pytest.raises(RuntimeError):
-            d.release_qubit(0)
+        d.allocate_qubits(n)
+        res = run(d)
+        return res, d.num_qubits()
+
+    for res, nq in gpu.run_spmd(world, prog, seed=37):
+        assert nq == n
+        for g, w in zip(res, want):
+            assert np.max(np.abs(g - w)) < 1e-11
+
+
+def test_dynamic_qubits_sharded_limits(gpu):
+    def prog(d, r):
+        with pytest.raises(RuntimeError, match="must be an array"):
+            d.allocate_qubit()                           # no register yet on a sharded device
+        d.allocate_qubits(4)
+        with pytest.raises(RuntimeError, match="keeps at least"):
+            d.release_qubit(0)                           # 4 ranks need >= 4 qubits
         return True
-    assert all(gpu.run_spmd(2, prog))
+    assert all(gpu.run_spmd(4, prog))
 
 
 # ---- through librt_capi + the plugin (RuntimeCAPI.cpp:305-372) -----------------------------------------

@@ -295,3 +295,31 @@ def test_shots_var_and_probs(oracle_mod):
         o.var(build_obs(o, ("Ham", [1.0, 1.0], [("N", "PauliX", 0), ("N", "PauliZ", 1)])))
     with pytest.raises(RuntimeError):
         o.expval(build_obs(o, ("H", np.eye(2), [0])))
+
+
+def test_shots_hermitian_expval_and_var_converge(oracle_mod):
+    """Finite-shot Hermitian observables in the oracle: sampled in the eigenbasis of the matrix, the estimates
+    converge to the analytic Expval / Var (5 sigma) and are deterministic for a fixed device seed."""
+    n, shots = 4, 200000
+    rng = np.random.default_rng(0)
+    H = rng.normal(size=(4, 4)) + 1j * rng.normal(size=(4, 4))
+    H = H + H.conj().T
+
+    def make():
+        o = oracle_mod.OracleDevice(n, seed=5)
+        for w in range(n):
+            o.named_op("RY", [0.3 + w], [w])
+        o.named_op("CNOT", [], [0, 2])
+        o.named_op("CNOT", [], [1, 3])
+        return o, o.obs_tensor([o.obs_hermitian(H, [2, 0]), o.obs_named("PauliX", 3)])
+    a, ka = make()
+    exact_e, exact_v = a.expval(ka), a.var(ka)
+    a.set_shots(shots)
+    ea, va = a.expval(ka), a.var(ka)
+    b, kb = make()
+    b.set_shots(shots)
+    assert (b.expval(kb), b.var(kb)) == (ea, va)
+    assert abs(ea - exact_e) < 5 * np.sqrt(exact_v / shots)
+    assert abs(va - exact_v) < 0.05 * exact_v
+    a.set_shots(0)
+    assert abs(a.expval(ka) - exact_e) < 1e-13            # the state was restored
