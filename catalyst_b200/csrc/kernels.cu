@@ -14,6 +14,10 @@
 //   k_sampler_* ........... Sample :384 / Counts :433 (alias sampler of SURVEY.md Appendix A.4)
 #include <atomic>
 #include <cuda_runtime.h>
+#include <thrust/copy.h>
+#include <thrust/execution_policy.h>
+#include <thrust/iterator/counting_iterator.h>
+#include <thrust/system/cuda/execution_policy.h>
 #include <stdint.h>
 #include <string.h>
 
@@ -1289,4 +1293,76 @@ extern "C" int b200k_dfma_peak(double *scratch, double *dfma_per_second, void *s
     cudaEventDestroy(e1);
     *dfma_per_second = best;
     return (int)cudaGetLastError();
+}
+
+// =================================================================================================
+// MCMC sampling (device kwargs mcmc / num_burnin / kernel_name of lightning.qubit).
+// A Metropolis chain over basis states is sequential by nature: ONE thread walks it, reading two amplitudes
+// per step from HBM; the proposal stream (site / value or a random rank among the non-zero amplitudes, plus
+// one uniform per step) is drawn on the host from the same mt19937 the alias sampler uses, so the chain is
+// reproducible and comparable with the CPU restatement.  The state must be in canonical layout (index =
+// logical index).  "NonZeroRandom" needs the ascending list of basis states with |amplitude|^2 > eps:
+// an ordered stream compaction (thrust::copy_if over a counting iterator).
+// =================================================================================================
+__global__ void k_mcmc_chain(const cplx *__restrict__ psi, int n, int64_t steps, int64_t burnin, const uint32_t *__restrict__ site,
+                             const uint64_t *__restrict__ jump, const int64_t *__restrict__ nz, int64_t nnz,
+                             const double *__restrict__ u, int64_t *__restrict__ out)
+{
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    uint64_t cur = 0;
+    cplx a = psi[0];
+    double pc = a.x * a.x + a.y * a.y;
+    for (int64_t s = 0; s < steps; s++) {
+        uint64_t cand;
+        if (nz) cand = (uint64_t)nz[jump[s] % (uint64_t)nnz];
+        else {
+            const uint32_t w = site[s]; // bit 31: value, low bits: qubit site
+            const uint32_t q = w & 0x7fffffffu;
+            cand = (cur & ~(1ull << q)) | ((uint64_t)(w >> 31) << q);
+        }
+        const cplx b = psi[cand];
+        const double pn = b.x * b.x + b.y * b.y;
+        if (pc == 0.0 || pn > u[s] * pc) {
+            cur = cand;
+            pc = pn;
+        }
+        if (s >= burnin) out[s - burnin] = (int64_t)cur;
+    }
+}
+
+extern "C" int b200k_mcmc_chain(const double *psi, int n, int64_t steps, int64_t burnin, const uint32_t *site,
+                                const uint64_t *jump, const int64_t *nz, int64_t nnz, const double *u, int64_t *out,
+                                void *stream)
+{
+    if (steps <= burnin) return 0;
+    if (nz && nnz <= 0) return (int)cudaErrorInvalidValue;
+    k_mcmc_chain<<<1, 32, 0, (cudaStream_t)stream>>>((const cplx *)psi, n, steps, burnin, site, jump, nz, nnz, u, out);
+    return (int)cudaGetLastError();
+}
+
+struct NonZeroAmp {
+    const cplx *psi;
+    double eps;
+    __device__ bool operator()(int64_t i) const
+    {
+        const cplx a = psi[i];
+        return a.x * a.x + a.y * a.y > eps;
+    }
+};
+
+// out (capacity 2^n int64) <- ascending indices with |psi_i|^2 > eps; *count receives how many.  Synchronises.
+extern "C" int b200k_nonzero_indices(const double *psi, int n, double eps, int64_t *out, int64_t *count, void *stream)
+{
+    const int64_t N = int64_t(1) << n;
+    NonZeroAmp pred{(const cplx *)psi, eps};
+    try {
+        auto end = thrust::copy_if(thrust::cuda::par.on((cudaStream_t)stream), thrust::counting_iterator<int64_t>(0),
+                                   thrust::counting_iterator<int64_t>(N), out, pred);
+        *count = (int64_t)(end - out);
+    }
+    catch (...) {
+        cudaGetLastError();
+        return (int)cudaErrorUnknown;
+    }
+    return (int)cudaStreamSynchronize((cudaStream_t)stream);
 }

@@ -98,6 +98,9 @@ Options parse_kwargs(const char *kwargs)
             }
         };
         if (k == "shots") o.shots = as_int(0);
+        else if (k == "mcmc") o.mcmc = as_int(0) != 0;
+        else if (k == "num_burnin") o.num_burnin = as_int(o.num_burnin);
+        else if (k == "kernel_name") o.kernel_name = v;
         else if (k == "tile_bits") o.tile_bits = (int)as_int(o.tile_bits);
         else if (k == "min_row_bits") o.min_row_bits = (int)as_int(o.min_row_bits);
         else if (k == "fuse") o.fuse = as_int(1) != 0;
@@ -134,6 +137,9 @@ Options parse_kwargs(const char *kwargs)
     B200_FAIL_IF(o.rank < 0 || o.rank >= o.world, "rank out of range");
     B200_FAIL_IF(o.world > 1 && o.comm.empty(), "world_size > 1 needs a 'comm' kwarg (nccl:<id> or local:<group>)");
     B200_FAIL_IF(o.stage_mib < 1, "stage_mib out of range");
+    B200_FAIL_IF(o.num_burnin < 0, "num_burnin out of range");
+    B200_FAIL_IF(o.mcmc && o.kernel_name != "Local" && o.kernel_name != "NonZeroRandom",
+                 "kernel_name must be 'Local' or 'NonZeroRandom'");
     B200_FAIL_IF(o.tile_bits < 1 || o.tile_bits > B200K_MAX_TILE_BITS, "tile_bits out of range");
     B200_FAIL_IF(o.min_row_bits < 0, "min_row_bits out of range");
     B200_FAIL_IF(o.jit < 0 || o.jit > 2, "jit must be 0/off, 1/auto or 2/always");
@@ -2720,9 +2726,82 @@ void Simulator::probs(const std::vector<int64_t> &wires_in, double *out, int64_t
 // Reference stream (verified against doc/releases/changelog-0.9.0.md:
 // 299-315): one 32-bit output of the runtime generator seeds a fresh mt19937 per call; each shot
 // takes two uniform_real_distribution<double> draws from it.
+// MCMC sampling (kwargs mcmc / num_burnin / kernel_name, reference shape: frontend/catalyst/from_plxpr/from_plxpr.py:194):
+// PARITY UNPINNED -- the algorithm is pennylane-lightning's generate_samples_metropolis, whose transition kernels seed
+// themselves from std::random_device; restated with one mt19937 per call (seeded like the alias sampler) so that it
+// is reproducible.  The proposal stream is drawn here, the chain runs as one thread on the GPU.
+std::vector<int64_t> Simulator::mcmc_indices(const std::vector<int64_t> &wires_in, int64_t shots)
+{
+    B200_FAIL_IF(sharded(), "MCMC sampling is not supported on a sharded register");
+    B200_FAIL_IF(opt_.kernel_name != "Local" && opt_.kernel_name != "NonZeroRandom",
+                 "Unsupported MCMC kernel '" + opt_.kernel_name + "' (Local, NonZeroRandom)");
+    check_wires(wires_in, {});
+    if (!wire_identity()) restore_wire_order(); // the chain walks logical indices: canonical layout
+    flush();
+    std::vector<int64_t> wires = wires_in;
+    if (wires.empty())
+        for (int64_t w = 0; w < n_; w++) wires.push_back(w);
+    std::mt19937 rng(fresh_seed());
+    const bool local = opt_.kernel_name == "Local";
+    const int64_t steps = opt_.num_burnin + shots;
+    std::vector<int64_t> idx((size_t)shots);
+    if (shots == 0) return idx;
+    int64_t nnz = 0;
+    std::unique_ptr<DeviceBuffer> nzbuf;
+    if (!local) {
+        nzbuf = std::make_unique<DeviceBuffer>(sizeof(int64_t) << n_);
+        CUDA_CHECK(b200k_nonzero_indices(psi_->d(), (int)n_, 1e-24, static_cast<int64_t *>(nzbuf->p()), &nnz, stream_));
+        note_launch();
+        B200_FAIL_IF(nnz <= 0, "MCMC sampling: the state has no non-zero amplitude");
+    }
+    std::vector<uint32_t> site(local ? (size_t)steps : 0);
+    std::vector<uint64_t> jump(local ? 0 : (size_t)steps);
+    std::vector<double> u((size_t)steps);
+    std::uniform_real_distribution<double> U(0.0, 1.0);
+    for (int64_t s = 0; s < steps; s++) {
+        if (local) {
+            const uint32_t q = (uint32_t)rng() % (uint32_t)n_, v = (uint32_t)rng() & 1u;
+            site[(size_t)s] = q | (v << 31);
+        }
+        else {
+            const uint64_t hi = (uint32_t)rng(), lo = (uint32_t)rng();
+            jump[(size_t)s] = (hi << 32) | lo;
+        }
+        u[(size_t)s] = U(rng);
+    }
+    const size_t b_site = (site.size() * 4 + 15) & ~size_t(15), b_jump = jump.size() * 8, b_u = u.size() * 8, b_out = idx.size() * 8;
+    ensure_buffer(misc_, b_site + b_jump + b_u + b_out + 64);
+    char *base = static_cast<char *>(misc_->p());
+    uint32_t *dsite = reinterpret_cast<uint32_t *>(base);
+    uint64_t *djump = reinterpret_cast<uint64_t *>(base + b_site);
+    double *du = reinterpret_cast<double *>(base + b_site + b_jump);
+    int64_t *dout = reinterpret_cast<int64_t *>(base + b_site + b_jump + b_u);
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (local) CUDA_CHECK(cudaMemcpyAsync(dsite, site.data(), site.size() * 4, cudaMemcpyHostToDevice, st));
+    else CUDA_CHECK(cudaMemcpyAsync(djump, jump.data(), b_jump, cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(du, u.data(), b_u, cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(b200k_mcmc_chain(psi_->d(), (int)n_, steps, opt_.num_burnin, local ? dsite : nullptr, local ? nullptr : djump,
+                                local ? nullptr : static_cast<const int64_t *>(nzbuf->p()), nnz, du, dout, stream_));
+    note_launch();
+    CUDA_CHECK(cudaMemcpyAsync(idx.data(), dout, b_out, cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    stats_.h2d_bytes += (double)(site.size() * 4 + b_jump + b_u);
+    stats_.d2h_bytes += (double)b_out;
+    // the chain recorded full-register indices (wire 0 = most significant bit): project onto the requested wires
+    const size_t k = wires.size();
+    for (auto &x : idx) {
+        const uint64_t full = (uint64_t)x;
+        uint64_t o = 0;
+        for (size_t j = 0; j < k; j++) o = (o << 1) | ((full >> (n_ - 1 - wires[j])) & 1ull);
+        x = (int64_t)o;
+    }
+    return idx;
+}
+
 std::vector<int64_t> Simulator::sample_indices(const std::vector<int64_t> &wires, int64_t shots)
 {
     B200_FAIL_IF(shots < 0, "Invalid number of shots");
+    if (opt_.mcmc) return mcmc_indices(wires, shots);
     probs(wires, nullptr, 1); // leaves the distribution in probs_buf_ on the device
     const size_t k = wires.empty() ? (size_t)n_ : wires.size();
     const int64_t nbins = int64_t(1) << k;

@@ -84,6 +84,11 @@ struct PauliTerm {
 
 struct Options {
     int64_t shots = 0;
+    // lightning.qubit's sampling kwargs (frontend/catalyst/from_plxpr/from_plxpr.py:194): Metropolis chain instead of
+    // the alias sampler; transition kernels "Local" and "NonZeroRandom"
+    bool mcmc = false;
+    int64_t num_burnin = 100;
+    std::string kernel_name = "Local";
     int tile_bits = 11;
     int min_row_bits = 3;     // shortest contiguous row of a tile: 2^3 amplitudes = 128 B (one cache line)
     bool adaptive_rows = true; // per pass, pick the row width that maximises gates per unit of pass time
@@ -158,6 +163,7 @@ class Simulator {
     void probs(const std::vector<int64_t> &wires, double *out, int64_t stride); // analytic
     void probs_measured(const std::vector<int64_t> &wires, double *out, int64_t stride); // sampled if shots > 0
     std::vector<int64_t> sample_indices(const std::vector<int64_t> &wires, int64_t shots);
+    std::vector<int64_t> mcmc_indices(const std::vector<int64_t> &wires, int64_t shots);
     bool measure(int64_t wire, int postselect);
     bool pauli_measure(const std::string &word, const std::vector<int64_t> &wires, int postselect);
 

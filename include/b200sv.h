@@ -36,9 +36,11 @@ const char *b200sv_version(void);
 
 /* <Name>Factory(kwargs) — QuantumDevice.hpp:30-33; kwargs is the Python str(dict) the frontend
  * bakes into quantum.device (runtime/lib/backend/common/Utils.hpp:107-156).  Recognised keys:
- * shots, tile_bits, min_row_bits, fuse (0/1), device (CUDA ordinal), world_size, rank, comm,
- * stage_mib (see "sharding" below).  Unknown keys are ignored
- * like lightning's mcmc/num_burnin/kernel_name. Returns NULL on error. */
+ * shots, mcmc / num_burnin / kernel_name (lightning.qubit's sampling kwargs: Sample, Counts and the finite-shot
+ * estimates then draw from a Metropolis chain, kernels 'Local' and 'NonZeroRandom'; parity unpinned, see
+ * Simulator::mcmc_indices), tile_bits, min_row_bits, fuse (0/1), device (CUDA ordinal), world_size, rank, comm,
+ * stage_mib, swap_push, p2p_swap (see "sharding" below), release_entangled ('error' | 'project'), jit ('off' |
+ * 'auto' | 'always') and its tuning keys.  Unknown keys are ignored.  Returns NULL on error. */
 b200sv_device *b200sv_create(const char *kwargs);
 void b200sv_destroy(b200sv_device *d);
 

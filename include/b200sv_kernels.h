@@ -235,6 +235,15 @@ int b200k_swap_p2p(double *mine, double *peer, const uint8_t *lpos, int m, uint3
 
 /* ---- alias-method sampler on device (reference algorithm: Walker alias table with LIFO pairing,
  * SURVEY.md Appendix A.4; restated as prefix sums so that no sequential pass over 2^n is needed) */
+/* MCMC sampling (kernels.cu): one thread walks a Metropolis chain of `steps` proposals over the basis states of a
+ * state in canonical layout and writes the visited index after each of the last steps - burnin proposals.
+ * Proposal s: nz == NULL ("Local"): qubit site[s] & 0x7fffffff is set to bit 31 of site[s]; else ("NonZeroRandom"):
+ * jump to nz[jump[s] % nnz].  Accepted when |psi_new|^2 > u[s] * |psi_old|^2 (or the chain sits on a zero). */
+int b200k_mcmc_chain(const double *psi, int n, int64_t steps, int64_t burnin, const uint32_t *site, const uint64_t *jump,
+                     const int64_t *nz, int64_t nnz, const double *u, int64_t *out, void *stream);
+/* ascending indices i with |psi_i|^2 > eps into out (capacity 2^n), their number into *count; synchronises */
+int b200k_nonzero_indices(const double *psi, int n, double eps, int64_t *out, int64_t *count, void *stream);
+
 /* Push-mode qubit swap (shard.cu): one launch writes chunk [push_j0, push_j0 + push_cnt) of this rank's
  * sub-block (of the vector push_state) for every peer p (lpos bits spell peer_pat[p]) into peer_dst[p] (the peer's receive staging, mapped
  * peer memory) and, in the same launch, scatters the previous chunk received from every peer (my_src[p]) into

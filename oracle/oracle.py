@@ -111,6 +111,11 @@ class OracleDevice:
     def gen_peek(self) -> int:
         return int(self.L.orc_gen_peek(self.h))
 
+    def set_mcmc(self, on=True, num_burnin=100, kernel_name="Local"):
+        """Device kwargs mcmc / num_burnin / kernel_name of lightning.qubit: Sample / Counts / finite-shot
+        estimates draw from a Metropolis chain instead of the alias sampler (parity unpinned, see sv_oracle.hpp)."""
+        self._chk(self.L.orc_set_mcmc(self.h, int(bool(on)), C.c_int64(num_burnin), kernel_name.encode()))
+
     # -- gates --------------------------------------------------------------------------------
     def named_op(self, name, params=(), wires=(), inverse=False, ctrl_wires=(), ctrl_values=(),
                  pauli_word=None):

@@ -821,6 +821,51 @@ class Oracle {
         }
         return a;
     }
+    // ---- MCMC sampling (device kwargs 'mcmc', 'num_burnin', 'kernel_name' of lightning.qubit; shape in-tree:
+    //      frontend/catalyst/from_plxpr/from_plxpr.py:194, frontend/test/lit/test_mcmc.py:15-41).  PARITY UNPINNED:
+    //      the algorithm lives in pennylane-lightning (generate_samples_metropolis: a Metropolis chain over basis
+    //      states from index 0, `num_burnin` discarded steps, transition kernels "Local" = set one random qubit to
+    //      a random value, "NonZeroRandom" = jump to a random basis state of non-zero amplitude; acceptance
+    //      |psi(new)|^2 / |psi(old)|^2 against a uniform draw) and its kernels seed themselves from
+    //      std::random_device, so the reference's own stream is not reproducible.  Restated here with ONE
+    //      mt19937 seeded like the alias sampler (one 32-bit output of the device generator), so that the
+    //      restatement is deterministic and the CUDA device can be compared with it.
+    bool mcmc = false;
+    size_t num_burnin = 0;
+    std::string kernel_name = "Local";
+    static constexpr double kNonZero = 1e-24; // |amplitude|^2 above this counts as non-zero
+    std::vector<uint64_t> mcmc_indices(const std::vector<size_t> &wires, size_t nshots, std::mt19937 &rng)
+    {
+        ORC_FAIL_IF(kernel_name != "Local" && kernel_name != "NonZeroRandom", "Unsupported MCMC kernel '" + kernel_name + "'");
+        const bool local = kernel_name == "Local";
+        std::vector<uint64_t> nz;
+        if (!local)
+            for (uint64_t i = 0; i < (uint64_t(1) << n); i++)
+                if (std::norm(psi[i]) > kNonZero) nz.push_back(i);
+        std::uniform_real_distribution<double> U(0.0, 1.0);
+        uint64_t cur = 0;
+        std::vector<uint64_t> out(nshots);
+        for (size_t s = 0; s < num_burnin + nshots; s++) {
+            uint64_t cand;
+            if (local) {
+                const uint32_t site = uint32_t(rng()) % uint32_t(n), val = uint32_t(rng()) & 1u;
+                cand = (cur & ~(uint64_t(1) << site)) | (uint64_t(val) << site);
+            }
+            else {
+                const uint64_t r = (uint64_t(uint32_t(rng())) << 32) | uint64_t(uint32_t(rng()));
+                cand = nz[r % nz.size()];
+            }
+            const double u = U(rng);
+            const double pc = std::norm(psi[cur]), pn = std::norm(psi[cand]);
+            if (pc == 0.0 || pn > u * pc) cur = cand;
+            if (s >= num_burnin) {
+                uint64_t o = 0;
+                for (size_t j = 0; j < wires.size(); j++) o = (o << 1) | (cur >> bit_of(wires[j]) & 1);
+                out[s - num_burnin] = o;
+            }
+        }
+        return out;
+    }
     // returns basis indices (MSB-first over `wires`)
     std::vector<uint64_t> sample_indices(const std::vector<size_t> &wires_in, size_t nshots)
     {
@@ -828,6 +873,7 @@ class Oracle {
         std::mt19937 rng;
         if (gen) rng = std::mt19937((*gen)()); // generateSeed(): one 32-bit output per call
         else rng = std::mt19937(std::random_device{}());
+        if (mcmc) return mcmc_indices(wires, nshots, rng);
         const auto p = probs_of(wires);
         const Alias a = build_alias(p);
         const size_t N = p.size();

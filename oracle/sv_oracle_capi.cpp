@@ -175,6 +175,11 @@ int orc_probs(void *h, const int64_t *wires, int nw, double *out)
     ORC_TRY(auto p = static_cast<Oracle *>(h)->probs(wv(wires, nw));
             std::memcpy(out, p.data(), p.size() * sizeof(double)))
 }
+int orc_set_mcmc(void *h, int on, int64_t num_burnin, const char *kernel_name)
+{
+    ORC_TRY(auto *o = static_cast<Oracle *>(h); o->mcmc = on != 0; o->num_burnin = size_t(num_burnin);
+            o->kernel_name = kernel_name ? kernel_name : "Local")
+}
 int orc_sample(void *h, const int64_t *wires, int nw, int64_t nshots, double *out)
 {
     ORC_TRY(auto s = static_cast<Oracle *>(h)->sample(wv(wires, nw), size_t(nshots));

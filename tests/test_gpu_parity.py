@@ -579,3 +579,37 @@ def test_stats_json_and_fp64_peak(gpu):
     assert js["specialised_passes"] == js["tile_passes"] and js["fp64_instructions"] > 0
     rate = d.fp64_peak()
     assert 1e12 < rate < 1e14, rate       # B200: 148 SMs x 64 FP64 lanes x ~1.9 GHz = 1.8e13 DFMA/s
+
+
+@pytest.mark.parametrize("kernel", ["Local", "NonZeroRandom"])
+@pytest.mark.parametrize("n,seed", [(4, 0), (9, 1), (14, 2)])
+def test_mcmc_sampling(gpu, oracle_mod, n, seed, kernel):
+    """Device kwargs mcmc / num_burnin / kernel_name (frontend/catalyst/from_plxpr/from_plxpr.py:194): Sample and
+    Counts draw from a Metropolis chain.  PARITY UNPINNED against lightning.qubit (its kernels seed themselves from
+    std::random_device); pinned here: device == CPU restatement bit for bit under a seed, wires relabelled by SWAPs
+    included, and the chain's frequencies converge to the analytic probabilities."""
+    ops = random_circuit(seed + 70, n, 40) + [("SWAP", [], [0, n - 1])]
+    shots = 4000
+    o = oracle_mod.OracleDevice(n, seed=37)
+    d = gpu.B200Device(n, seed=37, mcmc=True, num_burnin=200, kernel_name=kernel)
+    o.set_mcmc(True, 200, kernel)
+    apply_ops(o, ops); apply_ops(d, ops)
+    assert np.array_equal(o.sample(shots), d.sample(shots))
+    w = [n - 1, 0, n // 2]
+    assert np.array_equal(o.sample(shots, w), d.sample(shots, w))
+    eo, co = o.counts(shots, w[:2])
+    ed, cd = d.counts(shots, w[:2])
+    assert np.array_equal(co, cd) and np.array_equal(eo, ed)
+    assert np.max(np.abs(o.state() - d.state())) < 1e-11
+    if n == 4:
+        big = d.sample(200000)
+        idx = (big.astype(np.int64) * (1 << np.arange(n - 1, -1, -1))).sum(axis=1)
+        freq = np.bincount(idx, minlength=1 << n) / len(idx)
+        d2 = gpu.B200Device(n, seed=1)
+        apply_ops(d2, ops)
+        assert np.max(np.abs(freq - d2.probs())) < 0.02
+
+
+def test_mcmc_kwargs_are_validated(gpu):
+    with pytest.raises(RuntimeError, match="kernel_name"):
+        gpu.B200Device(2, mcmc=True, kernel_name="Gibbs")

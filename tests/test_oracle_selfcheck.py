@@ -293,8 +293,8 @@ def test_shots_var_and_probs(oracle_mod):
     o.set_shots(10)
     with pytest.raises(RuntimeError):
         o.var(build_obs(o, ("Ham", [1.0, 1.0], [("N", "PauliX", 0), ("N", "PauliZ", 1)])))
-    with pytest.raises(RuntimeError):
-        o.expval(build_obs(o, ("H", np.eye(2), [0])))
+    # Hermitian observables are sampled in their eigenbasis: the identity has the single eigenvalue 1
+    assert o.expval(build_obs(o, ("H", np.eye(2), [0]))) == 1.0
 
 
 def test_shots_hermitian_expval_and_var_converge(oracle_mod):
