@@ -48,6 +48,7 @@ class Stats(C.Structure):
 
 
 _lib = None
+_NAME_BYTES = {}
 
 
 def lib():
@@ -68,6 +69,9 @@ def lib():
         L.b200sv_prng_peek.restype = C.c_uint32
         L.b200sv_layout.restype = C.c_int64
         L.b200sv_layout.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int64]
+        L.b200sv_named_operation.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_double), C.c_int64,
+                                             C.POINTER(C.c_int64), C.c_int64, C.c_int, C.POINTER(C.c_int64),
+                                             C.POINTER(C.c_uint8), C.c_int64, C.c_char_p]
         L.b200sv_world_size.argtypes = [C.c_void_p]
         L.b200sv_rank.argtypes = [C.c_void_p]
         for name in ("b200sv_num_qubits", "b200sv_get_shots", "b200sv_observable",
@@ -141,6 +145,7 @@ class B200Device:
 
     def __init__(self, n: int | None = None, seed: int | None = None, **kwargs):
         self.L = lib()
+        self._named = self.L.b200sv_named_operation
         self.h = C.c_void_p(self.L.b200sv_create(str(dict(kwargs)).encode()))
         if not self.h:
             raise B200Error(self.L.b200sv_last_error().decode())
@@ -205,13 +210,22 @@ class B200Device:
     # -- gates (QuantumDevice.hpp:215-284) ------------------------------------------------------
     def named_op(self, name, params=(), wires=(), inverse=False, ctrl_wires=(), ctrl_values=(),
                  pauli_word=None):
-        p = np.ascontiguousarray(np.asarray(list(params), dtype=np.float64))
-        w, cw = _i64(wires), _i64(ctrl_wires)
-        cv = np.ascontiguousarray(np.asarray(list(ctrl_values), dtype=np.uint8))
-        self._chk(self.L.b200sv_named_operation(
-            self.h, name.encode(), _p(p, C.c_double), C.c_int64(len(p)), _p(w, C.c_int64),
-            C.c_int64(len(w)), int(bool(inverse)), _p(cw, C.c_int64), _p(cv, C.c_uint8),
-            C.c_int64(len(cw)), pauli_word.encode() if pauli_word else None))
+        # the hot host call (one per gate): plain ctypes arrays, no numpy round trip
+        bname = _NAME_BYTES.get(name)
+        if bname is None:
+            bname = _NAME_BYTES[name] = name.encode()
+        np_, nw, nc = len(params), len(wires), len(ctrl_wires)
+        p = (C.c_double * np_)(*params) if np_ else None
+        w = (C.c_int64 * nw)(*wires) if nw else None
+        if nc:
+            cw = (C.c_int64 * nc)(*ctrl_wires)
+            cv = (C.c_uint8 * nc)(*[1 if v else 0 for v in ctrl_values])
+        else:
+            cw = cv = None
+        rc = self._named(self.h, bname, p, np_, w, nw, 1 if inverse else 0, cw, cv, nc,
+                         pauli_word.encode() if pauli_word else None)
+        if rc != 0:
+            raise B200Error(self.L.b200sv_last_error().decode())
 
     def matrix_op(self, matrix, wires, inverse=False, ctrl_wires=(), ctrl_values=()):
         m = np.ascontiguousarray(np.asarray(matrix, dtype=np.complex128).reshape(-1))

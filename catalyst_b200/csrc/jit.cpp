@@ -497,6 +497,9 @@ const Kernel *Engine::lookup(int cuda_device, const std::string &key, int thresh
         p_->compile(*e);
         lk.lock();
         p_->finish_compile(*e);
+        // rank threads of one process share kernels (the key does not hold the rank): a peer that met this key
+        // while it was being compiled here waits on cv_done
+        p_->cv_done.notify_all();
         if (e->state == COMPILED) p_->make_ready(*e, cuda_device);
         return e->state == READY ? &e->k : nullptr;
     }

@@ -246,6 +246,11 @@ Simulator::~Simulator()
         if (ev_moved_[h]) cudaEventDestroy((cudaEvent_t)ev_moved_[h]);
     }
     if (xfer_stream_) cudaStreamDestroy((cudaStream_t)xfer_stream_);
+    collect_timing();
+    for (auto &p : ev_free_) {
+        cudaEventDestroy((cudaEvent_t)p.first);
+        cudaEventDestroy((cudaEvent_t)p.second);
+    }
     if (ev2_) cudaEventDestroy((cudaEvent_t)ev2_);
     if (ev3_) cudaEventDestroy((cudaEvent_t)ev3_);
     if (ev0_) cudaEventDestroy((cudaEvent_t)ev0_);
@@ -431,7 +436,11 @@ void Simulator::release()
     recording_ = false;
 }
 
-void Simulator::reset_stats() { stats_ = b200sv_stats{}; }
+void Simulator::reset_stats()
+{
+    collect_timing();
+    stats_ = b200sv_stats{};
+}
 
 double Simulator::fp64_peak()
 {
@@ -919,15 +928,40 @@ void Simulator::flush()
     NvtxRange nvtx("b200sv::flush");
     std::vector<GateOp> ops;
     ops.swap(queue_);
-    if (timing_) CUDA_CHECK(cudaEventRecord((cudaEvent_t)ev0_, (cudaStream_t)stream_));
+    // timing on (benchmarks): one CUDA-event pair per flush, read back LAZILY (stats() / synchronize) so that the
+    // host keeps enqueueing the next circuit while this one runs -- a synchronise per flush would serialise the
+    // host's gate calls with the device
+    std::pair<void *, void *> evp{nullptr, nullptr};
+    if (timing_) {
+        if (ev_free_.empty()) {
+            cudaEvent_t a, b;
+            CUDA_CHECK(cudaEventCreate(&a));
+            CUDA_CHECK(cudaEventCreate(&b));
+            ev_free_.push_back({a, b});
+        }
+        evp = ev_free_.back();
+        ev_free_.pop_back();
+        CUDA_CHECK(cudaEventRecord((cudaEvent_t)evp.first, (cudaStream_t)stream_));
+    }
     execute({psi_->d()}, pos_, ops);
     if (timing_) {
-        CUDA_CHECK(cudaEventRecord((cudaEvent_t)ev1_, (cudaStream_t)stream_));
-        CUDA_CHECK(cudaEventSynchronize((cudaEvent_t)ev1_));
-        float ms = 0;
-        CUDA_CHECK(cudaEventElapsedTime(&ms, (cudaEvent_t)ev0_, (cudaEvent_t)ev1_));
-        stats_.gate_device_ms += ms;
+        CUDA_CHECK(cudaEventRecord((cudaEvent_t)evp.second, (cudaStream_t)stream_));
+        ev_pending_.push_back(evp);
+        if (ev_pending_.size() > 256) collect_timing();
     }
+}
+
+void Simulator::collect_timing()
+{
+    for (auto &p : ev_pending_) {
+        if (cudaEventSynchronize((cudaEvent_t)p.second) == cudaSuccess) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, (cudaEvent_t)p.first, (cudaEvent_t)p.second) == cudaSuccess) stats_.gate_device_ms += ms;
+        }
+        ev_free_.push_back(p);
+    }
+    cudaGetLastError();
+    ev_pending_.clear();
 }
 
 void Simulator::synchronize()
@@ -2394,7 +2428,7 @@ void Simulator::d2h_strided(const void *dsrc, size_t elem_bytes, size_t count, v
         stats_.d2h_bytes += (double)total;
         return;
     }
-    const size_t CH = size_t(32) << 20; // bytes per staging buffer
+    const size_t CH = size_t(128) << 20; // bytes per staging buffer
     for (int h = 0; h < 2; h++)
         if (!stage_host_[h]) {
             CUDA_CHECK(cudaMallocHost(&stage_host_[h], CH));
@@ -2404,7 +2438,7 @@ void Simulator::d2h_strided(const void *dsrc, size_t elem_bytes, size_t count, v
         }
     const size_t per = CH / elem_bytes; // elements per chunk
     const size_t nchunks = (count + per - 1) / per;
-    unsigned nthreads = std::min(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
+    unsigned nthreads = std::min(16u, std::max(1u, std::thread::hardware_concurrency() - 2));
     auto drain = [&](size_t k) { // chunk k: staging buffer -> caller's memory
         const int h = (int)(k & 1);
         CUDA_CHECK(cudaEventSynchronize((cudaEvent_t)stage_ev_[h]));

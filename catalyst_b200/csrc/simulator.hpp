@@ -306,6 +306,8 @@ class Simulator {
     b200sv_stats stats_{};
     bool timing_ = false;
     void *ev0_ = nullptr, *ev1_ = nullptr, *ev2_ = nullptr, *ev3_ = nullptr;
+    std::vector<std::pair<void *, void *>> ev_free_, ev_pending_; // event pairs of timed flushes, read back lazily
+    void collect_timing();
 };
 
 Options parse_kwargs(const char *kwargs);

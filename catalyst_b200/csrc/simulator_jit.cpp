@@ -1060,6 +1060,7 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
 
 b200sv_stats Simulator::stats() const
 {
+    const_cast<Simulator *>(this)->collect_timing(); // resolves the CUDA-event pairs of the flushes so far (waits for them)
     b200sv_stats s = stats_;
     if (jit_mode_ != 0) {
         const jit::Counters c = jit::Engine::get().counters();

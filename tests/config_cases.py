@@ -133,6 +133,13 @@ FIXTURE_KEYS = {
 }
 
 
+def expval_err(got, ref, norm=1.0):
+    """Error of an expectation value relative to max(|ref|, ||O||): <O> of a near-maximally mixed marginal is
+    ~1e-4 while the rounding noise of the 2^n-term sum is set by ||O|| (1 for a Pauli word, sum |c_i| for a
+    Hamiltonian), so |ref| alone is the wrong yardstick for "1e-12 relative"."""
+    return abs(float(got) - float(ref)) / max(abs(float(ref)), float(norm))
+
+
 def rel_err(a, b):
     """max |a - b| relative to the largest magnitude of the reference b (the tolerance `north_star`
     states is relative: 1e-12)."""

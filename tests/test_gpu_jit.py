@@ -5,7 +5,7 @@ produced the result.  Same tolerance as the interpreted path: 1e-12 on amplitude
 import numpy as np
 import pytest
 
-from dsl import apply_ops, build_obs, random_circuit, random_state
+from dsl import assert_close, apply_ops, build_obs, random_circuit, random_state
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-12
@@ -183,7 +183,7 @@ def test_jit_gradient_and_expval(gpu, oracle_mod):
     ed, eo = d.expval(build_obs(d, obs)), o.expval(build_obs(o, obs))
     d.stop_tape(); o.stop_tape()
     assert abs(ed - eo) < 1e-12
-    assert np.max(np.abs(d.gradient() - o.gradient())) < 1e-11
+    assert_close(d.gradient(), o.gradient(), "jit: adjoint gradient")
     assert d.stats().jit_passes > 0
 
 

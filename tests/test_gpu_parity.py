@@ -5,7 +5,7 @@ outcomes and sample bitstrings."""
 import numpy as np
 import pytest
 
-from dsl import (apply_ops, build_obs, random_circuit, random_op, random_pauli_obs, random_state)
+from dsl import (apply_ops, assert_close, build_obs, random_circuit, random_op, random_pauli_obs, random_state)
 from golden import reference_cases as G
 
 pytestmark = pytest.mark.gpu
@@ -191,7 +191,7 @@ def test_expval_var_random_observables(gpu, oracle_mod, n, seed):
         eo, ed = o.expval(ko), d.expval(kd)
         assert abs(eo - ed) < TOL * max(1.0, abs(eo)), (obs, eo, ed)
         vo, vd = o.var(ko), d.var(kd)
-        assert abs(vo - vd) < 1e-11 * max(1.0, abs(vo)), (obs, vo, vd)
+        assert_close(vd, vo, "Var (random observables)")
 
 
 @pytest.mark.parametrize("n,seed", [(1, 0), (4, 1), (9, 2), (12, 3), (15, 4), (19, 5)])
@@ -256,7 +256,7 @@ def test_seeded_mid_circuit_measurements(gpu, oracle_mod, n, seed):
     p = o.probs([w])
     ps = int(p[1] > p[0])
     assert o.measure(w, ps) == d.measure(w, ps) == bool(ps)
-    assert np.max(np.abs(o.state() - d.state())) < 1e-11
+    assert_close(d.state(), o.state(), "state after measurement / relabelling")
     with pytest.raises(RuntimeError):
         d.measure(w, 1 - ps)  # probability of the other branch is now exactly 0
 
@@ -288,7 +288,7 @@ def test_seeded_pauli_measurements(gpu, oracle_mod, n, seed, cfg):
             out_o.append(o.measure(w))
             out_d.append(d.measure(w))
     assert out_o == out_d
-    assert np.max(np.abs(o.state() - d.state())) < 1e-11
+    assert_close(d.state(), o.state(), "state after measurement / relabelling")
     assert abs(np.linalg.norm(d.state()) - 1) < 1e-12
 
 
@@ -397,7 +397,7 @@ def test_shots_hermitian_observables(gpu, oracle_mod, n, seed):
         assert abs(eo - ed) < 1e-10 or (abs(eo - exact_e) < 5 * spread / np.sqrt(shots) and
                                           abs(ed - exact_e) < 5 * spread / np.sqrt(shots)), (eo, ed, exact_e)
     assert same >= 2
-    assert np.max(np.abs(o.state() - d.state())) < 1e-11
+    assert_close(d.state(), o.state(), "state after measurement / relabelling")
 
 
 # ---- adjoint gradient ----------------------------------------------------------------------------
@@ -524,9 +524,9 @@ def test_swap_relabelling(gpu, oracle_mod, n, seed, cfg):
     assert o.measure(n - 1) == d.measure(n - 1)
     more = [random_op(rng, n) for _ in range(10)]
     apply_ops(o, more); apply_ops(d, more)
-    assert np.max(np.abs(o.state() - d.state())) < 1e-11                      # State restores the order
+    assert_close(d.state(), o.state(), "state after measurement / relabelling")   # State restores the order
     # after State the relabelling is gone and everything still agrees
-    assert np.max(np.abs(o.probs() - d.probs())) < 1e-11
+    assert_close(d.probs(), o.probs(), "probs after relabelling")
 
 
 def test_swap_relabelling_with_tape_and_dynamic_qubits(gpu, oracle_mod):
@@ -542,7 +542,7 @@ def test_swap_relabelling_with_tape_and_dynamic_qubits(gpu, oracle_mod):
     eo, ed = o.expval(build_obs(o, obs)), d.expval(build_obs(d, obs))
     o.stop_tape(); d.stop_tape()
     assert abs(eo - ed) < TOL
-    assert np.max(np.abs(o.gradient() - d.gradient())) < 1e-11
+    assert_close(d.gradient(), o.gradient(), "adjoint gradient (closed-form cases)")
     # dynamic allocation on a relabelled register
     d2 = gpu.B200Device(3)
     apply_ops(d2, [("Hadamard", [], [0]), ("SWAP", [], [0, 2]), ("CNOT", [], [2, 1])])
@@ -600,7 +600,7 @@ def test_mcmc_sampling(gpu, oracle_mod, n, seed, kernel):
     eo, co = o.counts(shots, w[:2])
     ed, cd = d.counts(shots, w[:2])
     assert np.array_equal(co, cd) and np.array_equal(eo, ed)
-    assert np.max(np.abs(o.state() - d.state())) < 1e-11
+    assert_close(d.state(), o.state(), "state after measurement / relabelling")
     if n == 4:
         big = d.sample(200000)
         idx = (big.astype(np.int64) * (1 << np.arange(n - 1, -1, -1))).sum(axis=1)

@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 import rt_driver
-from dsl import apply_ops, build_obs, random_circuit, random_op, random_pauli_obs, random_state
+from dsl import assert_close, apply_ops, build_obs, random_circuit, random_op, random_pauli_obs, random_state
 from golden import reference_cases as G
 
 pytestmark = [pytest.mark.gpu,
@@ -49,7 +49,7 @@ def test_runtime_random_circuit(rt, oracle_mod, n, seed):
     for obs in obs_list:
         ko, kd = build_obs(o, obs), build_obs(d, obs)
         assert abs(o.expval(ko) - d.expval(kd)) < TOL * 10
-        assert abs(o.var(ko) - d.var(kd)) < 1e-10
+        assert_close(d.var(kd), o.var(ko), "plugin: Var")
     w = [int(x) for x in rng.permutation(n)[:max(1, n // 2)]]
     assert np.max(np.abs(o.probs(w) - d.probs(w))) < TOL
     assert np.max(np.abs(o.probs() - d.probs())) < TOL
@@ -121,7 +121,7 @@ def test_runtime_pauli_measure(rt, oracle_mod):
     apply_ops(d, ops)
     for word, wires, neg in [("XZ", [0, 3], False), ("YYX", [5, 1, 2], True), ("Z", [4], False), ("XIZY", [2, 0, 5, 3], True)]:
         assert d.pauli_measure(word, wires, negated=neg) == (o.pauli_measure(word, wires) != neg)
-    assert np.max(np.abs(o.state() - d.state())) < 1e-11
+    assert_close(d.state(), o.state(), "plugin: state after measurement")
 
 
 DIFF = ["RX", "RY", "RZ", "PhaseShift", "IsingXX", "IsingZZ", "CRX", "CRY", "CRZ", "ControlledPhaseShift",
@@ -260,7 +260,7 @@ def test_runtime_mbqc_measure_in_basis(rt, oracle_mod):
     for wire, post in [(0, -1), (3, -1), (1, 1), (4, -1)]:
         r = d.L.mbqc__measure_in_basis(d.q[wire], C.c_uint32(0), C.c_double(0.25), C.c_int32(post))
         assert bool(r[0]) == o.measure(wire, None if post < 0 else post)
-    assert np.max(np.abs(o.state() - d.state())) < 1e-11
+    assert_close(d.state(), o.state(), "plugin: state after measurement")
 
 
 def test_runtime_print_state(rt, capfd):

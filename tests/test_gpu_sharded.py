@@ -5,7 +5,7 @@ NCCL build — only the transport differs.  Every rank must return the same, ora
 import numpy as np
 import pytest
 
-from dsl import apply_ops, build_obs, random_circuit, random_pauli_obs, random_state
+from dsl import assert_close, apply_ops, build_obs, random_circuit, random_pauli_obs, random_state
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-12
@@ -83,7 +83,7 @@ def test_expval_var_probs(gpu, oracle_mod, world):
 
     for e, v, p, st in gpu.run_spmd(world, prog, tile_bits=5):
         assert np.max(np.abs(np.array(e) - want_e)) < TOL
-        assert np.max(np.abs(np.array(v) - want_v)) < 1e-11
+        assert_close(np.array(v), want_v, "sharded: Var")
         for a, b in zip(p, want_p):
             assert np.max(np.abs(a - b)) < TOL
         assert np.max(np.abs(st - o.state())) < TOL  # swaps made by the measurements are consistent
@@ -174,7 +174,7 @@ def test_adjoint_gradient(gpu, oracle_mod, world):
 
     for e, g, st in gpu.run_spmd(world, prog, tile_bits=5):
         assert np.max(np.abs(np.array(e) - want_e)) < TOL
-        assert np.max(np.abs(g - want_g)) < 1e-11
+        assert_close(g, want_g, "sharded: adjoint gradient")
         assert np.max(np.abs(st - o.state())) < TOL
 
 
@@ -220,7 +220,7 @@ def test_pauli_measure_sharded(gpu, oracle_mod, world):
 
     for m, st in gpu.run_spmd(world, prog, tile_bits=4, min_row_bits=2):
         assert m == want
-        assert np.max(np.abs(st - want_state)) < 1e-11
+        assert_close(st, want_state, "sharded: state after PauliMeasure")
 
 
 @pytest.mark.parametrize("world", [2, 4])

@@ -13,7 +13,7 @@ suites so that a surprise here cannot hide them under `pytest -x`."""
 import numpy as np
 import pytest
 
-from dsl import DynamicRegister, apply_ops, random_circuit
+from dsl import DynamicRegister, assert_close, apply_ops, random_circuit
 from golden import reference_cases as G
 
 pytestmark = pytest.mark.gpu
@@ -64,13 +64,13 @@ def test_release_matches_oracle(gpu, oracle_mod, n, seed, cfg):
     assert np.array_equal(o.sample(500), d.sample(500))
     tail = random_circuit(seed + 7, n, 20)
     apply_ops(o, tail); apply_ops(d, tail)
-    assert np.max(np.abs(o.state() - d.state())) < 1e-11
+    assert_close(d.state(), o.state(), "dynamic qubits: state")
     # a state that is not a product: the more probable branch is kept on both sides
     o.named_op("RY", [0.7], [0]); d.named_op("RY", [0.7], [0])
     if n > 1:
         o.named_op("CNOT", [], [0, n - 1]); d.named_op("CNOT", [], [0, n - 1])
         o.release_qubit(n - 1); d.release_qubit(n - 1)
-        assert np.max(np.abs(o.state() - d.state())) < 1e-11
+        assert_close(d.state(), o.state(), "dynamic qubits: state")
 
 
 def test_release_of_entangled_wire_is_an_error_by_default(gpu):
@@ -145,7 +145,7 @@ def test_dynamic_qubits_on_a_sharded_register(gpu, oracle_mod, world):
     for res, nq in gpu.run_spmd(world, prog, seed=37):
         assert nq == n
         for g, w in zip(res, want):
-            assert np.max(np.abs(g - w)) < 1e-11
+            assert_close(g, w, "dynamic qubits (runtime): probs")
 
 
 def test_dynamic_qubits_sharded_limits(gpu):
