@@ -394,37 +394,35 @@ struct Engine::Impl {
             if (stop) return;
             std::shared_ptr<Entry> e = jobs.front();
             jobs.pop_front();
+            active++;
             lk.unlock();
             compile_shared(*e);
             lk.lock();
             finish_compile(*e);
+            active--;
             ctr.pending--;
             cv_done.notify_all();
         }
     }
 
     // The engine is never destroyed (the library may be loaded RTLD_NODELETE), but a process must not run static
-    // destructors (NVRTC's among them) while a pool thread is still inside nvrtcCompileProgram: at exit the pool is
-    // told to stop, queued jobs are dropped and the threads are joined after their current compilation.
-    static void stop_pool_at_exit()
+    // destructors (NVRTC's among them) while a pool thread is still inside nvrtcCompileProgram: at exit queued
+    // jobs are dropped and the handler waits (bounded) until no compilation is in flight.  The threads themselves
+    // are left parked on their condition variable; the process is going away.
+    int active = 0; // compilations running on pool threads
+    static void quiesce_pool_at_exit()
     {
         Engine &E = Engine::get();
-        {
-            std::lock_guard<std::mutex> lk(E.p_->mu);
-            E.p_->stop = true;
-            E.p_->jobs.clear();
-        }
-        E.p_->cv_jobs.notify_all();
-        for (auto &t : E.p_->pool)
-            if (t.joinable()) t.join();
-        E.p_->pool.clear();
+        std::unique_lock<std::mutex> lk(E.p_->mu);
+        E.p_->jobs.clear(); // (no stop flag: a thread that exits now would run its TLS destructors during teardown)
+        E.p_->cv_done.wait_for(lk, std::chrono::seconds(30), [&] { return E.p_->active == 0; });
     }
 
     void ensure_pool()
     {
         if (!pool.empty()) return;
         static std::once_flag reg;
-        std::call_once(reg, [] { std::atexit(&Impl::stop_pool_at_exit); });
+        std::call_once(reg, [] { std::atexit(&Impl::quiesce_pool_at_exit); });
         unsigned n = std::thread::hardware_concurrency();
         if (const char *s = std::getenv("B200SV_JIT_THREADS")) n = (unsigned)std::atoi(s);
         n = n < 1 ? 1 : (n > 16 ? 16 : n);

@@ -66,6 +66,7 @@ struct JPlan {
     int nm = 0;
     std::vector<UAcc> uaccs;
     int nu = 0, uoff = 0; // uniform-table entries (8 doubles each) and their offset in the parameter doubles
+    int direct_store = 1; // option: the last round stores its registers straight to global memory
     int uniform = 1;      // option: evaluate tile-uniform diagonal factors once per tile
 };
 
@@ -402,6 +403,7 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
 
     // ---- rounds ------------------------------------------------------------------------------------
     int rix = 0;
+    bool direct_store = false;
     for (const JRound &R : P.rounds) {
         std::vector<int> rb, q;
         for (int b = 0; b < t; b++) ((R.S >> b) & 1u ? rb : q).push_back(b);
@@ -754,14 +756,40 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
             if (!cond.empty()) o << "      if (" << cond << ") {\n" << body << "      }\n";
             else o << "      {\n" << body << "      }\n";
         }
-        for (uint32_t k = 0; k < nslots; k++)
-            o << "      s[" << slot_expr("sb", pat[k]) << "] = make_double2(v" << k << "r, v" << k << "i);\n";
-        o << "    }\n    __syncthreads();\n";
+        // Last round: the 2^nr amplitudes go from registers straight to global memory (16 STS + 16 LDS + one
+        // barrier less per thread and tile: the light passes stall on the shared-memory instruction queue,
+        // profiles/r2_v1_pass_summary.txt).  Lane bits sit on the lowest non-register tile positions, so a warp
+        // still writes whole 32-byte sectors as long as tile position 0 is not a register bit.
+        const bool last = rix == (int)P.rounds.size();
+        direct_store = last && P.direct_store && !(R.S & 1u);
+        if (direct_store) {
+            o << "      const unsigned long long gib = 0ull";
+            for (int k = 0; k < (int)qq.size();) {
+                auto gpos = [&](int tp_) { return tp_ < c ? tp_ : P.high[tp_ - c]; };
+                int len = 1;
+                while (k + len < (int)qq.size() && qq[k + len] == qq[k] + len && gpos(qq[k + len]) == gpos(qq[k]) + len) len++;
+                const uint32_t m = ((1u << len) - 1u) << k;
+                const int sh = gpos(qq[k]) - k;
+                o << " | ((unsigned long long)(tid & " << hex32(m) << ")" << (sh > 0 ? " << " + std::to_string(sh) : (sh < 0 ? " >> " + std::to_string(-sh) : "")) << ")";
+                k += len;
+            }
+            o << ";\n";
+            o << "      cplx *__restrict__ gp = psi + (base | gib);\n";
+            for (uint32_t k = 0; k < nslots; k++)
+                o << "      gp[" << hex64(off_of(pat[k])) << "] = make_double2(v" << k << "r, v" << k << "i);\n";
+            o << "    }\n";
+        }
+        else {
+            for (uint32_t k = 0; k < nslots; k++)
+                o << "      s[" << slot_expr("sb", pat[k]) << "] = make_double2(v" << k << "r, v" << k << "i);\n";
+            o << "    }\n    __syncthreads();\n";
+        }
     }
     // ---- store -------------------------------------------------------------------------------------
-    for (uint32_t k = 0; k < niter; k++)
-        o << "    tp[" << hex64(off_of(k * TT)) << "] = s[" << slot_expr("swtid", k * TT) << "];\n";
-    o << "    __syncthreads();\n";
+    if (!direct_store)
+        for (uint32_t k = 0; k < niter; k++)
+            o << "    tp[" << hex64(off_of(k * TT)) << "] = s[" << slot_expr("swtid", k * TT) << "];\n";
+    o << "    __syncthreads();\n"; // every thread is done with this tile's buffer before it is refilled
     if (P.dbuf) o << "    cur ^= 1u;\n";
     o << "  }\n}\n";
 
@@ -928,6 +956,7 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
     }
     if (opt_.jit_factor) factor_scales(P);
     P.uniform = opt_.jit_uniform;
+    P.direct_store = opt_.jit_direct_store;
     analyze_uniform(P);
     for (JRound &R : P.rounds)
         for (JOp &o : R.ops) {
@@ -968,9 +997,10 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
     // structural key
     std::string key;
     key.reserve(64 + 64 * ops.size());
-    put(key, (int)9); // generator version
+    put(key, (int)10); // generator version
     put(key, P.fuse_diag);
     put(key, P.uniform);
+    put(key, P.direct_store);
     put(key, P.t); put(key, P.c); put(key, P.nr); put(key, P.nl); put(key, P.dbuf);
     for (int h : P.high) put(key, (uint8_t)h);
     for (const JRound &R : P.rounds) {

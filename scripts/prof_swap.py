@@ -1,12 +1,14 @@
 """Micro-benchmark of the global<->local qubit swap and of a tile pass on a sharded register, one process,
-one thread per GPU: `python scripts/prof_swap.py [n] [world] [p2p]`."""
+one thread per GPU: `python scripts/prof_swap.py [n] [world] [mode]`, mode = p2p (in-place pairwise kernel over mapped
+shards), push (one kernel writes into every peer's staging) or staged (pack -> device-to-device copies -> unpack)."""
 import sys, time, os
 R = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, R); sys.path.insert(0, os.path.join(R, "tests"))
 from catalyst_b200 import capi
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 32
 world = int(sys.argv[2]) if len(sys.argv) > 2 else 2
-p2p = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+mode = sys.argv[3] if len(sys.argv) > 3 else "p2p"
+kw = {"p2p": dict(p2p_swap=1, swap_push=0), "push": dict(p2p_swap=0, swap_push=1), "staged": dict(p2p_swap=0, swap_push=0)}[mode]
 g = world.bit_length() - 1
 
 
@@ -18,7 +20,8 @@ def prog(d, r):
             d.synchronize(); d.reset_stats()
             t0 = time.perf_counter(); fn(); d.synchronize(); dt = time.perf_counter() - t0
             s = d.stats()
-        out.append("rank %d %-34s %.1f ms  passes %d exchanges %d (p2p %d)" % (r, label, 1e3 * dt, s.tile_passes, s.exchanges, s.p2p_exchanges))
+        out.append("%s rank %d %-34s %.1f ms  passes %d exchanges %d (in-place %d, push %d) sent %.1f GiB" % (
+            mode, r, label, 1e3 * dt, s.tile_passes, s.exchanges, s.p2p_exchanges, s.swap_push_exchanges, s.exchange_bytes / 2**30))
     timed("local H (1 pass)", lambda: d.named_op("Hadamard", [], [n - 1]))
     timed("H on a middle local wire", lambda: d.named_op("Hadamard", [], [g + 1]))
     # a Hadamard on every wire needs every qubit local at some point: >= 1 swap per repetition
@@ -30,5 +33,5 @@ def prog(d, r):
     return out
 
 
-for lines in capi.run_spmd(world, prog, devices=list(range(world)), p2p_swap=p2p, jit="off"):
+for lines in capi.run_spmd(world, prog, devices=list(range(world)), jit="off", **kw):
     print("\n".join(lines))

@@ -253,14 +253,15 @@ def test_jit_disk_cache_across_processes(tmp_path):
         "d = capi.B200Device(16, jit_min_qubits=10, jit_threshold=1)\n"
         "apply_ops(d, workloads.c3_qft_random(16, layers=3)); d.synchronize(); d.jit_wait()\n"
         "d.set_basis_state([0]*16, list(range(16))); apply_ops(d, workloads.c3_qft_random(16, layers=3)); st = d.state()\n"
-        "s = d.stats()\n"
+        "s = d.stats(); d.close()\n"
         "print(json.dumps({'compiled': s.jit_compiled, 'disk': s.jit_disk_hits, 'jit_passes': s.jit_passes,\n"
         "                  'tile_passes': s.tile_passes, 'norm': float(abs((st.conj()*st).sum())), 'a0': [st[5].real, st[5].imag]}))\n"
     ) % (root, os.path.join(root, "tests"))
     env = dict(os.environ, B200SV_JIT_CACHE=str(tmp_path / "cache"), B200SV_JIT="auto")
     runs = []
     for _ in range(2):
-        out = subprocess.run([sys.executable, "-c", prog], env=env, capture_output=True, text=True, timeout=600)
+        out = subprocess.run([sys.executable, "-X", "faulthandler", "-c", prog], env=env, capture_output=True, text=True,
+                             timeout=600)
         assert out.returncode == 0, out.stderr[-2000:]
         runs.append(json.loads(out.stdout.strip().splitlines()[-1]))
     first, second = runs

@@ -36,17 +36,24 @@ def _worker(rank, world, uid, n, ops, obs_list, q, kwargs=None):
         m = d.measure(0)
         smp = d.sample(200, [1, 2, n - 1])
         st = d.state()
-        q.put((rank, e, p, m, smp, st, d.stats().exchanges, None))
+        s = d.stats()
+        q.put((rank, e, p, m, smp, st, (s.exchanges, s.swap_push_exchanges, s.p2p_exchanges), None))
         d.close()
     except BaseException as ex:  # noqa: BLE001
-        q.put((rank, None, None, None, None, None, 0, repr(ex)))
+        q.put((rank, None, None, None, None, None, (0, 0, 0), repr(ex)))
 
 
-@pytest.mark.parametrize("world,n,kwargs", [(2, 14, None), (4, 14, None), (8, 14, None),
-                                            # 1 MiB staging buffer at 18 qubits: every qubit swap runs as
-                                            # several pipelined chunks (pack k+1 / transfer k / unpack k-1)
-                                            (2, 18, {"stage_mib": 1, "p2p_swap": 0}),
-                                            (4, 18, {"stage_mib": 1, "p2p_swap": 0})])
+@pytest.mark.parametrize("world,n,kwargs", [
+    # default over NCCL process groups: the push-mode swap (one kernel writes into every peer's staging, mapped
+    # through CUDA IPC)
+    (2, 14, None), (4, 14, None), (8, 14, None),
+    # 1 MiB staging at 18 qubits: every swap runs as several chunks -- push mode (both staging halves, the trailing
+    # unpack-only round) and the staged NCCL path (pack k+1 / ncclSend+ncclRecv k / unpack k-1)
+    (2, 18, {"stage_mib": 1}), (4, 18, {"stage_mib": 1}), (8, 18, {"stage_mib": 1}),
+    (2, 18, {"stage_mib": 1, "p2p_swap": 0, "swap_push": 0}), (4, 18, {"stage_mib": 1, "p2p_swap": 0, "swap_push": 0}),
+    (8, 16, {"p2p_swap": 0, "swap_push": 0}),
+    # the in-place pairwise kernel over the peers' mapped shards
+    (2, 14, {"p2p_swap": 1, "swap_push": 0}), (8, 14, {"p2p_swap": 1, "swap_push": 0})])
 def test_nccl_ranks_match_oracle(oracle_mod, world, n, kwargs):
     if _ngpus() < world:
         pytest.skip(f"needs {world} GPUs")
@@ -77,4 +84,9 @@ def test_nccl_ranks_match_oracle(oracle_mod, world, n, kwargs):
         assert m == want_m
         assert np.array_equal(smp, want_s)
         assert np.max(np.abs(st - want_st)) < 1e-12
-        assert nx > 0
+        assert nx[0] > 0
+        kw = kwargs or {}
+        if kw.get("swap_push", -1) != 0 and not kw.get("p2p_swap", 0):
+            assert nx[1] == nx[0], f"expected every swap in push mode, got {nx}"
+        print(f"[nccl parity] world={world} n={n} {kw}: swaps (all, push, in-place) = {nx}, "
+              f"max state err {np.max(np.abs(st - want_st)):.2e}")

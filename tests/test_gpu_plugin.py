@@ -175,7 +175,7 @@ def test_runtime_strided_and_offset_memrefs(rt, oracle_mod):
     ops = random_circuit(21, n, 40)
     init = random_state(5, n)
     o = oracle_mod.OracleDevice(n, seed=11)
-    d = rt(n, seed=11, shots=shots)
+    d = rt(n, seed=11)                                       # analytic device: State, Probs, PartialProbs
     L = d.L
     # SetState from a strided complex view: element i at base[3 + 2 i]
     src = np.full(3 + 2 * (1 << n), 7.0 + 7.0j, dtype=np.complex128)
@@ -207,7 +207,13 @@ def test_runtime_strided_and_offset_memrefs(rt, oracle_mod):
     mr = _strided_memref(rt_driver.MR_d1, C.c_double, pp, 2, [8], [5])
     L.qis__Probs(C.byref(mr), C.c_int64(3), *[d.q[x] for x in w])
     assert np.max(np.abs(pp[2::5][:8] - o.probs(w))) < TOL
-    # Sample into a column-major-like 2-D view: element (s, k) at base[7 + s * 2 + k * (2 * shots + 3)]
+    d.close()
+    # Sample (a device with shots) into a column-major-like 2-D view: element (s, k) at base[7 + 2 s + k (2 shots + 3)]
+    o = oracle_mod.OracleDevice(n, seed=11)
+    d = rt(n, seed=11, shots=shots)
+    L = d.L
+    apply_ops(o, ops)
+    apply_ops(d, ops)
     st1 = 2 * shots + 3
     sd = np.full(7 + 2 * shots + n * st1, -1.0)
     mr = _strided_memref(rt_driver.MR_d2, C.c_double, sd, 7, [shots, n], [2, st1])

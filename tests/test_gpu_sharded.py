@@ -190,8 +190,11 @@ def test_sharded_errors(gpu):
         with pytest.raises(gpu.B200Error):
             d.allocate_qubits(3)  # 8 ranks need >= 6 qubits
         d.allocate_qubits(6)
+        d.allocate_qubit()                     # dynamic allocation works on a sharded register (a new local bit)
+        assert d.num_qubits() == 7
+        d.release_qubit(6)
         with pytest.raises(gpu.B200Error):
-            d.allocate_qubit()
+            d.release_qubit(0)                 # ... but 8 ranks keep at least 6 qubits
         return True
 
     assert all(gpu.run_spmd(8, prog))
