@@ -15,7 +15,9 @@
 #include <sstream>
 #include <thread>
 
+#include <execinfo.h>
 #include <fcntl.h>
+#include <signal.h>
 #include <sys/stat.h>
 #include <sys/types.h>
 #include <unistd.h>
@@ -65,8 +67,23 @@ template <typename F> bool sym(void *h, const char *name, F &out, std::string &w
     return out != nullptr;
 }
 
+// $B200SV_DEBUG_SEGV=1 (diagnosis): print a native backtrace on SIGSEGV / SIGABRT, then leave with the usual code
+void debug_fault_handler(int sig)
+{
+    void *frames[64];
+    const int n = backtrace(frames, 64);
+    const char msg[] = "[b200sv] fatal signal, native backtrace:\n";
+    (void)!write(2, msg, sizeof msg - 1);
+    backtrace_symbols_fd(frames, n, 2);
+    _exit(128 + sig);
+}
+
 void load_api(Api &a)
 {
+    if (std::getenv("B200SV_DEBUG_SEGV")) {
+        signal(SIGSEGV, debug_fault_handler);
+        signal(SIGABRT, debug_fault_handler);
+    }
     const char *env = std::getenv("B200SV_NVRTC");
     const char *nvrtc_names[] = {env ? env : "libnvrtc.so.12", "libnvrtc.so.12", "/usr/local/cuda/lib64/libnvrtc.so.12",
                                  "/usr/local/cuda/lib64/libnvrtc.so", "libnvrtc.so"};

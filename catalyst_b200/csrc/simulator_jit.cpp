@@ -66,7 +66,7 @@ struct JPlan {
     int nm = 0;
     std::vector<UAcc> uaccs;
     int nu = 0, uoff = 0; // uniform-table entries (8 doubles each) and their offset in the parameter doubles
-    int direct_store = 1; // option: the last round stores its registers straight to global memory
+    int direct_store = 0; // option: the last round stores its registers straight to global memory
     int uniform = 1;      // option: evaluate tile-uniform diagonal factors once per tile
 };
 

@@ -257,12 +257,12 @@ def test_jit_disk_cache_across_processes(tmp_path):
         "print(json.dumps({'compiled': s.jit_compiled, 'disk': s.jit_disk_hits, 'jit_passes': s.jit_passes,\n"
         "                  'tile_passes': s.tile_passes, 'norm': float(abs((st.conj()*st).sum())), 'a0': [st[5].real, st[5].imag]}))\n"
     ) % (root, os.path.join(root, "tests"))
-    env = dict(os.environ, B200SV_JIT_CACHE=str(tmp_path / "cache"), B200SV_JIT="auto")
+    env = dict(os.environ, B200SV_JIT_CACHE=str(tmp_path / "cache"), B200SV_JIT="auto", B200SV_DEBUG_SEGV="1")
     runs = []
     for _ in range(2):
         out = subprocess.run([sys.executable, "-X", "faulthandler", "-c", prog], env=env, capture_output=True, text=True,
                              timeout=600)
-        assert out.returncode == 0, out.stderr[-2000:]
+        assert out.returncode == 0, (out.stdout[-600:], out.stderr[-3000:])
         runs.append(json.loads(out.stdout.strip().splitlines()[-1]))
     first, second = runs
     assert first["compiled"] > 0 and first["disk"] == 0
