@@ -418,6 +418,10 @@ struct Engine::Impl {
             finish_compile(*e);
             active--;
             ctr.pending--;
+            {
+                static std::once_flag late;
+                std::call_once(late, [] { std::atexit(&Impl::quiesce_pool_at_exit); });
+            }
             cv_done.notify_all();
         }
     }
@@ -427,13 +431,24 @@ struct Engine::Impl {
     // jobs are dropped and the handler waits (bounded) until no compilation is in flight.  The threads themselves
     // are left parked on their condition variable; the process is going away.
     int active = 0; // compilations running on pool threads
-    static void quiesce_pool_at_exit()
+    // Drop queued compilations (their entries go back to "seen", so a later device resubmits them) and wait,
+    // bounded, until no pool thread is inside NVRTC.  Called when the LAST device object of the process is
+    // destroyed and again from atexit: a process must not run exit-time destructors (NVRTC registers some
+    // lazily, during its first compilation, i.e. AFTER any handler registered here) while a pool thread is
+    // still inside nvrtcCompileProgram -- seen on the GPU box as SIGSEGV at exit of a short-lived process
+    // whose last call (State() restoring the wire order) had just submitted a new pass structure.
+    void quiesce(int max_seconds)
     {
-        Engine &E = Engine::get();
-        std::unique_lock<std::mutex> lk(E.p_->mu);
-        E.p_->jobs.clear(); // (no stop flag: a thread that exits now would run its TLS destructors during teardown)
-        E.p_->cv_done.wait_for(lk, std::chrono::seconds(30), [&] { return E.p_->active == 0; });
+        std::unique_lock<std::mutex> lk(mu);
+        for (auto &e : jobs) {
+            e->state = SEEN;
+            ctr.pending--;
+        }
+        jobs.clear();
+        cv_done.notify_all();
+        cv_done.wait_for(lk, std::chrono::seconds(max_seconds), [&] { return active == 0; });
     }
+    static void quiesce_pool_at_exit() { Engine::get().p_->quiesce(30); }
 
     void ensure_pool()
     {
@@ -551,6 +566,8 @@ int Engine::launch(const Kernel &k, unsigned grid, double *psi, const double *m,
     return p_->api.cuLaunchKernel(k.fn, grid, 1, 1, (unsigned)k.threads, 1, 1, (unsigned)k.smem_bytes, stream, args,
                                   nullptr);
 }
+
+void Engine::quiesce() { p_->quiesce(60); }
 
 void Engine::wait_all()
 {

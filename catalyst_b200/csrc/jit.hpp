@@ -72,6 +72,8 @@ class Engine {
     // launch with parameter block = { psi pointer, m[param_doubles] }
     int launch(const Kernel &k, unsigned grid, double *psi, const double *m, void *stream);
     void wait_all(); // block until no compilation is pending
+    // cancel queued compilations and wait for the running ones (last device of the process going away, exit)
+    void quiesce();
     Counters counters();
     int sm_count(int cuda_device);
     // last generated source of a key (debugging / tests)

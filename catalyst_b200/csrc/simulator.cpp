@@ -11,6 +11,7 @@
 #include <nvtx3/nvToolsExt.h> // header-only; a no-op unless a profiler injects its library
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -3290,6 +3291,7 @@ using b200::Simulator;
 struct b200sv_device {
     std::unique_ptr<Simulator> sim;
 };
+static std::atomic<int> g_live_devices{0};
 
 static thread_local std::string g_err;
 
@@ -3328,6 +3330,7 @@ b200sv_device *b200sv_create(const char *kwargs)
     try {
         auto d = std::make_unique<b200sv_device>();
         d->sim = std::make_unique<Simulator>(b200::parse_kwargs(kwargs));
+        g_live_devices.fetch_add(1);
         return d.release();
     }
     catch (const std::exception &e) {
@@ -3352,7 +3355,10 @@ void b200sv_destroy(b200sv_device *d)
         catch (...) {
         }
     }
+    const bool jit_used = d->sim->uses_jit();
     delete d;
+    // the last device of the process: no background compilation may outlive it (see jit::Engine::quiesce)
+    if (g_live_devices.fetch_sub(1) == 1 && jit_used) b200::jit_quiesce();
 }
 
 int b200sv_allocate_qubits(b200sv_device *d, int64_t n) { B200_TRY(d->sim->allocate(n)) }

@@ -186,6 +186,7 @@ class Simulator {
     void flush();
     void synchronize();
     void jit_wait(); // block until no specialised pass is being compiled
+    bool uses_jit() const { return jit_mode_ != 0 && !dry_; }
     void *device_pointer();
     int world() const { return opt_.world; }
     int rank() const { return opt_.rank; }
@@ -313,5 +314,6 @@ class Simulator {
 };
 
 Options parse_kwargs(const char *kwargs);
+void jit_quiesce(); // simulator_jit.cpp: cancel queued background compilations, wait for the running ones
 
 } // namespace b200

@@ -1102,6 +1102,8 @@ b200sv_stats Simulator::stats() const
     return s;
 }
 
+void jit_quiesce() { jit::Engine::get().quiesce(); }
+
 void Simulator::jit_wait()
 {
     if (jit_mode_ != 0) jit::Engine::get().wait_all();
