@@ -1366,3 +1366,81 @@ extern "C" int b200k_nonzero_indices(const double *psi, int n, double eps, int64
     }
     return (int)cudaStreamSynchronize((cudaStream_t)stream);
 }
+
+// =================================================================================================
+// Allocation-free variant of b200k_bilinear_pauli (no counterpart in the reference).
+// Some callers cannot call cudaMalloc: code under CUDA graph capture, tight serving
+// loops, harnesses that forbid it.  The reduction scratch (the per-block partials the plain entry point takes
+// from the caller) lives in a file-scope device array instead: B200K_NOALLOC_SCRATCH_DOUBLES doubles =
+// 18 944 bytes, held by every GPU that loads this library until the process exits.
+//   * In HOST code the array's name is a host-side stand-in, not a device address.  Its device address is
+//     resolved with cudaGetSymbolAddress once per device, with that device current, and cached per ordinal.
+//   * Nothing in the array must start at zero: every block of k_bilinear_pauli stores its own partial slot
+//     before k_reduce_final (next on the same stream) reads exactly those slots, so the previous call's
+//     leftovers are never read.
+//   * ALL calls share the array: calls that overlap on the GPU (different streams, or different host threads
+//     on the same device without stream ordering between them) race on it.  Order them on one stream.
+//   * This function calls no cudaMalloc / cudaFree / allocating library routine.  The first call on a device
+//     resolves the symbol (which may load the module lazily): make one call outside graph capture first.
+// =================================================================================================
+static __device__ __align__(256) double g_noalloc_scratch[B200K_NOALLOC_SCRATCH_DOUBLES];
+
+static void noalloc_err(char *buf, int64_t cap, const char *msg)
+{
+    if (!buf || cap <= 0) return;
+    int64_t i = 0;
+    for (; msg[i] && i < cap - 1; i++) buf[i] = msg[i];
+    buf[i] = 0;
+}
+
+extern "C" int b200k_bilinear_pauli_noalloc(const double *phi, const double *lam, int n_local, uint64_t rank_base,
+                                            uint64_t xmask, uint64_t zmask, int ny, uint64_t cmask, uint64_t cval,
+                                            double *out, void *stream, char *errbuf, int64_t errcap)
+{
+    static_assert(B200K_NOALLOC_SCRATCH_DOUBLES >= RED_BLOCKS * RED_MAXVALS, "no-alloc scratch smaller than the reduction grid");
+    noalloc_err(errbuf, errcap, "");
+    if (!phi || !lam || !out) {
+        noalloc_err(errbuf, errcap, "b200k_bilinear_pauli_noalloc: null input / output pointer");
+        return (int)cudaErrorInvalidValue;
+    }
+    if (n_local < 0 || n_local > B200K_NOALLOC_MAX_LOCAL_QUBITS) {
+        noalloc_err(errbuf, errcap, "b200k_bilinear_pauli_noalloc: n_local outside 0.." B200K_STR(B200K_NOALLOC_MAX_LOCAL_QUBITS)
+                                    " (the static scratch serves vectors of at most 2^" B200K_STR(B200K_NOALLOC_MAX_LOCAL_QUBITS)
+                                    " amplitudes)");
+        return (int)cudaErrorInvalidValue;
+    }
+    if (xmask >> n_local) {
+        noalloc_err(errbuf, errcap, "b200k_bilinear_pauli_noalloc: xmask has bits outside the local index");
+        return (int)cudaErrorInvalidValue;
+    }
+    const uint64_t work = xmask ? (1ull << (n_local > 0 ? n_local - 1 : 0)) : (1ull << n_local);
+    const int nb = red_blocks_for(work);
+    if ((int64_t)nb * RED_MAXVALS > (int64_t)B200K_NOALLOC_SCRATCH_DOUBLES) {
+        noalloc_err(errbuf, errcap, "b200k_bilinear_pauli_noalloc: reduction needs more partial slots than the static scratch holds");
+        return (int)cudaErrorInvalidValue;
+    }
+    // device address of the array: once per device, with that device current
+    static std::atomic<double *> dev_ptr[64];
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) {
+        noalloc_err(errbuf, errcap, "b200k_bilinear_pauli_noalloc: no current CUDA device (or ordinal >= 64)");
+        return (int)(e != cudaSuccess ? e : cudaErrorInvalidDevice);
+    }
+    double *scratch = dev_ptr[dev].load(std::memory_order_acquire);
+    if (!scratch) {
+        e = cudaGetSymbolAddress((void **)&scratch, g_noalloc_scratch);
+        if (e != cudaSuccess || !scratch) {
+            cudaGetLastError();
+            noalloc_err(errbuf, errcap, "b200k_bilinear_pauli_noalloc: cudaGetSymbolAddress of the static scratch failed");
+            return (int)(e != cudaSuccess ? e : cudaErrorInvalidSymbol);
+        }
+        dev_ptr[dev].store(scratch, std::memory_order_release); // the same value whichever thread stores it
+    }
+    k_bilinear_pauli<<<nb, RED_THREADS, 0, (cudaStream_t)stream>>>((const cplx *)phi, (const cplx *)lam, n_local, rank_base,
+                                                                   xmask, zmask, ny, cmask, cval, scratch);
+    k_reduce_final<2><<<1, RED_THREADS, 0, (cudaStream_t)stream>>>(scratch, nb, out);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) noalloc_err(errbuf, errcap, cudaGetErrorString(e));
+    return (int)e;
+}

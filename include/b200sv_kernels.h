@@ -156,6 +156,24 @@ int b200k_bilinear_pauli(const double *phi, const double *lam, int n_local, uint
                          uint64_t xmask, uint64_t zmask, int ny, uint64_t cmask, uint64_t cval,
                          double *scratch, double *out, void *stream);
 
+/* Allocation-free variant of b200k_bilinear_pauli.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, same result in out[0..1] (device), but the reduction scratch is a file-scope
+ * `static __device__` array of B200K_NOALLOC_SCRATCH_DOUBLES doubles (18 944 bytes, held by every GPU that loads
+ * the library until exit) instead of a caller buffer; no cudaMalloc / cudaFree / allocating routine is called.
+ * Limit: 0 <= n_local <= B200K_NOALLOC_MAX_LOCAL_QUBITS; anything else (or a null pointer, or xmask outside the
+ * local index) returns cudaErrorInvalidValue and, when errbuf != NULL, a message in errbuf[0..errcap).
+ * All calls share the array: calls that OVERLAP on the GPU race on it -- order them on one stream.  The array
+ * keeps the previous call's contents; nothing in it needs to start at zero (every slot read was written by the
+ * same call).  The first call on a device resolves the array's address: make it outside graph capture. */
+#define B200K_NOALLOC_SCRATCH_DOUBLES 2368 /* 1184 blocks x 2 partials */
+#define B200K_NOALLOC_MAX_LOCAL_QUBITS 36
+#define B200K_STR_(x) #x
+#define B200K_STR(x) B200K_STR_(x)
+int b200k_bilinear_pauli_noalloc(const double *phi, const double *lam, int n_local, uint64_t rank_base,
+                                 uint64_t xmask, uint64_t zmask, int ny, uint64_t cmask, uint64_t cval,
+                                 double *out, void *stream, char *errbuf, int64_t errcap);
+
 /* out[0..1] = sum over base indices i (tmask bits zero, control predicate true) of
  * [phi_{i|a}, phi_{i|b}]^dagger * g(2x2, row-major complex) * [lam_{i|a}, lam_{i|b}]^T. */
 int b200k_bilinear_pair(const double *phi, const double *lam, int n_local, uint64_t rank_base,
