@@ -44,12 +44,13 @@ def _worker(rank, world, uid, n, ops, obs_list, q, kwargs=None):
 
 
 @pytest.mark.parametrize("world,n,kwargs", [
-    # default over NCCL process groups: the push-mode swap (one kernel writes into every peer's staging, mapped
-    # through CUDA IPC)
+    # automatic policy: pairwise swaps (every swap at world 2) run in push mode, swaps that span more ranks staged
     (2, 14, None), (4, 14, None), (8, 14, None),
+    # push mode forced (one kernel writes into every peer's staging, mapped through CUDA IPC) at 4 and 8 ranks
+    (4, 14, {"swap_push": 1}), (8, 14, {"swap_push": 1}),
     # 1 MiB staging at 18 qubits: every swap runs as several chunks -- push mode (both staging halves, the trailing
     # unpack-only round) and the staged NCCL path (pack k+1 / ncclSend+ncclRecv k / unpack k-1)
-    (2, 18, {"stage_mib": 1}), (4, 18, {"stage_mib": 1}), (8, 18, {"stage_mib": 1}),
+    (2, 18, {"stage_mib": 1, "swap_push": 1}), (4, 18, {"stage_mib": 1, "swap_push": 1}), (8, 18, {"stage_mib": 1, "swap_push": 1}),
     (2, 18, {"stage_mib": 1, "p2p_swap": 0, "swap_push": 0}), (4, 18, {"stage_mib": 1, "p2p_swap": 0, "swap_push": 0}),
     (8, 16, {"p2p_swap": 0, "swap_push": 0}),
     # the in-place pairwise kernel over the peers' mapped shards
@@ -86,7 +87,9 @@ def test_nccl_ranks_match_oracle(oracle_mod, world, n, kwargs):
         assert np.max(np.abs(st - want_st)) < 1e-12
         assert nx[0] > 0
         kw = kwargs or {}
-        if kw.get("swap_push", -1) != 0 and not kw.get("p2p_swap", 0):
+        if kw.get("swap_push", -1) == 1 or (not kw and world == 2):
             assert nx[1] == nx[0], f"expected every swap in push mode, got {nx}"
+        if kw.get("swap_push", -1) == 0:
+            assert nx[1] == 0
         print(f"[nccl parity] world={world} n={n} {kw}: swaps (all, push, in-place) = {nx}, "
               f"max state err {np.max(np.abs(st - want_st)):.2e}")
