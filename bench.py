@@ -270,11 +270,17 @@ def e2e_plugin_single(args, n, ops, ngates):
     apply_ops(d, ops)
     d.probs(out=probs_out)                               # untimed: buffers, kernels from the process-wide cache
     n_before = len(read_stats_lines(stats_path))
+    split_a = [0.0, 0.0, 0.0]
     t0 = time.perf_counter()
     for _ in range(args.steps):
+        t1 = time.perf_counter()
         d.reset()
+        t2 = time.perf_counter()
         apply_ops(d, ops)
+        t3 = time.perf_counter()
         d.probs(out=probs_out)
+        t4 = time.perf_counter()
+        split_a = [split_a[0] + t2 - t1, split_a[1] + t3 - t2, split_a[2] + t4 - t3]
     ta = (time.perf_counter() - t0) / args.steps
     d.close()
     lines_a = read_stats_lines(stats_path)[n_before:]
@@ -284,11 +290,17 @@ def e2e_plugin_single(args, n, ops, ngates):
     apply_ops(d, ops)
     d.sample(SHOTS, out=sample_out)
     n_before = len(read_stats_lines(stats_path))
+    split_b = [0.0, 0.0, 0.0]
     t0 = time.perf_counter()
     for _ in range(args.steps):
+        t1 = time.perf_counter()
         d.reset()
+        t2 = time.perf_counter()
         apply_ops(d, ops)
+        t3 = time.perf_counter()
         d.sample(SHOTS, out=sample_out)
+        t4 = time.perf_counter()
+        split_b = [split_b[0] + t2 - t1, split_b[1] + t3 - t2, split_b[2] + t4 - t3]
     tb = (time.perf_counter() - t0) / args.steps
     d.close()
     lines_b = read_stats_lines(stats_path)[n_before:]
@@ -314,6 +326,11 @@ def e2e_plugin_single(args, n, ops, ngates):
                     f"Sample({SHOTS} shots) into a host array",
         "run_a_probs_ms": 1e3 * ta, "run_b_sample_ms": 1e3 * tb,
         "run_a_gates_per_s": ngates / ta, "run_b_gates_per_s": ngates / tb,
+        "host_split_ms": {
+            "note": "wall time on the host per program: release + device_release + device_init + allocate | the gate "
+                    "calls (they only enqueue; the GPU starts at the first flush) | the measurement call (waits for the "
+                    "circuit, then reduces / samples and copies device -> host)",
+            "run_a": [1e3 * x / args.steps for x in split_a], "run_b": [1e3 * x / args.steps for x in split_b]},
         "bytes_source": "counted by the device library ($B200SV_STATS_FILE): kernel parameter blocks, sampler "
                         "uniforms (H2D); probabilities, sampled indices, reduction scalars (D2H)",
         "check": {"probs_sum": res["probs_mass"], "sample_mean": float(sample_out.mean())}})

@@ -8,6 +8,9 @@
 #include "comm.hpp"
 
 #include <cuda_runtime.h>
+#if defined(__x86_64__)
+#include <immintrin.h>
+#endif
 #include <nvtx3/nvToolsExt.h> // header-only; a no-op unless a profiler injects its library
 
 #include <algorithm>
@@ -15,6 +18,9 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <functional>
+#include <condition_variable>
 #include <sstream>
 #include <thread>
 
@@ -49,8 +55,17 @@ class DeviceBuffer {
     static bool dry; // B200SV_DRYRUN (development): plan + generate + compile only, no device memory
     explicit DeviceBuffer(size_t bytes) : bytes_(bytes)
     {
-        if (dry) p_ = std::malloc(64);
-        else CUDA_CHECK(cudaMalloc(&p_, bytes ? bytes : 16));
+        if (dry) {
+            p_ = std::malloc(64);
+            return;
+        }
+        cudaError_t e = cudaMalloc(&p_, bytes ? bytes : 16);
+        if (e == cudaErrorMemoryAllocation) { // buffers kept across ReleaseQubits by ANY device object of the process go first
+            cudaGetLastError();
+            Simulator::trim_kept_buffers();
+            e = cudaMalloc(&p_, bytes ? bytes : 16);
+        }
+        CUDA_CHECK(e);
     }
     ~DeviceBuffer()
     {
@@ -69,6 +84,25 @@ class DeviceBuffer {
 };
 
 bool DeviceBuffer::dry = false;
+
+// ---- allocations kept across ReleaseQubits -------------------------------------------------------------------
+// Catalyst's runtime pools device objects: a program is device_init -> AllocateQubits -> ... -> ReleaseQubits ->
+// device_release, and the next execution of the same program gets the same object back.  Freeing and re-allocating
+// the state (16 GiB at 30 qubits) and the |psi|^2 buffer (8 GiB) costs ~10 ms per execution, so a released device
+// KEEPS them for an allocation of the same size (kwarg keep_allocation, default on).  Kept buffers are not lost
+// memory: any cudaMalloc of this library that fails first frees every kept buffer of every device object in the
+// process (except shards that peers still map) and retries.
+static std::mutex g_keep_mu;
+static std::vector<Simulator *> g_sims;
+
+void Simulator::trim_kept_buffers()
+{
+    std::lock_guard<std::mutex> lk(g_keep_mu);
+    for (Simulator *sim : g_sims) {
+        if (!sim->psi_keep_mapped_) sim->psi_keep_.reset();
+        sim->probs_keep_.reset();
+    }
+}
 
 // -------------------------------------------------------------------------------------------------
 Options parse_kwargs(const char *kwargs)
@@ -130,6 +164,7 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "adaptive_rows") o.adaptive_rows = as_int(1) != 0;
         else if (k == "virtual_swap") o.virtual_swap = as_int(1) != 0;
         else if (k == "batch_overlaps") o.batch_overlaps = as_int(1) != 0;
+        else if (k == "keep_allocation") o.keep_allocation = as_int(1) != 0;
         else if (k == "release_entangled") {
             B200_FAIL_IF(v != "error" && v != "project", "release_entangled must be 'error' or 'project'");
             o.release_project = v == "project";
@@ -210,6 +245,7 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
     CUDA_CHECK(cudaMallocHost((void **)&pinned_, pinned_doubles_ * sizeof(double)));
     scratch_ = std::make_unique<DeviceBuffer>((size_t)b200k_reduce_scratch_doubles() * sizeof(double));
     results_ = std::make_unique<DeviceBuffer>(4096 * sizeof(double));
+    if (const char *e = std::getenv("B200SV_KEEP_ALLOC")) opt_.keep_allocation = std::atoi(e) != 0;
     while ((1 << g_) < opt_.world) g_++;
     if (opt_.world > 1) {
         try {
@@ -219,6 +255,9 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
             B200_FAIL(std::string("b200sv: cannot join the rank group: ") + e.what());
         }
     }
+    // last: a constructor that throws does not run the destructor, so nothing may fail after the registration
+    std::lock_guard<std::mutex> lk(g_keep_mu);
+    g_sims.push_back(this);
 }
 
 Simulator::~Simulator()
@@ -229,7 +268,12 @@ Simulator::~Simulator()
     drop_psi_peers();
     if (stage_peers_ok_ && comm_) comm_->unmap_peers(stage_peers_ptr_); // no rendezvous in a destructor
     psi_.reset();
-    psi_keep_.reset();
+    {
+        std::lock_guard<std::mutex> lk(g_keep_mu);
+        g_sims.erase(std::remove(g_sims.begin(), g_sims.end(), this), g_sims.end());
+        psi_keep_.reset();
+        probs_keep_.reset();
+    }
     tmp_.reset();
     acc_.reset();
     stage_.reset();
@@ -240,7 +284,7 @@ Simulator::~Simulator()
     misc_.reset();
     matrix_arena_.reset();
     if (pinned_) cudaFreeHost(pinned_);
-    for (int h = 0; h < 2; h++) {
+    for (int h = 0; h < kStage; h++) {
         if (stage_host_[h]) cudaFreeHost(stage_host_[h]);
         if (stage_ev_[h]) cudaEventDestroy((cudaEvent_t)stage_ev_[h]);
     }
@@ -288,11 +332,18 @@ void Simulator::allocate(int64_t n)
     try {
         // a shard whose peers hold a mapping of it (peer-to-peer qubit swap) is kept across
         // release/allocate of the same size, so the mapping stays valid
-        if (psi_keep_ && psi_keep_->bytes() == bytes) psi_ = std::move(psi_keep_);
-        else {
+        {
+            std::lock_guard<std::mutex> lk(g_keep_mu);
+            if (psi_keep_ && psi_keep_->bytes() == bytes) psi_ = std::move(psi_keep_);
+            psi_keep_mapped_ = false;
+        }
+        if (!psi_) {
             drop_psi_peers();
-            psi_keep_.reset();
-            psi_ = std::make_unique<DeviceBuffer>(bytes);
+            {
+                std::lock_guard<std::mutex> lk(g_keep_mu);
+                psi_keep_.reset();
+            }
+            psi_ = std::make_unique<DeviceBuffer>(bytes); // (outside the lock: a failing cudaMalloc trims kept buffers)
         }
     }
     catch (const Error &e) {
@@ -320,7 +371,10 @@ void Simulator::allocate_one()
     note_launch();
     CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
     drop_psi_peers(); // peers mapped the old allocation (collective: every rank is in this call)
-    psi_keep_.reset();
+    {
+        std::lock_guard<std::mutex> lk(g_keep_mu);
+        psi_keep_.reset();
+    }
     psi_ = std::move(nb);
     tmp_.reset();
     acc_.reset();
@@ -404,7 +458,10 @@ void Simulator::release_one(int64_t wire)
     CUDA_CHECK(cudaMemcpyAsync(nb->p(), psi_->p(), bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
     CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_));
     drop_psi_peers();
-    psi_keep_.reset();
+    {
+        std::lock_guard<std::mutex> lk(g_keep_mu);
+        psi_keep_.reset();
+    }
     psi_ = std::move(nb);
     tmp_.reset();
     acc_.reset();
@@ -425,7 +482,14 @@ void Simulator::release()
 {
     if (stream_ && !dry_) cudaStreamSynchronize((cudaStream_t)stream_);
     queue_.clear();
-    if (psi_peers_ok_ && psi_) psi_keep_ = std::move(psi_); // peers still map this allocation
+    {
+        std::lock_guard<std::mutex> lk(g_keep_mu);
+        if (psi_ && (psi_peers_ok_ || (opt_.keep_allocation && !dry_))) { // peers still map this allocation / pooled device
+            psi_keep_ = std::move(psi_);
+            psi_keep_mapped_ = psi_peers_ok_;
+        }
+        if (probs_buf_ && opt_.keep_allocation && !dry_) probs_keep_ = std::move(probs_buf_);
+    }
     psi_.reset();
     tmp_.reset();
     acc_.reset();
@@ -2422,9 +2486,106 @@ double Simulator::var(int64_t key)
 }
 
 // ---- State / Probs ----------------------------------------------------------------------------------
+// Copy out of a pinned staging buffer into the caller's memory with non-temporal stores: the destination is written
+// once and not read here, so ordinary stores would first READ every destination line (read-for-ownership) -- a third of
+// the host-memory traffic of the copy, on a memory bus the incoming DMA shares.
+#if defined(__x86_64__)
+__attribute__((target("avx2"))) static void stream_copy_avx2(char *dst, const char *src, size_t n)
+{
+    size_t head = (32 - (reinterpret_cast<uintptr_t>(dst) & 31)) & 31;
+    if (head > n) head = n;
+    std::memcpy(dst, src, head);
+    dst += head; src += head; n -= head;
+    size_t i = 0;
+    for (; i + 128 <= n; i += 128) {
+        const __m256i a = _mm256_loadu_si256(reinterpret_cast<const __m256i *>(src + i));
+        const __m256i b = _mm256_loadu_si256(reinterpret_cast<const __m256i *>(src + i + 32));
+        const __m256i c = _mm256_loadu_si256(reinterpret_cast<const __m256i *>(src + i + 64));
+        const __m256i d = _mm256_loadu_si256(reinterpret_cast<const __m256i *>(src + i + 96));
+        _mm256_stream_si256(reinterpret_cast<__m256i *>(dst + i), a);
+        _mm256_stream_si256(reinterpret_cast<__m256i *>(dst + i + 32), b);
+        _mm256_stream_si256(reinterpret_cast<__m256i *>(dst + i + 64), c);
+        _mm256_stream_si256(reinterpret_cast<__m256i *>(dst + i + 96), d);
+    }
+    _mm_sfence();
+    std::memcpy(dst + i, src + i, n - i);
+}
+static void stream_copy(char *dst, const char *src, size_t n)
+{
+    static const bool avx2 = __builtin_cpu_supports("avx2") && !std::getenv("B200SV_NO_STREAM_COPY");
+    if (avx2 && n >= 4096) stream_copy_avx2(dst, src, n);
+    else std::memcpy(dst, src, n);
+}
+#else
+static void stream_copy(char *dst, const char *src, size_t n) { std::memcpy(dst, src, n); }
+#endif
+
+// A few parked host threads that copy staged chunks into the caller's (pageable) memory: spawning threads per chunk
+// costs ~0.4 ms of every ~1.5 ms chunk.  Process-wide, one job at a time, never destroyed (parked threads at exit).
+namespace {
+class HostCopyPool {
+  public:
+    static HostCopyPool &get()
+    {
+        static HostCopyPool *p = new HostCopyPool;
+        return *p;
+    }
+    // runs fn(i0, i1) over [0, n) split into one slice per thread (the caller's thread takes the first slice)
+    void run(size_t n, const std::function<void(size_t, size_t)> &fn)
+    {
+        std::unique_lock<std::mutex> job(job_mu_); // one job at a time
+        const size_t parts = workers_.size() + 1, step = (n + parts - 1) / parts;
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            fn_ = &fn;
+            n_ = n;
+            step_ = step;
+            remaining_ = (int)workers_.size();
+            generation_++;
+        }
+        cv_.notify_all();
+        fn(0, std::min(n, step));
+        std::unique_lock<std::mutex> lk(mu_);
+        done_.wait(lk, [&] { return remaining_ == 0; });
+    }
+
+  private:
+    HostCopyPool()
+    {
+        unsigned hw = std::thread::hardware_concurrency();
+        unsigned n = hw > 3 ? std::min(15u, hw - 2) : 1;
+        if (const char *e = std::getenv("B200SV_COPY_THREADS")) n = (unsigned)std::max(1, std::atoi(e));
+        for (unsigned t = 1; t < n; t++) workers_.emplace_back([this, t] { loop(t); });
+    }
+    void loop(unsigned t)
+    {
+        uint64_t seen = 0;
+        std::unique_lock<std::mutex> lk(mu_);
+        for (;;) {
+            cv_.wait(lk, [&] { return generation_ != seen; });
+            seen = generation_;
+            const std::function<void(size_t, size_t)> *fn = fn_;
+            const size_t i0 = std::min(n_, t * step_), i1 = std::min(n_, (t + 1) * step_);
+            lk.unlock();
+            if (i1 > i0) (*fn)(i0, i1);
+            lk.lock();
+            if (--remaining_ == 0) done_.notify_all();
+        }
+    }
+    std::mutex job_mu_, mu_;
+    std::condition_variable cv_, done_;
+    std::vector<std::thread> workers_;
+    const std::function<void(size_t, size_t)> *fn_ = nullptr;
+    size_t n_ = 0, step_ = 0;
+    int remaining_ = 0;
+    uint64_t generation_ = 0;
+};
+} // namespace
+
 // Device -> caller's host buffer (pageable memory, DataView strides: runtime/include/DataView.hpp:124-134).
-// Large results (Probs of 30 wires = 8 GiB, State) go through two pinned staging buffers: the DMA of chunk k+1
-// runs while host threads copy (or scatter, for a strided view) chunk k out of the other buffer.
+// Large results (Probs of 30 wires = 8 GiB, State) go through kStage pinned staging buffers: up to kStage - 1 DMAs are
+// queued ahead, so the copy engine never waits for the host, while the host-copy pool moves (or scatters, for a strided
+// view) the oldest finished chunk into the caller's memory.
 void Simulator::d2h_strided(const void *dsrc, size_t elem_bytes, size_t count, void *hdst, int64_t stride)
 {
     cudaStream_t st = (cudaStream_t)stream_;
@@ -2435,51 +2596,45 @@ void Simulator::d2h_strided(const void *dsrc, size_t elem_bytes, size_t count, v
         stats_.d2h_bytes += (double)total;
         return;
     }
-    const size_t CH = size_t(128) << 20; // bytes per staging buffer
-    for (int h = 0; h < 2; h++)
+    const size_t CH = size_t(64) << 20; // bytes per staging buffer
+    const size_t per = CH / elem_bytes; // elements per chunk
+    const size_t nchunks = (count + per - 1) / per;
+    const int nbuf = (int)std::min<size_t>(kStage, nchunks);
+    for (int h = 0; h < nbuf; h++)
         if (!stage_host_[h]) {
             CUDA_CHECK(cudaMallocHost(&stage_host_[h], CH));
             cudaEvent_t e;
             CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
             stage_ev_[h] = e;
         }
-    const size_t per = CH / elem_bytes; // elements per chunk
-    const size_t nchunks = (count + per - 1) / per;
-    unsigned nthreads = std::min(16u, std::max(1u, std::thread::hardware_concurrency() - 2));
     auto drain = [&](size_t k) { // chunk k: staging buffer -> caller's memory
-        const int h = (int)(k & 1);
+        const int h = (int)(k % (size_t)nbuf);
         CUDA_CHECK(cudaEventSynchronize((cudaEvent_t)stage_ev_[h]));
         const size_t o = k * per, cnt = std::min(per, count - o);
         const char *src = static_cast<const char *>(stage_host_[h]);
         auto part = [&](size_t i0, size_t i1) {
             if (stride == 1) {
-                std::memcpy(static_cast<char *>(hdst) + (o + i0) * elem_bytes, src + i0 * elem_bytes, (i1 - i0) * elem_bytes);
+                stream_copy(static_cast<char *>(hdst) + (o + i0) * elem_bytes, src + i0 * elem_bytes, (i1 - i0) * elem_bytes);
                 return;
             }
             for (size_t i = i0; i < i1; i++)
                 std::memcpy(static_cast<char *>(hdst) + (int64_t)(o + i) * stride * (int64_t)elem_bytes, src + i * elem_bytes,
                             elem_bytes);
         };
-        if (cnt * elem_bytes < (size_t(4) << 20) || nthreads == 1) {
-            part(0, cnt);
-            return;
-        }
-        std::vector<std::thread> th;
-        const size_t step = (cnt + nthreads - 1) / nthreads;
-        for (unsigned t = 1; t < nthreads; t++)
-            if (t * step < cnt) th.emplace_back(part, t * step, std::min(cnt, (t + 1) * step));
-        part(0, std::min(cnt, step));
-        for (auto &x : th) x.join();
+        if (cnt * elem_bytes < (size_t(4) << 20)) part(0, cnt);
+        else HostCopyPool::get().run(cnt, part);
     };
+    const size_t ahead = (size_t)nbuf - 1 > 0 ? (size_t)nbuf - 1 : 1; // DMAs in flight before the oldest is drained
     for (size_t k = 0; k < nchunks; k++) {
-        const int h = (int)(k & 1);
+        const int h = (int)(k % (size_t)nbuf);
         const size_t o = k * per, cnt = std::min(per, count - o);
+        // buffer h was drained at iteration k - 1 (chunk k - nbuf): free again
         CUDA_CHECK(cudaMemcpyAsync(stage_host_[h], static_cast<const char *>(dsrc) + o * elem_bytes, cnt * elem_bytes,
                                    cudaMemcpyDeviceToHost, st));
         CUDA_CHECK(cudaEventRecord((cudaEvent_t)stage_ev_[h], st));
-        if (k >= 1) drain(k - 1); // overlaps the DMA of chunk k; buffer (k-1)&1 is free again before chunk k+1 is issued
+        if (k + 1 >= ahead && nbuf > 1) drain(k + 1 - ahead);
     }
-    drain(nchunks - 1);
+    for (size_t k = (nchunks >= ahead && nbuf > 1) ? nchunks + 1 - ahead : 0; k < nchunks; k++) drain(k);
     stats_.d2h_bytes += (double)total;
 }
 
@@ -2681,6 +2836,11 @@ void Simulator::probs(const std::vector<int64_t> &wires_in, double *out, int64_t
         for (size_t j = 0; j < wires_in.size(); j++) all = all && wires_in[j] == (int64_t)j;
     }
     const size_t k = wires_in.empty() ? (size_t)n_ : wires_in.size();
+    if (!probs_buf_) {
+        std::lock_guard<std::mutex> lk(g_keep_mu);
+        if (probs_keep_ && probs_keep_->bytes() >= (sizeof(double) << k)) probs_buf_ = std::move(probs_keep_);
+        else probs_keep_.reset();
+    }
     ensure_buffer(probs_buf_, sizeof(double) << k);
     if (!sharded()) {
         if (all && wire_identity()) {

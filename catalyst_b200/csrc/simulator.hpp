@@ -117,6 +117,8 @@ struct Options {
     int swap_push = -1;       // qubit swap as one push kernel into all peers' staging: 1 on, 0 off, -1 auto (over NCCL,
                               // for swaps between pairs of ranks; larger groups take the staged NCCL path)
     bool batch_overlaps = true; // adjoint gradient: evaluate commuting generators' overlaps in batched read passes
+    bool keep_allocation = true;  // a released device keeps its state / probability buffers for the next allocation of the
+                                  // same size (the runtime pools device objects); freed process-wide when any cudaMalloc fails
     bool release_project = false; // ReleaseQubit of a wire that is not in a basis state: error (default) or keep
                                   // the more probable branch (release_entangled='project')
     bool lazy_adjoint = true; // adjoint gradient: apply U^dagger only when the next generator does not commute with it
@@ -183,6 +185,7 @@ class Simulator {
     double fp64_peak();            // measured thread-level DFMA instructions per second (microbenchmark)
     std::string stats_json() const; // counters as one JSON object
     void make_current(); // every public entry point runs on this object's CUDA device
+    static void trim_kept_buffers(); // free every buffer kept across ReleaseQubits, process-wide (a cudaMalloc failed)
     void set_timing(bool on) { timing_ = on; }
     void flush();
     void synchronize();
@@ -231,7 +234,8 @@ class Simulator {
     std::vector<void *> psi_peers_;
     void *psi_peers_ptr_ = nullptr;
     bool psi_peers_tried_ = false, psi_peers_ok_ = false;
-    std::unique_ptr<DeviceBuffer> psi_keep_;
+    std::unique_ptr<DeviceBuffer> psi_keep_, probs_keep_; // guarded by the process-wide keep mutex (simulator.cpp)
+    bool psi_keep_mapped_ = false;                        // peers hold a mapping of psi_keep_: never trimmed
     void reduce_results(std::vector<double> &host); // sum over ranks, fixed order
     // plan + launch a list of canonical ops (PHYSICAL bit space, non-diagonal targets all local) on a
     // device vector holding this rank's 2^nl_ amplitudes
@@ -274,8 +278,9 @@ class Simulator {
 
     void ensure_buffer(std::unique_ptr<DeviceBuffer> &buf, size_t bytes);
     void d2h_strided(const void *dsrc, size_t elem_bytes, size_t count, void *hdst, int64_t stride);
-    void *stage_host_[2] = {nullptr, nullptr}; // pinned staging of large device -> host results
-    void *stage_ev_[2] = {nullptr, nullptr};
+    static constexpr int kStage = 4;
+    void *stage_host_[kStage] = {nullptr, nullptr, nullptr, nullptr}; // pinned staging of large device -> host results
+    void *stage_ev_[kStage] = {nullptr, nullptr, nullptr, nullptr};
     void note_launch() { stats_.other_launches++; }
 
     Options opt_;

@@ -218,3 +218,42 @@ def test_adjoint_gradient_closed_form(gpu, case):
     d.expval(build_obs(d, obs))
     d.stop_tape()
     assert np.allclose(d.gradient(), [want], rtol=0, atol=1e-12)
+
+
+# ---- allocations kept across ReleaseQubits (the runtime pools device objects) ---------------------------------
+def test_released_device_keeps_its_allocation_and_gives_it_back_under_memory_pressure(gpu):
+    """ReleaseQubits keeps the state buffer for the next AllocateQubits of the same size (no cudaFree / cudaMalloc
+    of 16 GiB per program execution); a cudaMalloc that fails anywhere in the library frees every kept buffer of the
+    process first and retries, so kept buffers never cause an out-of-memory error."""
+    import torch
+    d1 = gpu.B200Device(20)
+    p0 = d1.device_pointer()
+    d1.named_op("PauliX", [], [0])
+    d1.release_qubits()
+    d1.allocate_qubits(20)
+    assert d1.device_pointer() == p0                         # the same allocation ...
+    assert np.array_equal(d1.probs([0]), [1.0, 0.0])         # ... reset to |0..0>
+    d1.release_qubits()
+    d1.allocate_qubits(21)                                   # another size: a fresh allocation
+    assert np.array_equal(d1.probs([20]), [1.0, 0.0])
+    d1.release_qubits()
+    off = gpu.B200Device(20, keep_allocation=False)
+    q0 = off.device_pointer()
+    off.release_qubits()
+    assert off.device_pointer() == 0
+    off.close()
+    free, total = torch.cuda.mem_get_info()
+    if total < 170 * 2**30 or free < 165 * 2**30:
+        d1.close()
+        pytest.skip("needs a GPU with >= 170 GiB of free memory for the memory-pressure leg")
+    d1.allocate_qubits(32)                                   # 64 GiB
+    d1.release_qubits()                                      # ... kept
+    d2 = gpu.B200Device(33)                                  # 128 GiB: only fits once d1's kept buffer is given back
+    d2.named_op("Hadamard", [], [32])
+    assert np.max(np.abs(d2.probs([32]) - [0.5, 0.5])) < TOL
+    with pytest.raises(RuntimeError, match="cannot allocate"):
+        d1.allocate_qubits(32)                               # 128 + 64 GiB do not fit: a clean error, not a crash
+    d2.close()
+    d1.allocate_qubits(32)                                   # and the object is still usable
+    assert np.array_equal(d1.probs([0]), [1.0, 0.0])
+    d1.close()
