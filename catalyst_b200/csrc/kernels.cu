@@ -514,13 +514,38 @@ struct PermTile {
     uint8_t rest_src[64];        // non-tile source positions (ascending)
     uint8_t rest_dst[64];        // their destination positions
     uint8_t nrest;
+    // shared-memory swizzle: index ^= bit(index, swz_from[q]) << swz_to[q].  The host picks it so that BOTH phases are
+    // bank-conflict free for any permutation: a half-warp writes 16 consecutive source-order slots and reads the 16
+    // slots spanned by the source-order bits dst_rank[0..3]; each of those that is not itself one of the low four
+    // bits is folded onto a low bit none of the others uses (a plain 64 x 64 transposition read with stride 64:
+    // 16-way conflicts, 12.1 ms at 30 qubits instead of the ~5 ms the 25.8 GB of traffic cost).
+    uint8_t swz_from[4], swz_to[4], nswz;
 };
+__device__ __forceinline__ uint32_t perm_swz(uint32_t i, const PermTile &T)
+{
+#pragma unroll
+    for (int q = 0; q < 4; q++)
+        if (q < T.nswz) i ^= ((i >> T.swz_from[q]) & 1u) << T.swz_to[q];
+    return i;
+}
 __global__ void __launch_bounds__(256)
-k_probs_all_perm(const cplx *__restrict__ psi, double *__restrict__ out, PermTile T)
+k_probs_all_perm(const cplx *__restrict__ psi, double *__restrict__ out, const __grid_constant__ PermTile T)
 {
     __shared__ double sm[1 << (2 * PP_C)];
     const uint32_t nel = 1u << T.nt;
     const uint64_t ntiles = 1ull << T.nrest;
+    const uint32_t tid = threadIdx.x;
+    const int nlow = T.nt < 8 ? T.nt : 8; // tile bits covered by the thread index; the rest by the slice counter k
+    const uint32_t nk = nel > 256u ? nel / 256u : 1u;
+    // per-thread parts of the offsets (hoisted out of the tile loop)
+    uint64_t s_tid = 0, d_tid = 0;
+    uint32_t se_tid = 0;
+    for (int j = 0; j < nlow; j++) {
+        const uint32_t bit = (tid >> j) & 1u;
+        s_tid |= (uint64_t)bit << T.src_pos[j];
+        d_tid |= (uint64_t)bit << T.dst_pos[j];
+        se_tid |= bit << T.dst_rank[j];
+    }
     for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         uint64_t sbase = 0, dbase = 0;
         for (int q = 0; q < T.nrest; q++) {
@@ -528,22 +553,31 @@ k_probs_all_perm(const cplx *__restrict__ psi, double *__restrict__ out, PermTil
             sbase |= bit << T.rest_src[q];
             dbase |= bit << T.rest_dst[q];
         }
-        for (uint32_t e = threadIdx.x; e < nel; e += blockDim.x) {
-            uint64_t off = 0;
-            for (int j = 0; j < T.nt; j++) off |= (uint64_t)((e >> j) & 1u) << T.src_pos[j];
-            const cplx a = psi[sbase | off];
-            sm[e] = a.x * a.x + a.y * a.y;
-        }
-        __syncthreads();
-        for (uint32_t e = threadIdx.x; e < nel; e += blockDim.x) { // e enumerates in destination order
-            uint64_t off = 0;
-            uint32_t se = 0;
-            for (int j = 0; j < T.nt; j++) {
-                const uint32_t bit = (e >> j) & 1u;
-                off |= (uint64_t)bit << T.dst_pos[j];
-                se |= bit << T.dst_rank[j];
+        cplx a[16];
+#pragma unroll
+        for (uint32_t k = 0; k < 16; k++) { // all loads of the thread in flight before the first use
+            if (k < nk && tid + k * 256u < nel) {
+                uint64_t s_k = 0;
+                for (int j = 8; j < T.nt; j++) s_k |= (uint64_t)((k >> (j - 8)) & 1u) << T.src_pos[j];
+                a[k] = psi[sbase | s_tid | s_k];
             }
-            out[dbase | off] = sm[se];
+        }
+#pragma unroll
+        for (uint32_t k = 0; k < 16; k++)
+            if (k < nk && tid + k * 256u < nel) sm[perm_swz(tid + k * 256u, T)] = a[k].x * a[k].x + a[k].y * a[k].y;
+        __syncthreads();
+#pragma unroll
+        for (uint32_t k = 0; k < 16; k++) { // slot tid + 256 k now enumerates in DESTINATION order
+            if (k < nk && tid + k * 256u < nel) {
+                uint64_t d_k = 0;
+                uint32_t se_k = 0;
+                for (int j = 8; j < T.nt; j++) {
+                    const uint32_t bit = (k >> (j - 8)) & 1u;
+                    d_k |= (uint64_t)bit << T.dst_pos[j];
+                    se_k |= bit << T.dst_rank[j];
+                }
+                out[dbase | d_tid | d_k] = sm[perm_swz(se_tid | se_k, T)];
+            }
         }
         __syncthreads();
     }
@@ -578,6 +612,23 @@ extern "C" int b200k_probs_all_perm(const double *psi, double *out, int n, const
         T.dst_rank[j] = (uint8_t)order[j];
         T.dst_pos[j] = perm[T.src_pos[order[j]]];
     }
+    // swizzle (see PermTile): the source-order bits behind the four lowest destination-order bits
+    {
+        bool used[4] = {false, false, false, false};
+        const int nd = nt < 4 ? nt : 4;
+        for (int j = 0; j < nd; j++)
+            if (T.dst_rank[j] < 4) used[T.dst_rank[j]] = true;
+        int free_low = 0;
+        for (int j = 0; j < nd; j++) {
+            if (T.dst_rank[j] < 4) continue;
+            while (free_low < 4 && used[free_low]) free_low++;
+            if (free_low >= 4) break;
+            T.swz_from[T.nswz] = T.dst_rank[j];
+            T.swz_to[T.nswz] = (uint8_t)free_low;
+            used[free_low] = true;
+            T.nswz++;
+        }
+    }
     int nr = 0;
     for (int b = 0; b < n; b++)
         if (!in_tile[b]) {
@@ -587,7 +638,7 @@ extern "C" int b200k_probs_all_perm(const double *psi, double *out, int n, const
         }
     T.nrest = (uint8_t)nr;
     uint64_t nb = 1ull << nr;
-    if (nb > 148 * 16) nb = 148 * 16;
+    if (nb > 148 * 7) nb = 148 * 7; // 32 KiB of shared memory per CTA: 7 resident CTAs per SM
     k_probs_all_perm<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>((const cplx *)psi, out, T);
     return (int)cudaGetLastError();
 }
@@ -882,78 +933,151 @@ extern "C" int b200k_append_qubit(double *dst, const double *src, int n_local_ol
 // =================================================================================================
 #define SAMP_CH 1024
 
-// scratch layout (doubles): [cumD: nch+1][cumE: nch+1]   (exclusive prefix over descending chunks)
+// scratch layout (doubles): [cumD: nch+1][cumE: nch+1][sumD: nch+1][sumE: nch+1][segD: 1024][segE: 1024]
+// (cum*: exclusive prefix over descending chunks)
 extern "C" int64_t b200k_sampler_scratch_doubles(int64_t nbins)
 {
     const int64_t nch = (nbins + SAMP_CH - 1) / SAMP_CH;
-    return 4 * (nch + 1);
+    return 4 * (nch + 1) + 2048;
 }
 
-__global__ void k_samp_chunk_sums(const double *__restrict__ p, int64_t N, int64_t nch,
-                                  double *__restrict__ sumD, double *__restrict__ sumE)
+// One thread per chunk sums its SAMP_CH entries sequentially in descending index order (the order is part of the
+// arithmetic the sampled stream depends on); the loads are made coalesced by a warp-level transposition: a warp owns
+// 32 consecutive chunks, its lanes fetch 32 consecutive entries of one chunk at a time (256-byte segments) into shared
+// memory, then every lane walks its own chunk's row.  (One uncoalesced 8-byte load per thread and step: 3.9 ms at
+// 2^30 entries; now bound by the 8 GiB read.)
+#define SAMP_WARPS 4
+__global__ void __launch_bounds__(32 * SAMP_WARPS)
+k_samp_chunk_sums(const double *__restrict__ p, int64_t N, int64_t nch, double *__restrict__ sumD,
+                  double *__restrict__ sumE)
 {
-    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= nch) return;
-    // chunk q covers descending positions [q*CH, (q+1)*CH): indices N-1-q*CH downwards
-    const int64_t hi = N - 1 - q * SAMP_CH;
-    int64_t lo = hi - SAMP_CH + 1;
-    if (lo < 0) lo = 0;
+    __shared__ double sm[SAMP_WARPS][32][33];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t q0 = ((int64_t)blockIdx.x * SAMP_WARPS + w) * 32; // first chunk of this warp
+    if (q0 >= nch) return;                                           // whole warp
     const double dN = (double)N;
+    const int64_t q = q0 + lane; // the chunk this lane sums
     double d = 0.0, e = 0.0;
-    for (int64_t i = hi; i >= lo; i--) {
-        const double f = dN * p[i];
-        if (f < 1.0) d += 1.0 - f;
-        else e += f - 1.0;
+    for (int t = 0; t < SAMP_CH / 32; t++) {
+#pragma unroll 8
+        for (int row = 0; row < 32; row++) {
+            const int64_t qr = q0 + row;
+            const int64_t i = N - 1 - qr * SAMP_CH - 32 * (int64_t)t - lane; // descending within the chunk
+            sm[w][row][lane] = (qr < nch && i >= 0) ? dN * p[i] : -1.0;        // -1: past the end of the vector
+        }
+        __syncwarp();
+        if (q < nch) {
+#pragma unroll 8
+            for (int c = 0; c < 32; c++) {
+                const double f = sm[w][lane][c];
+                if (f >= 0.0) {
+                    if (f < 1.0) d += 1.0 - f;
+                    else e += f - 1.0;
+                }
+            }
+        }
+        __syncwarp();
     }
-    sumD[q] = d;
-    sumE[q] = e;
+    if (q < nch) {
+        sumD[q] = d;
+        sumE[q] = e;
+    }
 }
 
-// single block, 1024 threads: exclusive scan of the chunk sums in a fixed sequential order
-__global__ void __launch_bounds__(1024)
-k_samp_scan(const double *__restrict__ sumD, const double *__restrict__ sumE, int64_t nch,
-            double *__restrict__ cumD, double *__restrict__ cumE)
+// Exclusive scan of the chunk sums in a fixed sequential order: 1024 segments of `per` consecutive chunks; segment
+// totals and the running values inside a segment are plain sequential sums (again part of the arithmetic), the 1024
+// totals are scanned by one thread.  Segments are walked by one lane each with the same warp transposition, 32 segments
+// per warp, one warp per CTA (a single CTA of 1024 threads with strided loads took 4.2 ms at 2^20 chunks).
+__global__ void __launch_bounds__(32)
+k_samp_seg_totals(const double *__restrict__ sumD, const double *__restrict__ sumE, int64_t nch, int64_t per,
+                  double *__restrict__ segD, double *__restrict__ segE)
 {
-    __shared__ double segD[1024], segE[1024];
-    __shared__ double totD, totE;
-    const int tid = threadIdx.x;
-    const int64_t per = (nch + 1023) / 1024;
-    int64_t q0 = tid * per, q1 = q0 + per;
+    __shared__ double smD[32][33], smE[32][33];
+    const int lane = threadIdx.x;
+    const int64_t seg0 = (int64_t)blockIdx.x * 32;
+    int64_t q0 = (seg0 + lane) * per, q1 = q0 + per;
     if (q0 > nch) q0 = nch;
     if (q1 > nch) q1 = nch;
     double d = 0.0, e = 0.0;
-    for (int64_t q = q0; q < q1; q++) {
-        d += sumD[q];
-        e += sumE[q];
-    }
-    segD[tid] = d;
-    segE[tid] = e;
-    __syncthreads();
-    if (tid == 0) {
-        double rd = 0.0, re = 0.0;
-        for (int i = 0; i < 1024; i++) {
-            const double td = segD[i], te = segE[i];
-            segD[i] = rd;
-            segE[i] = re;
-            rd += td;
-            re += te;
+    for (int64_t t = 0; t < per; t += 32) {
+        for (int row = 0; row < 32; row++) {
+            int64_t r0 = (seg0 + row) * per, r1 = r0 + per;
+            if (r1 > nch) r1 = nch;
+            const int64_t i = r0 + t + lane;
+            const bool ok = i < r1;
+            smD[row][lane] = ok ? sumD[i] : 0.0;
+            smE[row][lane] = ok ? sumE[i] : 0.0;
         }
-        totD = rd;
-        totE = re;
+        __syncwarp();
+        for (int c = 0; c < 32; c++)
+            if (q0 + t + c < q1) {
+                d += smD[lane][c];
+                e += smE[lane][c];
+            }
+        __syncwarp();
     }
-    __syncthreads();
-    const double bd = segD[tid], be = segE[tid];
-    d = 0.0;
-    e = 0.0;
-    for (int64_t q = q0; q < q1; q++) {
-        cumD[q] = bd + d;
-        cumE[q] = be + e;
-        d += sumD[q];
-        e += sumE[q];
+    segD[seg0 + lane] = d;
+    segE[seg0 + lane] = e;
+}
+
+__global__ void k_samp_seg_scan(double *__restrict__ segD, double *__restrict__ segE, double *__restrict__ totD,
+                                double *__restrict__ totE)
+{
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    double rd = 0.0, re = 0.0;
+    for (int i = 0; i < 1024; i++) {
+        const double td = segD[i], te = segE[i];
+        segD[i] = rd;
+        segE[i] = re;
+        rd += td;
+        re += te;
     }
-    if (tid == 0) {
-        cumD[nch] = totD;
-        cumE[nch] = totE;
+    *totD = rd;
+    *totE = re;
+}
+
+__global__ void __launch_bounds__(32)
+k_samp_seg_write(const double *__restrict__ sumD, const double *__restrict__ sumE, int64_t nch, int64_t per,
+                 const double *__restrict__ segD, const double *__restrict__ segE, double *__restrict__ cumD,
+                 double *__restrict__ cumE)
+{
+    __shared__ double smD[32][33], smE[32][33];
+    const int lane = threadIdx.x;
+    const int64_t seg0 = (int64_t)blockIdx.x * 32;
+    int64_t q0 = (seg0 + lane) * per, q1 = q0 + per;
+    if (q0 > nch) q0 = nch;
+    if (q1 > nch) q1 = nch;
+    const double bd = segD[seg0 + lane], be = segE[seg0 + lane];
+    double d = 0.0, e = 0.0;
+    for (int64_t t = 0; t < per; t += 32) {
+        for (int row = 0; row < 32; row++) {
+            int64_t r0 = (seg0 + row) * per, r1 = r0 + per;
+            if (r1 > nch) r1 = nch;
+            const int64_t i = r0 + t + lane;
+            const bool ok = i < r1;
+            smD[row][lane] = ok ? sumD[i] : 0.0;
+            smE[row][lane] = ok ? sumE[i] : 0.0;
+        }
+        __syncwarp();
+        for (int c = 0; c < 32; c++)
+            if (q0 + t + c < q1) { // exclusive: the value BEFORE adding this chunk
+                const double xd = smD[lane][c], xe = smE[lane][c];
+                smD[lane][c] = bd + d;
+                smE[lane][c] = be + e;
+                d += xd;
+                e += xe;
+            }
+        __syncwarp();
+        for (int row = 0; row < 32; row++) {
+            int64_t r0 = (seg0 + row) * per, r1 = r0 + per;
+            if (r1 > nch) r1 = nch;
+            const int64_t i = r0 + t + lane;
+            if (i < r1) {
+                cumD[i] = smD[row][lane];
+                cumE[i] = smE[row][lane];
+            }
+        }
+        __syncwarp();
     }
 }
 
@@ -963,9 +1087,14 @@ extern "C" int b200k_sampler_prepare(const double *probs, int64_t nbins, double 
     const int64_t nch = (nbins + SAMP_CH - 1) / SAMP_CH;
     double *cumD = scratch, *cumE = scratch + (nch + 1);
     double *sumD = scratch + 2 * (nch + 1), *sumE = scratch + 3 * (nch + 1);
+    double *segD = scratch + 4 * (nch + 1), *segE = segD + 1024;
     cudaStream_t st = (cudaStream_t)stream;
-    k_samp_chunk_sums<<<(unsigned)((nch + 127) / 128), 128, 0, st>>>(probs, nbins, nch, sumD, sumE);
-    k_samp_scan<<<1, 1024, 0, st>>>(sumD, sumE, nch, cumD, cumE);
+    const int64_t warps = (nch + 31) / 32;
+    k_samp_chunk_sums<<<(unsigned)((warps + SAMP_WARPS - 1) / SAMP_WARPS), 32 * SAMP_WARPS, 0, st>>>(probs, nbins, nch, sumD, sumE);
+    const int64_t per = (nch + 1023) / 1024;
+    k_samp_seg_totals<<<32, 32, 0, st>>>(sumD, sumE, nch, per, segD, segE);
+    k_samp_seg_scan<<<1, 32, 0, st>>>(segD, segE, cumD + nch, cumE + nch);
+    k_samp_seg_write<<<32, 32, 0, st>>>(sumD, sumE, nch, per, segD, segE, cumD, cumE);
     return (int)cudaGetLastError();
 }
 
