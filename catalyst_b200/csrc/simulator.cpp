@@ -1384,7 +1384,7 @@ void Simulator::swap_bits_impl(const std::vector<double *> &vecs, std::vector<in
         }
         return;
     }
-    // Push path (default over NCCL process groups for swaps between PAIRS of ranks): every rank maps its peers' receive staging once; per chunk
+    // Push path (default over NCCL process groups of TWO ranks): every rank maps its peers' receive staging once; per chunk
     // ONE kernel reads this rank's sub-blocks and writes them straight into all peers' staging over NVLink while
     // it scatters the previously received chunk into the slots that chunk vacated; a stream-ordered rendezvous
     // separates the rounds.  Against the staged path below: no pack pass, no send-side staging, no NCCL transfer.
@@ -1392,7 +1392,8 @@ void Simulator::swap_bits_impl(const std::vector<double *> &vecs, std::vector<in
     // (2 GPUs: 601 ms of swap per circuit against 788 ms staged) and loses when a swap spans 4 or 8 ranks (8 GPUs:
     // 592 ms against 452 ms: its strided gather sits in the same dependency chain as the NVLink writes, while the
     // staged path hides pack / unpack behind the NCCL transfer of the neighbouring chunk)
-    const bool want_push = opt_.swap_push == 1 || (opt_.swap_push < 0 && std::string(comm_->kind()) == "nccl" && npat == 2);
+    // (decided per communicator, not per swap, so that every run uses exactly one of the measured configurations)
+    const bool want_push = opt_.swap_push == 1 || (opt_.swap_push < 0 && std::string(comm_->kind()) == "nccl" && opt_.world == 2);
     if (want_push && npat - 1 <= (uint32_t)B200K_PUSH_MAX_PEERS) {
         const uint64_t budget = ((uint64_t)opt_.stage_mib << 20) / sizeof(cplx);
         uint64_t chunk = budget / (2ull * (npat - 1));

@@ -114,8 +114,8 @@ struct Options {
     int jit_factor = 1;       // factor u00 out of uncontrolled one-qubit gates, fold the product into one op
     bool virtual_swap = true; // uncontrolled SWAP gates relabel wires instead of moving amplitudes
     int p2p_swap = -1;        // qubit swap over mapped peer memory: 1 on, 0 off, -1 auto (on for 'local:' rank groups)
-    int swap_push = -1;       // qubit swap as one push kernel into all peers' staging: 1 on, 0 off, -1 auto (over NCCL,
-                              // for swaps between pairs of ranks; larger groups take the staged NCCL path)
+    int swap_push = -1;       // qubit swap as one push kernel into all peers' staging: 1 on, 0 off, -1 auto (over NCCL
+                              // with 2 ranks; larger worlds take the staged NCCL path -- by measurement)
     bool batch_overlaps = true; // adjoint gradient: evaluate commuting generators' overlaps in batched read passes
     bool keep_allocation = true;  // a released device keeps its state / probability buffers for the next allocation of the
                                   // same size (the runtime pools device objects); freed process-wide when any cudaMalloc fails

@@ -44,7 +44,7 @@ def _worker(rank, world, uid, n, ops, obs_list, q, kwargs=None):
 
 
 @pytest.mark.parametrize("world,n,kwargs", [
-    # automatic policy: pairwise swaps (every swap at world 2) run in push mode, swaps that span more ranks staged
+    # automatic policy: push mode in a world of 2 ranks, the staged NCCL path at 4 and 8
     (2, 14, None), (4, 14, None), (8, 14, None),
     # push mode forced (one kernel writes into every peer's staging, mapped through CUDA IPC) at 4 and 8 ranks
     (4, 14, {"swap_push": 1}), (8, 14, {"swap_push": 1}),
