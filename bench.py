@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the C1/C2/C4 timings and the cold-start probe")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--only-extra", action="store_true", help="run only the C1/C2/C4 timings and print them")
     ap.add_argument("--cpu-sample-gates", type=int, default=32)
     ap.add_argument("--tile-bits", type=int, default=0)
     ap.add_argument("--depth", type=int, default=40, help="depth of the sharded C5 circuit (N > 1)")
@@ -371,9 +372,13 @@ def extra_configs(args):
             times["expval_ms"] = 1e3 * (time.perf_counter() - t0)
             if grad:
                 d.stop_tape()
+                d.reset_stats()
                 t0 = time.perf_counter()
                 g = d.gradient()
                 times["gradient_ms"] = 1e3 * (time.perf_counter() - t0)
+                sg = d.stats()
+                times["gradient_launches"] = {"tile_passes": int(sg.tile_passes), "specialised": int(sg.jit_passes),
+                                              "other": int(sg.other_launches), "kernels_compiling": int(sg.jit_pending)}
                 rec["parameters"] = int(g.shape[1])
                 floor_s = g.shape[1] * (2 * 32.0 + 32.0) * (1 << n) / (peak * 1e9)
                 # SURVEY 8(d)'s floor assumes one HBM pass set per parameter; lazy adjoints + batched overlaps evaluate
@@ -642,6 +647,8 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.cold_probe:
         cold_probe(args)
+    elif args.only_extra:
+        print(json.dumps(extra_configs(args)), flush=True)
     elif args.impl == "reference":
         run_reference(args, rank, world)
     else:

@@ -1228,119 +1228,296 @@ extern "C" int b200k_sampler_draw(const double *probs, int64_t nbins, const doub
 // warp reduces with shuffles into its own shared-memory slot; per-CTA partials go to `partial`, a
 // second kernel sums them in fixed order (run-to-run reproducible) and applies the i^ny factor.
 // =================================================================================================
+__device__ __forceinline__ void kw_cp_async16(void *smem_dst, const void *gmem_src)
+{
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void kw_cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N> __device__ __forceinline__ void kw_cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
 struct BatchParams {
     B200k2Header h;
     B200kBatchGen g[B200K_BATCH_GENS];
     int ngen;
 };
 
-__global__ void __launch_bounds__(256, 3)
+// What each generator costs is issue + shared-memory bandwidth, not HBM (2^26 amplitudes x up to 32 generators per
+// 1 GiB read), so the kernel is built around the instruction count per (amplitude, generator):
+//  * every caller needs ONE real number per generator (Expval the real part of <phi|P|lam>, the adjoint gradient the
+//    imaginary part), which after the i^ny phase is either Re or Im of the raw sum: a batch is uniform in that choice
+//    (template RC), tr = a . b, ti = (i a) . b, two DFMA per pair;
+//  * the thread's own amplitudes of phi stay in registers across all generators of the tile, only the partner
+//    lam[e ^ x] comes from shared memory (one LDS.128);
+//  * one register accumulator per generator lives across ALL tiles of the CTA: the warp-shuffle tree runs once per
+//    kernel instead of once per (generator, tile);
+//  * the Z-parity sign costs no POPC per pair (POPC issues at 16 / clk / SM): parity((e ^ x) & z) splits into a part
+//    shared by the thread's 8 elements (its tid bits, the tile's outside bits, parity(x & z)) and a host-made 8-bit
+//    table over the elements' bits 8..10 (upper half of the zin field), XORed into the sign bit of phi's amplitude;
+//  * tiles are double-buffered with cp.async (lam: two buffers; phi: one, copied to registers first), so the next tile
+//    is in flight while the generators of the current one are summed.  A C2 RX layer packs only 7 generators per
+//    launch: without the prefetch such a launch took 5.6 ms at 28 qubits against 1.5 ms of HBM time.
+// (Round 1's version reloaded phi per generator, computed both components and reduced per generator and tile:
+// ~0.2 ms per word at 26 qubits, the cost of a separate read pass per word.)
+template <int RC, int HASCTL> __global__ void __launch_bounds__(256, 2)
 k_bilinear_batch(const cplx *__restrict__ phi, const cplx *__restrict__ lam, const __grid_constant__ BatchParams P,
                  double *__restrict__ partial)
 {
-    extern __shared__ cplx sm2[]; // phi tile, lam tile
-    __shared__ double wacc[B200K_BATCH_GENS][8][2];
-    const int t = P.h.t, c = P.h.c, nhigh = P.h.nhigh;
-    const uint32_t nelem = 1u << t, lowmask = (1u << c) - 1u, tid = threadIdx.x;
-    cplx *sA = sm2, *sB = sm2 + nelem;
-    for (int q = tid; q < P.ngen * 16; q += blockDim.x) (&wacc[0][0][0])[q] = 0.0;
-    auto off_of = [&](uint32_t e) -> uint64_t {
-        uint64_t o = e & lowmask;
-        const uint32_t r = e >> c;
-        for (int hh = 0; hh < nhigh; hh++) o |= (uint64_t)((r >> hh) & 1u) << P.h.high_pos[hh];
-        return o;
-    };
+    extern __shared__ cplx sT[]; // lam tile x 2, then the phi tile (when phi != lam)
+    __shared__ double wacc[B200K_BATCH_GENS][8];
+    __shared__ unsigned long long koff[8];
+    const int t = P.h.t, c = P.h.c;
+    const uint32_t nelem = 1u << t, tid = threadIdx.x;
+    // global offset of tile-local index e = tid + 256 k: the tid part is hoisted, the k part (tile bits 8..10) tabulated
+    auto pos_of = [&](int bpos) -> int { return bpos < c ? bpos : (int)P.h.high_pos[bpos - c]; };
+    uint64_t off_tid = 0;
+    for (int bpos = 0; bpos < 8 && bpos < t; bpos++) off_tid |= (uint64_t)((tid >> bpos) & 1u) << pos_of(bpos);
+    if (tid < 8) {
+        uint64_t o = 0;
+        for (int j = 0; j < 3; j++)
+            if (8 + j < t && ((tid >> j) & 1u)) o |= 1ull << pos_of(8 + j);
+        koff[tid] = o;
+    }
+    double acc[B200K_BATCH_GENS];
+#pragma unroll
+    for (int g = 0; g < B200K_BATCH_GENS; g++) acc[g] = 0.0;
     const bool same = phi == lam;
-    __syncthreads();
-    for (uint64_t tile = blockIdx.x; tile < P.h.ntiles; tile += gridDim.x) {
+    cplx *sPhi = sT + ((size_t)2 << t);
+    auto base_of = [&](uint64_t tile) {
         uint64_t base = tile << c;
-        for (int hh = 0; hh < nhigh; hh++) {
+        for (int hh = 0; hh < P.h.nhigh; hh++) {
             const int p = P.h.high_pos[hh];
             base = ((base >> p) << (p + 1)) | (base & ((1ull << p) - 1ull));
         }
-        const uint64_t obase = base | P.h.rank_base;
-        for (uint32_t e = tid; e < nelem; e += blockDim.x) {
-            const uint64_t o = base | off_of(e);
-            const cplx b = lam[o];
-            sB[e] = b;
-            sA[e] = same ? b : phi[o];
-        }
-        __syncthreads();
-        for (int g = 0; g < P.ngen; g++) {
-            const B200kBatchGen &G = P.g[g];
-            if ((obase & G.co_m) != G.co_v) continue; // uniform per tile
-            const uint32_t opar = __popcll(obase & G.zo) & 1u;
-            double ar = 0.0, ai = 0.0;
-            for (uint32_t e = tid; e < nelem; e += blockDim.x) {
-                if ((e & G.cin_m) != G.cin_v) continue;
-                const uint32_t j = e ^ G.xin;
-                const cplx a = sA[e], b = sB[j];
-                // conj(a) * b, signed by the parity of the Z factors at index j
-                double tr = a.x * b.x + a.y * b.y, ti = a.x * b.y - a.y * b.x;
-                if ((__popc(j & G.zin) + opar) & 1u) {
-                    tr = -tr;
-                    ti = -ti;
-                }
-                ar += tr;
-                ai += ti;
-            }
+        return base;
+    };
+    auto fetch = [&](uint64_t tile, cplx *lbuf) {
+        const uint64_t b = base_of(tile) | off_tid;
 #pragma unroll
-            for (int off = 16; off > 0; off >>= 1) {
-                ar += __shfl_down_sync(0xffffffffu, ar, off);
-                ai += __shfl_down_sync(0xffffffffu, ai, off);
-            }
-            if ((tid & 31u) == 0) {
-                wacc[g][tid >> 5][0] += ar;
-                wacc[g][tid >> 5][1] += ai;
+        for (int k = 0; k < 8; k++) {
+            const uint32_t e = tid + 256u * k;
+            if (e < nelem) {
+                kw_cp_async16(&lbuf[e], &lam[b | koff[k]]);
+                if (!same) kw_cp_async16(&sPhi[e], &phi[b | koff[k]]);
             }
         }
-        __syncthreads();
+    };
+    __syncthreads(); // koff
+    if (blockIdx.x < P.h.ntiles) fetch(blockIdx.x, sT);
+    kw_cp_async_commit();
+    int cur = 0;
+    for (uint64_t tile = blockIdx.x; tile < P.h.ntiles; tile += gridDim.x, cur ^= 1) {
+        cplx *sB = sT + ((size_t)cur << t);
+        kw_cp_async_wait<0>();
+        __syncthreads(); // this tile has landed; every thread is done with the previous tile's buffers
+        const uint64_t obase = base_of(tile) | P.h.rank_base;
+        cplx av[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const uint32_t e = tid + 256u * k;
+            av[k] = make_double2(0.0, 0.0);
+            if (e < nelem) {
+                const cplx a = same ? sB[e] : sPhi[e];
+                av[k] = RC ? make_double2(-a.y, a.x) : a; // (i a) . b = Im(conj(a) b);  a . b = Re(conj(a) b)
+            }
+        }
+        __syncthreads(); // phi's buffer is free again
+        const uint64_t next = tile + gridDim.x;
+        if (next < P.h.ntiles) fetch(next, sT + ((size_t)(cur ^ 1) << t));
+        kw_cp_async_commit();
+#pragma unroll
+        for (int g = 0; g < B200K_BATCH_GENS; g++) {
+            if (g < P.ngen) {
+                const B200kBatchGen &G = P.g[g];
+                if ((obase & G.co_m) == G.co_v) { // uniform per tile
+                    // bit k of M = parity of the Z factors at the partner of element k
+                    const uint32_t common = (__popc(tid & G.zin) + (G.zin >> 24) + __popcll(obase & G.zo)) & 1u;
+                    const uint32_t M = (0u - common) ^ ((G.zin >> 16) & 0xffu);
+                    double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+                    for (int k = 0; k < 8; k++) {
+                        const uint32_t e = tid + 256u * k;
+                        if (e < nelem && (!HASCTL || (e & G.cin_m) == G.cin_v)) {
+                            const cplx b = sB[e ^ G.xin];
+                            const long long sign = (long long)((M << (31 - k)) & 0x80000000u) << 32;
+                            const double ax = __longlong_as_double(__double_as_longlong(av[k].x) ^ sign);
+                            const double ay = __longlong_as_double(__double_as_longlong(av[k].y) ^ sign);
+                            if (k & 1) s1 = fma(ay, b.y, fma(ax, b.x, s1));
+                            else s0 = fma(ay, b.y, fma(ax, b.x, s0));
+                        }
+                    }
+                    acc[g] += s0 + s1;
+                }
+            }
+        }
+    }
+    kw_cp_async_wait<0>();
+    // one reduction per kernel: warp tree, then the eight warps in fixed order
+#pragma unroll
+    for (int g = 0; g < B200K_BATCH_GENS; g++) {
+        if (g < P.ngen) {
+            double v = acc[g];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+            if ((tid & 31u) == 0) wacc[g][tid >> 5] = v;
+        }
     }
     __syncthreads();
-    for (int q = tid; q < P.ngen * 2; q += blockDim.x) {
-        const int g = q >> 1, comp = q & 1;
+    for (int g = tid; g < P.ngen; g += blockDim.x) {
         double s = 0.0;
-        for (int w = 0; w < 8; w++) s += wacc[g][w][comp];
-        partial[((size_t)blockIdx.x * B200K_BATCH_GENS + g) * 2 + comp] = s;
+        for (int w = 0; w < 8; w++) s += wacc[g][w];
+        partial[(size_t)blockIdx.x * B200K_BATCH_GENS + g] = s;
     }
 }
 
 struct BatchOut {
     double *out[B200K_BATCH_GENS];
-    int ny[B200K_BATCH_GENS];
+    int8_t slot[B200K_BATCH_GENS]; // 0: the sum is the real part of the result, 1: the imaginary part
+    int8_t neg[B200K_BATCH_GENS];  // result = -sum
 };
 __global__ void __launch_bounds__(256)
 k_bilinear_batch_final(const double *__restrict__ partial, int nblocks, BatchOut O)
 {
     const int g = blockIdx.x;
-    double v[2] = {0.0, 0.0};
-    for (int i = threadIdx.x; i < nblocks; i += 256) {
-        v[0] += partial[((size_t)i * B200K_BATCH_GENS + g) * 2];
-        v[1] += partial[((size_t)i * B200K_BATCH_GENS + g) * 2 + 1];
-    }
-    __shared__ double sh[2][8];
+    double v = 0.0;
+    for (int i = threadIdx.x; i < nblocks; i += 256) v += partial[(size_t)i * B200K_BATCH_GENS + g];
+    __shared__ double sh[8];
 #pragma unroll
-    for (int q = 0; q < 2; q++)
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) v[q] += __shfl_down_sync(0xffffffffu, v[q], off);
-    if ((threadIdx.x & 31) == 0) {
-        sh[0][threadIdx.x >> 5] = v[0];
-        sh[1][threadIdx.x >> 5] = v[1];
-    }
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
     __syncthreads();
     if (threadIdx.x == 0) {
-        double a = 0.0, b = 0.0;
-        for (int i = 0; i < 8; i++) {
-            a += sh[0][i];
-            b += sh[1][i];
-        }
-        cplx r = cmul_ipow(make_double2(a, b), O.ny[g]);
-        O.out[g][0] = r.x;
-        O.out[g][1] = r.y;
+        double a = 0.0;
+        for (int i = 0; i < 8; i++) a += sh[i];
+        if (O.neg[g]) a = -a;
+        O.out[g][O.slot[g]] = a;
+        O.out[g][O.slot[g] ^ 1] = 0.0; // the component the caller did not ask for is not computed
     }
 }
 
-extern "C" int64_t b200k_bilinear_batch_scratch_doubles(void) { return (int64_t)148 * 3 * B200K_BATCH_GENS * 2; }
+#define BATCH_MAX_BLOCKS (148 * 4)
+extern "C" int64_t b200k_bilinear_batch_scratch_doubles(void) { return (int64_t)BATCH_MAX_BLOCKS * B200K_BATCH_GENS; }
+
+// Diagonal generators (Z words: RZ, MultiRZ, IsingZZ, CRZ's Z factor, PhaseShift-type projectors): <phi|P_g|lam> =
+// sum_i sign_g(i) conj(phi_i) lam_i, so the one real number r_i every caller needs (Re or Im of conj(phi_i) lam_i) is
+// computed ONCE per amplitude and each generator costs a parity, a sign flip and an add -- no tile, no shared memory,
+// a plain streaming pass over the two vectors.  (Through k_bilinear_batch a diagonal generator cost the same ~0.1 ms
+// at 26 qubits as an X/Y one: half of C4's and 60 % of C2's parameters.)
+// The parity of (i & z_g) for all 32 generators at once is a GF(2) matrix-vector product: S(i) = XOR over the set bits b
+// of i of the column word C_b (bit g of C_b = bit b of z_g).  POPC runs at 16 / clk / SM, and 2 x 32 of them per amplitude
+// made the first version of this kernel POPC-bound (5.4 ms per launch at 28 qubits against 1.5 ms of HBM time); here
+// S(i) = S(tid) ^ T0[bits 8..17] ^ T1[bits 18..27] ^ T2[bits 28..37] ^ S(rank bits) with three 1024-entry tables built
+// per CTA, and generator g's sign is bit g of S(i) shifted into the sign bit of r.
+#define DIAG_COLS 38
+struct DiagBatchParams {
+    uint64_t cm[B200K_BATCH_GENS], cv[B200K_BATCH_GENS];
+    uint32_t col[DIAG_COLS]; // column words of the local index bits
+    uint32_t s_const;        // contribution of the rank bits (and of any bit >= DIAG_COLS)
+    uint64_t rank_base;
+    int ngen;
+};
+template <int RC, int HASCTL> __global__ void __launch_bounds__(256, 3)
+k_bilinear_diag_batch(const cplx *__restrict__ phi, const cplx *__restrict__ lam, uint64_t N,
+                      const __grid_constant__ DiagBatchParams P, double *__restrict__ partial)
+{
+    __shared__ double wacc[B200K_BATCH_GENS][8];
+    __shared__ uint32_t T[3][1024];
+    const uint32_t tid = threadIdx.x;
+    for (uint32_t idx = tid; idx < 3 * 1024; idx += 256) {
+        const uint32_t tb = idx >> 10, v = idx & 1023u;
+        uint32_t sgn = 0;
+        for (int b = 0; b < 10; b++)
+            if ((v >> b) & 1u) sgn ^= P.col[8 + 10 * tb + b];
+        T[tb][v] = sgn;
+    }
+    uint32_t s_thread = P.s_const;
+    for (int b = 0; b < 8; b++)
+        if ((tid >> b) & 1u) s_thread ^= P.col[b];
+    __syncthreads();
+    double acc[B200K_BATCH_GENS];
+#pragma unroll
+    for (int g = 0; g < B200K_BATCH_GENS; g++) acc[g] = 0.0;
+    const bool same = phi == lam;
+    const uint64_t stride = (uint64_t)gridDim.x * 256u; // a multiple of 256: the low 8 index bits of a thread are its tid
+    for (uint64_t i = (uint64_t)blockIdx.x * 256u + tid; i < N; i += stride) {
+        const cplx b = lam[i];
+        const cplx a = same ? b : phi[i];
+        const double r = RC ? fma(a.x, b.y, -(a.y * b.x)) : fma(a.x, b.x, a.y * b.y); // Im / Re of conj(a) b
+        const uint64_t q = i >> 8;
+        const uint32_t S = s_thread ^ T[0][q & 1023u] ^ T[1][(q >> 10) & 1023u] ^ T[2][(q >> 20) & 1023u];
+        const uint64_t gi = i | P.rank_base;
+#pragma unroll
+        for (int g = 0; g < B200K_BATCH_GENS; g++) {
+            if (g < P.ngen && (!HASCTL || (gi & P.cm[g]) == P.cv[g])) {
+                const long long sign = (long long)((S << (31 - g)) & 0x80000000u) << 32;
+                acc[g] += __longlong_as_double(__double_as_longlong(r) ^ sign);
+            }
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < B200K_BATCH_GENS; g++) {
+        if (g < P.ngen) {
+            double v = acc[g];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+            if ((tid & 31u) == 0) wacc[g][tid >> 5] = v;
+        }
+    }
+    __syncthreads();
+    for (int g = tid; g < P.ngen; g += blockDim.x) {
+        double s = 0.0;
+        for (int w = 0; w < 8; w++) s += wacc[g][w];
+        partial[(size_t)blockIdx.x * B200K_BATCH_GENS + g] = s;
+    }
+}
+
+extern "C" int b200k_bilinear_diag_batch(const double *phi, const double *lam, int n_local, uint64_t rank_base,
+                                         const uint64_t *zmasks, const uint64_t *cmasks, const uint64_t *cvals,
+                                         const int *nys, int want, int ngen, double *const *outs, double *scratch,
+                                         void *stream)
+{
+    if (ngen < 1 || ngen > B200K_BATCH_GENS || (want != B200K_WANT_REAL && want != B200K_WANT_IMAG))
+        return (int)cudaErrorInvalidValue;
+    const bool imag = want == B200K_WANT_IMAG;
+    int rc = -1;
+    DiagBatchParams P;
+    memset(&P, 0, sizeof(P));
+    P.rank_base = rank_base;
+    P.ngen = ngen;
+    BatchOut O;
+    memset(&O, 0, sizeof(O));
+    for (int g = 0; g < ngen; g++) {
+        const int ny = nys[g] & 3; // a diagonal word has no Y factor; the phase argument is honoured all the same
+        const int my_rc = (ny & 1) ^ (imag ? 1 : 0);
+        if (rc < 0) rc = my_rc;
+        if (rc != my_rc) return (int)cudaErrorInvalidValue;
+        for (int b = 0; b < 64; b++) {
+            if (!((zmasks[g] >> b) & 1ull)) continue;
+            if (b < DIAG_COLS && b < n_local) P.col[b] |= 1u << g;
+            else if ((rank_base >> b) & 1ull) P.s_const ^= 1u << g; // a bit the local index does not reach
+        }
+        P.cm[g] = cmasks[g];
+        P.cv[g] = cvals[g];
+        O.out[g] = outs[g];
+        O.slot[g] = imag ? 1 : 0;
+        O.neg[g] = imag ? (ny == 2 || ny == 3) : (ny == 1 || ny == 2);
+    }
+    if (n_local > DIAG_COLS) return (int)cudaErrorInvalidValue;
+    const uint64_t N = 1ull << n_local;
+    uint64_t grid = (N + 255) / 256;
+    if (grid > 148 * 3) grid = 148 * 3; // three resident CTAs per SM (registers): one wave
+    bool ctl = false;
+    for (int g = 0; g < ngen; g++) ctl = ctl || cmasks[g] != 0;
+    const cplx *ph = (const cplx *)phi, *la = (const cplx *)lam;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (rc && ctl) k_bilinear_diag_batch<1, 1><<<(unsigned)grid, 256, 0, st>>>(ph, la, N, P, scratch);
+    else if (rc) k_bilinear_diag_batch<1, 0><<<(unsigned)grid, 256, 0, st>>>(ph, la, N, P, scratch);
+    else if (ctl) k_bilinear_diag_batch<0, 1><<<(unsigned)grid, 256, 0, st>>>(ph, la, N, P, scratch);
+    else k_bilinear_diag_batch<0, 0><<<(unsigned)grid, 256, 0, st>>>(ph, la, N, P, scratch);
+    k_bilinear_batch_final<<<ngen, 256, 0, (cudaStream_t)stream>>>(scratch, (int)grid, O);
+    return (int)cudaGetLastError();
+}
+
 
 extern "C" int b200k_bilinear_batch(const double *phi, const double *lam, int n_local, const B200k2Header *hdr,
                                     const B200kBatchGen *gens, int ngen, double *const *outs, double *scratch,
@@ -1349,29 +1526,287 @@ extern "C" int b200k_bilinear_batch(const double *phi, const double *lam, int n_
     if (ngen < 1 || ngen > B200K_BATCH_GENS || hdr->t > 11 || hdr->t > n_local || hdr->c + hdr->nhigh != hdr->t ||
         hdr->ntiles != (1ull << (n_local - hdr->t)))
         return (int)cudaErrorInvalidValue;
-    static std::atomic<unsigned long long> attr_mask{0}; // threads of one process may launch concurrently
-    int cur_dev = 0;
-    cudaGetDevice(&cur_dev);
-    if (!((attr_mask.load(std::memory_order_acquire) >> (cur_dev & 63)) & 1ull)) {
-        cudaError_t e = cudaFuncSetAttribute(k_bilinear_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 16 * 2048);
-        if (e != cudaSuccess) return (int)e;
-        attr_mask.fetch_or(1ull << (cur_dev & 63), std::memory_order_release);
-    }
+    // result = i^ny (tr + i ti): which raw component carries the wanted part, and with which sign
+    //   real part: ny 0: tr, 1: -ti, 2: -tr, 3: ti        imaginary part: ny 0: ti, 1: tr, 2: -ti, 3: -tr
+    int rc = -1;
+    bool ctl = false;
     BatchParams P;
     memset(&P, 0, sizeof(P));
     P.h = *hdr;
     P.ngen = ngen;
     BatchOut O;
+    memset(&O, 0, sizeof(O));
     for (int g = 0; g < ngen; g++) {
+        const int ny = gens[g].ny & 3, want = gens[g].want;
+        if (want != B200K_WANT_REAL && want != B200K_WANT_IMAG) return (int)cudaErrorInvalidValue;
+        const bool imag = want == B200K_WANT_IMAG;
+        const int my_rc = (ny & 1) ^ (imag ? 1 : 0);
+        if (rc < 0) rc = my_rc;
+        if (rc != my_rc) return (int)cudaErrorInvalidValue; // a batch is uniform in the raw component it needs
         P.g[g] = gens[g];
+        if ((gens[g].xin >> hdr->t) || (gens[g].zin >> hdr->t)) return (int)cudaErrorInvalidValue;
+        // sign table of the elements' bits 8..10 (bits 16..23 of zin) and parity(xin & zin) (bit 24): see the kernel
+        uint32_t kpar = 0;
+        for (uint32_t kk = 0; kk < 8; kk++) kpar |= (uint32_t)(__builtin_popcount(kk & (gens[g].zin >> 8)) & 1) << kk;
+        P.g[g].zin = gens[g].zin | (kpar << 16) | ((uint32_t)(__builtin_popcount(gens[g].xin & gens[g].zin) & 1) << 24);
+        ctl = ctl || gens[g].cin_m != 0;
         O.out[g] = outs[g];
-        O.ny[g] = gens[g].ny;
+        O.slot[g] = imag ? 1 : 0;
+        O.neg[g] = imag ? (ny == 2 || ny == 3) : (ny == 1 || ny == 2);
     }
-    uint64_t grid = 148 * 3;
+    const bool same = phi == lam;
+    const size_t smem = (same ? 2 : 3) * (sizeof(cplx) << hdr->t);
+    static std::atomic<unsigned long long> attr_mask{0}; // threads of one process may launch concurrently
+    int cur_dev = 0;
+    cudaGetDevice(&cur_dev);
+    if (!((attr_mask.load(std::memory_order_acquire) >> (cur_dev & 63)) & 1ull)) {
+        const int cap = 3 * 16 * 2048;
+        cudaError_t e = cudaFuncSetAttribute(k_bilinear_batch<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bilinear_batch<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bilinear_batch<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bilinear_batch<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+        if (e != cudaSuccess) return (int)e;
+        attr_mask.fetch_or(1ull << (cur_dev & 63), std::memory_order_release);
+    }
+    uint64_t grid = 148 * 2;
     if (grid > hdr->ntiles) grid = hdr->ntiles;
-    k_bilinear_batch<<<(unsigned)grid, 256, (size_t)2 * sizeof(cplx) << hdr->t, (cudaStream_t)stream>>>(
-        (const cplx *)phi, (const cplx *)lam, P, scratch);
+    const cplx *ph = (const cplx *)phi, *la = (const cplx *)lam;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (rc && ctl) k_bilinear_batch<1, 1><<<(unsigned)grid, 256, smem, st>>>(ph, la, P, scratch);
+    else if (rc) k_bilinear_batch<1, 0><<<(unsigned)grid, 256, smem, st>>>(ph, la, P, scratch);
+    else if (ctl) k_bilinear_batch<0, 1><<<(unsigned)grid, 256, smem, st>>>(ph, la, P, scratch);
+    else k_bilinear_batch<0, 0><<<(unsigned)grid, 256, smem, st>>>(ph, la, P, scratch);
     k_bilinear_batch_final<<<ngen, 256, 0, (cudaStream_t)stream>>>(scratch, (int)grid, O);
+    return (int)cudaGetLastError();
+}
+
+// =================================================================================================
+// Sum of Pauli words on tiles: sigma = sum_w coef_w P_w in, either written out (phi = H psi of the adjoint method)
+// or contracted on the fly with a bra (Expval of a Hamiltonian: no vector is written at all).
+// k_pauli_apply_batch gathers in[i ^ x_w] from HBM/L2 once per WORD (C4, 26 qubits, 1000 words: 63 launches of
+// 2.2 ms); here the tile is staged once per launch and every word whose X/Y bits lie inside it is a shared-memory
+// permutation, so HBM sees 1 read (+ the accumulator) per BIN of up to 96 words.
+// Per (amplitude, word): one LDS.128, the Z-parity sign folded into the coefficient's sign bit, 2 DFMA for the usual
+// real-coefficient word (i^ny makes the factor purely real or purely imaginary), 4 for a general one.
+// =================================================================================================
+struct TileWordK { // 32 bytes, coefficient with i^ny and (-1)^popc(xin & zin) folded in
+    uint32_t xin, zin; // zin: bits 0..10 the mask, bits 16..23 the sign table of the elements' bits 8..10
+    uint64_t zo;
+    double cr, ci;
+};
+struct TileWordsParams {
+    B200k2Header h;
+    int n, accumulate;
+    TileWordK w[B200K_TILE_WORDS];
+};
+
+// Persistent CTAs, two tile buffers: the next tile's amplitudes are in flight (cp.async, no registers) while the words
+// of the current tile are summed.  (The first version loaded tile after tile with nothing in flight and spent ~1.2 ms
+// per launch of ~14 words at 26 qubits, against 0.17 ms of HBM time and ~0.4 ms of shared-memory time.)
+template <int DOT, int FULL> __global__ void __launch_bounds__(256, 2)
+k_pauli_words_tile(cplx *__restrict__ out, const cplx *__restrict__ in, const cplx *__restrict__ bra,
+                   const __grid_constant__ TileWordsParams P, double *__restrict__ partial)
+{
+    extern __shared__ cplx sT[]; // 2 x 2^t amplitudes
+    __shared__ unsigned long long koff[8];
+    const int t = P.h.t, c = P.h.c;
+    const uint32_t nelem = 1u << t, tid = threadIdx.x;
+    auto pos_of = [&](int bpos) -> int { return bpos < c ? bpos : (int)P.h.high_pos[bpos - c]; };
+    uint64_t off_tid = 0;
+    for (int bpos = 0; bpos < 8 && bpos < t; bpos++) off_tid |= (uint64_t)((tid >> bpos) & 1u) << pos_of(bpos);
+    if (tid < 8) {
+        uint64_t o = 0;
+        for (int j = 0; j < 3; j++)
+            if (8 + j < t && ((tid >> j) & 1u)) o |= 1ull << pos_of(8 + j);
+        koff[tid] = o;
+    }
+    auto base_of = [&](uint64_t tile) {
+        uint64_t base = tile << c;
+        for (int hh = 0; hh < P.h.nhigh; hh++) {
+            const int p = P.h.high_pos[hh];
+            base = ((base >> p) << (p + 1)) | (base & ((1ull << p) - 1ull));
+        }
+        return base;
+    };
+    auto fetch = [&](uint64_t tile, cplx *buf) {
+        const uint64_t b = base_of(tile) | off_tid;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const uint32_t e = tid + 256u * k;
+            if (FULL || e < nelem) kw_cp_async16(&buf[e], &in[b | koff[k]]);
+        }
+    };
+    double dot[2] = {0.0, 0.0};
+    const bool same = bra == in;
+    __syncthreads(); // koff
+    if (blockIdx.x < P.h.ntiles) fetch(blockIdx.x, sT);
+    kw_cp_async_commit();
+    int cur = 0;
+    for (uint64_t tile = blockIdx.x; tile < P.h.ntiles; tile += gridDim.x, cur ^= 1) {
+        cplx *sB = sT + ((size_t)cur << t);
+        __syncthreads(); // every thread is done with the buffer the prefetch below overwrites
+        const uint64_t next = tile + gridDim.x;
+        if (next < P.h.ntiles) fetch(next, sT + ((size_t)(cur ^ 1) << t));
+        kw_cp_async_commit();
+        kw_cp_async_wait<1>(); // this tile's group has landed; the next one may still be in flight
+        __syncthreads();
+        const uint64_t base = base_of(tile);
+        const uint64_t obase = base | P.h.rank_base;
+        cplx acc[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) { // accumulating into out: its old values are loaded first, behind the word loop
+            const uint32_t e = tid + 256u * k;
+            acc[k] = (!DOT && P.accumulate && (FULL || e < nelem)) ? out[base | off_tid | koff[k]] : make_double2(0.0, 0.0);
+        }
+        for (int w = 0; w < P.n; w++) {
+            const TileWordK &W = P.w[w];
+            // sign of element e = tid + 256 k: parity(e & zin) ^ parity(obase & zo).  The tid part and the tile part are
+            // shared by the thread's 8 elements; the k part is a host-made 8-bit table (bit k = parity(k & (zin >> 8)))
+            // in the upper half of the zin field.  M bit k = sign of element k.
+            const uint32_t common = (__popc(tid & W.zin) + __popcll(obase & W.zo)) & 1u;
+            const uint32_t M = (0u - common) ^ (W.zin >> 16);
+            const uint32_t x16 = W.xin;
+            if (W.ci == 0.0) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const uint32_t e = tid + 256u * k;
+                    if (FULL || e < nelem) {
+                        const cplx b = sB[e ^ x16];
+                        const long long sg = (long long)((M << (31 - k)) & 0x80000000u) << 32;
+                        const double cr = __longlong_as_double(__double_as_longlong(W.cr) ^ sg);
+                        acc[k].x = fma(cr, b.x, acc[k].x);
+                        acc[k].y = fma(cr, b.y, acc[k].y);
+                    }
+                }
+            }
+            else if (W.cr == 0.0) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const uint32_t e = tid + 256u * k;
+                    if (FULL || e < nelem) {
+                        const cplx b = sB[e ^ x16];
+                        const long long sg = (long long)((M << (31 - k)) & 0x80000000u) << 32;
+                        const double ci = __longlong_as_double(__double_as_longlong(W.ci) ^ sg);
+                        acc[k].x = fma(-ci, b.y, acc[k].x);
+                        acc[k].y = fma(ci, b.x, acc[k].y);
+                    }
+                }
+            }
+            else {
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const uint32_t e = tid + 256u * k;
+                    if (FULL || e < nelem) {
+                        const cplx b = sB[e ^ x16];
+                        const long long sg = (long long)((M << (31 - k)) & 0x80000000u) << 32;
+                        const double cr = __longlong_as_double(__double_as_longlong(W.cr) ^ sg);
+                        const double ci = __longlong_as_double(__double_as_longlong(W.ci) ^ sg);
+                        acc[k].x = fma(cr, b.x, fma(-ci, b.y, acc[k].x));
+                        acc[k].y = fma(cr, b.y, fma(ci, b.x, acc[k].y));
+                    }
+                }
+            }
+        }
+        if (DOT) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) { // conj(bra) * acc
+                const uint32_t e = tid + 256u * k;
+                if (FULL || e < nelem) {
+                    const cplx a = same ? sB[e] : bra[base | off_tid | koff[k]];
+                    dot[0] += fma(a.x, acc[k].x, a.y * acc[k].y);
+                    dot[1] += fma(a.x, acc[k].y, -(a.y * acc[k].x));
+                }
+            }
+        }
+        else {
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const uint32_t e = tid + 256u * k;
+                if (FULL || e < nelem) {
+                    out[base | off_tid | koff[k]] = acc[k];
+                }
+            }
+        }
+    }
+    kw_cp_async_wait<0>();
+    if (DOT) block_reduce_store<2>(dot, partial);
+}
+
+extern "C" int b200k_pauli_words_tile(double *out, const double *in, const double *bra, int n_local,
+                                      const B200k2Header *hdr, const B200kTileWord *words, int nwords, int accumulate,
+                                      double *scratch, double *dot_out, void *stream)
+{
+    if (nwords < 1 || nwords > B200K_TILE_WORDS || hdr->t > 11 || hdr->t > n_local || hdr->c + hdr->nhigh != hdr->t ||
+        hdr->ntiles != (1ull << (n_local - hdr->t)) || !in || out == in)
+        return (int)cudaErrorInvalidValue;
+    if (!out && (!bra || !scratch || !dot_out)) return (int)cudaErrorInvalidValue;
+    static_assert(sizeof(TileWordsParams) <= 4000, "kernel parameter space");
+    TileWordsParams P;
+    memset(&P, 0, sizeof(P));
+    P.h = *hdr;
+    P.n = nwords;
+    P.accumulate = accumulate;
+    for (int w = 0; w < nwords; w++) {
+        const B200kTileWord &W = words[w];
+        if ((W.xin >> hdr->t) || (W.zin >> hdr->t)) return (int)cudaErrorInvalidValue;
+        // coef * i^ny * (-1)^popc(xin & zin): the Z factors act at the partner index j = e ^ xin
+        double cr = W.cr, ci = W.ci;
+        switch (W.ny & 3) {
+        case 1: { const double r = -ci; ci = cr; cr = r; break; }
+        case 2: cr = -cr; ci = -ci; break;
+        case 3: { const double r = ci; ci = -cr; cr = r; break; }
+        default: break;
+        }
+        if (__builtin_popcount(W.xin & W.zin) & 1) { cr = -cr; ci = -ci; }
+        if (cr == 0.0) cr = 0.0; // no negative zeros: the kernel classifies words by exact zero tests
+        if (ci == 0.0) ci = 0.0;
+        P.w[w].xin = W.xin;
+        uint32_t kpar = 0; // bit k = parity(k & (zin >> 8)), k = the element's tile bits 8..10
+        for (uint32_t kk = 0; kk < 8; kk++) kpar |= (uint32_t)(__builtin_popcount(kk & (W.zin >> 8)) & 1) << kk;
+        P.w[w].zin = W.zin | (kpar << 16);
+        P.w[w].zo = W.zo;
+        P.w[w].cr = cr;
+        P.w[w].ci = ci;
+    }
+    static std::atomic<unsigned long long> attr_mask{0};
+    int cur_dev = 0;
+    cudaGetDevice(&cur_dev);
+    if (!((attr_mask.load(std::memory_order_acquire) >> (cur_dev & 63)) & 1ull)) {
+        cudaError_t e = cudaFuncSetAttribute(k_pauli_words_tile<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 16 * 2048);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pauli_words_tile<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 16 * 2048);
+        if (e != cudaSuccess) return (int)e;
+        attr_mask.fetch_or(1ull << (cur_dev & 63), std::memory_order_release);
+    }
+    const size_t smem = 2 * (sizeof(cplx) << hdr->t); // two tile buffers
+    const bool full = hdr->t == 11;
+    // persistent CTAs: as many as are resident at once (2 or 3 per SM, by registers and the two tile buffers)
+    static std::atomic<int> resident[2] = {{0}, {0}};
+    int per_sm = resident[out ? 0 : 1].load(std::memory_order_relaxed);
+    if (per_sm == 0 || !full) {
+        per_sm = 2;
+        if (full) {
+            int nb = 0;
+            cudaError_t e = out ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_pauli_words_tile<0, 1>, 256, smem)
+                                : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_pauli_words_tile<1, 1>, 256, smem);
+            if (e == cudaSuccess && nb >= 1) per_sm = nb;
+            resident[out ? 0 : 1].store(per_sm, std::memory_order_relaxed);
+        }
+    }
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cur_dev);
+    uint64_t grid = (uint64_t)sms * per_sm;
+    if (grid > hdr->ntiles) grid = hdr->ntiles;
+    if (grid > RED_BLOCKS) grid = RED_BLOCKS; // the contraction's partials live in the shared reduction scratch
+    cudaStream_t st = (cudaStream_t)stream;
+    if (out) {
+        if (full) k_pauli_words_tile<0, 1><<<(unsigned)grid, 256, smem, st>>>((cplx *)out, (const cplx *)in, nullptr, P, nullptr);
+        else k_pauli_words_tile<0, 0><<<(unsigned)grid, 256, smem, st>>>((cplx *)out, (const cplx *)in, nullptr, P, nullptr);
+    }
+    else {
+        if (full) k_pauli_words_tile<1, 1><<<(unsigned)grid, 256, smem, st>>>(nullptr, (const cplx *)in, (const cplx *)bra, P, scratch);
+        else k_pauli_words_tile<1, 0><<<(unsigned)grid, 256, smem, st>>>(nullptr, (const cplx *)in, (const cplx *)bra, P, scratch);
+        k_reduce_final<2><<<1, RED_THREADS, 0, (cudaStream_t)stream>>>(scratch, (int)grid, dot_out);
+    }
     return (int)cudaGetLastError();
 }
 

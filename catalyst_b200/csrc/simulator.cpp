@@ -2317,10 +2317,20 @@ void Simulator::apply_observable(int64_t key, const double *vin, double *vout, c
         first = false;
         bx.clear(); bz.clear(); bny.clear(); bc.clear();
     };
+    // Pauli words whose X/Y bits fit a tile: tile-staged, up to 96 words per read of vin (k_pauli_words_tile)
+    const int fit = (int)std::min<int64_t>(11, nl_) - 3;
+    std::vector<TileWordRef> tiled;
+    auto tileable = [&](const PauliTerm &p) {
+        return opt_.batch_overlaps && nl_ >= 3 && __builtin_popcountll(p.xmask) <= fit;
+    };
     for (auto &t : terms) {
         std::vector<PauliTerm> pts;
         if (term_to_paulis(t, pts)) {
             for (auto &p : pts) {
+                if (tileable(p)) {
+                    tiled.push_back({p.xmask, p.zmask, p.ny, p.coef});
+                    continue;
+                }
                 bx.push_back(to_phys(pos, p.xmask));
                 bz.push_back(to_phys(pos, p.zmask));
                 bny.push_back(p.ny);
@@ -2350,6 +2360,22 @@ void Simulator::apply_observable(int64_t key, const double *vin, double *vout, c
         first = false;
     }
     flush_words();
+    if (tiled.size() > 1) {
+        std::vector<int> lay = pos; // every X/Y bit is local already (precondition): no swap can happen
+        pauli_words_binned(std::move(tiled), {}, lay, [&](const B200k2Header &H, const std::vector<B200kTileWord> &ws) {
+            CUDA_CHECK(b200k_pauli_words_tile(vout, vin, nullptr, (int)nl_, &H, ws.data(), (int)ws.size(), first ? 0 : 1,
+                                              nullptr, nullptr, stream_));
+            note_launch();
+            first = false;
+        });
+    }
+    else if (tiled.size() == 1) { // a single word: the gather pass moves the same bytes without staging
+        const TileWordRef &w = tiled[0];
+        CUDA_CHECK(b200k_pauli_apply(vout, vin, (int)nl_, rank_base_, to_phys(pos, w.xmask), to_phys(pos, w.zmask), w.ny,
+                                     w.coef.real(), w.coef.imag(), first ? 0 : 1, stream_));
+        note_launch();
+        first = false;
+    }
     if (first) CUDA_CHECK(cudaMemsetAsync(vout, 0, bytes, (cudaStream_t)stream_));
 }
 
@@ -2402,31 +2428,39 @@ double Simulator::expval(int64_t key)
         }
         CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream_)); // zm/cf are stack-owned
     }
-    // the layout may change between terms (a word with X/Y on a rank bit pulls that qubit in), so
-    // masks are translated term by term
-    bool batched = false;
-    if (opt_.batch_overlaps && nl_ >= 3 && offd.size() > 1) { // many words per read pass
-        std::vector<OvTerm> ov;
-        bool ok = true;
-        int sl = slot;
+    // Off-diagonal words: those whose X/Y bits fit one tile are evaluated many per read pass -- sum_w c_w <psi|P_w|psi>
+    // per BIN of words (pauli_words_binned -> k_pauli_words_tile in its contraction mode: psi is read once per bin and
+    // nothing is written).  A word with more X/Y factors than a tile has free bits takes a read pass of its own.
+    // (Round 1 switched batching off for the WHOLE Hamiltonian when a single word did not fit: C4's 1000 terms, one of
+    // them with 9 X/Y factors, ran as 950 separate passes.)
+    int nbin_slots = 0;
+    std::vector<const PauliTerm *> single;
+    {
+        const int fit = (int)std::min<int64_t>(11, nl_) - 3;
+        std::vector<TileWordRef> binned;
         for (auto &p : offd) {
-            ok = ok && __builtin_popcountll(p.xmask) <= std::min<int64_t>(11, nl_) - 3;
-            ov.push_back({p.xmask, p.zmask, 0, 0, p.ny, result_slot(sl++), 0});
+            if (opt_.batch_overlaps && nl_ >= 3 && offd.size() > 1 && __builtin_popcountll(p.xmask) <= fit)
+                binned.push_back({p.xmask, p.zmask, p.ny, p.coef});
+            else single.push_back(&p);
         }
-        if (ok) {
-            overlaps_batched(psi_->d(), psi_->d(), {psi_->d()}, pos_, ov);
-            slot = sl;
-            batched = true;
-        }
-    }
-    if (!batched)
-        for (auto &p : offd) {
+        if (!binned.empty())
+            pauli_words_binned(std::move(binned), {psi_->d()}, pos_, [&](const B200k2Header &H, const std::vector<B200kTileWord> &ws) {
+                CUDA_CHECK(b200k_pauli_words_tile(nullptr, psi_->d(), psi_->d(), (int)nl_, &H, ws.data(), (int)ws.size(), 0,
+                                                  scratch_->d(), result_slot(slot++), stream_));
+                note_launch();
+                nbin_slots++;
+            });
+        // the layout may change between terms (a word with X/Y on a rank bit pulls that qubit in), so
+        // masks are translated term by term
+        for (auto *pp : single) {
+            const PauliTerm &p = *pp;
             make_local({psi_->d()}, pos_, p.xmask);
             CUDA_CHECK(b200k_bilinear_pauli(psi_->d(), psi_->d(), (int)nl_, rank_base_, to_phys(pos_, p.xmask),
                                             to_phys(pos_, p.zmask), p.ny, 0, 0, scratch_->d(),
                                             result_slot(slot++), stream_));
             note_launch();
         }
+    }
     const size_t bytes = sizeof(cplx) << nl_;
     for (auto *t : generic) {
         uint64_t xm = 0;
@@ -2452,7 +2486,8 @@ double Simulator::expval(int64_t key)
     double e = 0.0;
     slot = 0;
     for (int i = 0; i < ndiag_slots; i++) e += h[2 * slot++];
-    for (auto &p : offd) e += p.coef.real() * h[2 * slot++];
+    for (int i = 0; i < nbin_slots; i++) e += h[2 * slot++]; // coefficients applied on the device
+    for (auto *p : single) e += p->coef.real() * h[2 * slot++];
     for (auto *t : generic) e += t->coef * h[2 * slot++];
     return e;
 }
@@ -3177,14 +3212,16 @@ struct Generator {
 // (k_bilinear_batch) instead of one pass per term.  `movable` / `lay`: the vectors that share the
 // layout of phi and lam (sharded registers: a term with an X/Y factor on a rank bit pulls that qubit in).
 void Simulator::overlaps_batched(const double *phi, const double *lam, const std::vector<double *> &movable,
-                                 std::vector<int> &lay, const std::vector<OvTerm> &terms)
+                                 std::vector<int> &lay, const std::vector<OvTerm> &terms, int want)
 {
     const int bt = (int)std::min<int64_t>(11, nl_);
     const int cmin = std::min(3, bt);
     struct Bin {
         uint64_t req = 0;
+        int rc = 0; // raw component the batch computes (the kernel is uniform in it)
         std::vector<const OvTerm *> t;
     };
+    auto rc_of = [&](const OvTerm &t) { return (t.ny & 1) ^ (want == B200K_WANT_IMAG ? 1 : 0); };
     auto launch = [&](const Bin &b) {
         const int c = fit_rows(b.req, bt);
         std::vector<int> high;
@@ -3227,6 +3264,7 @@ void Simulator::overlaps_batched(const double *phi, const double *lam, const std
             split(to_phys(lay, p.cmask), G.cin_m, G.co_m);
             split(to_phys(lay, p.cval), G.cin_v, G.co_v);
             G.ny = p.ny;
+            G.want = want;
             outs[q] = p.out;
         }
         ensure_buffer(batch_scratch_, (size_t)b200k_bilinear_batch_scratch_doubles() * sizeof(double));
@@ -3234,8 +3272,31 @@ void Simulator::overlaps_batched(const double *phi, const double *lam, const std
                                         batch_scratch_->d(), stream_));
         note_launch();
     };
+    // diagonal words (no X/Y factor): a streaming pass per 32 of them, any layout (rank bits enter through rank_base)
     std::vector<const OvTerm *> rest;
-    for (auto &t : terms) rest.push_back(&t);
+    {
+        std::vector<const OvTerm *> dg[2];
+        for (auto &t : terms) (t.xmask == 0 ? dg[rc_of(t)] : rest).push_back(&t);
+        for (auto &grp : dg)
+            for (size_t o = 0; o < grp.size(); o += B200K_BATCH_GENS) {
+                const int cnt = (int)std::min<size_t>(B200K_BATCH_GENS, grp.size() - o);
+                uint64_t z[B200K_BATCH_GENS], cm[B200K_BATCH_GENS], cv[B200K_BATCH_GENS];
+                int ny[B200K_BATCH_GENS];
+                double *outs[B200K_BATCH_GENS];
+                for (int q = 0; q < cnt; q++) {
+                    const OvTerm &p = *grp[o + q];
+                    z[q] = to_phys(lay, p.zmask);
+                    cm[q] = to_phys(lay, p.cmask);
+                    cv[q] = to_phys(lay, p.cval);
+                    ny[q] = p.ny;
+                    outs[q] = p.out;
+                }
+                ensure_buffer(batch_scratch_, (size_t)b200k_bilinear_batch_scratch_doubles() * sizeof(double));
+                CUDA_CHECK(b200k_bilinear_diag_batch(phi, lam, (int)nl_, rank_base_, z, cm, cv, ny, want, cnt, outs,
+                                                     batch_scratch_->d(), stream_));
+                note_launch();
+            }
+    }
     while (!rest.empty()) {
         // every term whose X/Y bits are local under the current layout, packed first-fit
         std::vector<Bin> bins;
@@ -3249,7 +3310,7 @@ void Simulator::overlaps_batched(const double *phi, const double *lam, const std
             B200_FAIL_IF(fit_rows(x, bt) < 0, "internal: a Pauli word acts non-diagonally on more qubits than a tile holds");
             bool placed = false;
             for (auto &b : bins)
-                if (b.t.size() < (size_t)B200K_BATCH_GENS && fit_rows(b.req | x, bt) >= cmin) {
+                if (b.rc == rc_of(*t) && b.t.size() < (size_t)B200K_BATCH_GENS && fit_rows(b.req | x, bt) >= cmin) {
                     b.req |= x;
                     b.t.push_back(t);
                     placed = true;
@@ -3258,11 +3319,103 @@ void Simulator::overlaps_batched(const double *phi, const double *lam, const std
             if (!placed) {
                 bins.emplace_back();
                 bins.back().req = x;
+                bins.back().rc = rc_of(*t);
                 bins.back().t.push_back(t);
             }
         }
         for (auto &b : bins) launch(b);
         if (!later.empty()) make_local(movable, lay, later[0]->xmask); // sharded: one more qubit comes in
+        rest.swap(later);
+    }
+}
+
+// Weighted Pauli words, many per read pass: words are packed (largest X/Y support first, first fit) into bins whose
+// combined X/Y bits fit one tile -- the low c >= 3 index bits plus up to 11 - c scattered higher ones -- and every bin
+// is one launch of b200k_pauli_words_tile.  C4 (26 qubits, 1000 random words): 70 bins instead of 950 passes.
+void Simulator::pauli_words_binned(std::vector<TileWordRef> words, const std::vector<double *> &movable,
+                                   std::vector<int> &lay,
+                                   const std::function<void(const B200k2Header &, const std::vector<B200kTileWord> &)> &launch)
+{
+    const int bt = (int)std::min<int64_t>(11, nl_);
+    const int cmin = std::min(3, bt);
+    std::stable_sort(words.begin(), words.end(), [](const TileWordRef &a, const TileWordRef &b) {
+        return __builtin_popcountll(a.xmask) > __builtin_popcountll(b.xmask);
+    });
+    struct Bin {
+        uint64_t req = 0;
+        std::vector<const TileWordRef *> w;
+    };
+    auto emit = [&](const Bin &b) {
+        const int c = fit_rows(b.req, bt);
+        std::vector<int> high;
+        for (int p = c; p < 64; p++)
+            if ((b.req >> p) & 1) high.push_back(p);
+        for (int p = c; (int)high.size() < bt - c; p++)
+            if (!((b.req >> p) & 1)) high.push_back(p);
+        std::sort(high.begin(), high.end());
+        int loc[64];
+        for (int p = 0; p < 64; p++) loc[p] = p < c ? p : -1;
+        for (size_t h = 0; h < high.size(); h++) loc[high[h]] = c + (int)h;
+        B200k2Header H;
+        std::memset(&H, 0, sizeof(H));
+        H.t = bt;
+        H.c = c;
+        H.nhigh = (int)high.size();
+        for (size_t h = 0; h < high.size(); h++) H.high_pos[h] = (uint8_t)high[h];
+        H.rank_base = rank_base_;
+        H.ntiles = 1ull << (nl_ - bt);
+        std::vector<B200kTileWord> ws(b.w.size());
+        for (size_t q = 0; q < b.w.size(); q++) {
+            const TileWordRef &r = *b.w[q];
+            B200kTileWord &W = ws[q];
+            std::memset(&W, 0, sizeof(W));
+            for (uint64_t m = to_phys(lay, r.xmask); m; m &= m - 1) {
+                const int p = __builtin_ctzll(m);
+                B200_FAIL_IF(loc[p] < 0, "internal: Pauli word bit outside the tile");
+                W.xin |= 1u << loc[p];
+            }
+            for (uint64_t m = to_phys(lay, r.zmask); m; m &= m - 1) {
+                const int p = __builtin_ctzll(m);
+                if (loc[p] >= 0) W.zin |= 1u << loc[p];
+                else W.zo |= 1ull << p;
+            }
+            W.cr = r.coef.real();
+            W.ci = r.coef.imag();
+            W.ny = r.ny;
+        }
+        launch(H, ws);
+    };
+    std::vector<const TileWordRef *> rest;
+    for (auto &w : words) rest.push_back(&w);
+    while (!rest.empty()) {
+        std::vector<Bin> bins;
+        std::vector<const TileWordRef *> later;
+        for (const TileWordRef *w : rest) {
+            const uint64_t x = to_phys(lay, w->xmask);
+            if (x >> nl_) { // an X/Y factor on a rank bit: that qubit has to come in first
+                later.push_back(w);
+                continue;
+            }
+            B200_FAIL_IF(fit_rows(x, bt) < cmin, "internal: a Pauli word acts non-diagonally on more qubits than a tile holds");
+            bool placed = false;
+            for (auto &b : bins)
+                if (b.w.size() < (size_t)B200K_TILE_WORDS && fit_rows(b.req | x, bt) >= cmin) {
+                    b.req |= x;
+                    b.w.push_back(w);
+                    placed = true;
+                    break;
+                }
+            if (!placed) {
+                bins.emplace_back();
+                bins.back().req = x;
+                bins.back().w.push_back(w);
+            }
+        }
+        for (auto &b : bins) emit(b);
+        if (!later.empty()) {
+            B200_FAIL_IF(movable.empty(), "internal: Pauli word with a non-local X/Y factor");
+            make_local(movable, lay, later[0]->xmask);
+        }
         rest.swap(later);
     }
 }
@@ -3366,7 +3519,7 @@ std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
         for (size_t k = 0; k < K; k++) {
             std::vector<OvTerm> terms = pend_ov;
             for (auto &t : terms) t.out = result_slot((int)(k * T + t.tag));
-            overlaps_batched(phi[k]->d(), lambda.d(), vecs, lay, terms);
+            overlaps_batched(phi[k]->d(), lambda.d(), vecs, lay, terms, B200K_WANT_IMAG); // jac = -2 sigma Im<phi|G|lambda>
         }
         pend_ov.clear();
     };

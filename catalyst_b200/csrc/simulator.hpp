@@ -268,7 +268,15 @@ class Simulator {
         size_t tag;
     };
     void overlaps_batched(const double *phi, const double *lam, const std::vector<double *> &movable,
-                          std::vector<int> &lay, const std::vector<OvTerm> &terms);
+                          std::vector<int> &lay, const std::vector<OvTerm> &terms, int want);
+    struct TileWordRef { // one weighted Pauli word (logical masks)
+        uint64_t xmask, zmask;
+        int ny;
+        std::complex<double> coef;
+    };
+    // Packs words into bins whose X/Y bits fit one tile and calls `launch` once per bin (b200k_pauli_words_tile).
+    void pauli_words_binned(std::vector<TileWordRef> words, const std::vector<double *> &movable, std::vector<int> &lay,
+                            const std::function<void(const B200k2Header &, const std::vector<B200kTileWord> &)> &launch);
     bool draw_outcome(const double p[2], int postselect);
     double sampled_term_mean(const ObsTerm &t);
     void sampled_term_moments(const ObsTerm &t, double &m1, double &m2);

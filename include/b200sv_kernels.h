@@ -183,7 +183,8 @@ int b200k_bilinear_pair(const double *phi, const double *lam, int n_local, uint6
 /* Batched version of b200k_bilinear_pauli: up to B200K_BATCH_GENS Pauli-word generators evaluated in
  * ONE read pass over phi and lam (tile geometry of the gate passes: header fields t, c, nhigh, high_pos,
  * rank_base, ntiles).  Masks are split like the gate ops: inside the tile (tile-local bit positions) and
- * outside (physical positions, incl. rank bits).  outs[g] receives (re, im) of generator g. */
+ * outside (physical positions, incl. rank bits).  outs[g] receives (re, im) of generator g, of which only the
+ * component named by `want` is computed. */
 #define B200K_BATCH_GENS 32
 typedef struct B200kBatchGen {
     uint32_t xin;            /* X/Y bits (tile-local); all of them must lie inside the tile        */
@@ -191,11 +192,46 @@ typedef struct B200kBatchGen {
     uint32_t cin_m, cin_v;   /* control predicate inside the tile                                   */
     uint64_t zo;             /* Z bits outside the tile                                             */
     uint64_t co_m, co_v;     /* control predicate outside the tile                                  */
-    int32_t ny, pad;         /* number of Y factors (phase i^ny)                                    */
+    int32_t ny;              /* number of Y factors (phase i^ny)                                    */
+    int32_t want;            /* B200K_WANT_REAL / _IMAG: the part of the result the caller uses; the other
+                                is written as 0.  All generators of one call must need the same RAW component
+                                ((ny & 1) ^ (want == imag) equal across the batch)                       */
 } B200kBatchGen;
+enum { B200K_WANT_REAL = 1, B200K_WANT_IMAG = 2 };
 int64_t b200k_bilinear_batch_scratch_doubles(void);
 int b200k_bilinear_batch(const double *phi, const double *lam, int n_local, const struct B200k2Header *hdr,
                          const B200kBatchGen *gens, int ngen, double *const *outs, double *scratch, void *stream);
+
+/* Sum of up to B200K_TILE_WORDS Pauli words, tile-staged: ONE read of `in` for the whole set instead of one gather
+ * per word.  Serves QuantumDevice::Expval of a HamiltonianObservable (runtime/include/QuantumDevice.hpp:353,488;
+ * "copy psi, apply O (per-term copy + gates + axpy), inner product: >= 3S traffic per term")
+ * and the phi = H psi initialisation of QuantumDevice::Gradient (:564).
+ * Tile geometry as in b200k_bilinear_batch (hdr: t <= 11, c, nhigh, high_pos, rank_base, ntiles); every word's
+ * X/Y bits lie inside the tile.
+ *   out != NULL:  out_i = (accumulate ? out_i : 0) + sum_w coef_w (P_w in)_i            (out must not alias in)
+ *   out == NULL:  dot_out[0..1] = sum_i conj(bra_i) * sum_w coef_w (P_w in)_i  (re, im); `scratch` holds
+ *                 b200k_reduce_scratch_doubles() doubles; bra may equal in.
+ * (P v)_i = i^ny (-1)^popc(j & z) v_j, j = i ^ x, as in b200k_bilinear_pauli. */
+#define B200K_TILE_WORDS 96
+typedef struct B200kTileWord {
+    uint32_t xin;  /* X/Y bits (tile-local positions)             */
+    uint32_t zin;  /* Z/Y bits inside the tile (tile-local)       */
+    uint64_t zo;   /* Z/Y bits outside the tile (physical, incl. rank bits) */
+    double cr, ci; /* coefficient                                 */
+    int32_t ny;    /* number of Y factors                         */
+    int32_t pad;
+} B200kTileWord;
+int b200k_pauli_words_tile(double *out, const double *in, const double *bra, int n_local,
+                           const struct B200k2Header *hdr, const B200kTileWord *words, int nwords, int accumulate,
+                           double *scratch, double *dot_out, void *stream);
+
+/* The same bilinear forms for up to B200K_BATCH_GENS DIAGONAL words (no X/Y factor) in one streaming pass:
+ * outs[g] = (re, im) of sum_i [((rank_base|i) & cmasks[g]) == cvals[g]] i^ny (-1)^popc((rank_base|i) & zmasks[g])
+ * conj(phi_i) lam_i, of which only the component named by `want` is computed (the other is written as 0).  Masks are
+ * physical (rank bits included).  scratch: b200k_bilinear_batch_scratch_doubles() doubles. */
+int b200k_bilinear_diag_batch(const double *phi, const double *lam, int n_local, uint64_t rank_base,
+                              const uint64_t *zmasks, const uint64_t *cmasks, const uint64_t *cvals, const int *nys,
+                              int want, int ngen, double *const *outs, double *scratch, void *stream);
 
 /* out[0] = sum_i |psi_i|^2 * sum_t coef[t] * (-1)^popc((rank_base|i) & zmask[t]). */
 int b200k_expval_diag_batch(const double *psi, int n_local, uint64_t rank_base,

@@ -613,3 +613,85 @@ def test_mcmc_sampling(gpu, oracle_mod, n, seed, kernel):
 def test_mcmc_kwargs_are_validated(gpu):
     with pytest.raises(RuntimeError, match="kernel_name"):
         gpu.B200Device(2, mcmc=True, kernel_name="Gibbs")
+
+
+# ---- tile-staged sums of Pauli words (b200k_pauli_words_tile), called directly through the C ABI -----------------
+@pytest.mark.parametrize("n,c,high", [(13, 4, [5, 6, 8, 9, 10, 11, 12]), (9, 3, [3, 4, 5, 6, 7, 8]), (12, 11, []),
+                                      (4, 2, [2, 3])])
+def test_pauli_words_tile_entry_point(gpu, n, c, high):
+    """out = sum_w coef_w P_w in (written, and accumulated on a second call) and <bra| sum_w coef_w P_w |in> against
+    numpy, with real, imaginary and general complex coefficients, Z factors inside and outside the tile."""
+    import ctypes as C
+    import torch
+    L = gpu.lib()
+
+    class Hdr(C.Structure):
+        _fields_ = [("n_rounds", C.c_int32), ("n_ops", C.c_int32), ("t", C.c_int32), ("c", C.c_int32),
+                    ("nhigh", C.c_int32), ("pad", C.c_int32), ("high_pos", C.c_uint8 * 16), ("rank_base", C.c_uint64),
+                    ("ntiles", C.c_uint64)]
+
+    class Word(C.Structure):
+        _fields_ = [("xin", C.c_uint32), ("zin", C.c_uint32), ("zo", C.c_uint64), ("cr", C.c_double), ("ci", C.c_double),
+                    ("ny", C.c_int32), ("pad", C.c_int32)]
+
+    L.b200k_pauli_words_tile.restype = C.c_int
+    L.b200k_pauli_words_tile.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(Hdr), C.POINTER(Word),
+                                         C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.b200k_reduce_scratch_doubles.restype = C.c_int64
+    t = c + len(high)
+    assert t == min(11, n)
+    loc = {p: p for p in range(c)}
+    loc.update({p: c + i for i, p in enumerate(high)})
+    rng = np.random.default_rng(100 + n)
+    da, db = gpu.B200Device(n, seed=1, virtual_swap=False), gpu.B200Device(n, seed=2, virtual_swap=False)
+    apply_ops(da, random_circuit(21, n, 30))
+    apply_ops(db, random_circuit(22, n, 30))
+    va, vb = da.state(), db.state()  # wire 0 = most significant index bit: index i <-> physical amplitude i
+    pa, pb = da.device_pointer(), db.device_pointer()
+    H = Hdr(t=t, c=c, nhigh=len(high), rank_base=0, ntiles=1 << (n - t))
+    for i, p in enumerate(high):
+        H.high_pos[i] = p
+    nw = 40
+    words = (Word * nw)()
+    idx = np.arange(1 << n, dtype=np.uint64)
+    want = np.zeros(1 << n, dtype=np.complex128)
+    inside = sorted(loc)
+    for w in range(nw):
+        xbits = [int(b) for b in rng.choice(inside, size=int(rng.integers(0, min(4, t) + 1)), replace=False)]
+        zbits = [int(b) for b in rng.choice(n, size=int(rng.integers(0, n + 1)), replace=False)]
+        x = sum(1 << b for b in xbits)
+        z = sum(1 << b for b in zbits)
+        ny = bin(x & z).count("1")
+        kind = w % 3
+        coef = complex(rng.normal(), 0.0) if kind == 0 else complex(0.0, rng.normal()) if kind == 1 else \
+            complex(rng.normal(), rng.normal())
+        words[w] = Word(xin=sum(1 << loc[b] for b in xbits), zin=sum(1 << loc[b] for b in zbits if b in loc),
+                        zo=sum(1 << b for b in zbits if b not in loc), cr=coef.real, ci=coef.imag, ny=ny)
+        j = idx ^ np.uint64(x)
+        par = np.zeros(1 << n, dtype=np.int64)
+        for b in zbits:
+            par ^= ((j >> np.uint64(b)) & np.uint64(1)).astype(np.int64)
+        want += coef * (1j ** ny) * (1 - 2 * par) * va[j.astype(np.int64)]
+    torch.cuda.set_device(0)
+    out = torch.zeros(2 << n, dtype=torch.float64, device="cuda")
+    scratch = torch.zeros(int(L.b200k_reduce_scratch_doubles()), dtype=torch.float64, device="cuda")
+    dot = torch.zeros(2, dtype=torch.float64, device="cuda")
+    scale = float(np.max(np.abs(want)))
+    for rep in range(2):  # written, then accumulated
+        assert L.b200k_pauli_words_tile(out.data_ptr(), pa, None, n, H, words, nw, rep, None, None, None) == 0
+        torch.cuda.synchronize()
+        got = out.cpu().numpy().view(np.complex128)
+        assert np.max(np.abs(got - (rep + 1) * want)) <= TOL * scale * (rep + 1)
+    for bra_ptr, bra in ((pa, va), (pb, vb)):
+        assert L.b200k_pauli_words_tile(None, pa, bra_ptr, n, H, words, nw, 0, scratch.data_ptr(), dot.data_ptr(), None) == 0
+        torch.cuda.synchronize()
+        g = dot.cpu().numpy()
+        ref = np.vdot(bra, want)
+        assert abs(complex(g[0], g[1]) - ref) <= TOL * max(1.0, abs(ref), scale)
+    # argument checks: a word bit outside the tile, too many words, out aliasing in
+    bad = (Word * 1)(Word(xin=1 << t, zin=0, zo=0, cr=1.0, ci=0.0, ny=0))
+    assert L.b200k_pauli_words_tile(out.data_ptr(), pa, None, n, H, bad, 1, 0, None, None, None) != 0
+    assert L.b200k_pauli_words_tile(out.data_ptr(), pa, None, n, H, words, 97, 0, None, None, None) != 0
+    assert L.b200k_pauli_words_tile(pa, pa, None, n, H, words, nw, 0, None, None, None) != 0
+    da.close()
+    db.close()
