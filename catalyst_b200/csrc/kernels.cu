@@ -948,14 +948,13 @@ extern "C" int64_t b200k_sampler_scratch_doubles(int64_t nbins)
 // 2^30 entries; now bound by the 8 GiB read.)
 #define SAMP_WARPS 4
 __global__ void __launch_bounds__(32 * SAMP_WARPS)
-k_samp_chunk_sums(const double *__restrict__ p, int64_t N, int64_t nch, double *__restrict__ sumD,
+k_samp_chunk_sums(const double *__restrict__ p, int64_t N, double dN, int64_t nch, double *__restrict__ sumD,
                   double *__restrict__ sumE)
-{
+{ // N: entries of p (this rank's slice when the distribution is sharded); dN: bins of the WHOLE distribution
     __shared__ double sm[SAMP_WARPS][32][33];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int64_t q0 = ((int64_t)blockIdx.x * SAMP_WARPS + w) * 32; // first chunk of this warp
     if (q0 >= nch) return;                                           // whole warp
-    const double dN = (double)N;
     const int64_t q = q0 + lane; // the chunk this lane sums
     double d = 0.0, e = 0.0;
     for (int t = 0; t < SAMP_CH / 32; t++) {
@@ -1081,21 +1080,54 @@ k_samp_seg_write(const double *__restrict__ sumD, const double *__restrict__ sum
     }
 }
 
-extern "C" int b200k_sampler_prepare(const double *probs, int64_t nbins, double *scratch,
-                                     void *stream)
+static int sampler_finish(double *scratch, int64_t nbins, cudaStream_t st)
 {
     const int64_t nch = (nbins + SAMP_CH - 1) / SAMP_CH;
     double *cumD = scratch, *cumE = scratch + (nch + 1);
     double *sumD = scratch + 2 * (nch + 1), *sumE = scratch + 3 * (nch + 1);
     double *segD = scratch + 4 * (nch + 1), *segE = segD + 1024;
-    cudaStream_t st = (cudaStream_t)stream;
-    const int64_t warps = (nch + 31) / 32;
-    k_samp_chunk_sums<<<(unsigned)((warps + SAMP_WARPS - 1) / SAMP_WARPS), 32 * SAMP_WARPS, 0, st>>>(probs, nbins, nch, sumD, sumE);
     const int64_t per = (nch + 1023) / 1024;
     k_samp_seg_totals<<<32, 32, 0, st>>>(sumD, sumE, nch, per, segD, segE);
     k_samp_seg_scan<<<1, 32, 0, st>>>(segD, segE, cumD + nch, cumE + nch);
     k_samp_seg_write<<<32, 32, 0, st>>>(sumD, sumE, nch, per, segD, segE, cumD, cumE);
     return (int)cudaGetLastError();
+}
+
+extern "C" int b200k_sampler_prepare(const double *probs, int64_t nbins, double *scratch,
+                                     void *stream)
+{
+    const int64_t nch = (nbins + SAMP_CH - 1) / SAMP_CH;
+    double *sumD = scratch + 2 * (nch + 1), *sumE = scratch + 3 * (nch + 1);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t warps = (nch + 31) / 32;
+    k_samp_chunk_sums<<<(unsigned)((warps + SAMP_WARPS - 1) / SAMP_WARPS), 32 * SAMP_WARPS, 0, st>>>(probs, nbins, (double)nbins, nch, sumD, sumE);
+    return sampler_finish(scratch, nbins, st);
+}
+
+// ---- the same sampler over a distribution SHARDED by its top index bits ------------------------------------------
+// Chunk sums are independent per chunk, so each rank sums the chunks of its own slice (scaled by the bins of the WHOLE
+// distribution); the host gathers them into the scratch of every rank in global descending order (the slice of rank
+// r holds global chunks (W-1-r) * nch_local ...), after which the segment totals / scan / exclusive prefixes are the
+// very same kernels on the very same numbers as on one GPU: the sampled stream is bit-identical.
+extern "C" int b200k_sampler_chunk_sums(const double *probs_slice, int64_t nbins_slice, int64_t nbins_total, double *sumD,
+                                        double *sumE, void *stream)
+{
+    if (nbins_slice < SAMP_CH || nbins_slice % SAMP_CH) return (int)cudaErrorInvalidValue; // slices hold whole chunks
+    const int64_t nch = nbins_slice / SAMP_CH;
+    const int64_t warps = (nch + 31) / 32;
+    k_samp_chunk_sums<<<(unsigned)((warps + SAMP_WARPS - 1) / SAMP_WARPS), 32 * SAMP_WARPS, 0, (cudaStream_t)stream>>>(
+        probs_slice, nbins_slice, (double)nbins_total, nch, sumD, sumE);
+    return (int)cudaGetLastError();
+}
+extern "C" void b200k_sampler_sum_offsets(int64_t nbins, int64_t *off_sumD, int64_t *off_sumE)
+{
+    const int64_t nch = (nbins + SAMP_CH - 1) / SAMP_CH;
+    *off_sumD = 2 * (nch + 1);
+    *off_sumE = 3 * (nch + 1);
+}
+extern "C" int b200k_sampler_finish(double *scratch, int64_t nbins_total, void *stream)
+{
+    return sampler_finish(scratch, nbins_total, (cudaStream_t)stream);
 }
 
 // first chunk q in [0, nch) with cum[q+1] >= x (strict=false) or cum[q+1] > x (strict=true);
@@ -1113,8 +1145,17 @@ __device__ __forceinline__ int64_t samp_find_chunk(const double *cum, int64_t nc
     return lo;
 }
 
-__global__ void __launch_bounds__(128)
-k_samp_draw(const double *__restrict__ p, int64_t N, int64_t nch, const double *__restrict__ cumD,
+struct SampFlat { // the whole distribution in one buffer
+    const double *p;
+    __device__ __forceinline__ double operator[](int64_t i) const { return p[i]; }
+};
+struct SampSharded { // slice r = entries [r << nl, (r + 1) << nl), reachable through peer memory
+    const double *s[B200K_SAMPLER_MAX_SHARDS];
+    int nl;
+    __device__ __forceinline__ double operator[](int64_t i) const { return s[i >> nl][i & ((int64_t(1) << nl) - 1)]; }
+};
+template <class Acc> __global__ void __launch_bounds__(128)
+k_samp_draw(const Acc p, int64_t N, int64_t nch, const double *__restrict__ cumD,
             const double *__restrict__ cumE, const double *__restrict__ u, int64_t nshots,
             int64_t *__restrict__ out)
 {
@@ -1213,8 +1254,26 @@ extern "C" int b200k_sampler_draw(const double *probs, int64_t nbins, const doub
     if (nshots <= 0) return 0;
     const int64_t nch = (nbins + SAMP_CH - 1) / SAMP_CH;
     const double *cumD = scratch, *cumE = scratch + (nch + 1);
-    k_samp_draw<<<(unsigned)((nshots + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
-        probs, nbins, nch, cumD, cumE, u, nshots, out_idx);
+    k_samp_draw<SampFlat><<<(unsigned)((nshots + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+        SampFlat{probs}, nbins, nch, cumD, cumE, u, nshots, out_idx);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int b200k_sampler_draw_sharded(const double *const *slices, int nslices, int n_local, const double *scratch,
+                                          const double *u, int64_t nshots, int64_t *out_idx, void *stream)
+{
+    if (nshots <= 0) return 0;
+    if (nslices < 1 || nslices > B200K_SAMPLER_MAX_SHARDS || (nslices & (nslices - 1)) || n_local < 10 || n_local > 40)
+        return (int)cudaErrorInvalidValue;
+    const int64_t nbins = (int64_t)nslices << n_local;
+    const int64_t nch = (nbins + SAMP_CH - 1) / SAMP_CH;
+    const double *cumD = scratch, *cumE = scratch + (nch + 1);
+    SampSharded A;
+    memset(&A, 0, sizeof(A));
+    for (int r = 0; r < nslices; r++) A.s[r] = slices[r];
+    A.nl = n_local;
+    k_samp_draw<SampSharded><<<(unsigned)((nshots + 127) / 128), 128, 0, (cudaStream_t)stream>>>(A, nbins, nch, cumD, cumE, u,
+                                                                                              nshots, out_idx);
     return (int)cudaGetLastError();
 }
 

@@ -161,6 +161,11 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "lazy_adjoint") o.lazy_adjoint = as_int(1) != 0;
         else if (k == "p2p_swap") o.p2p_swap = (int)as_int(-1);
         else if (k == "swap_push") o.swap_push = (int)as_int(-1);
+        else if (k == "dist_sampler") o.dist_sampler = (int)as_int(-1);
+        else if (k == "gather") {
+            B200_FAIL_IF(v != "all" && v != "slice", "gather must be 'all' or 'slice'");
+            o.gather_slices = v == "slice";
+        }
         else if (k == "adaptive_rows") o.adaptive_rows = as_int(1) != 0;
         else if (k == "virtual_swap") o.virtual_swap = as_int(1) != 0;
         else if (k == "batch_overlaps") o.batch_overlaps = as_int(1) != 0;
@@ -2683,6 +2688,12 @@ void Simulator::state(double *out_ri, int64_t stride)
         d2h_strided(psi_->p(), sizeof(cplx), size_t(1) << n_, out_ri, stride);
         return;
     }
+    if (opt_.gather_slices) { // gather='slice': this rank's amplitudes only, at their place in the caller's array
+        canonical_local_bits();
+        const int64_t off = (int64_t)opt_.rank << nl_;
+        d2h_strided(psi_->p(), sizeof(cplx), size_t(1) << nl_, out_ri + 2 * off * stride, stride);
+        return;
+    }
     // SPMD contract: every rank returns the whole vector.  Shards are gathered through the host and
     // the layout is undone there; meant for the register sizes a host can hold anyway.
     const size_t nloc = size_t(1) << nl_;
@@ -2872,6 +2883,21 @@ void Simulator::probs(const std::vector<int64_t> &wires_in, double *out, int64_t
         for (size_t j = 0; j < wires_in.size(); j++) all = all && wires_in[j] == (int64_t)j;
     }
     const size_t k = wires_in.empty() ? (size_t)n_ : wires_in.size();
+    if (sharded() && all && opt_.gather_slices) { // gather='slice': |psi|^2 of this rank's slice only, no collective but the swaps
+        canonical_rank_bits();
+        ensure_buffer(probs_buf_, sizeof(double) << nl_);
+        bool local_identity = true;
+        for (int q = 0; q < (int)nl_; q++) local_identity = local_identity && pos_[q] == q;
+        if (local_identity) CUDA_CHECK(b200k_probs_all(psi_->d(), probs_buf_->d(), (int)nl_, stream_));
+        else {
+            uint8_t perm[64];
+            for (int q = 0; q < (int)nl_; q++) perm[pos_[q]] = (uint8_t)q;
+            CUDA_CHECK(b200k_probs_all_perm(psi_->d(), probs_buf_->d(), (int)nl_, perm, stream_));
+        }
+        note_launch();
+        if (out) d2h_strided(probs_buf_->p(), sizeof(double), size_t(1) << nl_, out + ((int64_t)opt_.rank << nl_) * stride, stride);
+        return;
+    }
     if (!probs_buf_) {
         std::lock_guard<std::mutex> lk(g_keep_mu);
         if (probs_keep_ && probs_keep_->bytes() >= (sizeof(double) << k)) probs_buf_ = std::move(probs_keep_);
@@ -3035,10 +3061,168 @@ std::vector<int64_t> Simulator::mcmc_indices(const std::vector<int64_t> &wires_i
     return idx;
 }
 
+// Sharded register: bring the layout to wire order, so that rank r's shard IS the slice [r << n_local, (r+1) << n_local)
+// of the canonical index (wire 0 = most significant bit).  Rank bits first: every wire w < log2(world) whose qubit is
+// not on rank bit n-1-w is exchanged into place with qubit swaps (a qubit that sits on ANOTHER rank bit is pulled in
+// first); all ranks run the same host logic on the same layout, so the collective calls match.
+void Simulator::canonical_rank_bits()
+{
+    if (!sharded()) return;
+    if (!wire_identity()) restore_wire_order(); // virtual SWAP labels back to identity: logical bit of wire w = n-1-w
+    flush();
+    for (int round = 0; round < 8; round++) {
+        std::vector<std::pair<int, int>> pairs;
+        uint64_t pull = 0;
+        for (int p = (int)nl_; p < (int)n_; p++) { // rank-bit position p must hold logical bit p
+            if (pos_[p] == p) continue;
+            if (pos_[p] < nl_) pairs.push_back({p, pos_[p]});
+            else pull |= 1ull << p;
+        }
+        if (pairs.empty() && !pull) return;
+        if (!pairs.empty()) swap_bits({psi_->d()}, pos_, pairs);
+        else make_local({psi_->d()}, pos_, pull); // sits on another rank bit: comes in now, goes to its place next round
+    }
+    B200_FAIL("internal: rank bits did not reach wire order");
+}
+
+// ... then the local bits.  A transposition of two PHYSICAL index bits A, B of the shard is what a content SWAP of the
+// two logical bits that sit there does; a sequence of them (each moving one qubit's data to its own position) sorts the
+// local bits, after which pos_ is the identity.  All SWAPs run under the layout they were planned in and fuse into
+// tile passes; the logical state never changes, only where its qubits are stored.
+void Simulator::canonical_local_bits()
+{
+    if (!sharded()) return;
+    canonical_rank_bits();
+    std::vector<int> inv0((size_t)n_, -1), cur(pos_.begin(), pos_.end());
+    for (int q = 0; q < (int)n_; q++) inv0[(size_t)pos_[q]] = q;
+    std::vector<GateOp> ops;
+    for (int q = 0; q < (int)nl_; q++) {
+        if (cur[q] == q) continue;
+        const int A = cur[q], B = q;
+        int q2 = -1;
+        for (int r = 0; r < (int)nl_; r++)
+            if (cur[r] == B) q2 = r;
+        B200_FAIL_IF(q2 < 0 || A >= nl_, "internal: local layout is not a permutation of the local bits");
+        canonicalize(ops, "SWAP", {}, {n_ - 1 - inv0[(size_t)A], n_ - 1 - inv0[(size_t)B]}, false, {}, {}, "");
+        cur[q] = B;
+        cur[q2] = A;
+    }
+    if (ops.empty()) return;
+    std::vector<int> work = pos_;
+    execute({psi_->d()}, work, ops);
+    B200_FAIL_IF(work != pos_, "internal: local SWAPs moved a rank bit");
+    pos_ = cur;
+}
+
+// Sample / Counts of ALL wires of a sharded register without gathering 2^n probabilities anywhere: every rank keeps
+// |psi|^2 of its own slice (canonical order), the chunk sums of the alias restatement are computed per slice and
+// gathered (2^n / 1024 x 2 doubles), and every rank draws every shot, reading the few chunks a shot walks from the
+// owning rank's slice through peer memory.  Same kernels on the same numbers as on one GPU: bit-identical samples.
+// false = not applicable here (peer memory unavailable, slices smaller than a chunk): the caller gathers instead.
+bool Simulator::sample_all_distributed(int64_t shots, std::vector<int64_t> &idx)
+{
+    if (!sharded() || opt_.dist_sampler == 0 || nl_ < 10 || opt_.world > B200K_SAMPLER_MAX_SHARDS) return false;
+    canonical_rank_bits();
+    cudaStream_t st = (cudaStream_t)stream_;
+    const int64_t nloc = int64_t(1) << nl_, ntot = int64_t(1) << n_;
+    ensure_buffer(probs_buf_, sizeof(double) << nl_);
+    bool local_identity = true;
+    for (int q = 0; q < (int)nl_; q++) local_identity = local_identity && pos_[q] == q;
+    if (local_identity) CUDA_CHECK(b200k_probs_all(psi_->d(), probs_buf_->d(), (int)nl_, stream_));
+    else {
+        uint8_t perm[64];
+        for (int q = 0; q < (int)nl_; q++) perm[pos_[q]] = (uint8_t)q; // source (physical) bit -> canonical bit
+        CUDA_CHECK(b200k_probs_all_perm(psi_->d(), probs_buf_->d(), (int)nl_, perm, stream_));
+    }
+    note_launch();
+    std::vector<void *> peers;
+    bool ok = false;
+    try {
+        ok = comm_->map_peers(probs_buf_->p(), peers); // collective; the same answer on every rank
+    }
+    catch (const std::exception &) {
+        ok = false;
+    }
+    if (!ok) return false;
+    idx.assign((size_t)shots, 0);
+    auto done = [&]() { // nobody may still be reading this rank's slice when it is reused
+        cudaStreamSynchronize(st);
+        comm_->unmap_peers(probs_buf_->p());
+        try {
+            comm_->barrier();
+        }
+        catch (const std::exception &) {
+        }
+    };
+    try {
+        const int64_t nch_l = nloc / 1024;
+        const size_t scr = (size_t)b200k_sampler_scratch_doubles(ntot) * sizeof(double);
+        const size_t ubytes = 2 * (size_t)shots * sizeof(double), ibytes = (size_t)shots * sizeof(int64_t);
+        const size_t sums = 2 * (size_t)nch_l * sizeof(double);
+        auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+        ensure_buffer(misc_, up(scr) + up(ubytes) + up(ibytes) + up(sums) + up(sums * (size_t)opt_.world) + 256);
+        char *base = static_cast<char *>(misc_->p());
+        double *dscr = reinterpret_cast<double *>(base);
+        double *du = reinterpret_cast<double *>(base + up(scr));
+        int64_t *di = reinterpret_cast<int64_t *>(base + up(scr) + up(ubytes));
+        double *mine = reinterpret_cast<double *>(base + up(scr) + up(ubytes) + up(ibytes));
+        double *all = reinterpret_cast<double *>(base + up(scr) + up(ubytes) + up(ibytes) + up(sums));
+        CUDA_CHECK(b200k_sampler_chunk_sums(probs_buf_->d(), nloc, ntot, mine, mine + nch_l, stream_));
+        comm_->allgather(mine, all, 2 * (size_t)nch_l, stream_);
+        int64_t offD = 0, offE = 0;
+        b200k_sampler_sum_offsets(ntot, &offD, &offE);
+        for (int r = 0; r < opt_.world; r++) { // descending global order: the highest rank's chunks come first
+            const int64_t blk = (int64_t)(opt_.world - 1 - r) * nch_l;
+            const double *src = all + (size_t)r * 2 * (size_t)nch_l;
+            CUDA_CHECK(cudaMemcpyAsync(dscr + offD + blk, src, (size_t)nch_l * 8, cudaMemcpyDeviceToDevice, st));
+            CUDA_CHECK(cudaMemcpyAsync(dscr + offE + blk, src + nch_l, (size_t)nch_l * 8, cudaMemcpyDeviceToDevice, st));
+        }
+        CUDA_CHECK(b200k_sampler_finish(dscr, ntot, stream_));
+        std::mt19937 rng(fresh_seed());
+        if (shots > 0) {
+            std::vector<double> u(2 * (size_t)shots);
+            std::uniform_real_distribution<double> U(0.0, 1.0);
+            for (auto &x : u) x = U(rng);
+            CUDA_CHECK(cudaMemcpyAsync(du, u.data(), ubytes, cudaMemcpyHostToDevice, st));
+            std::vector<const double *> sl((size_t)opt_.world);
+            for (int r = 0; r < opt_.world; r++) sl[(size_t)r] = static_cast<const double *>(peers[(size_t)r]);
+            comm_->stream_barrier(stream_); // every rank's slice is complete before anyone reads it
+            CUDA_CHECK(b200k_sampler_draw_sharded(sl.data(), opt_.world, (int)nl_, dscr, du, shots, di, stream_));
+            note_launch();
+            CUDA_CHECK(cudaMemcpyAsync(idx.data(), di, ibytes, cudaMemcpyDeviceToHost, st));
+            CUDA_CHECK(cudaStreamSynchronize(st)); // u is stack-owned
+            stats_.h2d_bytes += (double)ubytes;
+            stats_.d2h_bytes += (double)ibytes;
+        }
+    }
+    catch (...) {
+        done();
+        throw;
+    }
+    done();
+    return true;
+}
+
 std::vector<int64_t> Simulator::sample_indices(const std::vector<int64_t> &wires, int64_t shots)
 {
     B200_FAIL_IF(shots < 0, "Invalid number of shots");
     if (opt_.mcmc) return mcmc_indices(wires, shots);
+    if (sharded() && opt_.dist_sampler != 0) {
+        B200_FAIL_IF(!psi_, "No qubits allocated");
+        check_wires(wires, {});
+        bool all = wires.empty();
+        if ((int64_t)wires.size() == n_) {
+            all = true;
+            for (size_t j = 0; j < wires.size(); j++) all = all && wires[j] == (int64_t)j;
+        }
+        if (all) {
+            std::vector<int64_t> idx;
+            if (sample_all_distributed(shots, idx)) return idx;
+        }
+        B200_FAIL_IF(all && opt_.dist_sampler == 1,
+                     "dist_sampler=1: the distributed sampler is not available here (no peer memory between the ranks, "
+                     "or fewer than 2^10 amplitudes per rank)");
+    }
     probs(wires, nullptr, 1); // leaves the distribution in probs_buf_ on the device
     const size_t k = wires.empty() ? (size_t)n_ : wires.size();
     const int64_t nbins = int64_t(1) << k;

@@ -116,6 +116,11 @@ struct Options {
     int p2p_swap = -1;        // qubit swap over mapped peer memory: 1 on, 0 off, -1 auto (on for 'local:' rank groups)
     int swap_push = -1;       // qubit swap as one push kernel into all peers' staging: 1 on, 0 off, -1 auto (over NCCL
                               // with 2 ranks; larger worlds take the staged NCCL path -- by measurement)
+    int dist_sampler = -1;    // sharded register, Sample / Counts of ALL wires: every rank draws every shot from the
+                              // slices of |psi|^2 the ranks keep, read through peer memory (1 = required, 0 = gather the
+                              // whole marginal on every rank, -1 = use it when peer memory is available)
+    bool gather_slices = false; // sharded register: State() / Probs() of all wires fill only THIS rank's slice
+                                // [rank << n_local, (rank + 1) << n_local) of the caller's array (gather='slice')
     bool batch_overlaps = true; // adjoint gradient: evaluate commuting generators' overlaps in batched read passes
     bool keep_allocation = true;  // a released device keeps its state / probability buffers for the next allocation of the
                                   // same size (the runtime pools device objects); freed process-wide when any cudaMalloc fails
@@ -226,6 +231,9 @@ class Simulator {
     bool sharded() const { return opt_.world > 1; }
     bool ensure_psi_peers(); // collective: map every rank's state shard into this GPU's address space
     void drop_psi_peers();
+    void canonical_rank_bits();                    // sharded: wire w < log2(world) onto rank bit n-1-w (qubit swaps)
+    void canonical_local_bits();                   // ... and the local index bits into wire order (SWAP passes)
+    bool sample_all_distributed(int64_t shots, std::vector<int64_t> &idx);
     bool ensure_stage_peers(size_t bytes); // collective: swap staging of >= bytes, mapped on every rank
     void drop_stage_peers();
     std::vector<void *> stage_peers_;

@@ -317,6 +317,22 @@ int b200k_sampler_prepare(const double *probs, int64_t nbins, double *scratch, v
 int b200k_sampler_draw(const double *probs, int64_t nbins, const double *scratch, const double *u,
                        int64_t nshots, int64_t *out_idx, void *stream);
 
+/* The same sampler over a distribution sharded by its top index bits (Sample / Counts of all wires of a
+ * sharded register; QuantumDevice.hpp:384,433).  Every rank: (1) b200k_sampler_chunk_sums over its own slice
+ * (nbins_slice = 2^n_local >= 1024 entries, scaled by the bins of the whole distribution) into nbins_slice/1024
+ * doubles each of sumD / sumE; (2) the host gathers all ranks' sums into EVERY rank's scratch
+ * (b200k_sampler_scratch_doubles(nbins_total) doubles) at the offsets b200k_sampler_sum_offsets returns, in global
+ * descending order: rank r's block at chunk index (W-1-r) * nbins_slice/1024; (3) b200k_sampler_finish;
+ * (4) b200k_sampler_draw_sharded with slices[r] = a pointer THIS GPU can read rank r's slice through (peer memory).
+ * Every rank draws every shot: same arithmetic on the same numbers as on one GPU, bit-identical samples. */
+#define B200K_SAMPLER_MAX_SHARDS 64
+int b200k_sampler_chunk_sums(const double *probs_slice, int64_t nbins_slice, int64_t nbins_total, double *sumD,
+                             double *sumE, void *stream);
+void b200k_sampler_sum_offsets(int64_t nbins_total, int64_t *off_sumD, int64_t *off_sumE);
+int b200k_sampler_finish(double *scratch, int64_t nbins_total, void *stream);
+int b200k_sampler_draw_sharded(const double *const *slices, int nslices, int n_local, const double *scratch,
+                               const double *u, int64_t nshots, int64_t *out_idx, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -93,3 +93,61 @@ def test_nccl_ranks_match_oracle(oracle_mod, world, n, kwargs):
             assert nx[1] == 0
         print(f"[nccl parity] world={world} n={n} {kw}: swaps (all, push, in-place) = {nx}, "
               f"max state err {np.max(np.abs(st - want_st)):.2e}")
+
+
+def _worker_sampler(rank, world, uid, n, ops, q):
+    try:
+        root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+        sys.path[:0] = [root, os.path.join(root, "tests")]
+        from catalyst_b200 import capi
+        # dist_sampler=1: the distributed sampler is REQUIRED (the slices of |psi|^2 are read through CUDA IPC mappings)
+        d = capi.B200Device(world_size=world, rank=rank, comm="nccl:" + uid, device=rank, seed=37, dist_sampler=1,
+                            gather="slice")
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        smp = d.sample(3000)
+        cnt = d.counts(500)
+        smp2 = d.sample(100, [2, n - 1])
+        st = np.full(1 << n, np.nan + 0j, dtype=np.complex128)
+        d.state(out=st)
+        p = np.full(1 << n, np.nan)
+        d.probs(out=p)
+        q.put((rank, smp, cnt, smp2, st, p, None))
+        d.close()
+    except BaseException as ex:  # noqa: BLE001
+        q.put((rank, None, None, None, None, None, repr(ex)))
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_nccl_distributed_sampler_and_slices(oracle_mod, world):
+    """Sample / Counts of all wires through the distributed sampler (peer reads of the ranks' |psi|^2 slices) and
+    State / Probs in gather='slice' mode, one process per GPU over NCCL: bit-exact samples, 1e-12 slices."""
+    if _ngpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    from catalyst_b200 import capi
+    n = 16
+    nl = n - (world.bit_length() - 1)
+    ops = random_circuit(900 + world, n, 150)
+    o = oracle_mod.OracleDevice(n, seed=37)
+    apply_ops(o, ops)
+    want_s, want_c, want_s2 = o.sample(3000), o.counts(500), o.sample(100, [2, n - 1])
+    want_st, want_p = o.state(), o.probs()
+    uid = capi.nccl_unique_id()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_sampler, args=(r, world, uid, n, ops, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, smp, cnt, smp2, st, p, err in res:
+        assert err is None, f"rank {rank}: {err}"
+        assert np.array_equal(smp, want_s)
+        assert np.array_equal(cnt[0], want_c[0]) and np.array_equal(cnt[1], want_c[1])
+        assert np.array_equal(smp2, want_s2)
+        lo, hi = rank << nl, (rank + 1) << nl
+        assert np.max(np.abs(st[lo:hi] - want_st[lo:hi])) < 1e-12
+        assert np.max(np.abs(p[lo:hi] - want_p[lo:hi])) < 1e-12
+        assert np.all(np.isnan(p[:lo])) and np.all(np.isnan(p[hi:]))
+    print(f"[nccl parity] world={world} n={n}: distributed sampler bit-exact (3000 + 500 + 100 shots), slices 1e-12")

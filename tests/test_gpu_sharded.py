@@ -366,3 +366,81 @@ def test_swap_push_mode(gpu, oracle_mod, world, stage_mib):
         assert np.max(np.abs(st - want)) < TOL
         assert ex > 0 and pushed == ex
         assert np.max(np.abs(jd - jo)) < 1e-12
+
+
+# ---- Sample / Counts of ALL wires without gathering the marginal (the distributed sampler of SURVEY 8(e)) ----------
+def _ghz(n):
+    return [("Hadamard", [], [0])] + [("CNOT", [], [w, w + 1]) for w in range(n - 1)]
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("kind", ["random", "ghz", "basis"])
+def test_distributed_sampler_all_wires(gpu, oracle_mod, world, kind):
+    """dist_sampler=1 REQUIRES the distributed path (an error if it cannot run): every rank keeps |psi|^2 of its own
+    slice, chunk sums are gathered, every rank draws every shot through peer memory.  Bit-exact with the oracle's
+    (= the unsharded device's) seeded stream, for a spread-out state, for two peaks on different ranks and for a basis
+    state; partial-wire Sample between the calls keeps the generator in step."""
+    n = 14
+    ops = {"random": random_circuit(57, n, 120), "ghz": _ghz(n), "basis": [("PauliX", [], [2]), ("PauliX", [], [n - 1])]}[kind]
+    o = _oracle(oracle_mod, n, ops, seed=37)
+    want = (o.sample(2000), o.counts(1000), o.sample(300, [3, 0]), o.sample(500), o.state())
+
+    def prog(d, r):
+        d.seed(37)
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        return d.sample(2000), d.counts(1000), d.sample(300, [3, 0]), d.sample(500), d.state()
+
+    for s, c, sp, s2, st in gpu.run_spmd(world, prog, dist_sampler=1):
+        assert np.array_equal(s, want[0])
+        assert np.array_equal(c[0], want[1][0]) and np.array_equal(c[1], want[1][1])
+        assert np.array_equal(sp, want[2])
+        assert np.array_equal(s2, want[3])
+        assert np.max(np.abs(st - want[4])) < TOL
+
+
+def test_distributed_sampler_refused_when_required_but_unavailable(gpu):
+    def prog(d, r):
+        d.allocate_qubits(6)  # 2^5 amplitudes per rank: less than one chunk
+        with pytest.raises(gpu.B200Error, match="dist_sampler=1"):
+            d.sample(10)
+        return True
+
+    assert all(gpu.run_spmd(2, prog, dist_sampler=1))
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_state_and_probs_slices(gpu, oracle_mod, world):
+    """gather='slice': State() and Probs() of all wires fill only this rank's slice of the caller's array (no rank ever
+    holds 2^n entries); the register stays usable afterwards (its layout was brought to wire order)."""
+    n = 12
+    nl = n - (world.bit_length() - 1)
+    ops = random_circuit(61, n, 100)
+    o = _oracle(oracle_mod, n, ops)
+    want_state, want_probs = o.state(), o.probs()
+    apply_ops(o, [("Hadamard", [], [n - 1]), ("CNOT", [], [0, n - 1])])
+    want_e = o.expval(o.obs_named("PauliZ", 0))
+    want_after = o.state()
+
+    def prog(d, r):
+        d.allocate_qubits(n)
+        apply_ops(d, ops)
+        p = np.full(1 << n, np.nan)
+        d.probs(out=p)
+        st = np.full(1 << n, np.nan + 0j, dtype=np.complex128)
+        d.state(out=st)
+        apply_ops(d, [("Hadamard", [], [n - 1]), ("CNOT", [], [0, n - 1])])
+        e = d.expval(d.obs_named("PauliZ", 0))
+        st2 = np.full(1 << n, np.nan + 0j, dtype=np.complex128)
+        d.state(out=st2)
+        return st, p, e, st2
+
+    for r, (st, p, e, st2) in enumerate(gpu.run_spmd(world, prog, gather="slice")):
+        lo, hi = r << nl, (r + 1) << nl
+        assert np.max(np.abs(st[lo:hi] - want_state[lo:hi])) < TOL
+        assert np.max(np.abs(p[lo:hi] - want_probs[lo:hi])) < TOL
+        assert np.max(np.abs(st2[lo:hi] - want_after[lo:hi])) < TOL
+        mask = np.ones(1 << n, dtype=bool)
+        mask[lo:hi] = False
+        assert np.all(np.isnan(st[mask].real)) and np.all(np.isnan(p[mask])), "entries outside the slice were written"
+        assert abs(e - want_e) < TOL
