@@ -39,7 +39,8 @@ const char *b200sv_version(void);
  * shots, mcmc / num_burnin / kernel_name (lightning.qubit's sampling kwargs: Sample, Counts and the finite-shot
  * estimates then draw from a Metropolis chain, kernels 'Local' and 'NonZeroRandom'; parity unpinned, see
  * Simulator::mcmc_indices), tile_bits, min_row_bits, fuse (0/1), device (CUDA ordinal), world_size, rank, comm,
- * stage_mib, swap_push, p2p_swap (see "sharding" below), release_entangled ('error' | 'project'), jit ('off' |
+ * stage_mib, swap_push, p2p_swap, dist_sampler, gather ('all' | 'slice') (see "sharding" below), release_entangled
+ * ('error' | 'project'), jit ('off' |
  * 'auto' | 'always') and its tuning keys.  Unknown keys are ignored.  Returns NULL on error. */
 b200sv_device *b200sv_create(const char *kwargs);
 void b200sv_destroy(b200sv_device *d);
@@ -173,7 +174,14 @@ void *b200sv_device_pointer(b200sv_device *d);
  *   'world_size': G, 'rank': r, 'comm': 'nccl:<256 hex digits>' | 'local:<group name>'
  * where the hex digits are an ncclUniqueId created once by b200sv_nccl_unique_id() and distributed
  * by the host program (any out-of-band channel: torch.distributed, MPI, a file).  'local:' joins the
- * ranks of one process by name (threads; several ranks may share a GPU — used by the tests). */
+ * ranks of one process by name (threads; several ranks may share a GPU — used by the tests).
+ * Results on a sharded register:
+ *   'gather': 'all' (default) — State / Probs of all wires return the whole vector on every rank (gathered through
+ *             the host; small registers); 'slice' — each rank fills ONLY entries [rank << n_local, (rank+1) << n_local)
+ *             of the caller's array, nothing is gathered (the layout is brought to wire order first).
+ *   'dist_sampler': Sample / Counts of ALL wires draw from the ranks' slices of |psi|^2 through peer memory instead of
+ *             gathering 2^n probabilities on every rank; samples are bit-identical to the unsharded device.
+ *             -1 (default) when peer memory is available, 0 never, 1 required (error otherwise). */
 int b200sv_nccl_unique_id(char hex_out[257]);
 int b200sv_world_size(b200sv_device *d);
 int b200sv_rank(b200sv_device *d);
