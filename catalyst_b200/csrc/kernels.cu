@@ -1318,7 +1318,9 @@ struct BatchParams {
 //    launch: without the prefetch such a launch took 5.6 ms at 28 qubits against 1.5 ms of HBM time.
 // (Round 1's version reloaded phi per generator, computed both components and reduced per generator and tile:
 // ~0.2 ms per word at 26 qubits, the cost of a separate read pass per word.)
-template <int RC, int HASCTL> __global__ void __launch_bounds__(256, 2)
+// GENERIC = 0: full 2^11 tiles and no generator with a control inside the tile (the common case: no bounds or control
+// predicate per element); GENERIC = 1: anything else.
+template <int RC, int GENERIC> __global__ void __launch_bounds__(256, 2)
 k_bilinear_batch(const cplx *__restrict__ phi, const cplx *__restrict__ lam, const __grid_constant__ BatchParams P,
                  double *__restrict__ partial)
 {
@@ -1355,7 +1357,7 @@ k_bilinear_batch(const cplx *__restrict__ phi, const cplx *__restrict__ lam, con
 #pragma unroll
         for (int k = 0; k < 8; k++) {
             const uint32_t e = tid + 256u * k;
-            if (e < nelem) {
+            if (!GENERIC || e < nelem) {
                 kw_cp_async16(&lbuf[e], &lam[b | koff[k]]);
                 if (!same) kw_cp_async16(&sPhi[e], &phi[b | koff[k]]);
             }
@@ -1375,7 +1377,7 @@ k_bilinear_batch(const cplx *__restrict__ phi, const cplx *__restrict__ lam, con
         for (int k = 0; k < 8; k++) {
             const uint32_t e = tid + 256u * k;
             av[k] = make_double2(0.0, 0.0);
-            if (e < nelem) {
+            if (!GENERIC || e < nelem) {
                 const cplx a = same ? sB[e] : sPhi[e];
                 av[k] = RC ? make_double2(-a.y, a.x) : a; // (i a) . b = Im(conj(a) b);  a . b = Re(conj(a) b)
             }
@@ -1392,17 +1394,19 @@ k_bilinear_batch(const cplx *__restrict__ phi, const cplx *__restrict__ lam, con
                     // bit k of M = parity of the Z factors at the partner of element k
                     const uint32_t common = (__popc(tid & G.zin) + (G.zin >> 24) + __popcll(obase & G.zo)) & 1u;
                     const uint32_t M = (0u - common) ^ ((G.zin >> 16) & 0xffu);
+                    // partner of e = tid | k << 8 is (tid ^ x) ^ (k << 8): one XOR per thread and generator, then a
+                    // constant XOR per element; the sign goes onto the product (in place, no register-pair copies)
+                    const uint32_t A = tid ^ G.xin;
                     double s0 = 0.0, s1 = 0.0;
 #pragma unroll
                     for (int k = 0; k < 8; k++) {
                         const uint32_t e = tid + 256u * k;
-                        if (e < nelem && (!HASCTL || (e & G.cin_m) == G.cin_v)) {
-                            const cplx b = sB[e ^ G.xin];
-                            const long long sign = (long long)((M << (31 - k)) & 0x80000000u) << 32;
-                            const double ax = __longlong_as_double(__double_as_longlong(av[k].x) ^ sign);
-                            const double ay = __longlong_as_double(__double_as_longlong(av[k].y) ^ sign);
-                            if (k & 1) s1 = fma(ay, b.y, fma(ax, b.x, s1));
-                            else s0 = fma(ay, b.y, fma(ax, b.x, s0));
+                        if (!GENERIC || (e < nelem && (e & G.cin_m) == G.cin_v)) {
+                            const cplx b = sB[A ^ ((uint32_t)k << 8)];
+                            double v = fma(av[k].y, b.y, av[k].x * b.x);
+                            v = __hiloint2double(__double2hiint(v) ^ (int)((M << (31 - k)) & 0x80000000u), __double2loint(v));
+                            if (k & 1) s1 += v;
+                            else s0 += v;
                         }
                     }
                     acc[g] += s0 + s1;
@@ -1631,9 +1635,10 @@ extern "C" int b200k_bilinear_batch(const double *phi, const double *lam, int n_
     if (grid > hdr->ntiles) grid = hdr->ntiles;
     const cplx *ph = (const cplx *)phi, *la = (const cplx *)lam;
     cudaStream_t st = (cudaStream_t)stream;
-    if (rc && ctl) k_bilinear_batch<1, 1><<<(unsigned)grid, 256, smem, st>>>(ph, la, P, scratch);
+    const bool generic = ctl || hdr->t != 11;
+    if (rc && generic) k_bilinear_batch<1, 1><<<(unsigned)grid, 256, smem, st>>>(ph, la, P, scratch);
     else if (rc) k_bilinear_batch<1, 0><<<(unsigned)grid, 256, smem, st>>>(ph, la, P, scratch);
-    else if (ctl) k_bilinear_batch<0, 1><<<(unsigned)grid, 256, smem, st>>>(ph, la, P, scratch);
+    else if (generic) k_bilinear_batch<0, 1><<<(unsigned)grid, 256, smem, st>>>(ph, la, P, scratch);
     else k_bilinear_batch<0, 0><<<(unsigned)grid, 256, smem, st>>>(ph, la, P, scratch);
     k_bilinear_batch_final<<<ngen, 256, 0, (cudaStream_t)stream>>>(scratch, (int)grid, O);
     return (int)cudaGetLastError();

@@ -101,6 +101,7 @@ void Simulator::trim_kept_buffers()
     for (Simulator *sim : g_sims) {
         if (!sim->psi_keep_mapped_) sim->psi_keep_.reset();
         sim->probs_keep_.reset();
+        if (!sim->grad_busy_) sim->grad_work_.clear();
     }
 }
 
@@ -499,6 +500,10 @@ void Simulator::release()
     tmp_.reset();
     acc_.reset();
     probs_buf_.reset();
+    if (!opt_.keep_allocation || dry_) {
+        std::lock_guard<std::mutex> lk(g_keep_mu);
+        grad_work_.clear();
+    }
     n_ = nl_ = 0;
     rank_base_ = 0;
     pos_.clear();
@@ -3633,12 +3638,28 @@ std::vector<double> Simulator::gradient(const std::vector<int64_t> &train_in)
     for (size_t k = 0; k < K; k++) obs_x |= observable_xmask(tape_obs_[k].first);
     make_local({psi_->d()}, pos_, obs_x);
     std::vector<int> lay = pos_;
-    DeviceBuffer lambda(bytes);
-    std::vector<std::unique_ptr<DeviceBuffer>> phi;
+    // lambda and the phi_k live in buffers kept between calls (see grad_work_)
+    struct Lease {
+        Simulator *s;
+        ~Lease()
+        {
+            std::lock_guard<std::mutex> lk(g_keep_mu);
+            s->grad_busy_ = false;
+            if (!s->opt_.keep_allocation) s->grad_work_.clear();
+        }
+    } lease{this};
+    {
+        std::lock_guard<std::mutex> lk(g_keep_mu);
+        grad_busy_ = true;
+        if (!grad_work_.empty() && grad_work_[0]->bytes() != bytes) grad_work_.clear();
+    }
+    while (grad_work_.size() < K + 1) grad_work_.push_back(std::make_unique<DeviceBuffer>(bytes)); // may trim OTHER devices
+    DeviceBuffer &lambda = *grad_work_[0];
+    std::vector<DeviceBuffer *> phi;
     CUDA_CHECK(cudaMemcpyAsync(lambda.p(), psi_->p(), bytes, cudaMemcpyDeviceToDevice, st));
     std::vector<double *> vecs{lambda.d()};
     for (size_t k = 0; k < K; k++) {
-        phi.push_back(std::make_unique<DeviceBuffer>(bytes));
+        phi.push_back(grad_work_[1 + k].get());
         apply_observable(tape_obs_[k].first, psi_->d(), phi[k]->d(), pos_);
         vecs.push_back(phi[k]->d());
     }

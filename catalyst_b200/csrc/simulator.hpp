@@ -243,6 +243,11 @@ class Simulator {
     void *psi_peers_ptr_ = nullptr;
     bool psi_peers_tried_ = false, psi_peers_ok_ = false;
     std::unique_ptr<DeviceBuffer> psi_keep_, probs_keep_; // guarded by the process-wide keep mutex (simulator.cpp)
+    // work vectors of the adjoint method (lambda, phi_k), kept between Gradient calls (and across ReleaseQubits of a
+    // pooled device): cudaMalloc + cudaFree of two state-sized buffers cost 10-40 ms per call at 26 qubits, more than
+    // some of the gradients they serve.  Freed by trim_kept_buffers() when idle; grad_busy_ guarded by the keep mutex.
+    std::vector<std::unique_ptr<DeviceBuffer>> grad_work_;
+    bool grad_busy_ = false;
     bool psi_keep_mapped_ = false;                        // peers hold a mapping of psi_keep_: never trimmed
     void reduce_results(std::vector<double> &host); // sum over ranks, fixed order
     // plan + launch a list of canonical ops (PHYSICAL bit space, non-diagonal targets all local) on a

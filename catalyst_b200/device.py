@@ -134,9 +134,11 @@ try:  # pragma: no cover - exercised only where PennyLane is installed
         config_filepath = CONFIG_FILEPATH
 
         def __init__(self, wires=None, shots=None, tile_bits=None, fuse=True, cuda_device=None,
-                     world_size=1, rank=0, comm=None):
+                     world_size=1, rank=0, comm=None, **options):
             super().__init__(wires=wires, shots=shots)
-            self.device_kwargs = {"fuse": bool(fuse)}
+            # further factory kwargs travel unchanged (include/b200sv.h: mcmc / num_burnin / kernel_name, gather,
+            # dist_sampler, release_entangled, jit, ...)
+            self.device_kwargs = {"fuse": bool(fuse), **options}
             if tile_bits is not None:
                 self.device_kwargs["tile_bits"] = int(tile_bits)
             if cuda_device is not None:
