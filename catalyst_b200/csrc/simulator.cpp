@@ -158,6 +158,7 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "jit_fuse_diag") o.jit_fuse_diag = (int)as_int(o.jit_fuse_diag);
         else if (k == "jit_factor") o.jit_factor = (int)as_int(o.jit_factor);
         else if (k == "jit_uniform") o.jit_uniform = (int)as_int(o.jit_uniform);
+        else if (k == "jit_memhint") o.jit_memhint = (int)as_int(o.jit_memhint);
         else if (k == "jit_direct_store") o.jit_direct_store = (int)as_int(o.jit_direct_store);
         else if (k == "lazy_adjoint") o.lazy_adjoint = as_int(1) != 0;
         else if (k == "p2p_swap") o.p2p_swap = (int)as_int(-1);
@@ -207,7 +208,8 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
             jit_mode_ = v == "off" || v == "0" ? 0 : (v == "always" || v == "2" ? 2 : 1);
         }
         if (const char *e = std::getenv("B200SV_JIT_UNIFORM")) opt_.jit_uniform = std::atoi(e);
-    if (const char *e = std::getenv("B200SV_JIT_DIRECT")) opt_.jit_direct_store = std::atoi(e);
+        if (const char *e = std::getenv("B200SV_JIT_DIRECT")) opt_.jit_direct_store = std::atoi(e);
+        if (const char *e = std::getenv("B200SV_JIT_MEMHINT")) opt_.jit_memhint = std::atoi(e);
         if (const char *e = std::getenv("B200SV_JIT_REGBITS")) opt_.jit_regbits = std::max(1, std::min(5, std::atoi(e)));
         if (const char *e = std::getenv("B200SV_MIN_ROW_BITS")) opt_.min_row_bits = std::max(0, std::min(opt_.tile_bits, std::atoi(e)));
         return;
@@ -232,6 +234,7 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
         jit_mode_ = v == "off" || v == "0" ? 0 : (v == "always" || v == "2" ? 2 : 1);
     }
     if (const char *e = std::getenv("B200SV_JIT_DBUF")) opt_.jit_dbuf = std::atoi(e);
+    if (const char *e = std::getenv("B200SV_JIT_MEMHINT")) opt_.jit_memhint = std::atoi(e);
     if (const char *e = std::getenv("B200SV_JIT_FACTOR")) opt_.jit_factor = std::atoi(e);
     if (const char *e = std::getenv("B200SV_JIT_UNIFORM")) opt_.jit_uniform = std::atoi(e);
     if (const char *e = std::getenv("B200SV_P2P_SWAP")) opt_.p2p_swap = std::atoi(e);

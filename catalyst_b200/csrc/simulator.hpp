@@ -108,6 +108,8 @@ struct Options {
     int jit_min_qubits = 22;  // smaller local states stay on the interpreter
     int jit_dbuf = 1;         // cp.async double-buffered tiles in specialised passes
     int jit_fuse_diag = 1;    // fuse runs of diagonal ops inside a register round
+    int jit_memhint = 0;      // cache hints in specialised passes (experiment, B200SV_JIT_MEMHINT): 1 = streaming stores
+                              // (st.global.cs), 2 = L2::256B prefetch on the tile loads of rows >= 256 B, 4 = L2::128B
     int jit_direct_store = 0; // the last register round of a specialised pass stores straight to global memory
                               // (measured at 30 qubits on a B200: 134.8 ms per circuit with and without, so off)
     int jit_uniform = 1;      // evaluate tile-uniform diagonal factors once per tile (warp-collective), not per thread

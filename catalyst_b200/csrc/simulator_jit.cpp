@@ -67,6 +67,7 @@ struct JPlan {
     std::vector<UAcc> uaccs;
     int nu = 0, uoff = 0; // uniform-table entries (8 doubles each) and their offset in the parameter doubles
     int direct_store = 0; // option: the last round stores its registers straight to global memory
+    int memhint = 0;      // option: cache hints (Options::jit_memhint)
     int uniform = 1;      // option: evaluate tile-uniform diagonal factors once per tile
 };
 
@@ -274,7 +275,8 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
     o << "struct Params { unsigned long long rank_base; double m[" << std::max(1, P.nm) << "]; };\n";
     o << "__device__ __forceinline__ void cpa16(void *d, const void *s) {\n"
          "  const unsigned a = (unsigned)__cvta_generic_to_shared(d);\n"
-         "  asm volatile(\"cp.async.cg.shared.global [%0], [%1], 16;\\n\" :: \"r\"(a), \"l\"(s) : \"memory\");\n}\n";
+         "  asm volatile(\"cp.async.cg.shared.global" << std::string((P.memhint & 2) && c >= 4 ? ".L2::256B" : (P.memhint & 4) ? ".L2::128B" : "")
+      << " [%0], [%1], 16;\\n\" :: \"r\"(a), \"l\"(s) : \"memory\");\n}\n";
     o << "__device__ __forceinline__ unsigned long long base_of(unsigned long long tile) {\n"
          "  unsigned long long b = tile << "
       << c << ";\n";
@@ -788,7 +790,8 @@ std::string generate(const JPlan &P, jit::Kernel &K, const std::string &name)
     // ---- store -------------------------------------------------------------------------------------
     if (!direct_store)
         for (uint32_t k = 0; k < niter; k++)
-            o << "    tp[" << hex64(off_of(k * TT)) << "] = s[" << slot_expr("swtid", k * TT) << "];\n";
+            if (P.memhint & 1) o << "    __stcs(&tp[" << hex64(off_of(k * TT)) << "], s[" << slot_expr("swtid", k * TT) << "]);\n";
+            else o << "    tp[" << hex64(off_of(k * TT)) << "] = s[" << slot_expr("swtid", k * TT) << "];\n";
     o << "    __syncthreads();\n"; // every thread is done with this tile's buffer before it is refilled
     if (P.dbuf) o << "    cur ^= 1u;\n";
     o << "  }\n}\n";
@@ -957,6 +960,7 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
     if (opt_.jit_factor) factor_scales(P);
     P.uniform = opt_.jit_uniform;
     P.direct_store = opt_.jit_direct_store;
+    P.memhint = opt_.jit_memhint;
     analyze_uniform(P);
     for (JRound &R : P.rounds)
         for (JOp &o : R.ops) {
@@ -1001,6 +1005,7 @@ bool Simulator::launch_pass_jit(double *vec, const std::vector<const GateOp *> &
     put(key, P.fuse_diag);
     put(key, P.uniform);
     put(key, P.direct_store);
+    put(key, P.memhint);
     put(key, P.t); put(key, P.c); put(key, P.nr); put(key, P.nl); put(key, P.dbuf);
     for (int h : P.high) put(key, (uint8_t)h);
     for (const JRound &R : P.rounds) {
