@@ -190,6 +190,8 @@ Options parse_kwargs(const char *kwargs)
     B200_FAIL_IF(o.jit_regbits < 1 || o.jit_regbits > 5, "jit_regbits out of range (1..5)");
     B200_FAIL_IF(o.jit_threshold < 1, "jit_threshold out of range");
     o.min_row_bits = std::min(o.min_row_bits, o.tile_bits);
+    // a tile has at most B200K_MAX_HIGH scattered bits: rows cannot be shorter than the rest of it
+    o.min_row_bits = std::max(o.min_row_bits, o.tile_bits - B200K_MAX_HIGH);
     return o;
 }
 
@@ -211,7 +213,7 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
         if (const char *e = std::getenv("B200SV_JIT_DIRECT")) opt_.jit_direct_store = std::atoi(e);
         if (const char *e = std::getenv("B200SV_JIT_MEMHINT")) opt_.jit_memhint = std::atoi(e);
         if (const char *e = std::getenv("B200SV_JIT_REGBITS")) opt_.jit_regbits = std::max(1, std::min(5, std::atoi(e)));
-        if (const char *e = std::getenv("B200SV_MIN_ROW_BITS")) opt_.min_row_bits = std::max(0, std::min(opt_.tile_bits, std::atoi(e)));
+        if (const char *e = std::getenv("B200SV_MIN_ROW_BITS")) opt_.min_row_bits = std::max(std::max(0, opt_.tile_bits - B200K_MAX_HIGH), std::min(opt_.tile_bits, std::atoi(e)));
         return;
     }
     int count = 0;
@@ -239,7 +241,7 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
     if (const char *e = std::getenv("B200SV_JIT_UNIFORM")) opt_.jit_uniform = std::atoi(e);
     if (const char *e = std::getenv("B200SV_P2P_SWAP")) opt_.p2p_swap = std::atoi(e);
     if (const char *e = std::getenv("B200SV_SWAP_PUSH")) opt_.swap_push = std::atoi(e);
-    if (const char *e = std::getenv("B200SV_MIN_ROW_BITS")) opt_.min_row_bits = std::max(0, std::min(opt_.tile_bits, std::atoi(e)));
+    if (const char *e = std::getenv("B200SV_MIN_ROW_BITS")) opt_.min_row_bits = std::max(std::max(0, opt_.tile_bits - B200K_MAX_HIGH), std::min(opt_.tile_bits, std::atoi(e)));
     if (const char *e = std::getenv("B200SV_JIT_REGBITS")) opt_.jit_regbits = std::max(1, std::min(5, std::atoi(e)));
     CUDA_CHECK(cudaSetDevice(dev));
     cudaStream_t st;
@@ -1129,8 +1131,13 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
     };
     // Relative duration of a pass by row width 2^c amplitudes (measured at 30 qubits, specialised
     // passes: 5.9 ms at c >= 7, 6.6 / 7.1 / 7.7 / 8.1 ms at c = 6 / 5 / 4 / 3): shorter rows cost DRAM
-    // efficiency but free tile bits for the high qubits, so fewer passes are needed.
-    auto pass_cost = [](int c) { return c >= 7 ? 1.0 : (c == 6 ? 1.12 : (c == 5 ? 1.2 : (c == 4 ? 1.3 : (c == 3 ? 1.38 : 1.6)))); };
+    // efficiency but free tile bits for the high qubits, so fewer passes are needed.  64-byte rows (c = 2):
+    // 6.8-10.7 ms depending on the rounds they carry, weighted 1.6 (1.45 and 1.8 plan C3 / C5 into 17 / 49 and
+    // 18 / 51 passes, 1.6 into 17 / 47); 32-byte rows measured 16-19 ms per pass and are never worth it.
+    static const double cost_c2 = [] { const char *e = std::getenv("B200SV_COST_C2"); return e ? std::atof(e) : 1.6; }();
+    auto pass_cost = [](int c) {
+        return c >= 7 ? 1.0 : (c == 6 ? 1.12 : (c == 5 ? 1.2 : (c == 4 ? 1.3 : (c == 3 ? 1.38 : (c == 2 ? cost_c2 : 3.0)))));
+    };
     while (remaining) {
         // a pass that starts with a DENSE op runs on the first-generation kernel (which knows
         // DENSE); every other pass runs on the register-blocked kernel and defers DENSE ops

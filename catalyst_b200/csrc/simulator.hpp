@@ -90,7 +90,9 @@ struct Options {
     int64_t num_burnin = 100;
     std::string kernel_name = "Local";
     int tile_bits = 11;
-    int min_row_bits = 3;     // shortest contiguous row of a tile: 2^3 amplitudes = 128 B (one cache line)
+    int min_row_bits = 2;     // shortest contiguous row of a tile: 2^2 amplitudes = 64 B (two sectors).  128-B rows
+                              // were the limit until the end of round 2; 64-B rows cost ~1.6x a long-row pass but
+                              // save a pass in C3 (18 -> 17: 132.7 -> 127.8 ms) and five in C5 at 30 qubits (412 -> 406 ms)
     bool adaptive_rows = true; // per pass, pick the row width that maximises gates per unit of pass time
     bool fuse = true;
     int device = -1; // -1: LOCAL_RANK or 0

@@ -7,7 +7,7 @@ from catalyst_b200 import capi, workloads
 from dsl import apply_ops
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 30
 cfgs = sys.argv[2:] or ["4:11:1"]
-ops = workloads.c3_qft_random(n)
+ops = workloads.c5_random_depth(n, depth=40) if os.environ.get('JIT30_WORKLOAD') == 'c5' else workloads.c3_qft_random(n)
 for cfg in cfgs:
     f = [int(x) for x in cfg.split(":")]
     rb, tb, db = f[:3]
