@@ -187,3 +187,169 @@ def test_reference_arm_runs_on_rank0_only(capsys):
     import bench
     assert bench.run_reference(None, 1, 2) is None
     assert capsys.readouterr().out == ""
+
+
+# ---- the distributed sampler's protocol (C++: Simulator::sample_all_distributed, kernels
+# k_samp_chunk_sums / k_samp_seg_* / k_samp_draw<SampSharded>) as a numpy model on two gloo ranks -------------------
+SAMP_CH = 1024
+
+
+def _mt19937_u32(seed, count):
+    """Raw 32-bit outputs of std::mt19937(seed) (numpy's legacy seeding is init_genrand)."""
+    bg = np.random.MT19937()
+    bg._legacy_seeding(int(seed))
+    return bg.random_raw(count).astype(np.uint64)
+
+
+def _uniform_doubles(seed, count):
+    """std::uniform_real_distribution<double>(0, 1) over std::mt19937(seed) as libstdc++ computes it
+    (generate_canonical<double, 53>: two engine outputs per double, low word first)."""
+    x = _mt19937_u32(seed, 2 * count).astype(np.float64)
+    u = (x[0::2] + x[1::2] * 4294967296.0) / 18446744073709551616.0
+    return np.where(u >= 1.0, np.nextafter(1.0, 0.0), u)
+
+
+def _chunk_sums(p_slice, n_total):
+    """Deficit / excess sums of the slice's 1024-entry chunks, each summed sequentially in DESCENDING index order."""
+    n = len(p_slice)
+    nch = n // SAMP_CH
+    D, E = np.zeros(nch), np.zeros(nch)
+    for q in range(nch):
+        d = e = 0.0
+        for i in range(n - 1 - q * SAMP_CH, n - 1 - (q + 1) * SAMP_CH, -1):
+            f = n_total * p_slice[i]
+            if f < 1.0:
+                d += 1.0 - f
+            else:
+                e += f - 1.0
+        D[q], E[q] = d, e
+    return D, E
+
+
+def _exclusive(sums):
+    cum = np.zeros(len(sums) + 1)
+    run = 0.0
+    for q, v in enumerate(sums):
+        cum[q] = run
+        run += v
+    cum[len(sums)] = run
+    return cum
+
+
+def _find_chunk(cum, nch, x, strict):
+    for q in range(nch):
+        if (cum[q + 1] > x) if strict else (cum[q + 1] >= x):
+            return q
+    return nch
+
+
+def _draw(P, N, nch, cumD, cumE, u1, u2):
+    """One shot of the alias sampler restated with prefix sums (kernels.cu: k_samp_draw); P(i) reads bin i."""
+    dN = float(N)
+    idx = min(int(u1 * dN), N - 1)
+    f = dN * P(idx)
+    q = (N - 1 - idx) // SAMP_CH
+    chunk_hi = N - 1 - q * SAMP_CH
+    if f < 1.0:
+        if u2 < f:
+            return idx
+        x = 0.0
+        for i in range(chunk_hi, idx, -1):
+            fi = dN * P(i)
+            if fi < 1.0:
+                x += 1.0 - fi
+        x = cumD[q] + x
+        qq = _find_chunk(cumE, nch, x, False)
+        while qq < nch:
+            hi = N - 1 - qq * SAMP_CH
+            e = 0.0
+            for i in range(hi, max(hi - SAMP_CH + 1, 0) - 1, -1):
+                fi = dN * P(i)
+                if fi >= 1.0:
+                    e += fi - 1.0
+                    if cumE[qq] + e >= x:
+                        return i
+            qq += 1
+        return idx
+    e = 0.0
+    for i in range(chunk_hi, idx - 1, -1):
+        fi = dN * P(i)
+        if fi >= 1.0:
+            e += fi - 1.0
+    Em = cumE[q] + e
+    qq = _find_chunk(cumD, nch, Em, True)
+    while qq < nch:
+        hi = N - 1 - qq * SAMP_CH
+        d = 0.0
+        for i in range(hi, max(hi - SAMP_CH + 1, 0) - 1, -1):
+            fi = dN * P(i)
+            if fi < 1.0:
+                d += 1.0 - fi
+                if cumD[qq] + d > Em:
+                    first = 1.0 - (cumD[qq] + d - Em)
+                    if u2 >= first:
+                        for j in range(idx - 1, -1, -1):
+                            if dN * P(j) >= 1.0:
+                                return j
+                    return idx
+        qq += 1
+    return idx
+
+
+def _sampler_worker(rank, world, port, nl, p_slice, seed, shots, q):
+    try:
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+        import torch
+        import torch.distributed as dist
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        N = world << nl
+        nch_l = (1 << nl) // SAMP_CH
+        D, E = _chunk_sums(p_slice, N)                          # (1) this rank's chunks, scaled by the WHOLE bin count
+        box = [torch.zeros(2 * nch_l, dtype=torch.float64) for _ in range(world)]
+        dist.all_gather(box, torch.from_numpy(np.concatenate([D, E])))   # (2) 2 * 2^n / 1024 doubles in total
+        gD, gE = np.zeros(world * nch_l), np.zeros(world * nch_l)
+        for r in range(world):                                  # global DESCENDING order: the highest rank comes first
+            blk = (world - 1 - r) * nch_l
+            gD[blk:blk + nch_l] = box[r].numpy()[:nch_l]
+            gE[blk:blk + nch_l] = box[r].numpy()[nch_l:]
+        cumD, cumE = _exclusive(gD), _exclusive(gE)             # (3) the same scan on every rank
+        # (4) every rank draws every shot; bins of other ranks are read from THEIR slices ("peer memory": here a gather)
+        sl = [torch.zeros(1 << nl, dtype=torch.float64) for _ in range(world)]
+        dist.all_gather(sl, torch.from_numpy(np.ascontiguousarray(p_slice)))
+        slices = [t.numpy() for t in sl]
+        mask = (1 << nl) - 1
+        u = _uniform_doubles(seed, 2 * shots)
+        idx = [_draw(lambda i: slices[i >> nl][i & mask], N, world * nch_l, cumD, cumE, u[2 * s], u[2 * s + 1])
+               for s in range(shots)]
+        dist.destroy_process_group()
+        q.put((rank, idx, None))
+    except BaseException as ex:  # noqa: BLE001
+        q.put((rank, None, repr(ex)))
+
+
+def test_world2_distributed_sampler_protocol_matches_oracle(oracle_mod):
+    """Slices of |psi|^2 on two ranks -> per-slice chunk sums -> all-gather in global descending order -> the same
+    scan everywhere -> every rank draws every shot.  The result must be the ORACLE's seeded samples (the true alias
+    table built sequentially over all 2^n bins, one mt19937 per call seeded from the device generator)."""
+    from dsl import apply_ops, random_circuit
+    n, world, shots, dev_seed = 12, 2, 300, 37
+    nl = n - 1
+    o = oracle_mod.OracleDevice(n, seed=dev_seed)
+    apply_ops(o, random_circuit(77, n, 80))
+    p = o.probs()
+    smp = o.sample(shots)
+    want = (smp.astype(np.int64) * (1 << np.arange(n - 1, -1, -1))).sum(axis=1)
+    call_seed = int(_mt19937_u32(dev_seed, 1)[0])               # the device generator's first output seeds the call
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_sampler_worker, args=(r, world, port, nl, p[r << nl:(r + 1) << nl].copy(), call_seed, shots, q))
+             for r in range(world)]
+    for pr in procs:
+        pr.start()
+    res = sorted((q.get(timeout=240) for _ in range(world)), key=lambda t: t[0])
+    for pr in procs:
+        pr.join(timeout=60)
+    for rank, idx, err in res:
+        assert err is None, f"rank {rank}: {err}"
+        assert np.array_equal(np.asarray(idx, dtype=np.int64), want), f"rank {rank}: samples differ from the oracle's"
