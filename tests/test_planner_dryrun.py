@@ -1,0 +1,56 @@
+"""The pass planner without a GPU: with B200SV_DRYRUN=1 the device library canonicalises the gate calls and plans them
+into tile passes exactly as on the GPU but launches nothing (scripts/jit_dryrun.py is the development tool built on the
+same switch).  These are regression guards on the planner's output for BASELINE.json's circuits -- the number of
+HBM round trips IS the cost of a circuit -- and on option handling that used to fail only at
+the first launch."""
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+PROG = r"""
+import json, sys
+sys.path[:0] = [%r, %r]
+from catalyst_b200 import capi, workloads
+from dsl import apply_ops
+out = {}
+def plan(tag, n, ops, **kw):
+    d = capi.B200Device(n, **kw)
+    apply_ops(d, ops)
+    d.synchronize()
+    s = d.stats()
+    out[tag] = {"passes": int(s.tile_passes), "gates": int(s.gates_enqueued)}
+    d.close()
+c3 = workloads.c3_qft_random(30)
+c5 = workloads.c5_random_depth(30, depth=40)
+plan("c3", 30, c3)
+plan("c3_rows128", 30, c3, min_row_bits=3)
+plan("c3_rows2k", 30, c3, min_row_bits=7)
+plan("c5", 30, c5)
+plan("c1", 20, workloads.c1_strongly_entangling(20, 4, seed=0)[0])
+plan("c2", 28, workloads.c2_qaoa_maxcut(28, 6, seed=0)[0])
+plan("c4", 26, workloads.c4_vqe(26, 4, 1000, seed=0)[0])
+plan("clamped", 20, workloads.c3_qft_random(20), tile_bits=11, min_row_bits=0)
+plan("unfused", 12, workloads.c3_qft_random(12), fuse=False)
+print(json.dumps(out))
+""" % (ROOT, os.path.join(ROOT, "tests"))
+
+
+def test_planner_pass_counts_of_the_baseline_circuits():
+    env = dict(os.environ, B200SV_DRYRUN="1", B200SV_JIT="off")
+    r = subprocess.run([sys.executable, "-c", PROG], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["c3"]["gates"] == 930 and out["c5"]["gates"] == 1800
+    # measured on the B200 at these plans: C3 127.8 ms (17 passes) against 132.7 ms (18 passes, 128-byte rows)
+    assert out["c3"]["passes"] <= 17, out
+    assert out["c3_rows128"]["passes"] <= 18, out
+    assert out["c3_rows2k"]["passes"] > out["c3_rows128"]["passes"], out      # short rows are what cut the pass count
+    assert out["c5"]["passes"] <= 47, out
+    assert out["c1"]["passes"] <= 9 and out["c2"]["passes"] <= 14 and out["c4"]["passes"] <= 10, out
+    # min_row_bits below tile_bits - 10 is clamped (the tile has at most ten scattered bits), not an error at launch
+    assert out["clamped"]["passes"] > 0
+    # fuse=False: one pass per canonical op
+    assert out["unfused"]["passes"] >= out["unfused"]["gates"] - 20, out
