@@ -54,3 +54,42 @@ def test_planner_pass_counts_of_the_baseline_circuits():
     assert out["clamped"]["passes"] > 0
     # fuse=False: one pass per canonical op
     assert out["unfused"]["passes"] >= out["unfused"]["gates"] - 20, out
+
+
+def _nvrtc_present():
+    import ctypes
+    for name in ("libnvrtc.so.12", "libnvrtc.so"):
+        try:
+            ctypes.CDLL(name)
+            return True
+        except OSError:
+            pass
+    return False
+
+
+JIT_PROG = r"""
+import json, sys
+sys.path[:0] = [%r, %r]
+from catalyst_b200 import capi, workloads
+from dsl import apply_ops
+d = capi.B200Device(30)
+apply_ops(d, workloads.c3_qft_random(30))
+d.synchronize()
+s = d.stats()
+print(json.dumps({"passes": int(s.tile_passes), "specialised": int(s.jit_passes)}))
+d.close()
+""" % (ROOT, os.path.join(ROOT, "tests"))
+
+
+def test_every_pass_of_config_3_generates_and_compiles_for_sm_100a():
+    """The run-time specialisation path without a GPU: every pass of the 30-qubit benchmark circuit is turned into
+    CUDA source and compiled by NVRTC for sm_100a (what the first step on a GPU box does in the background)."""
+    import pytest
+    if not _nvrtc_present():
+        pytest.skip("libnvrtc is not on the loader path")
+    env = dict(os.environ, B200SV_DRYRUN="1", B200SV_JIT_CACHE="off")
+    env.pop("B200SV_JIT", None)
+    r = subprocess.run([sys.executable, "-c", JIT_PROG], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["passes"] == out["specialised"] > 0, out
