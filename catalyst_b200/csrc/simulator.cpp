@@ -164,6 +164,7 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "p2p_swap") o.p2p_swap = (int)as_int(-1);
         else if (k == "swap_push") o.swap_push = (int)as_int(-1);
         else if (k == "dist_sampler") o.dist_sampler = (int)as_int(-1);
+        else if (k == "plan_refine") o.plan_refine = (int)as_int(-1);
         else if (k == "gather") {
             B200_FAIL_IF(v != "all" && v != "slice", "gather must be 'all' or 'slice'");
             o.gather_slices = v == "slice";
@@ -212,6 +213,8 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
         if (const char *e = std::getenv("B200SV_JIT_UNIFORM")) opt_.jit_uniform = std::atoi(e);
         if (const char *e = std::getenv("B200SV_JIT_DIRECT")) opt_.jit_direct_store = std::atoi(e);
         if (const char *e = std::getenv("B200SV_JIT_MEMHINT")) opt_.jit_memhint = std::atoi(e);
+    if (const char *e = std::getenv("B200SV_PLAN_REFINE")) opt_.plan_refine = std::atoi(e);
+        if (const char *e = std::getenv("B200SV_PLAN_REFINE")) opt_.plan_refine = std::atoi(e);
         if (const char *e = std::getenv("B200SV_JIT_REGBITS")) opt_.jit_regbits = std::max(1, std::min(5, std::atoi(e)));
         if (const char *e = std::getenv("B200SV_MIN_ROW_BITS")) opt_.min_row_bits = std::max(std::max(0, opt_.tile_bits - B200K_MAX_HIGH), std::min(opt_.tile_bits, std::atoi(e)));
         return;
@@ -1074,6 +1077,7 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
     const int t = (int)std::min<int64_t>(opt_.tile_bits, nl_);
     const int cmin = std::min(opt_.min_row_bits, t);
     const size_t LOOKAHEAD = 4096;
+    const int refine_iters = opt_.plan_refine >= 0 ? opt_.plan_refine : (nl_ >= 27 ? 6 : 0);
     std::vector<char> done(ops.size(), 0);
     size_t first = 0, remaining = ops.size();
     std::vector<const GateOp *> pass;
@@ -1089,9 +1093,15 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
         std::vector<size_t> idx;
         uint64_t req = 0;
         int c = 0;
+        int cm = 0;          // the minimum row width it was built with
+        uint16_t use[64] = {}; // how many of its ops act non-diagonally on each bit
     };
-    auto build = [&](int cmin_try, bool dense_pass, Cand &out) {
+    // `forbid`: bits no op of this candidate may act on non-diagonally (such ops are deferred like any op that does
+    // not fit) -- the refinement step below uses it to trade a tile bit that serves one op for one that serves many
+    auto build = [&](int cmin_try, bool dense_pass, Cand &out, uint64_t forbid = 0) {
         uint64_t req = 0, blockedX = 0, blockedZ = 0;
+        out.cm = cmin_try;
+        std::memset(out.use, 0, sizeof(out.use));
         int c_cur = t;
         int64_t pass_params = 0;
         size_t dense_bytes = 0; // matrices of a dense pass live in the device arena until the pass has run
@@ -1101,7 +1111,7 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
             if (done[i]) continue;
             const GateOp &op = ops[i];
             const uint64_t xs = op.xmask, zs = op.zsupport();
-            const bool commutes = !(xs & (blockedX | blockedZ)) && !(zs & blockedX);
+            const bool commutes = !(xs & forbid) && !(xs & (blockedX | blockedZ)) && !(zs & blockedX);
             // a specialised pass carries its matrices in the kernel parameter block (<= 32 KB)
             const int64_t pcost = op.kind == GateOp::DENSE ? 2 * (int64_t)op.matrix->size() : 8;
             const size_t dbytes = op.kind == GateOp::DENSE ? arena_aligned(op.matrix->size() * sizeof(cplx)) : 0;
@@ -1116,6 +1126,7 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
                     req = nreq;
                     c_cur = c;
                     out.idx.push_back(i);
+                    for (uint64_t m = xs; m; m &= m - 1) out.use[__builtin_ctzll(m)]++;
                     pass_params += pcost;
                     dense_bytes += dbytes;
                     if (!opt_.fuse) break;
@@ -1154,6 +1165,31 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
                     best_score = sc;
                     std::swap(best, cand);
                 }
+            }
+        }
+        // Refinement (large states only: it costs a dozen scans of the queue per pass, hidden behind the previous pass
+        // on the GPU).  The greedy scan hands tile bits to whichever ops come first; a bit that ends up serving a
+        // single op may keep out a bit that would serve ten.  So: forbid the least-used bit of the candidate (never
+        // one the first op needs), rebuild, keep the better of the two, and repeat from the rebuilt candidate.
+        // Planner model on the BASELINE circuits: C3 17 -> 14 passes, C5 (30 qubits) 47 -> 45.
+        if (refine_iters > 0 && opt_.adaptive_rows && opt_.fuse && !dense_pass && best.idx.size() > 1) {
+            double best_score = (double)best.idx.size() / pass_cost(best.c);
+            const uint64_t keep = ops[best.idx[0]].xmask;
+            uint64_t forbid = 0;
+            Cand cur = best;
+            for (int it = 0; it < refine_iters; it++) {
+                int victim = -1;
+                for (int b = 0; b < 64; b++)
+                    if (cur.use[b] && !((keep >> b) & 1) && (victim < 0 || cur.use[b] < cur.use[victim])) victim = b;
+                if (victim < 0) break;
+                forbid |= 1ull << victim;
+                build(cur.cm, dense_pass, cand, forbid);
+                const double sc = (double)cand.idx.size() / pass_cost(cand.c);
+                if (sc > best_score * 1.0001) {
+                    best_score = sc;
+                    best = cand;
+                }
+                std::swap(cur, cand);
             }
         }
         pass.clear();
