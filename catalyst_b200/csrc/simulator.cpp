@@ -213,7 +213,6 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
         if (const char *e = std::getenv("B200SV_JIT_UNIFORM")) opt_.jit_uniform = std::atoi(e);
         if (const char *e = std::getenv("B200SV_JIT_DIRECT")) opt_.jit_direct_store = std::atoi(e);
         if (const char *e = std::getenv("B200SV_JIT_MEMHINT")) opt_.jit_memhint = std::atoi(e);
-    if (const char *e = std::getenv("B200SV_PLAN_REFINE")) opt_.plan_refine = std::atoi(e);
         if (const char *e = std::getenv("B200SV_PLAN_REFINE")) opt_.plan_refine = std::atoi(e);
         if (const char *e = std::getenv("B200SV_JIT_REGBITS")) opt_.jit_regbits = std::max(1, std::min(5, std::atoi(e)));
         if (const char *e = std::getenv("B200SV_MIN_ROW_BITS")) opt_.min_row_bits = std::max(std::max(0, opt_.tile_bits - B200K_MAX_HIGH), std::min(opt_.tile_bits, std::atoi(e)));
@@ -240,6 +239,7 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
     }
     if (const char *e = std::getenv("B200SV_JIT_DBUF")) opt_.jit_dbuf = std::atoi(e);
     if (const char *e = std::getenv("B200SV_JIT_MEMHINT")) opt_.jit_memhint = std::atoi(e);
+    if (const char *e = std::getenv("B200SV_PLAN_REFINE")) opt_.plan_refine = std::atoi(e);
     if (const char *e = std::getenv("B200SV_JIT_FACTOR")) opt_.jit_factor = std::atoi(e);
     if (const char *e = std::getenv("B200SV_JIT_UNIFORM")) opt_.jit_uniform = std::atoi(e);
     if (const char *e = std::getenv("B200SV_P2P_SWAP")) opt_.p2p_swap = std::atoi(e);

@@ -120,7 +120,8 @@ struct Options {
     int p2p_swap = -1;        // qubit swap over mapped peer memory: 1 on, 0 off, -1 auto (on for 'local:' rank groups)
     int swap_push = -1;       // qubit swap as one push kernel into all peers' staging: 1 on, 0 off, -1 auto (over NCCL
                               // with 2 ranks; larger worlds take the staged NCCL path -- by measurement)
-    int plan_refine = 0;      // planner refinement iterations per pass (0 = off; -1: 6 from 2^27 local amplitudes, else 0)
+    int plan_refine = -1;     // planner refinement iterations per pass (-1: 6 from 2^27 local amplitudes on, else 0 --
+                              // the dozen extra scans of the queue per pass then hide behind the previous pass on the GPU)
     int dist_sampler = -1;    // sharded register, Sample / Counts of ALL wires: every rank draws every shot from the
                               // slices of |psi|^2 the ranks keep, read through peer memory (1 = required, 0 = gather the
                               // whole marginal on every rank, -1 = use it when peer memory is available)

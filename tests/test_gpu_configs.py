@@ -171,3 +171,25 @@ def test_c5_single_gpu_fixture():
     report(f"C5 n={n} depth=40 single GPU (fixture)", expval=cc.expval_err(got["expval"], z["expval"]),
            partial_probs=cc.rel_err(got["partial_probs"], z["partial_probs"]),
            state=cc.rel_err(got["state_probe"], z["state_probe"]))
+
+
+# ---- the planner's refinement step (automatic from 2^27 local amplitudes) forced on at test sizes ---------------------
+def test_planner_refinement_forced_c3(oracle_mod):
+    n = 22
+    ref = cc.run_c3(oracle_mod.OracleDevice(n, seed=cc.SEED), n)
+    d = capi.B200Device(n, seed=cc.SEED, jit="always", plan_refine=6)
+    got = cc.run_c3(d, n)
+    d.close()
+    report(f"C3 n={n} plan_refine=6", probs=cc.rel_err(got["probs"], ref["probs"]))
+    assert np.array_equal(got["sample_idx"], ref["sample_idx"])
+
+
+@pytest.mark.parametrize("world", [1, 4])
+def test_planner_refinement_forced_c5(oracle_mod, world):
+    n, depth = 22, 40
+    ref = c5_reference(oracle_mod, n, depth)
+    res = capi.run_spmd(world, lambda d, r: (d.allocate_qubits(n), cc.run_c5(d, n, depth))[1], seed=cc.SEED,
+                        plan_refine=6, jit_min_qubits=10)
+    for r, got in enumerate(res):
+        report(f"C5 n={n} world={world} plan_refine=6 rank {r}", expval=cc.expval_err(got["expval"], ref["expval"]),
+               partial_probs=cc.rel_err(got["partial_probs"], ref["partial_probs"]), state=cc.rel_err(got["state"], ref["state"]))
