@@ -1167,26 +1167,45 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
                 }
             }
         }
-        // Refinement (large states only: it costs a dozen scans of the queue per pass, hidden behind the previous pass
-        // on the GPU).  The greedy scan hands tile bits to whichever ops come first; a bit that ends up serving a
-        // single op may keep out a bit that would serve ten.  So: forbid the least-used bit of the candidate (never
-        // one the first op needs), rebuild, keep the better of the two, and repeat from the rebuilt candidate.
-        // Planner model on the BASELINE circuits: C3 17 -> 14 passes, C5 (30 qubits) 47 -> 45.
+        // Refinement (large states only: it costs about twenty scans of the queue per pass, hidden behind the previous
+        // pass on the GPU).  The greedy scan hands tile bits to whichever ops come first; a SCATTERED tile bit (one at
+        // or above the row width: bits inside the row are free) that ends up serving a single op may keep out a bit
+        // that would serve ten.  So: forbid one of the three least-used scattered bits of the candidate (never one the
+        // first op needs) -- whichever rebuild scores best --, keep the better of old and new, and repeat from the
+        // rebuilt candidate.  Planner model on the BASELINE circuits (pass count / cost-weighted): C3 17 / 21.2 ->
+        // 15 / 18.7, C5 at 30 qubits 47 / 61.3 -> 40 / 51.3, C5 at 33 local qubits 54 / 67.9 -> 43 / 55.1.
         if (refine_iters > 0 && opt_.adaptive_rows && opt_.fuse && !dense_pass && best.idx.size() > 1) {
-            double best_score = (double)best.idx.size() / pass_cost(best.c);
+            auto score = [&](const Cand &k) { return (double)k.idx.size() / pass_cost(k.c); };
+            double best_score = score(best);
             const uint64_t keep = ops[best.idx[0]].xmask;
             uint64_t forbid = 0;
-            Cand cur = best;
+            Cand cur = best, trial;
             for (int it = 0; it < refine_iters; it++) {
-                int victim = -1;
-                for (int b = 0; b < 64; b++)
-                    if (cur.use[b] && !((keep >> b) & 1) && (victim < 0 || cur.use[b] < cur.use[victim])) victim = b;
-                if (victim < 0) break;
-                forbid |= 1ull << victim;
-                build(cur.cm, dense_pass, cand, forbid);
-                const double sc = (double)cand.idx.size() / pass_cost(cand.c);
-                if (sc > best_score * 1.0001) {
-                    best_score = sc;
+                int victims[3], nv = 0; // the least-used scattered bits, ascending by (use, position)
+                for (int b = cur.c; b < 64; b++) {
+                    if (!cur.use[b] || ((keep >> b) & 1)) continue;
+                    int at = nv;
+                    while (at > 0 && cur.use[b] < cur.use[victims[at - 1]]) at--;
+                    if (at >= 3) continue;
+                    for (int q = std::min(nv, 2); q > at; q--) victims[q] = victims[q - 1];
+                    victims[at] = b;
+                    if (nv < 3) nv++;
+                }
+                if (nv == 0) break;
+                int chosen = -1;
+                double chosen_score = -1.0;
+                for (int v = 0; v < nv; v++) {
+                    build(cur.cm, dense_pass, trial, forbid | (1ull << victims[v]));
+                    const double sc = score(trial);
+                    if (sc > chosen_score) { // ties: the lower bit position (victims are visited in ascending order of use)
+                        chosen_score = sc;
+                        chosen = victims[v];
+                        std::swap(cand, trial);
+                    }
+                }
+                forbid |= 1ull << chosen;
+                if (chosen_score > best_score * 1.0001) {
+                    best_score = chosen_score;
                     best = cand;
                 }
                 std::swap(cur, cand);

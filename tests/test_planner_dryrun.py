@@ -45,13 +45,13 @@ def test_planner_pass_counts_of_the_baseline_circuits():
     assert r.returncode == 0, r.stderr[-2000:]
     out = json.loads(r.stdout.strip().splitlines()[-1])
     assert out["c3"]["gates"] == 930 and out["c5"]["gates"] == 1800
-    # measured on the B200 at these plans: C3 119.1 ms (16 passes: 64-byte rows + refinement), 127.8-130.0 ms (17 passes,
-    # no refinement), 132.7 ms (18 passes, 128-byte rows)
-    assert out["c3"]["passes"] <= 16, out
+    # measured on the B200: C3 119.1 ms with 16 passes (64-byte rows + the first refinement), 127.8-130.0 ms with 17
+    # (no refinement), 132.7 ms with 18 (128-byte rows); the refinement over scattered bits plans 15 (not measured)
+    assert out["c3"]["passes"] <= 15, out
     assert out["c3_norefine"]["passes"] <= 17, out
     assert out["c3_rows128"]["passes"] <= 17, out
     assert out["c3_rows2k"]["passes"] > out["c3_rows128"]["passes"], out      # short rows are what cut the pass count
-    assert out["c5"]["passes"] <= 45, out
+    assert out["c5"]["passes"] <= 41, out
     assert out["c1"]["passes"] <= 9 and out["c2"]["passes"] <= 13 and out["c4"]["passes"] <= 10, out
     # min_row_bits below tile_bits - 10 is clamped (the tile has at most ten scattered bits), not an error at launch
     assert out["clamped"]["passes"] > 0
