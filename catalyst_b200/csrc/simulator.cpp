@@ -165,6 +165,7 @@ Options parse_kwargs(const char *kwargs)
         else if (k == "swap_push") o.swap_push = (int)as_int(-1);
         else if (k == "dist_sampler") o.dist_sampler = (int)as_int(-1);
         else if (k == "plan_refine") o.plan_refine = (int)as_int(-1);
+        else if (k == "plan_refine_mode") o.plan_refine_mode = (int)as_int(1);
         else if (k == "gather") {
             B200_FAIL_IF(v != "all" && v != "slice", "gather must be 'all' or 'slice'");
             o.gather_slices = v == "slice";
@@ -214,6 +215,8 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
         if (const char *e = std::getenv("B200SV_JIT_DIRECT")) opt_.jit_direct_store = std::atoi(e);
         if (const char *e = std::getenv("B200SV_JIT_MEMHINT")) opt_.jit_memhint = std::atoi(e);
         if (const char *e = std::getenv("B200SV_PLAN_REFINE")) opt_.plan_refine = std::atoi(e);
+    if (const char *e = std::getenv("B200SV_PLAN_REFINE_MODE")) opt_.plan_refine_mode = std::atoi(e);
+        if (const char *e = std::getenv("B200SV_PLAN_REFINE_MODE")) opt_.plan_refine_mode = std::atoi(e);
         if (const char *e = std::getenv("B200SV_JIT_REGBITS")) opt_.jit_regbits = std::max(1, std::min(5, std::atoi(e)));
         if (const char *e = std::getenv("B200SV_MIN_ROW_BITS")) opt_.min_row_bits = std::max(std::max(0, opt_.tile_bits - B200K_MAX_HIGH), std::min(opt_.tile_bits, std::atoi(e)));
         return;
@@ -1181,15 +1184,18 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
             uint64_t forbid = 0;
             Cand cur = best, trial;
             for (int it = 0; it < refine_iters; it++) {
-                int victims[3], nv = 0; // the least-used scattered bits, ascending by (use, position)
-                for (int b = cur.c; b < 64; b++) {
+                // mode 1 (measured): the single least-used bit of the candidate; mode 2: the three least-used SCATTERED
+                // bits, each tried
+                const int width = opt_.plan_refine_mode == 2 ? 3 : 1;
+                int victims[3], nv = 0; // ascending by (use, position)
+                for (int b = opt_.plan_refine_mode == 2 ? cur.c : 0; b < 64; b++) {
                     if (!cur.use[b] || ((keep >> b) & 1)) continue;
                     int at = nv;
                     while (at > 0 && cur.use[b] < cur.use[victims[at - 1]]) at--;
-                    if (at >= 3) continue;
-                    for (int q = std::min(nv, 2); q > at; q--) victims[q] = victims[q - 1];
+                    if (at >= width) continue;
+                    for (int q = std::min(nv, width - 1); q > at; q--) victims[q] = victims[q - 1];
                     victims[at] = b;
-                    if (nv < 3) nv++;
+                    if (nv < width) nv++;
                 }
                 if (nv == 0) break;
                 int chosen = -1;

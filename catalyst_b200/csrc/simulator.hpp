@@ -122,6 +122,9 @@ struct Options {
                               // with 2 ranks; larger worlds take the staged NCCL path -- by measurement)
     int plan_refine = -1;     // planner refinement iterations per pass (-1: 6 from 2^27 local amplitudes on, else 0 --
                               // the dozen extra scans of the queue per pass then hide behind the previous pass on the GPU)
+    int plan_refine_mode = 2; // 1: trade the least-used bit of the candidate (measured on the B200: C3 119.1 ms); 2: try
+                              // the three least-used SCATTERED bits per step (fewer passes; predicted by the per-pass
+                              // time model fitted to the measured passes; not measured itself)
     int dist_sampler = -1;    // sharded register, Sample / Counts of ALL wires: every rank draws every shot from the
                               // slices of |psi|^2 the ranks keep, read through peer memory (1 = required, 0 = gather the
                               // whole marginal on every rank, -1 = use it when peer memory is available)

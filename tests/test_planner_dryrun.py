@@ -27,6 +27,8 @@ c3 = workloads.c3_qft_random(30)
 c5 = workloads.c5_random_depth(30, depth=40)
 plan("c3", 30, c3)
 plan("c3_norefine", 30, c3, plan_refine=0)
+plan("c3_mode1", 30, c3, plan_refine_mode=1)
+plan("c5_mode1", 30, c5, plan_refine_mode=1)
 plan("c3_rows128", 30, c3, min_row_bits=3)
 plan("c3_rows2k", 30, c3, min_row_bits=7)
 plan("c5", 30, c5)
@@ -49,6 +51,7 @@ def test_planner_pass_counts_of_the_baseline_circuits():
     # (no refinement), 132.7 ms with 18 (128-byte rows); the refinement over scattered bits plans 15 (not measured)
     assert out["c3"]["passes"] <= 15, out
     assert out["c3_norefine"]["passes"] <= 17, out
+    assert out["c3_mode1"]["passes"] <= 16 and out["c5_mode1"]["passes"] <= 45, out   # the variant measured on the B200
     assert out["c3_rows128"]["passes"] <= 17, out
     assert out["c3_rows2k"]["passes"] > out["c3_rows128"]["passes"], out      # short rows are what cut the pass count
     assert out["c5"]["passes"] <= 41, out
