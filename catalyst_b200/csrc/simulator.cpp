@@ -1225,6 +1225,28 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
         }
         const uint64_t req = best.req;
         const int c_cur = best.c;
+        // $B200SV_PLAN_DUMP=<file>: the schedule as the planner made it, one JSON line per pass with its canonical ops
+        // in execution order (tests/test_planner_dryrun.py replays it in numpy against the oracle: reordering gates
+        // is only legal where they commute, and that is decided here)
+        static const char *plan_dump = std::getenv("B200SV_PLAN_DUMP");
+        if (plan_dump) {
+            std::ostringstream js;
+            js.precision(17);
+            js << "{\"c\": " << c_cur << ", \"ops\": [";
+            for (size_t q = 0; q < pass.size(); q++) {
+                const GateOp &g = *pass[q];
+                js << (q ? ", " : "") << "{\"kind\": " << (int)g.kind << ", \"x\": " << g.xmask << ", \"cm\": " << g.cmask
+                   << ", \"cv\": " << g.cval << ", \"a\": " << g.a << ", \"b\": " << g.b << ", \"z\": " << g.zmask
+                   << ", \"ny\": " << g.ny << ", \"m\": [";
+                for (int e = 0; e < 4; e++) js << (e ? ", " : "") << g.m[e].real() << ", " << g.m[e].imag();
+                js << "]}";
+            }
+            js << "]}\n";
+            if (FILE *f = std::fopen(plan_dump, "a")) {
+                std::fputs(js.str().c_str(), f);
+                std::fclose(f);
+            }
+        }
         while (first < ops.size() && done[first]) first++;
         // high tile bits: required positions >= c, padded with the lowest free positions
         std::vector<int> high;

@@ -99,3 +99,106 @@ def test_every_pass_of_config_3_generates_and_compiles_for_sm_100a():
     assert r.returncode == 0, r.stderr[-2000:]
     out = json.loads(r.stdout.strip().splitlines()[-1])
     assert out["passes"] == out["specialised"] > 0, out
+
+
+# ---- the planner's schedules replayed on the CPU against the oracle ------------------------------------------------------
+DUMP_PROG = r"""
+import json, os, pickle, subprocess, sys
+sys.path[:0] = [%r, %r]
+if len(sys.argv) > 1:   # one case per process: the dump file name is read once per process
+    from catalyst_b200 import capi
+    from dsl import apply_ops
+    tag, n, ops, kw = pickle.load(open(sys.argv[1], "rb"))
+    d = capi.B200Device(n, **kw)
+    apply_ops(d, ops)
+    d.synchronize()
+    d.close()
+else:
+    cases = pickle.load(open(os.environ["PLAN_DUMP_DIR"] + "/cases.pkl", "rb"))
+    for case in cases:
+        f = os.environ["PLAN_DUMP_DIR"] + "/" + case[0] + ".pkl"
+        pickle.dump(case, open(f, "wb"))
+        env = dict(os.environ, B200SV_PLAN_DUMP=os.environ["PLAN_DUMP_DIR"] + "/" + case[0] + ".jsonl")
+        subprocess.run([sys.executable, "-c", open(os.environ["PLAN_DUMP_DIR"] + "/prog.py").read(), f], check=True, env=env)
+""" % (ROOT, os.path.join(ROOT, "tests"))
+
+
+def _replay(n, passes):
+    """Apply the dumped canonical ops (simulator.hpp: GateOp) to |0...0> in the order the planner scheduled them."""
+    import numpy as np
+    psi = np.zeros(1 << n, dtype=np.complex128)
+    psi[0] = 1.0
+    idx = np.arange(1 << n, dtype=np.uint64)
+
+    def parity(v):
+        v = v.copy()
+        for s in (32, 16, 8, 4, 2, 1):
+            v ^= v >> np.uint64(s)
+        return (v & np.uint64(1)).astype(bool)
+
+    for p in passes:
+        for g in p["ops"]:
+            m = [complex(g["m"][2 * e], g["m"][2 * e + 1]) for e in range(4)]
+            act = (idx & np.uint64(g["cm"])) == np.uint64(g["cv"])
+            x = np.uint64(g["x"])
+            if g["kind"] == 0:      # PAIR: 2x2 between the patterns a and b of the bits x
+                ia = idx[act & ((idx & x) == np.uint64(g["a"]))]
+                ib = ia ^ np.uint64(g["a"]) ^ np.uint64(g["b"])
+                va, vb = psi[ia].copy(), psi[ib].copy()
+                psi[ia] = m[0] * va + m[1] * vb
+                psi[ib] = m[2] * va + m[3] * vb
+            elif g["kind"] == 1:    # PHASE
+                psi[act] *= m[0]
+            elif g["kind"] == 2:    # PARITY
+                odd = parity(idx & np.uint64(g["z"]))
+                psi[act & ~odd] *= m[0]
+                psi[act & odd] *= m[1]
+            elif g["kind"] == 3:    # PAULIROT: cos * v - i sin * (P v), (P v)_i = i^ny (-1)^par(j & z) v_j, j = i ^ x
+                cs, sn = m[0].real, m[0].imag
+                j = idx ^ x
+                sign = np.where(parity(j & np.uint64(g["z"])), -1.0, 1.0)
+                pv = (1j ** (g["ny"] % 4)) * sign * psi[j.astype(np.int64)]
+                psi = np.where(act, cs * psi - 1j * sn * pv, psi)
+            else:
+                raise AssertionError("DENSE ops are not part of this test")
+    return psi
+
+
+def test_planned_schedules_replayed_in_numpy_match_the_oracle(oracle_mod, tmp_path):
+    """Reordering gates into passes is only legal where they commute.  The schedules the planner makes -- greedy, with
+    short rows, with both refinement variants forced on, on tiles small enough that a 12-qubit circuit needs dozens of
+    passes -- are dumped in dry-run mode, replayed op by op in numpy and compared with the oracle running the gates in
+    program order."""
+    import numpy as np
+    from catalyst_b200 import workloads
+    from dsl import apply_ops, random_circuit
+    n = 12
+    circuits = {"c3": workloads.c3_qft_random(n), "c5": workloads.c5_random_depth(n, depth=12),
+                "rand": [op for op in random_circuit(5, n, 200) if op[0] != "QubitUnitary"]}
+    variants = {"greedy": dict(plan_refine=0), "mode1": dict(plan_refine=6, plan_refine_mode=1),
+                "mode2": dict(plan_refine=6, plan_refine_mode=2), "mode2_rows0": dict(plan_refine=8, plan_refine_mode=2, min_row_bits=0),
+                "mode2_tile4": dict(plan_refine=6, plan_refine_mode=2, tile_bits=4, min_row_bits=1)}
+    cases = []
+    for cn, ops in circuits.items():
+        for vn, kw in variants.items():
+            cases.append((f"{cn}_{vn}", n, ops, {**dict(tile_bits=6, virtual_swap=False), **kw}))
+    import pickle
+    pickle.dump(cases, open(tmp_path / "cases.pkl", "wb"))
+    open(tmp_path / "prog.py", "w").write(DUMP_PROG)
+    env = dict(os.environ, B200SV_DRYRUN="1", B200SV_JIT="off", PLAN_DUMP_DIR=str(tmp_path))
+    r = subprocess.run([sys.executable, "-c", DUMP_PROG], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+    want = {}
+    for cn, ops in circuits.items():
+        o = oracle_mod.OracleDevice(n)
+        apply_ops(o, ops)
+        want[cn] = o.state()
+    counts = {}
+    for tag, _, _, _ in cases:
+        passes = [json.loads(l) for l in open(tmp_path / f"{tag}.jsonl")]
+        got = _replay(n, passes)
+        err = float(np.max(np.abs(got - want[tag.split("_")[0]])))
+        assert err < 1e-12, (tag, err)
+        counts[tag] = len(passes)
+    assert len(set(counts.values())) > 1, counts     # the variants do produce different schedules
+    print("[planner] passes per schedule:", counts)
