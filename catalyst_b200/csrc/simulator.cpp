@@ -1186,9 +1186,9 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
             for (int it = 0; it < refine_iters; it++) {
                 // mode 1 (measured): the single least-used bit of the candidate; mode 2: the three least-used SCATTERED
                 // bits, each tried
-                const int width = opt_.plan_refine_mode == 2 ? 3 : 1;
-                int victims[3], nv = 0; // ascending by (use, position)
-                for (int b = opt_.plan_refine_mode == 2 ? cur.c : 0; b < 64; b++) {
+                const int width = opt_.plan_refine_mode >= 2 ? std::min(8, opt_.plan_refine_mode + 1) : 1;
+                int victims[8], nv = 0; // ascending by (use, position)
+                for (int b = opt_.plan_refine_mode >= 2 ? cur.c : 0; b < 64; b++) {
                     if (!cur.use[b] || ((keep >> b) & 1)) continue;
                     int at = nv;
                     while (at > 0 && cur.use[b] < cur.use[victims[at - 1]]) at--;
