@@ -1149,8 +1149,10 @@ void Simulator::run_ops(double *vec, std::vector<GateOp> &ops)
     // 6.8-10.7 ms depending on the rounds they carry, weighted 1.6 (1.45 and 1.8 plan C3 / C5 into 17 / 49 and
     // 18 / 51 passes, 1.6 into 17 / 47); 32-byte rows measured 16-19 ms per pass and are never worth it.
     static const double cost_c2 = [] { const char *e = std::getenv("B200SV_COST_C2"); return e ? std::atof(e) : 1.6; }();
+    static const double cost_blend = [] { const char *e = std::getenv("B200SV_COST_BLEND"); return e ? std::atof(e) : 1.0; }();
     auto pass_cost = [](int c) {
-        return c >= 7 ? 1.0 : (c == 6 ? 1.12 : (c == 5 ? 1.2 : (c == 4 ? 1.3 : (c == 3 ? 1.38 : (c == 2 ? cost_c2 : 3.0)))));
+        const double k = c >= 7 ? 1.0 : (c == 6 ? 1.12 : (c == 5 ? 1.2 : (c == 4 ? 1.3 : (c == 3 ? 1.38 : (c == 2 ? cost_c2 : 3.0)))));
+        return c >= 2 ? 1.0 + cost_blend * (k - 1.0) : k; // experiment knob: < 1 flattens the penalty of short rows
     };
     while (remaining) {
         // a pass that starts with a DENSE op runs on the first-generation kernel (which knows
