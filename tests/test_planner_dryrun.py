@@ -202,3 +202,35 @@ def test_planned_schedules_replayed_in_numpy_match_the_oracle(oracle_mod, tmp_pa
         counts[tag] = len(passes)
     assert len(set(counts.values())) > 1, counts     # the variants do produce different schedules
     print("[planner] passes per schedule:", counts)
+
+
+def test_python_planner_model_agrees_with_the_device_library():
+    """scripts/planner_model.py (the tool the planner heuristics were explored with) against the C++ planner in
+    dry-run mode: same pass counts for config 3 and config 5 at 30 qubits in every planner variant."""
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import planner_model as pm
+    from catalyst_b200 import workloads
+    prog = PROG.split("c3 = workloads")[0] + r"""
+c3 = workloads.c3_qft_random(30)
+c5 = workloads.c5_random_depth(30, depth=40)
+for tag, ops in (("c3", c3), ("c5", c5)):
+    plan(tag + "_rows128", 30, ops, min_row_bits=3, plan_refine=0)
+    plan(tag + "_greedy", 30, ops, plan_refine=0)
+    plan(tag + "_mode1", 30, ops, plan_refine_mode=1)
+    plan(tag + "_mode2", 30, ops, plan_refine_mode=2)
+print(json.dumps(out))
+"""
+    env = dict(os.environ, B200SV_DRYRUN="1", B200SV_JIT="off")
+    r = subprocess.run([sys.executable, "-c", prog], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+    got = json.loads(r.stdout.strip().splitlines()[-1])
+    variants = {"rows128": dict(cmin=3, iters=0), "greedy": dict(cmin=2, iters=0), "mode1": dict(cmin=2, iters=6, width=1),
+                "mode2": dict(cmin=2, iters=6, width=3)}
+    for tag, ops in (("c3", workloads.c3_qft_random(30)), ("c5", workloads.c5_random_depth(30, depth=40))):
+        co = pm.canon(ops, 30)
+        for vn, kw in variants.items():
+            assert len(pm.plan(co, **kw)) == got[f"{tag}_{vn}"]["passes"], (tag, vn, got[f"{tag}_{vn}"])
+    # the sharded executor of the model reproduces what the 8-GPU benchmark runs of round 2 reported
+    # (profiles/r2_v3_bench_n8_staged.json: 7 exchanges per step; DESIGN.md: 69 passes)
+    p, s = pm.execute_sharded(pm.canon(workloads.c5_random_depth(34, depth=40), 34), 34, 3, cmin=3, iters=0)
+    assert (len(p), s) == (69, [3] * 7)
