@@ -40,7 +40,8 @@ const char *b200sv_version(void);
  * estimates then draw from a Metropolis chain, kernels 'Local' and 'NonZeroRandom'; parity unpinned, see
  * Simulator::mcmc_indices), tile_bits, min_row_bits, fuse (0/1), device (CUDA ordinal), world_size, rank, comm,
  * stage_mib, swap_push, p2p_swap, dist_sampler, gather ('all' | 'slice') (see "sharding" below), release_entangled
- * ('error' | 'project'), jit ('off' |
+ * ('error' | 'project'), keep_allocation, plan_refine / plan_refine_mode (pass planner: refinement iterations per pass,
+ * -1 = automatic from 2^27 local amplitudes; 1 = any-bit variant, >= 2 = scattered-bit variant), jit ('off' |
  * 'auto' | 'always') and its tuning keys.  Unknown keys are ignored.  Returns NULL on error. */
 b200sv_device *b200sv_create(const char *kwargs);
 void b200sv_destroy(b200sv_device *d);
