@@ -201,6 +201,7 @@ Options parse_kwargs(const char *kwargs)
 Simulator::Simulator(const Options &opt) : opt_(opt)
 {
     if (const char *e = std::getenv("B200SV_DRYRUN")) dry_ = std::atoi(e) != 0;
+    if (const char *e = std::getenv("B200SV_PASS_OP_CAP")) pass_op_cap_ = std::max(8, std::min(460, std::atoi(e))); // experiments
     if (dry_) {
         // Development mode, no GPU needed: gate calls are canonicalised, planned into passes and the
         // specialised kernels are generated and compiled to cubins ($B200SV_JIT_DUMP), nothing is launched.
