@@ -205,7 +205,9 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
     if (dry_) {
         // Development mode, no GPU needed: gate calls are canonicalised, planned into passes and the
         // specialised kernels are generated and compiled to cubins ($B200SV_JIT_DUMP), nothing is launched.
-        B200_FAIL_IF(opt_.world != 1, "B200SV_DRYRUN supports unsharded registers only");
+        // sharded registers too: every rank plans alone (the plan is a function of the op stream and the rank count
+        // only), swaps just update the layout, and nothing that needs the other ranks' data can be called
+        while ((1 << g_) < opt_.world) g_++;
         DeviceBuffer::dry = true;
         jit_mode_ = opt_.jit;
         if (const char *e = std::getenv("B200SV_JIT")) {
@@ -216,7 +218,6 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
         if (const char *e = std::getenv("B200SV_JIT_DIRECT")) opt_.jit_direct_store = std::atoi(e);
         if (const char *e = std::getenv("B200SV_JIT_MEMHINT")) opt_.jit_memhint = std::atoi(e);
         if (const char *e = std::getenv("B200SV_PLAN_REFINE")) opt_.plan_refine = std::atoi(e);
-    if (const char *e = std::getenv("B200SV_PLAN_REFINE_MODE")) opt_.plan_refine_mode = std::atoi(e);
         if (const char *e = std::getenv("B200SV_PLAN_REFINE_MODE")) opt_.plan_refine_mode = std::atoi(e);
         if (const char *e = std::getenv("B200SV_JIT_REGBITS")) opt_.jit_regbits = std::max(1, std::min(5, std::atoi(e)));
         if (const char *e = std::getenv("B200SV_MIN_ROW_BITS")) opt_.min_row_bits = std::max(std::max(0, opt_.tile_bits - B200K_MAX_HIGH), std::min(opt_.tile_bits, std::atoi(e)));
@@ -244,6 +245,7 @@ Simulator::Simulator(const Options &opt) : opt_(opt)
     if (const char *e = std::getenv("B200SV_JIT_DBUF")) opt_.jit_dbuf = std::atoi(e);
     if (const char *e = std::getenv("B200SV_JIT_MEMHINT")) opt_.jit_memhint = std::atoi(e);
     if (const char *e = std::getenv("B200SV_PLAN_REFINE")) opt_.plan_refine = std::atoi(e);
+    if (const char *e = std::getenv("B200SV_PLAN_REFINE_MODE")) opt_.plan_refine_mode = std::atoi(e);
     if (const char *e = std::getenv("B200SV_JIT_FACTOR")) opt_.jit_factor = std::atoi(e);
     if (const char *e = std::getenv("B200SV_JIT_UNIFORM")) opt_.jit_uniform = std::atoi(e);
     if (const char *e = std::getenv("B200SV_P2P_SWAP")) opt_.p2p_swap = std::atoi(e);
@@ -1439,6 +1441,20 @@ void Simulator::swap_bits_impl(const std::vector<double *> &vecs, std::vector<in
     if (m == 0) return;
     NvtxRange nvtx("b200sv::qubit_swap");
     B200_FAIL_IF(m > 8 || m > g_, "internal: too many bits in one swap");
+    if (dry_) { // planning only: the layout changes, no data moves
+        for (auto &pr : pairs) {
+            B200_FAIL_IF(pr.first < nl_ || pr.second >= nl_, "internal: malformed swap");
+            int qg = -1, ql = -1;
+            for (int q = 0; q < (int)n_; q++) {
+                if (pos[q] == pr.first) qg = q;
+                if (pos[q] == pr.second) ql = q;
+            }
+            std::swap(pos[qg], pos[ql]);
+        }
+        stats_.exchanges++;
+        stats_.exchange_bytes += (double)(sizeof(cplx) << nl_) * (1.0 - std::ldexp(1.0, -m)) * (double)vecs.size();
+        return;
+    }
     std::sort(pairs.begin(), pairs.end(), [](auto &x, auto &y) { return x.second < y.second; });
     uint8_t lpos[8];
     int gsel[8];

@@ -234,3 +234,45 @@ print(json.dumps(out))
     # (profiles/r2_v3_bench_n8_staged.json: 7 exchanges per step; DESIGN.md: 69 passes)
     p, s = pm.execute_sharded(pm.canon(workloads.c5_random_depth(34, depth=40), 34), 34, 3, cmin=3, iters=0)
     assert (len(p), s) == (69, [3] * 7)
+
+
+SHARDED_PROG = r"""
+import json, sys
+sys.path[:0] = [%r, %r]
+from catalyst_b200 import capi, workloads
+from dsl import apply_ops
+ops = workloads.c5_random_depth(34, depth=40)
+out = {}
+for world in (2, 4, 8):
+    for tag, kw in (("bench_r2", dict(min_row_bits=3, plan_refine=0)), ("head", {})):
+        d = capi.B200Device(world_size=world, rank=world - 1, comm="local:dry", **kw)
+        d.allocate_qubits(34)
+        apply_ops(d, ops)
+        d.synchronize()
+        s = d.stats()
+        out["%%d_%%s" %% (world, tag)] = [int(s.tile_passes), int(s.exchanges), float(s.exchange_bytes)]
+        d.close()
+print(json.dumps(out))
+""" % (ROOT, os.path.join(ROOT, "tests"))
+
+
+def test_sharded_planner_of_the_34_qubit_benchmark_circuit():
+    """The sharded executor in dry-run mode (every rank plans alone; swaps only change the layout): with the planner
+    settings of round 2's multi-GPU benchmark runs it must reproduce what those runs REPORTED (profiles/r2_v3_bench_n*.json:
+    7 / 6 / 5 exchanges per step and 210 453 397 504 / 309 237 645 312 / 343 597 383 680 bytes sent per rank and step at
+    8 / 4 / 2 GPUs); at HEAD the same circuit needs fewer passes and the same swaps; the Python model agrees."""
+    env = dict(os.environ, B200SV_DRYRUN="1", B200SV_JIT="off")
+    r = subprocess.run([sys.executable, "-c", SHARDED_PROG], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["8_bench_r2"] == [69, 7, 210453397504.0]
+    assert out["4_bench_r2"][1:] == [6, 309237645312.0] and out["2_bench_r2"][1:] == [5, 343597383680.0]
+    assert out["8_head"][0] <= 58 and out["4_head"][0] <= 55 and out["2_head"][0] <= 53, out
+    assert [out[k][1] for k in ("8_head", "4_head", "2_head")] == [7, 6, 5]
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import planner_model as pm
+    from catalyst_b200 import workloads
+    co = pm.canon(workloads.c5_random_depth(34, depth=40), 34)
+    for g, world in ((3, 8), (2, 4), (1, 2)):
+        p, s = pm.execute_sharded(co, 34, g, cmin=2, iters=6, width=3)
+        assert (len(p), len(s)) == (out[f"{world}_head"][0], out[f"{world}_head"][1]), (world, len(p), s)
