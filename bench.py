@@ -532,6 +532,12 @@ def run_ours(args, rank, world, local_rank):
         "bound_frac": max(hbm_ms, fp64_ms) / avg_ms,
         "fused_algorithmic_gbs": s.algorithmic_bytes / pass_s / 1e9,
         "gates_per_launch": s.gates_enqueued / launches_tile,
+        "launches_per_step": launches_tile / float(args.steps),
+        "hbm_bytes_per_step": hbm_bytes * launches_tile / float(args.steps),
+        "step_hbm_floor_ms": hbm_ms * launches_tile / float(args.steps),
+        "history": "the planner trades launches for heavier launches: config 3 took 32 launches per step in round 1 "
+                   "(frac 0.88 on the light ones), 18 at frac 0.70-0.71, 15-17 now at a LOWER frac per launch and a "
+                   "shorter step -- read frac together with launches_per_step (DESIGN.md 4.1 items 7-9)",
         "note": "frac = physical HBM bytes of the tile passes (one read + one write of the shard per launch) / "
                 "CUDA-event time / measured copy peak; fp64_floor_ms = the generator's FP64 instruction count per "
                 "launch / the DFMA rate measured by b200sv_fp64_peak (upper bound: conditional bodies counted as "
